@@ -1,0 +1,314 @@
+#!/usr/bin/env python
+"""bench.py — audio-seconds decoded per second by the iSTFTNet waveform decoder on B200.
+
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--workload c2|c1|...]
+
+One "step" = one Decoder.forward over one batch of synthetic utterances (BASELINE.json config 1:
+LJSpeech iSTFTNet decoder, batch 32 x 800 mel frames = 320 s of 24 kHz audio, bf16 tensor-core path,
+random-init weights).  Under torchrun every rank decodes its own batch of that size (pure data
+parallelism, no collective on the path: SURVEY.md section 8e) -> "scaling": "weak"; `value` is the
+whole job's audio-seconds divided by the max-over-ranks device time.
+
+Prints ONE JSON line on rank 0 (contract in the task statement): value (inputs resident in HBM),
+e2e (through the public module with pinned HOST buffers, H2D + D2H inside the timed region),
+roofline (tcgen05 conv launches timed live with CUDA events on their stream), cpu_baseline (the
+oracle port of the reference's CPU decoder on this box's host cores, bounded sample), clocks.
+
+--impl reference times the reference's own CPU implementation of the path: the reference is pure
+Python/PyTorch and /root/reference does not exist on the GPU box, so this arm runs the oracle port
+(oracle/decoder_oracle.py: the same ATen CPU convolutions, same op order) with all host threads.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import statistics
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+WORKLOADS = {
+    # name: (kind, B, T, description)   T = mel frames (hop 300 @ 24 kHz) -> 300*T samples
+    "c1": ("istftnet", 1, 400, "BASELINE config 0: iSTFTNet B=1 x 400 frames (5 s)"),
+    "c2": ("istftnet", 32, 800, "BASELINE config 1: LJSpeech iSTFTNet B=32 x 800 frames (10 s each)"),
+    "c3": ("istftnet", 64, 800, "BASELINE config 2: multispeaker B=64 x 800 frames, one style row per item"),
+    "c4": ("hifigan", 32, 800, "BASELINE config 3: HiFi-GAN decoder B=32 x 800 frames"),
+    "c5shard": ("istftnet", 64, 2400, "BASELINE config 4 per-GPU shard at 8 GPUs: B=64 x 2400 frames (30 s each)"),
+}
+MFLOP_PER_FRAME = {"istftnet": 649.05, "hifigan": 873.90}  # SURVEY.md section 8d (2*MAC, convs + linears)
+METRIC = "audio-sec/sec decoded (iSTFTNet, bf16)"
+UNIT = "audio-sec/sec"
+
+
+def _peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        d = json.load(open(p))
+        return dict(tf_sustained=d.get("bf16_tflops_sustained", 1357.0), tf_burst=d.get("bf16_tflops", 1628.5),
+                    hbm=d.get("hbm_gbs", 6537.3), source="MEASURED_PEAKS.json")
+    return dict(tf_sustained=1400.0, tf_burst=1590.0, hbm=6650.0, source="fallback (B200_PROFILING.md)")
+
+
+class ClockSampler(threading.Thread):
+    """samples SM clock + throttle reasons of one GPU during the timed region (NVML)."""
+
+    def __init__(self, index: int, period=0.1):
+        super().__init__(daemon=True)
+        self.index, self.period = index, period
+        self.samples, self.reasons, self.max_mhz = [], set(), None
+        self._stop = threading.Event()
+        self.ok = False
+        try:
+            import pynvml
+            pynvml.nvmlInit()
+            self.nv = pynvml
+            self.h = pynvml.nvmlDeviceGetHandleByIndex(index)
+            self.max_mhz = pynvml.nvmlDeviceGetMaxClockInfo(self.h, pynvml.NVML_CLOCK_SM)
+            self.ok = True
+        except Exception as e:  # pragma: no cover
+            self.err = repr(e)
+
+    def run(self):
+        nv = self.nv
+        names = {
+            getattr(nv, "nvmlClocksEventReasonSwPowerCap", 0x4): "sw_power_cap",
+            getattr(nv, "nvmlClocksThrottleReasonHwSlowdown", 0x8): "hw_slowdown",
+            getattr(nv, "nvmlClocksEventReasonSwThermalSlowdown", 0x20): "sw_thermal_slowdown",
+            getattr(nv, "nvmlClocksThrottleReasonHwThermalSlowdown", 0x40): "hw_thermal_slowdown",
+            getattr(nv, "nvmlClocksThrottleReasonHwPowerBrakeSlowdown", 0x80): "hw_power_brake",
+        }
+        while not self._stop.is_set():
+            try:
+                self.samples.append(nv.nvmlDeviceGetClockInfo(self.h, nv.NVML_CLOCK_SM))
+                try:
+                    r = nv.nvmlDeviceGetCurrentClocksEventReasons(self.h)
+                except Exception:
+                    r = nv.nvmlDeviceGetCurrentClocksThrottleReasons(self.h)
+                for bit, name in names.items():
+                    if r & bit:
+                        self.reasons.add(name)
+            except Exception:
+                pass
+            time.sleep(self.period)
+
+    def stop(self):
+        self._stop.set()
+        if self.is_alive():
+            self.join(timeout=2)
+        if not self.ok or not self.samples:
+            return {"sm_mhz": None, "sm_max_mhz": self.max_mhz, "reasons": ["unavailable"]}
+        return {"sm_mhz": statistics.median(self.samples), "sm_max_mhz": self.max_mhz,
+                "reasons": sorted(self.reasons)}
+
+
+def _oracle_cpu_decoder(kind, B, T, steps, warmup, threads=None):
+    """times the oracle port (= the reference's CPU algorithm) on the host cores; returns audio-s/s."""
+    import torch
+    from oracle import decoder_oracle as orc
+    import synthetic as synth
+    threads = threads or os.cpu_count() or 1
+    torch.set_num_threads(threads)
+    cfg = synth.ISTFTNET_CFG if kind == "istftnet" else synth.HIFIGAN_CFG
+    sd = synth.synth_state_dict(cfg, seed=0)
+    inp = synth.synth_inputs(cfg, B, T, seed=1234)
+    times = []
+    for i in range(warmup + steps):
+        t0 = time.perf_counter()
+        out = orc.decoder_forward(sd, cfg, inp["asr"], inp["F0_curve"], inp["N"], inp["s"], noise=inp["noise"])
+        dt = time.perf_counter() - t0
+        assert out.shape[-1] == 300 * T
+        if i >= warmup:
+            times.append(dt)
+    audio_s = B * T * 300 / 24000.0
+    return audio_s / statistics.median(times), statistics.median(times) * 1e3, torch.get_num_threads()
+
+
+def run_reference(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return 0
+    kind, B, T, desc = WORKLOADS[args.workload]
+    sb, st = 1, T  # bounded sample: one utterance of the workload per step
+    v, ms, threads = _oracle_cpu_decoder(kind, sb, st, args.steps, max(1, args.warmup))
+    line = {
+        "impl": "reference", "metric": METRIC, "value": round(v, 4), "unit": UNIT, "n_gpus": args.gpus,
+        "steps": args.steps, "warmup": max(1, args.warmup), "ms_per_step": round(ms, 2),
+        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": {"workload": desc, "sample": f"B={sb} x {st} frames per step on the CPU"},
+        "cpu_baseline": {"value": round(v, 4), "unit": UNIT, "cores": threads, "kind": "port",
+                         "sample": f"{sb} utterance x {st} frames, fp32, torch CPU (oracle port of "
+                                   f"Modules/{kind}.py Decoder.forward)"},
+        "e2e": {"value": round(v, 4), "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+    print(json.dumps(line), flush=True)
+    return 0
+
+
+def run_ours(args):
+    import ctypes as C
+    import torch
+    import torch.distributed as dist
+    import styletts2_b200 as st2
+    from styletts2_b200 import _cabi
+    import synthetic as synth  # random-init weights / seeded inputs (no decoder arithmetic)
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a CUDA device: styletts2_b200 has no CPU fallback")
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+    kind, B, T, desc = WORKLOADS[args.workload]
+    cfg = synth.ISTFTNET_CFG if kind == "istftnet" else synth.HIFIGAN_CFG
+    prec = args.precision
+
+    dec = (st2.IstftnetDecoder if kind == "istftnet" else st2.HifiganDecoder)(
+        **{k: v for k, v in cfg.items() if k != "kind"})
+    dec.load_state_dict(synth.synth_state_dict(cfg, seed=0), strict=True)
+    dec = dec.to(dev).eval()
+    dec.precision = prec
+    inp = synth.synth_inputs(cfg, B, T, seed=1234 + rank, with_noise=False)  # per-rank shard, Philox noise
+    host = {k: v.pin_memory() for k, v in inp.items()}
+    d = {k: v.to(dev) for k, v in inp.items()}
+    audio_s = B * T * 300 / 24000.0
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def max_over_ranks(ms):
+        if world == 1:
+            return ms
+        t = torch.tensor([ms], device=dev, dtype=torch.float64)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+
+    # ---- device-resident arm
+    for _ in range(max(3, args.warmup)):
+        out = dec(d["asr"], d["F0_curve"], d["N"], d["s"])
+    barrier()
+    launches_per_step = dec.last_launches
+    sampler = ClockSampler(local)
+    if sampler.ok:
+        sampler.start()
+    _cabi.lib.st2_prof_enable(1)
+    _cabi.lib.st2_prof_read(None, None, None, 1)
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    barrier()
+    e0.record()
+    for _ in range(args.steps):
+        out = dec(d["asr"], d["F0_curve"], d["N"], d["s"])
+    e1.record()
+    barrier()
+    clocks = sampler.stop()
+    ms_total = max_over_ranks(e0.elapsed_time(e1))
+    umma_ms, umma_n, umma_fl = C.c_double(), C.c_int64(), C.c_double()
+    _cabi.lib.st2_prof_read(C.byref(umma_ms), C.byref(umma_n), C.byref(umma_fl), 1)
+    _cabi.lib.st2_prof_enable(0)
+    ms_step = ms_total / args.steps
+    value = world * audio_s / (ms_step * 1e-3)
+    assert torch.isfinite(out).all()
+
+    # ---- end-to-end arm: pinned host inputs -> H2D -> forward -> D2H of the waveform, every step
+    wav_host = torch.empty(B, 1, T * 300, dtype=torch.float32).pin_memory()
+    h2d = sum(host[k].numel() * 4 for k in ("asr", "F0_curve", "N", "s"))
+    d2h = wav_host.numel() * 4
+
+    def e2e_step():
+        a = {k: host[k].to(dev, non_blocking=True) for k in ("asr", "F0_curve", "N", "s")}
+        w = dec(a["asr"], a["F0_curve"], a["N"], a["s"])
+        wav_host.copy_(w, non_blocking=True)
+
+    for _ in range(2):
+        e2e_step()
+    barrier()
+    e0.record()
+    for _ in range(args.steps):
+        e2e_step()
+    e1.record()
+    barrier()
+    ms_e2e = max_over_ranks(e0.elapsed_time(e1)) / args.steps
+    e2e_value = world * audio_s / (ms_e2e * 1e-3)
+
+    if rank != 0:
+        if world > 1:
+            dist.destroy_process_group()
+        return 0
+
+    peaks = _peaks()
+    algo_tflop_step = MFLOP_PER_FRAME[kind] * 1e6 * B * T / 1e12
+    roof = None
+    if umma_n.value > 0 and umma_ms.value > 0:
+        ach = umma_fl.value / (umma_ms.value * 1e-3) / 1e12
+        roof = {"bound": "tensor", "achieved": round(ach, 2), "peak": peaks["tf_sustained"], "unit": "TFLOP/s",
+                "frac": round(ach / peaks["tf_sustained"], 4), "traffic": None,
+                "kernel": "conv_umma_kernel (tcgen05 implicit-GEMM conv)",
+                "launches_per_step": umma_n.value // args.steps,
+                "kernel_ms_per_step": round(umma_ms.value / args.steps, 3),
+                "kernel_share_of_step": round(umma_ms.value / args.steps / ms_step, 4),
+                "algo_tflop_per_step_in_kernel": round(umma_fl.value / args.steps / 1e12, 4),
+                "peak_source": peaks["source"] + " bf16_tflops_sustained (kernel timed inside a long step); "
+                               f"burst peak {peaks['tf_burst']}",
+                "whole_step_tflops": round(algo_tflop_step / (ms_step * 1e-3), 2)}
+    cpu = None
+    if world == 1 and not args.no_cpu_baseline:
+        v, ms_cpu, threads = _oracle_cpu_decoder(kind, 1, T, steps=2, warmup=1)
+        cpu = {"value": round(v, 4), "unit": UNIT, "cores": threads, "kind": "port",
+               "sample": f"1 utterance x {T} frames of the workload, fp32, torch CPU, median of 2 "
+                         f"({ms_cpu:.0f} ms per forward)"}
+    ws_bytes = int(_cabi.lib.st2_decoder_workspace_bytes(dec._native[local], B, T,
+                                                         _cabi.PREC_BF16 if prec == "bf16" else _cabi.PREC_FP32))
+    line = {
+        "metric": METRIC, "value": round(value, 2), "unit": UNIT, "n_gpus": world, "steps": args.steps,
+        "warmup": max(3, args.warmup), "ms_per_step": round(ms_step, 3), "higher_is_better": True,
+        "scaling": "weak", "vs_baseline": None, "dtype": prec, "data": "synthetic",
+        "config": {"workload": desc, "batch_per_gpu": B, "mel_frames": T, "decoder": kind,
+                   "weights": "random-init (synthetic.py, seed 0)", "noise": "in-kernel Philox",
+                   "l2": f"no explicit flush: every step streams a {ws_bytes / 1e9:.2f} GB working set "
+                         "through HBM (>> 126 MB L2)",
+                   "parallelism": f"dp{world} (independent batches, no collective)"},
+        "e2e": {"value": round(e2e_value, 2), "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
+                "ms_per_step": round(ms_e2e, 3)},
+        "gpu_launches": int(launches_per_step * args.steps),
+        "roofline": roof, "cpu_baseline": cpu, "clocks": clocks,
+    }
+    print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+    return 0
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--workload", default="c2", choices=sorted(WORKLOADS))
+    ap.add_argument("--precision", default="bf16", choices=["bf16", "fp32"])
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    if args.impl == "reference":
+        return run_reference(args)
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    if args.gpus > 1 and world == 1:
+        # convenience: relaunch under torchrun (the driver launches torchrun itself)
+        import subprocess
+        cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={args.gpus}",
+               "--master-addr", "127.0.0.1", "--master-port", "29541", os.path.abspath(__file__)] + sys.argv[1:]
+        return subprocess.call(cmd)
+    return run_ours(args)
+
+
+if __name__ == "__main__":
+    sys.exit(main())

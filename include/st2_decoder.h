@@ -1,0 +1,157 @@
+/*
+ * st2_decoder.h — C ABI of the B200-native StyleTTS2 waveform decoder (libst2dec.so).
+ *
+ * Drop-in boundary.  The reference exposes this path as a torch.nn.Module:
+ *   Decoder.__init__  /root/reference/Modules/istftnet.py:467-496  (hifigan.py:416-442)
+ *   Decoder.forward   /root/reference/Modules/istftnet.py:498-527  (hifigan.py:445-474)
+ *   wiring            /root/reference/models.py:1002-1032 (build_model), :1218-1239 (load_checkpoint)
+ * There is no FFI in the reference; the boundary is the constructor kwargs, forward(asr,
+ * F0_curve, N, s) and the state_dict key set.  This header is what a binding for that
+ * boundary calls (the Python module in styletts2_b200/ binds it with ctypes; see
+ * INTEGRATION.md for the reference-side stub).
+ *
+ * Conventions: plain C, no torch types.  Every function returns 0 on success or a
+ * negative ST2_E* code and never throws; st2_last_error() gives a thread-local message.
+ * All device pointers belong to the caller (torch allocates wav_out and the workspace).
+ * A handle is bound to the CUDA device current at create time, is immutable after load,
+ * and may be used concurrently from several streams as long as each call has its own
+ * workspace.  No hidden host synchronisation inside forward.  sm_100a only; there is no
+ * CPU fallback: without a usable GPU every compute entry point fails with ST2_ECUDA.
+ */
+#ifndef ST2_DECODER_H
+#define ST2_DECODER_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define ST2_OK 0
+#define ST2_EINVAL (-1)  /* bad argument / shape / missing weight */
+#define ST2_ECUDA (-2)   /* CUDA runtime error (message has the detail) */
+#define ST2_ESTATE (-3)  /* call order (forward before load, ...) */
+#define ST2_ENOMEM (-4)  /* workspace too small */
+
+#define ST2_KIND_ISTFTNET 0 /* Modules/istftnet.py */
+#define ST2_KIND_HIFIGAN 1  /* Modules/hifigan.py  */
+
+/* arithmetic of the dense contractions */
+#define ST2_PREC_FP32 0 /* fp32 FFMA kernels, fp32 activations: the parity path        */
+#define ST2_PREC_BF16 1 /* tcgen05 bf16 x bf16 -> fp32 (TMEM), bf16 activations in HBM */
+
+#define ST2_MAX_UPS 4
+#define ST2_MAX_RESK 4
+
+/* Constructor kwargs of the reference Decoder (istftnet.py:467-473, hifigan.py:416-421). */
+typedef struct St2Config {
+  int kind;                 /* ST2_KIND_* */
+  int dim_in;               /* 512 (hidden_dim) */
+  int style_dim;            /* 128 */
+  int dim_out;              /* 80, accepted and unused like the reference */
+  int n_resblock_kernels;   /* len(resblock_kernel_sizes) = 3 */
+  int resblock_kernel_sizes[ST2_MAX_RESK];      /* 3,7,11 */
+  int resblock_dilations[ST2_MAX_RESK][3];      /* 1,3,5 each */
+  int n_ups;                /* len(upsample_rates): 2 (istftnet) or 4 (hifigan) */
+  int upsample_rates[ST2_MAX_UPS];              /* 10,6 | 10,5,3,2 */
+  int upsample_kernel_sizes[ST2_MAX_UPS];       /* 20,12 | 20,10,6,4 */
+  int upsample_initial_channel;                 /* 512 */
+  int gen_istft_n_fft;      /* 20 (istftnet only) */
+  int gen_istft_hop_size;   /* 5  (istftnet only) */
+} St2Config;
+
+/* One state_dict entry (host fp32, contiguous, torch layout).  Names are the reference's
+ * keys ("decode.0.conv1.weight_v", ...); a leading "module." (DDP) is ignored like
+ * models.py:1126-1142 does. */
+typedef struct St2Tensor {
+  const char* name;
+  const float* data;
+  int ndim;
+  int64_t shape[4];
+} St2Tensor;
+
+typedef struct St2Decoder St2Decoder; /* opaque */
+
+/* Optional inputs of one forward call (all device pointers, may be NULL). */
+typedef struct St2ForwardOpts {
+  int precision;            /* ST2_PREC_* */
+  const float* noise;       /* [B, T*spf, 9] standard normal: the randn_like draw of
+                               SineGen.forward (istftnet.py:241).  NULL -> in-kernel Philox */
+  const float* har_source;  /* [B, T*spf] output of m_source (istftnet.py:353): skips SineGen */
+  const float* har;         /* [B, 22, 60T+1] NCL: cat(|STFT|, angle) (istftnet.py:356); istftnet only */
+  uint64_t seed;            /* Philox seed when noise == NULL */
+  float* har_source_out;    /* optional [B, T*spf]: the excitation that was used */
+  float* har_out;           /* optional [B, 22, 60T+1] NCL: the har that was used */
+} St2ForwardOpts;
+
+/* Decoder(**kwargs): validates the config and builds the layer plan (no weights yet). */
+int st2_decoder_create(const St2Config* cfg, St2Decoder** out);
+
+/* load_state_dict: folds weight-norm (w = g*v/||v||, dim 0), repacks every conv into the
+ * kernel layouts (fp32 tap-major and bf16 UMMA core-matrix blobs), expands ConvTranspose1d
+ * into polyphase form, concatenates all AdaIN fc layers, and uploads to the current device.
+ * Missing or mis-shaped keys -> ST2_EINVAL (strict, like load_state_dict). */
+int st2_decoder_load(St2Decoder* h, const St2Tensor* tensors, int n);
+
+/* Number of state-dict keys the decoder expects / the i-th expected key and shape. */
+int st2_decoder_num_keys(const St2Decoder* h);
+int st2_decoder_key(const St2Decoder* h, int i, const char** name, int* ndim, int64_t shape[4]);
+
+/* samples generated per mel frame (300 for both shipped configs). */
+int st2_decoder_samples_per_frame(const St2Decoder* h);
+
+/* Bytes of device scratch forward() needs for this batch/length/precision. */
+int64_t st2_decoder_workspace_bytes(const St2Decoder* h, int B, int T, int precision);
+
+/* Decoder.forward(asr, F0_curve, N, s) in eval mode.
+ *   asr [B, dim_in, T/2] fp32 NCL, f0 [B, T], n [B, T], s [B, style_dim]  (device, contiguous)
+ *   wav_out [B, 1, T*spf] fp32 (device).  T must be even (the reference's cat at
+ *   istftnet.py:513 raises otherwise).  stream is a cudaStream_t. */
+int st2_decoder_forward(St2Decoder* h, const float* asr, const float* f0, const float* n,
+                        const float* s, float* wav_out, void* workspace, int64_t workspace_bytes,
+                        int B, int T, const St2ForwardOpts* opts, void* stream);
+
+/* Number of kernel launches the last forward on this handle issued (bench bookkeeping). */
+int64_t st2_decoder_last_launches(const St2Decoder* h);
+
+void st2_decoder_destroy(St2Decoder* h);
+
+const char* st2_last_error(void);
+const char* st2_version(void);
+
+/* ---- single-kernel entry points (unit tests and micro-benchmarks call these) ---------- */
+
+/* Generic fused 1-D convolution on channels-last activations.  See csrc/conv_params.h for
+ * the meaning of every field; the struct is passed by pointer and copied. */
+struct St2ConvParams;
+int st2_conv_simt(const struct St2ConvParams* p, void* stream);
+int st2_conv_umma(const struct St2ConvParams* p, void* stream);
+/* packs fp32 [k][Cin][N] host weights into the UMMA blob layout (host only, no GPU). */
+int64_t st2_umma_packed_elems(int k, int cin_pad, int n);
+int st2_umma_pack_weights(const float* w_kcn, int k, int cin, int cin_pad, int n, uint16_t* out_bf16);
+/* host-only test hook: folds weight-norm and repacks one Conv1d (transposed=0) or
+ * ConvTranspose1d (transposed=1, polyphase form) exactly as st2_decoder_load does. */
+int st2_debug_pack_conv(const St2Tensor* tensors, int n, const char* prefix, int transposed, int K,
+                        int stride, int padding, float* w_out, int64_t w_cap, float* bias_out,
+                        int* k_out, int* pad_out, int* cin_out, int* ncols_out);
+/* Per-kernel timing of the tcgen05 conv launches (bench.py's roofline): when enabled, every
+ * st2_conv_umma launch of the calling thread is bracketed by CUDA events on its stream.
+ * st2_prof_read synchronises those events and returns the summed device time, the number of
+ * launches and their algorithmic FLOPs (St2ConvParams.algo_flops); reset != 0 clears the log. */
+int st2_prof_enable(int on);
+int st2_prof_read(double* umma_ms, int64_t* umma_launches, double* umma_flops, int reset);
+/* rows of the time tile and partial-statistics tiles each implementation uses. */
+int st2_conv_tile_rows(int use_umma);
+
+/* Harmonic source + STFT (istftnet.py:351-356) and exp/sin heads + inverse STFT (:377-379). */
+int st2_source_har(const float* f0, const float* noise, uint64_t seed, const float* lin_w9,
+                   float lin_b, int B, int T, int spf, float* phase_scratch, float* har_source,
+                   void* stream);
+int st2_stft_har(const float* har_source, int B, int Lw, float* har_cl32, void* stream);
+int st2_istft_head(const float* x_cl32, int B, int frames, float* wav, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* ST2_DECODER_H */

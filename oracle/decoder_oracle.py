@@ -24,7 +24,7 @@ envelope division, reflection pad, polyphase structure) is written out explicitl
 
 Pinning: the reference holds no tests or golden vectors, so parity
 is pinned by ``oracle/make_golden.py``, which imports the reference's own modules in
-the build container, loads the synthetic state dict from ``oracle/synth.py`` and stores
+the build container, loads the synthetic state dict from ``synthetic.py`` and stores
 inputs/outputs under ``tests/golden/``.  ``tests/test_oracle_golden.py`` checks this
 file against those vectors.
 
@@ -285,6 +285,7 @@ def generator_istftnet(x, s, f0_frames, P: Params, cfg, noise=None, har_source=N
             har_source = source_module(f0_frames, noise, P, spf)
         mag, ph = stft_transform(har_source.to(P.dtype), n_fft, hop)
         har = torch.cat([mag, ph], dim=1)  # :356
+    har = har.to(P.dtype)
     if taps is not None:
         taps["har_source"], taps["har"] = har_source, har
     for i in range(len(rates)):

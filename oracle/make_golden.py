@@ -1,7 +1,7 @@
 """Generate golden vectors from the REAL reference (run in the build container only).
 
 TEST INFRASTRUCTURE ONLY.  Imports ``/root/reference/Modules/{istftnet,hifigan}.py``
-unmodified, loads the synthetic state dict of ``oracle/synth.py`` into the reference
+unmodified, loads the synthetic state dict of ``synthetic.py`` into the reference
 ``Decoder``, captures the harmonic excitation with a forward hook on
 ``generator.m_source`` (no edits to reference files), and writes
 
@@ -25,7 +25,7 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, ROOT)
 REF = os.environ.get("ST2_REFERENCE", "/root/reference")
 
-from oracle import synth  # noqa: E402
+import synthetic as synth  # noqa: E402
 from oracle import decoder_oracle as orc  # noqa: E402
 
 

@@ -1,0 +1,130 @@
+// common.cuh — shared device/host helpers for libst2dec (sm_100a only).
+#pragma once
+#include <cuda_bf16.h>
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <stdio.h>
+
+#include <string>
+
+#include "../../include/st2_decoder.h"
+#include "conv_params.h"
+
+namespace st2 {
+
+void set_error(const std::string& msg);  // decoder.cu (thread-local)
+int64_t& launch_counter();               // decoder.cu (thread-local running count)
+
+#define ST2_CUDA_OK(expr)                                                              \
+  do {                                                                                 \
+    cudaError_t _e = (expr);                                                           \
+    if (_e != cudaSuccess) {                                                           \
+      st2::set_error(std::string(#expr) + ": " + cudaGetErrorString(_e));              \
+      return ST2_ECUDA;                                                                \
+    }                                                                                  \
+  } while (0)
+
+#define ST2_LAUNCH_OK(name)                                                            \
+  do {                                                                                 \
+    st2::launch_counter()++;                                                           \
+    cudaError_t _e = cudaGetLastError();                                               \
+    if (_e != cudaSuccess) {                                                           \
+      st2::set_error(std::string("launch ") + name + ": " + cudaGetErrorString(_e));   \
+      return ST2_ECUDA;                                                                \
+    }                                                                                  \
+  } while (0)
+
+#define ST2_REQUIRE(cond, msg)                                                         \
+  do {                                                                                 \
+    if (!(cond)) {                                                                     \
+      st2::set_error(std::string("invalid argument: ") + msg + " [" #cond "]");        \
+      return ST2_EINVAL;                                                               \
+    }                                                                                  \
+  } while (0)
+
+static inline int ceil_div(int a, int b) { return (a + b - 1) / b; }
+static inline int64_t round_up(int64_t a, int64_t b) { return (a + b - 1) / b * b; }
+
+// ---- dtype-generic element access (fp32 or bf16 storage, fp32 math) -------------------
+template <typename T>
+__device__ __forceinline__ float ld_f(const T* p);
+template <>
+__device__ __forceinline__ float ld_f<float>(const float* p) { return *p; }
+template <>
+__device__ __forceinline__ float ld_f<__nv_bfloat16>(const __nv_bfloat16* p) {
+  return __bfloat162float(*p);
+}
+template <typename T>
+__device__ __forceinline__ void st_f(T* p, float v);
+template <>
+__device__ __forceinline__ void st_f<float>(float* p, float v) { *p = v; }
+template <>
+__device__ __forceinline__ void st_f<__nv_bfloat16>(__nv_bfloat16* p, float v) {
+  *p = __float2bfloat16_rn(v);
+}
+// value as it will be read back (statistics are taken on the stored value)
+template <typename T>
+__device__ __forceinline__ float round_to(float v);
+template <>
+__device__ __forceinline__ float round_to<float>(float v) { return v; }
+template <>
+__device__ __forceinline__ float round_to<__nv_bfloat16>(float v) {
+  return __bfloat162float(__float2bfloat16_rn(v));
+}
+
+// pre-activation of the conv prologue (conv_params.h).  PRECISE selects sinf (fp32 parity
+// path) vs the SFU approximation (bf16 throughput path).
+template <bool PRECISE>
+__device__ __forceinline__ float apply_act(float v, int act, float slope, float a, float inv_a) {
+  if (act == ST2_ACT_LRELU) return v > 0.f ? v : v * slope;
+  if (act == ST2_ACT_SNAKE) {
+    float s = PRECISE ? sinf(a * v) : __sinf(a * v);
+    return v + inv_a * (s * s);  // x + (1/a) sin^2(a x), istftnet.py:69
+  }
+  return v;
+}
+
+__device__ __forceinline__ float warp_sum(float v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+  return v;
+}
+
+// ---- kernel launchers implemented across the .cu files --------------------------------
+int launch_conv_simt(const St2ConvParams& p, cudaStream_t st);
+int launch_conv_umma(const St2ConvParams& p, cudaStream_t st);
+int conv_tile_rows(bool umma);
+
+int launch_style_fc(const float* s, const float* W, const float* bvec, float* h, int B, int style,
+                    int rows, cudaStream_t st);
+int launch_stats_finalize(const float* partials, int n_tiles, int n_cols, int C, int64_t count,
+                          const float* h, int h_stride, int gamma_off, float* ss, int ss_stride,
+                          int c_off, int B, cudaStream_t st);
+template <typename T>
+int launch_colstats(const T* x, int64_t bstride, int ld, int L, int c0, int ncols, float* partials,
+                    int B, cudaStream_t st);
+int colstats_tiles(int L);
+template <typename T>
+int launch_prep_inputs(const float* asr, const float* f0, const float* n, const float* f0w,
+                       const float* nw, T* x0, int ld0, T* ca, T* cb, int ldc, int c_f0, int B,
+                       int dim_in, int T2, cudaStream_t st);
+template <typename T>
+int launch_pool_up2(const T* x, int64_t x_bstride, int ldx, const float* ss, int ss_stride,
+                    float slope, const float* w3, const float* bias, T* y, int64_t y_bstride, int ldy,
+                    int B, int Lin, int C, int Cpad, cudaStream_t st);
+template <typename T>
+int launch_reflect_row0(const T* xin, int64_t xin_bstride, int cin, float slope, const float* w_tap,
+                        const float* bias, const T* xs, int64_t xs_bstride, T* y, int64_t y_bstride,
+                        int cout, float* stats_slot, int64_t stats_bstride, int B, cudaStream_t st);
+int launch_cl_to_ncl(const float* cl, int ld, int C, int L, float* ncl, int B, cudaStream_t st);
+int launch_ncl_to_cl(const float* ncl, int C, int L, float* cl, int ld, int B, cudaStream_t st);
+
+int launch_phase_scan(const float* f0, int B, int T, int spf, float* phase, cudaStream_t st);
+int launch_har_source(const float* f0, const float* phase, const float* noise, uint64_t seed,
+                      const float* lin_w9, float lin_b, int B, int T, int spf, float* out,
+                      cudaStream_t st);
+int launch_stft(const float* hs, int B, int Lw, float* har_cl, int ld, cudaStream_t st);
+int launch_istft(const float* x_cl, int ld, int B, int frames, float* wav, cudaStream_t st);
+int launch_tanh_inplace(float* x, int64_t n, cudaStream_t st);
+
+}  // namespace st2

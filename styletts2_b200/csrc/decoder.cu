@@ -1,0 +1,1047 @@
+// decoder.cu — host runtime of libst2dec: handle, load-time weight folding / packing, workspace
+// planning and the layer schedule of Decoder.forward (Modules/istftnet.py:498-527,
+// Modules/hifigan.py:445-474), plus the extern "C" entry points declared in include/st2_decoder.h.
+#include <math.h>
+#include <string.h>
+
+#include <map>
+#include <string>
+#include <vector>
+
+#include "common.cuh"
+
+namespace st2 {
+
+static thread_local std::string g_err;
+static thread_local int64_t g_launches = 0;
+void set_error(const std::string& msg) { g_err = msg; }
+int64_t& launch_counter() { return g_launches; }
+int launch_tanh_inplace(float* x, int64_t n, cudaStream_t st);  // elementwise.cu
+
+// ------------------------------------------------------------------ layer records
+struct ConvW {
+  int k = 1, dil = 1, pad = 0, stride = 1;
+  int cin = 0;      // contraction channels of the fp32 layout
+  int cin_pad = 0;  // channels of the UMMA blob (multiple of 64), 0 = no blob
+  int n = 0;        // GEMM columns (Cout, or phases*Cout for a transposed conv)
+  int cstat = 0;    // real channels the columns fold onto for statistics
+  double flops_per_row = 0.0;  // algorithmic 2*MAC per output row (per INPUT row for a transposed conv)
+  int64_t w32 = -1, w16 = -1, bias = -1;  // byte offsets into the device weight arena
+};
+struct NormW {
+  int C = 0;
+  int h_off = 0;   // row offset of gamma in the concatenated fc output (beta at h_off + C)
+  int ss_off = 0;  // pair offset inside one batch row of the (scale, shift) arena
+};
+struct ResBlock1W {  // AdaINResBlock1, istftnet.py:27-75
+  int C = 0, k = 0;
+  ConvW c1[3], c2[3];
+  NormW n1[3], n2[3];
+  int64_t a1[3], a2[3];
+};
+struct ResBlk1dW {  // AdainResBlk1d, istftnet.py:409-453
+  int din = 0, dout = 0, din_pad = 0;
+  bool up = false, has_sc = false;
+  ConvW conv1, conv2, conv1x1;
+  NormW n1, n2;
+  int64_t pool_w3 = -1, pool_b = -1;
+};
+struct UpW {
+  ConvW conv;         // polyphase form
+  int rate = 0, cout = 0;
+  int64_t row0_tap = -1;  // [Cin][Cout] tap (1 + padding) for the reflection-padded row (istftnet only)
+};
+
+}  // namespace st2
+
+struct St2Decoder {
+  St2Config cfg;
+  int device = 0;
+  bool loaded = false;
+  int spf = 0;
+  std::vector<std::string> key_names;
+  std::vector<std::vector<int64_t>> key_shapes;
+  // device weights
+  uint8_t* dev = nullptr;
+  int64_t dev_bytes = 0;
+  // plan
+  st2::ResBlk1dW encode, decode[4];
+  st2::ConvW asr_res;
+  int64_t f0w = -1, nw = -1;  // {w0,w1,w2,bias}
+  int64_t fcW = -1, fcB = -1;
+  int fc_rows = 0;
+  int ss_pairs = 0;
+  int64_t lin_w = -1;
+  float lin_b = 0.f;
+  std::vector<st2::UpW> ups;
+  std::vector<st2::ConvW> noise_convs;
+  std::vector<st2::ResBlock1W> noise_res, resblocks;
+  std::vector<int64_t> alphas;  // hifigan generator.alphas
+  st2::ConvW conv_post;
+  int64_t last_launches = 0;
+};
+
+namespace st2 {
+
+// ------------------------------------------------------------------- key list
+static void add_key(St2Decoder* h, const std::string& n, std::vector<int64_t> s) {
+  h->key_names.push_back(n);
+  h->key_shapes.push_back(std::move(s));
+}
+static void keys_wn_conv(St2Decoder* h, const std::string& p, int64_t d0, int64_t d1, int64_t k, bool bias,
+                         int64_t bias_n) {
+  if (bias) add_key(h, p + ".bias", {bias_n});
+  add_key(h, p + ".weight_g", {d0, 1, 1});
+  add_key(h, p + ".weight_v", {d0, d1, k});
+}
+static void keys_adain(St2Decoder* h, const std::string& p, int style, int c) {
+  add_key(h, p + ".fc.weight", {2 * c, style});
+  add_key(h, p + ".fc.bias", {2 * c});
+}
+static void keys_resblk1d(St2Decoder* h, const std::string& p, int din, int dout, int style, bool up) {
+  keys_wn_conv(h, p + ".conv1", dout, din, 3, true, dout);
+  keys_wn_conv(h, p + ".conv2", dout, dout, 3, true, dout);
+  keys_adain(h, p + ".norm1", style, din);
+  keys_adain(h, p + ".norm2", style, dout);
+  if (din != dout) keys_wn_conv(h, p + ".conv1x1", dout, din, 1, false, 0);
+  if (up) keys_wn_conv(h, p + ".pool", din, 1, 3, true, din);
+}
+static void keys_resblock1(St2Decoder* h, const std::string& p, int c, int k, int style) {
+  const char* grp[2] = {"convs1", "convs2"};
+  for (auto g : grp)
+    for (int i = 0; i < 3; ++i) keys_wn_conv(h, p + "." + g + "." + std::to_string(i), c, c, k, true, c);
+  const char* ng[2] = {"adain1", "adain2"};
+  for (auto g : ng)
+    for (int i = 0; i < 3; ++i) keys_adain(h, p + "." + g + "." + std::to_string(i), style, c);
+  const char* ag[2] = {"alpha1", "alpha2"};
+  for (auto g : ag)
+    for (int i = 0; i < 3; ++i) add_key(h, p + "." + g + "." + std::to_string(i), {1, c, 1});
+}
+
+static int prod_from(const int* r, int from, int n) {
+  int p = 1;
+  for (int i = from; i < n; ++i) p *= r[i];
+  return p;
+}
+
+static void build_keys(St2Decoder* h) {
+  const St2Config& c = h->cfg;
+  const int style = c.style_dim;
+  for (int i = 0; i < 3; ++i) keys_resblk1d(h, "decode." + std::to_string(i), 1024 + 2 + 64, 1024, style, false);
+  keys_resblk1d(h, "decode.3", 1024 + 2 + 64, 512, style, true);
+  keys_resblk1d(h, "encode", c.dim_in + 2, 1024, style, false);
+  keys_wn_conv(h, "F0_conv", 1, 1, 3, true, 1);
+  keys_wn_conv(h, "N_conv", 1, 1, 3, true, 1);
+  keys_wn_conv(h, "asr_res.0", 64, 512, 1, true, 64);
+  const std::string g = "generator";
+  add_key(h, g + ".m_source.l_linear.weight", {1, 9});
+  add_key(h, g + ".m_source.l_linear.bias", {1});
+  const bool istft = c.kind == ST2_KIND_ISTFTNET;
+  const int src_ch = istft ? c.gen_istft_n_fft + 2 : 1;
+  const int c0 = c.upsample_initial_channel;
+  for (int i = 0; i < c.n_ups; ++i) {
+    const int cin = c0 >> i, cout = c0 >> (i + 1);
+    keys_wn_conv(h, g + ".ups." + std::to_string(i), cin, cout, c.upsample_kernel_sizes[i], true, cout);
+    int kk = 1, rk = 11;
+    if (i + 1 < c.n_ups) {
+      kk = 2 * prod_from(c.upsample_rates, i + 1, c.n_ups);
+      rk = 7;
+    }
+    add_key(h, g + ".noise_convs." + std::to_string(i) + ".weight", {cout, src_ch, kk});
+    add_key(h, g + ".noise_convs." + std::to_string(i) + ".bias", {cout});
+    keys_resblock1(h, g + ".noise_res." + std::to_string(i), cout, rk, style);
+    for (int j = 0; j < c.n_resblock_kernels; ++j)
+      keys_resblock1(h, g + ".resblocks." + std::to_string(i * c.n_resblock_kernels + j), cout,
+                     c.resblock_kernel_sizes[j], style);
+  }
+  const int ch_last = c0 >> c.n_ups;
+  if (istft) {
+    keys_wn_conv(h, g + ".conv_post", c.gen_istft_n_fft + 2, ch_last, 7, true, c.gen_istft_n_fft + 2);
+  } else {
+    keys_wn_conv(h, g + ".conv_post", 1, ch_last, 7, true, 1);
+    add_key(h, g + ".alphas.0", {1, c0, 1});
+    for (int i = 0; i < c.n_ups; ++i) add_key(h, g + ".alphas." + std::to_string(i + 1), {1, c0 >> (i + 1), 1});
+  }
+}
+
+// ------------------------------------------------------------------- host blob
+struct HostBlob {
+  std::vector<uint8_t> data;
+  int64_t add(const void* src, int64_t bytes) {
+    const int64_t off = round_up((int64_t)data.size(), 256);
+    data.resize(off + bytes);
+    if (src) memcpy(data.data() + off, src, bytes);
+    return off;
+  }
+};
+
+struct Loader {
+  std::map<std::string, const St2Tensor*> by_name;
+  HostBlob blob;
+  std::vector<float> fcW, fcB;  // concatenated AdaIN fc layers
+  int style = 0;
+  int ss_pairs = 0;
+  std::string err;
+
+  const St2Tensor* get(const std::string& n) {
+    auto it = by_name.find(n);
+    if (it == by_name.end()) {
+      if (err.empty()) err = "missing key " + n;
+      return nullptr;
+    }
+    return it->second;
+  }
+  // old-style weight_norm, dim 0: w = g * v / ||v|| over all dims but 0 (istftnet.py:5)
+  bool folded(const std::string& p, std::vector<float>& w, int64_t& d0, int64_t& d1, int64_t& d2) {
+    const St2Tensor* v = get(p + ".weight_v");
+    const St2Tensor* g = get(p + ".weight_g");
+    if (!v || !g) return false;
+    d0 = v->shape[0]; d1 = v->shape[1]; d2 = v->shape[2];
+    const int64_t inner = d1 * d2;
+    w.resize(d0 * inner);
+    for (int64_t o = 0; o < d0; ++o) {
+      double nrm = 0.0;
+      for (int64_t i = 0; i < inner; ++i) nrm += (double)v->data[o * inner + i] * v->data[o * inner + i];
+      const float scale = (float)((double)g->data[o] / sqrt(nrm));
+      for (int64_t i = 0; i < inner; ++i) w[o * inner + i] = v->data[o * inner + i] * scale;
+    }
+    return true;
+  }
+  void finish_conv(ConvW& c, const std::vector<float>& w_kcn, const std::vector<float>* bias, bool want_umma) {
+    c.w32 = blob.add(w_kcn.data(), (int64_t)w_kcn.size() * 4);
+    if (bias) c.bias = blob.add(bias->data(), (int64_t)bias->size() * 4);
+    if (want_umma && c.stride == 1 && c.n % 128 == 0 && (c.k - 1) * c.dil <= 50) {
+      c.cin_pad = (int)round_up(c.cin, 64);
+      const int64_t elems = st2_umma_packed_elems(c.k, c.cin_pad, c.n);
+      c.w16 = blob.add(nullptr, elems * 2);
+      st2_umma_pack_weights(w_kcn.data(), c.k, c.cin, c.cin_pad, c.n,
+                            reinterpret_cast<uint16_t*>(blob.data.data() + c.w16));
+    }
+  }
+  // Conv1d: torch [Cout][Cin][k] -> [k][Cin][Cout]
+  bool conv1d(ConvW& c, const std::string& p, bool weight_norm, bool has_bias, int k, int dil, int pad,
+              int stride, bool want_umma) {
+    std::vector<float> w;
+    int64_t d0, d1, d2;
+    if (weight_norm) {
+      if (!folded(p, w, d0, d1, d2)) return false;
+    } else {
+      const St2Tensor* t = get(p + ".weight");
+      if (!t) return false;
+      d0 = t->shape[0]; d1 = t->shape[1]; d2 = t->shape[2];
+      w.assign(t->data, t->data + d0 * d1 * d2);
+    }
+    c.k = k; c.dil = dil; c.pad = pad; c.stride = stride;
+    c.cin = (int)d1; c.n = (int)d0; c.cstat = (int)d0;
+    c.flops_per_row = 2.0 * (double)d0 * (double)d1 * (double)d2;
+    std::vector<float> kcn((size_t)d2 * d1 * d0);
+    for (int64_t co = 0; co < d0; ++co)
+      for (int64_t ci = 0; ci < d1; ++ci)
+        for (int64_t j = 0; j < d2; ++j) kcn[(j * d1 + ci) * d0 + co] = w[(co * d1 + ci) * d2 + j];
+    std::vector<float> b;
+    if (has_bias) {
+      const St2Tensor* bt = get(p + ".bias");
+      if (!bt) return false;
+      b.assign(bt->data, bt->data + d0);
+    }
+    finish_conv(c, kcn, has_bias ? &b : nullptr, want_umma);
+    return true;
+  }
+  // ConvTranspose1d [Cin][Cout][K] (stride s, padding p) -> polyphase conv over input offsets
+  // o in [omin, omax]: y[s*q + r] += x[q + o] * w[.., r + p - s*o]  (0 <= r + p - s*o < K)
+  bool conv_transpose(UpW& u, const std::string& p, int K, int s, int pd) {
+    std::vector<float> w;
+    int64_t d0, d1, d2;
+    if (!folded(p, w, d0, d1, d2)) return false;
+    const St2Tensor* bt = get(p + ".bias");
+    if (!bt) return false;
+    const int cin = (int)d0, cout = (int)d1;
+    const int omax = (s - 1 + pd) / s, omin = -((K - 1 - pd) / s);
+    ConvW& c = u.conv;
+    c.k = omax - omin + 1; c.dil = 1; c.pad = -omin; c.stride = 1;
+    c.cin = cin; c.n = s * cout; c.cstat = cout;
+    c.flops_per_row = 2.0 * (double)cin * (double)cout * (double)K;  // 2*Cin*Lin*Cout*K in total
+    std::vector<float> kcn((size_t)c.k * cin * c.n, 0.f);
+    for (int j = 0; j < c.k; ++j) {
+      const int o = j + omin;
+      for (int r = 0; r < s; ++r) {
+        const int kk = r + pd - s * o;
+        if (kk < 0 || kk >= K) continue;
+        for (int ci = 0; ci < cin; ++ci)
+          for (int co = 0; co < cout; ++co)
+            kcn[((size_t)j * cin + ci) * c.n + r * cout + co] = w[((size_t)ci * cout + co) * K + kk];
+      }
+    }
+    std::vector<float> b((size_t)c.n);
+    for (int r = 0; r < s; ++r)
+      for (int co = 0; co < cout; ++co) b[r * cout + co] = bt->data[co];
+    finish_conv(c, kcn, &b, true);
+    u.rate = s; u.cout = cout;
+    // tap seen by output t = 1 from input row 0 (reflection-padded row of the last iSTFTNet stage)
+    std::vector<float> tap((size_t)cin * cout);
+    const int kk1 = 1 + pd;
+    for (int ci = 0; ci < cin; ++ci)
+      for (int co = 0; co < cout; ++co) tap[(size_t)ci * cout + co] = kk1 < K ? w[((size_t)ci * cout + co) * K + kk1] : 0.f;
+    u.row0_tap = blob.add(tap.data(), (int64_t)tap.size() * 4);
+    return true;
+  }
+  bool norm(NormW& n, const std::string& p, int C) {
+    const St2Tensor* w = get(p + ".fc.weight");
+    const St2Tensor* b = get(p + ".fc.bias");
+    if (!w || !b) return false;
+    n.C = C;
+    n.h_off = (int)fcB.size();
+    fcW.insert(fcW.end(), w->data, w->data + (int64_t)2 * C * style);
+    fcB.insert(fcB.end(), b->data, b->data + 2 * C);
+    n.ss_off = ss_pairs;
+    ss_pairs += (int)round_up(C, 64);
+    return true;
+  }
+  bool vec(int64_t& off, const std::string& name, int64_t n) {
+    const St2Tensor* t = get(name);
+    if (!t) return false;
+    off = blob.add(t->data, n * 4);
+    return true;
+  }
+  bool resblk1d(ResBlk1dW& r, const std::string& p, int din, int dout, bool up) {
+    r.din = din; r.dout = dout; r.up = up; r.has_sc = din != dout;
+    r.din_pad = (int)round_up(din, 64);
+    bool ok = conv1d(r.conv1, p + ".conv1", true, true, 3, 1, 1, 1, true) &&
+              conv1d(r.conv2, p + ".conv2", true, true, 3, 1, 1, 1, true) && norm(r.n1, p + ".norm1", din) &&
+              norm(r.n2, p + ".norm2", dout);
+    if (ok && r.has_sc) ok = conv1d(r.conv1x1, p + ".conv1x1", true, false, 1, 1, 0, 1, true);
+    if (ok && up) {
+      std::vector<float> w;
+      int64_t d0, d1, d2;
+      ok = folded(p + ".pool", w, d0, d1, d2);  // [din][1][3], g per channel
+      if (ok) {
+        r.pool_w3 = blob.add(w.data(), (int64_t)w.size() * 4);
+        ok = vec(r.pool_b, p + ".pool.bias", din);
+      }
+    }
+    return ok;
+  }
+  bool resblock1(ResBlock1W& r, const std::string& p, int C, int k, const int* dils) {
+    r.C = C; r.k = k;
+    bool ok = true;
+    for (int i = 0; i < 3 && ok; ++i) {
+      const std::string si = std::to_string(i);
+      ok = conv1d(r.c1[i], p + ".convs1." + si, true, true, k, dils[i], dils[i] * (k - 1) / 2, 1, true) &&
+           conv1d(r.c2[i], p + ".convs2." + si, true, true, k, 1, (k - 1) / 2, 1, true) &&
+           norm(r.n1[i], p + ".adain1." + si, C) && norm(r.n2[i], p + ".adain2." + si, C) &&
+           vec(r.a1[i], p + ".alpha1." + si, C) && vec(r.a2[i], p + ".alpha2." + si, C);
+    }
+    return ok;
+  }
+};
+
+static int do_load(St2Decoder* h, const St2Tensor* tensors, int n) {
+  const St2Config& c = h->cfg;
+  Loader L;
+  L.style = c.style_dim;
+  std::vector<std::string> names(n);
+  for (int i = 0; i < n; ++i) {
+    ST2_REQUIRE(tensors[i].name && tensors[i].data, "tensor without name/data");
+    std::string nm = tensors[i].name;
+    if (nm.rfind("module.", 0) == 0) nm = nm.substr(7);  // DDP prefix, models.py:1126-1142
+    L.by_name[nm] = &tensors[i];
+  }
+  // strict key / shape check (load_state_dict semantics)
+  for (size_t i = 0; i < h->key_names.size(); ++i) {
+    auto it = L.by_name.find(h->key_names[i]);
+    ST2_REQUIRE(it != L.by_name.end(), "missing key " + h->key_names[i]);
+    const St2Tensor* t = it->second;
+    bool same = t->ndim == (int)h->key_shapes[i].size();
+    for (int d = 0; same && d < t->ndim; ++d) same = t->shape[d] == h->key_shapes[i][d];
+    ST2_REQUIRE(same, "shape mismatch for " + h->key_names[i]);
+  }
+  ST2_REQUIRE(L.by_name.size() == h->key_names.size(), "unexpected keys in state dict");
+
+  bool ok = true;
+  for (int i = 0; i < 3 && ok; ++i) ok = L.resblk1d(h->decode[i], "decode." + std::to_string(i), 1090, 1024, false);
+  ok = ok && L.resblk1d(h->decode[3], "decode.3", 1090, 512, true);
+  ok = ok && L.resblk1d(h->encode, "encode", c.dim_in + 2, 1024, false);
+  ok = ok && L.conv1d(h->asr_res, "asr_res.0", true, true, 1, 1, 0, 1, false);
+  for (int which = 0; which < 2 && ok; ++which) {
+    const std::string p = which == 0 ? "F0_conv" : "N_conv";
+    std::vector<float> w;
+    int64_t d0, d1, d2;
+    ok = L.folded(p, w, d0, d1, d2);
+    const St2Tensor* b = ok ? L.get(p + ".bias") : nullptr;
+    ok = ok && b;
+    if (ok) {
+      float four[4] = {w[0], w[1], w[2], b->data[0]};
+      (which == 0 ? h->f0w : h->nw) = L.blob.add(four, sizeof(four));
+    }
+  }
+  const std::string g = "generator";
+  if (ok) {
+    ok = L.vec(h->lin_w, g + ".m_source.l_linear.weight", 9);
+    const St2Tensor* lb = L.get(g + ".m_source.l_linear.bias");
+    ok = ok && lb;
+    if (ok) h->lin_b = lb->data[0];
+  }
+  const bool istft = c.kind == ST2_KIND_ISTFTNET;
+  const int c0 = c.upsample_initial_channel;
+  h->ups.assign(c.n_ups, UpW());
+  h->noise_convs.assign(c.n_ups, ConvW());
+  h->noise_res.assign(c.n_ups, ResBlock1W());
+  h->resblocks.assign(c.n_ups * c.n_resblock_kernels, ResBlock1W());
+  const int d135[3] = {1, 3, 5};
+  for (int i = 0; i < c.n_ups && ok; ++i) {
+    const std::string si = std::to_string(i);
+    const int cout = c0 >> (i + 1);
+    const int u = c.upsample_rates[i], K = c.upsample_kernel_sizes[i];
+    const int pd = istft ? (K - u) / 2 : (u / 2 + u % 2);  // istftnet.py:321, hifigan.py:293
+    ok = L.conv_transpose(h->ups[i], g + ".ups." + si, K, u, pd);
+    int rk = 11;
+    if (ok && i + 1 < c.n_ups) {
+      const int sf = prod_from(c.upsample_rates, i + 1, c.n_ups);
+      ok = L.conv1d(h->noise_convs[i], g + ".noise_convs." + si, false, true, 2 * sf, 1, (sf + 1) / 2, sf, false);
+      rk = 7;
+    } else if (ok) {
+      ok = L.conv1d(h->noise_convs[i], g + ".noise_convs." + si, false, true, 1, 1, 0, 1, false);
+    }
+    ok = ok && L.resblock1(h->noise_res[i], g + ".noise_res." + si, cout, rk, d135);
+    for (int j = 0; j < c.n_resblock_kernels && ok; ++j)
+      ok = L.resblock1(h->resblocks[i * c.n_resblock_kernels + j],
+                       g + ".resblocks." + std::to_string(i * c.n_resblock_kernels + j), cout,
+                       c.resblock_kernel_sizes[j], c.resblock_dilations[j]);
+  }
+  ok = ok && L.conv1d(h->conv_post, g + ".conv_post", true, true, 7, 1, 3, 1, false);
+  if (ok && !istft) {
+    h->alphas.assign(c.n_ups + 1, -1);
+    for (int i = 0; i <= c.n_ups && ok; ++i)
+      ok = L.vec(h->alphas[i], g + ".alphas." + std::to_string(i), i == 0 ? c0 : c0 >> i);
+  }
+  ST2_REQUIRE(ok, L.err);
+  h->fc_rows = (int)L.fcB.size();
+  h->ss_pairs = L.ss_pairs;
+  h->fcW = L.blob.add(L.fcW.data(), (int64_t)L.fcW.size() * 4);
+  h->fcB = L.blob.add(L.fcB.data(), (int64_t)L.fcB.size() * 4);
+
+  ST2_CUDA_OK(cudaSetDevice(h->device));
+  if (h->dev) ST2_CUDA_OK(cudaFree(h->dev));
+  h->dev = nullptr;
+  h->dev_bytes = (int64_t)L.blob.data.size();
+  ST2_CUDA_OK(cudaMalloc(&h->dev, h->dev_bytes));
+  ST2_CUDA_OK(cudaMemcpy(h->dev, L.blob.data.data(), h->dev_bytes, cudaMemcpyHostToDevice));
+  h->loaded = true;
+  return ST2_OK;
+}
+
+}  // namespace st2
+
+// =============================================================================== forward
+namespace st2 {
+
+struct Arena {
+  uint8_t* base = nullptr;
+  int64_t cap = 0, off = 0, peak = 0;
+  bool dry = false;
+  template <typename T>
+  T* alloc(int64_t count) {
+    off = round_up(off, 256);
+    T* p = reinterpret_cast<T*>((dry ? reinterpret_cast<uint8_t*>((uintptr_t)4096) : base) + off);
+    off += count * (int64_t)sizeof(T);
+    if (off > peak) peak = off;
+    return p;
+  }
+  int64_t mark() const { return off; }
+  void release(int64_t m) { off = m; }
+};
+
+template <typename AT>
+struct DT;
+template <>
+struct DT<float> { static constexpr int id = ST2_DT_F32; };
+template <>
+struct DT<__nv_bfloat16> { static constexpr int id = ST2_DT_BF16; };
+
+// channels-last activation view
+template <typename AT>
+struct Act {
+  AT* p = nullptr;
+  int64_t bstride = 0;
+  int ld = 0;
+  int L = 0;
+};
+
+template <typename AT>
+struct Fwd {
+  St2Decoder* h;
+  Arena ar;
+  cudaStream_t st;
+  int B, T;
+  bool dry;
+  const float* hall = nullptr;  // [B][fc_rows]
+  float* ss = nullptr;          // [B][ss_pairs][2]
+
+  template <typename U>
+  U* W(int64_t off) const { return off < 0 ? nullptr : reinterpret_cast<U*>(h->dev + off); }
+
+#define RUN(x)                 \
+  do {                         \
+    if (!dry) {                \
+      int _rc = (x);           \
+      if (_rc) return _rc;     \
+    }                          \
+  } while (0)
+
+  const float* ss_of(const NormW& n) const { return ss + (int64_t)n.ss_off * 2; }
+
+  // finalize InstanceNorm statistics of channels [c_off, c_off+C) of norm layer n
+  int finalize(const float* partials, int n_tiles, int n_cols, int C, int64_t count, const NormW& n,
+               int c_off) {
+    RUN(launch_stats_finalize(partials, n_tiles, n_cols, C, count, hall + n.h_off, h->fc_rows, n.C,
+                              ss + (int64_t)n.ss_off * 2, h->ss_pairs, c_off, B, st));
+    return ST2_OK;
+  }
+
+  struct ConvIO {
+    const void* x; int x_dtype; int64_t x_bstride; int ldx; int Lin;
+    void* y; int y_dtype; int64_t y_bstride; int ldy; int Lout;
+    const void* res = nullptr; int64_t res_bstride = 0; int ldres = 0; int res_shift = 0;
+    const NormW* pre_norm = nullptr; int act = ST2_ACT_NONE; float slope = 0.f; const float* alpha = nullptr;
+    float out_scale = 1.f; int accumulate = 0;
+    bool want_stats = false;
+    int extra_stat_tiles = 0;
+  };
+  // stats result of the last conv() call
+  float* last_partials = nullptr;
+  int last_tiles = 0, last_cols = 0;
+
+  // runs one fused conv; partial statistics (if requested) are left in arena scratch that the
+  // caller must consume (finalize) before the next arena allocation that follows a release.
+  int conv(const ConvW& c, const ConvIO& io) {
+    const bool umma = DT<AT>::id == ST2_DT_BF16 && c.w16 >= 0 && io.x_dtype == ST2_DT_BF16 &&
+                      io.y_dtype == ST2_DT_BF16;
+    St2ConvParams p;
+    memset(&p, 0, sizeof(p));
+    p.B = B;
+    p.x = io.x; p.x_dtype = io.x_dtype; p.x_bstride = io.x_bstride; p.ldx = io.ldx; p.Lin = io.Lin;
+    p.cin = umma ? c.cin_pad : c.cin;
+    if (io.pre_norm) {
+      p.ss = ss_of(*io.pre_norm);
+      p.ss_stride = h->ss_pairs;
+    }
+    p.act = io.act; p.slope = io.slope; p.alpha = io.alpha;
+    p.k = c.k; p.dil = c.dil; p.pad = c.pad; p.stride = c.stride;
+    p.w = umma ? (const void*)W<uint16_t>(c.w16) : (const void*)W<float>(c.w32);
+    p.bias = W<float>(c.bias);
+    p.n_cols = c.n;
+    p.y = io.y; p.y_dtype = io.y_dtype; p.y_bstride = io.y_bstride; p.ldy = io.ldy; p.Lout = io.Lout;
+    p.res = io.res; p.res_bstride = io.res_bstride; p.ldres = io.ldres; p.res_shift = io.res_shift;
+    p.out_scale = io.out_scale; p.accumulate = io.accumulate;
+    p.algo_flops = c.flops_per_row * (double)io.Lout * (double)B;
+    if (io.want_stats) {
+      const int tiles = ceil_div(io.Lout, conv_tile_rows(umma));
+      p.n_tiles = tiles + io.extra_stat_tiles;
+      p.stats = ar.alloc<float>((int64_t)B * p.n_tiles * c.n * 2);
+      last_partials = p.stats; last_tiles = p.n_tiles; last_cols = c.n;
+      if (io.extra_stat_tiles) RUN((cudaMemsetAsync(p.stats, 0, (size_t)B * p.n_tiles * c.n * 8, st) == cudaSuccess) ? ST2_OK : ST2_ECUDA);
+    }
+    RUN(umma ? launch_conv_umma(p, st) : launch_conv_simt(p, st));
+    return ST2_OK;
+  }
+
+  ConvIO io_of(const Act<AT>& x, const Act<AT>& y) const {
+    ConvIO io;
+    io.x = x.p; io.x_dtype = DT<AT>::id; io.x_bstride = x.bstride; io.ldx = x.ld; io.Lin = x.L;
+    io.y = y.p; io.y_dtype = DT<AT>::id; io.y_bstride = y.bstride; io.ldy = y.ld; io.Lout = y.L;
+    return io;
+  }
+  Act<AT> new_act(int L, int C) {
+    Act<AT> a;
+    a.p = ar.alloc<AT>((int64_t)B * L * C);
+    a.bstride = (int64_t)L * C; a.ld = C; a.L = L;
+    return a;
+  }
+
+  // AdainResBlk1d (istftnet.py:440-453).  `in` has r.din_pad columns; norm1 of `in` must already be
+  // finalized.  Output goes to out (any ld).  want_out_stats leaves partials in last_*.
+  int resblk1d(const ResBlk1dW& r, const Act<AT>& in, const Act<AT>& out, bool want_out_stats) {
+    const int64_t m0 = ar.mark();
+    const int L = in.L, Lo = r.up ? 2 * L : L;
+    Act<AT> cin1 = in;
+    if (r.up) {  // AdaIN + LeakyReLU + depthwise transposed conv, materialised at 2L
+      cin1 = new_act(Lo, r.din_pad);
+      RUN(launch_pool_up2<AT>(in.p, in.bstride, in.ld, ss_of(r.n1), h->ss_pairs, 0.2f, W<float>(r.pool_w3),
+                              W<float>(r.pool_b), cin1.p, cin1.bstride, cin1.ld, B, L, r.din, r.din_pad, st));
+    }
+    Act<AT> hbuf = new_act(Lo, r.dout);
+    {
+      ConvIO io = io_of(cin1, hbuf);
+      if (!r.up) { io.pre_norm = &r.n1; io.act = ST2_ACT_LRELU; io.slope = 0.2f; }
+      io.want_stats = true;
+      const int64_t m1 = ar.mark();
+      int rc = conv(r.conv1, io);
+      if (rc) return rc;
+      rc = finalize(last_partials, last_tiles, last_cols, r.dout, Lo, r.n2, 0);
+      if (rc) return rc;
+      ar.release(m1);
+    }
+    Act<AT> sc = in;  // identity shortcut when dims match (never the case in this decoder)
+    if (r.has_sc) {
+      sc = new_act(L, r.dout);
+      ConvIO io = io_of(in, sc);
+      int rc = conv(r.conv1x1, io);
+      if (rc) return rc;
+    }
+    {
+      ConvIO io = io_of(hbuf, out);
+      io.pre_norm = &r.n2; io.act = ST2_ACT_LRELU; io.slope = 0.2f;
+      io.res = sc.p; io.res_bstride = sc.bstride; io.ldres = sc.ld; io.res_shift = r.up ? 1 : 0;
+      io.out_scale = 0.70710678118654752440f;  // 1/sqrt(2), istftnet.py:452
+      io.want_stats = want_out_stats;
+      // partials of this conv stay allocated for the caller (it finalizes, then releases)
+      int rc = conv(r.conv2, io);
+      if (rc) return rc;
+    }
+    if (!want_out_stats) ar.release(m0);
+    return ST2_OK;
+  }
+
+  // AdaINResBlock1 (istftnet.py:66-75).  x: block input whose adain1[0] scale/shift are finalized.
+  // run: private running buffer (may alias x for the in-place noise_res), tmp: conv1 output.
+  // final: destination of the last iteration; final_scale / final_acc implement mean over resblocks.
+  int resblock1(const ResBlock1W& r, const Act<AT>& x, const Act<AT>& run, const Act<AT>& tmp,
+                const Act<AT>& fin, float final_scale, int final_acc) {
+    for (int it = 0; it < 3; ++it) {
+      const Act<AT>& src = it == 0 ? x : run;
+      const bool last = it == 2;
+      const int64_t m = ar.mark();
+      {
+        ConvIO io = io_of(src, tmp);
+        io.pre_norm = &r.n1[it]; io.act = ST2_ACT_SNAKE; io.alpha = W<float>(r.a1[it]);
+        io.want_stats = true;
+        int rc = conv(r.c1[it], io);
+        if (rc) return rc;
+        rc = finalize(last_partials, last_tiles, last_cols, r.C, tmp.L, r.n2[it], 0);
+        if (rc) return rc;
+        ar.release(m);
+      }
+      {
+        const Act<AT>& dst = last ? fin : run;
+        ConvIO io = io_of(tmp, dst);
+        io.pre_norm = &r.n2[it]; io.act = ST2_ACT_SNAKE; io.alpha = W<float>(r.a2[it]);
+        io.res = src.p; io.res_bstride = src.bstride; io.ldres = src.ld;
+        if (last) { io.out_scale = final_scale; io.accumulate = final_acc; }
+        io.want_stats = !last;
+        int rc = conv(r.c2[it], io);
+        if (rc) return rc;
+        if (!last) {
+          rc = finalize(last_partials, last_tiles, last_cols, r.C, dst.L, r.n1[it + 1], 0);
+          if (rc) return rc;
+        }
+        ar.release(m);
+      }
+    }
+    return ST2_OK;
+  }
+
+  int run(const float* asr, const float* f0, const float* nn, const float* s, float* wav,
+          const St2ForwardOpts& o);
+};
+
+template <typename AT>
+int Fwd<AT>::run(const float* asr, const float* f0, const float* nn, const float* s, float* wav,
+                 const St2ForwardOpts& o) {
+  const St2Config& c = h->cfg;
+  const bool istft = c.kind == ST2_KIND_ISTFTNET;
+  const int T2 = T / 2;
+  const int spf = h->spf;
+  const int64_t Lw = (int64_t)T * spf;
+
+  // ---- all AdaIN fc layers at once; zeroed (scale, shift) arena (padding channels stay 0)
+  float* hall_w = ar.alloc<float>((int64_t)B * h->fc_rows);
+  hall = hall_w;
+  ss = ar.alloc<float>((int64_t)B * h->ss_pairs * 2);
+  RUN(launch_style_fc(s, W<float>(h->fcW), W<float>(h->fcB), hall_w, B, c.style_dim, h->fc_rows, st));
+  RUN(cudaMemsetAsync(ss, 0, (size_t)B * h->ss_pairs * 8, st) == cudaSuccess ? ST2_OK : ST2_ECUDA);
+
+  // ---- encode / decode (istftnet.py:510-524)
+  const int din0 = c.dim_in + 2, ld0 = (int)round_up(din0, 64);
+  const int ldc = h->decode[0].din_pad, c_f0 = 1024 + 64;  // [x(1024) | asr_res(64) | F0 | N | 0...]
+  Act<AT> xg = new_act(T, 512);  // decode.3 output = generator input; lives past the decode scratch
+  const int64_t m_dec = ar.mark();
+  {
+    Act<AT> x0 = new_act(T2, ld0), ca = new_act(T2, ldc), cb = new_act(T2, ldc);
+    RUN(launch_prep_inputs<AT>(asr, f0, nn, W<float>(h->f0w), W<float>(h->nw), x0.p, ld0, ca.p, cb.p, ldc,
+                               c_f0, B, c.dim_in, T2, st));
+    // asr_res = Conv1d(512 -> 64, k1)(asr) written into columns [1024, 1088) of both concat buffers
+    for (int which = 0; which < 2; ++which) {
+      Act<AT>& dstb = which == 0 ? ca : cb;
+      ConvIO io = io_of(x0, dstb);
+      io.y = dstb.p + 1024;
+      int rc = conv(h->asr_res, io);
+      if (rc) return rc;
+    }
+    // statistics of tensors no conv epilogue produced: x0 (encode.norm1) and the constant concat columns
+    const int cs_tiles = colstats_tiles(T2);
+    float* p_x0 = ar.alloc<float>((int64_t)B * cs_tiles * din0 * 2);
+    const int n_const = h->decode[0].din - 1024;  // 66
+    float* p_const = ar.alloc<float>((int64_t)B * cs_tiles * n_const * 2);
+    RUN(launch_colstats<AT>(x0.p, x0.bstride, x0.ld, T2, 0, din0, p_x0, B, st));
+    RUN(launch_colstats<AT>(ca.p, ca.bstride, ca.ld, T2, 1024, n_const, p_const, B, st));
+    int rc = finalize(p_x0, cs_tiles, din0, din0, T2, h->encode.n1, 0);
+    if (rc) return rc;
+    for (int i = 0; i < 4; ++i) {
+      rc = finalize(p_const, cs_tiles, n_const, n_const, T2, h->decode[i].n1, 1024);
+      if (rc) return rc;
+    }
+    // encode: x0 -> ca[:, :1024]
+    Act<AT> in = x0;
+    Act<AT> bufs[2] = {ca, cb};
+    for (int blk = 0; blk < 5; ++blk) {
+      const ResBlk1dW& r = blk == 0 ? h->encode : h->decode[blk - 1];
+      const bool lastb = blk == 4;
+      Act<AT> out = lastb ? xg : bufs[blk & 1];
+      if (!lastb) out.L = T2;
+      const int64_t m = ar.mark();
+      rc = resblk1d(r, in, out, !lastb);
+      if (rc) return rc;
+      if (!lastb) {
+        rc = finalize(last_partials, last_tiles, last_cols, 1024, T2, h->decode[blk].n1, 0);
+        if (rc) return rc;
+        in = bufs[blk & 1];
+      }
+      ar.release(m);
+    }
+  }
+  ar.release(m_dec);
+
+  // ---- excitation (istftnet.py:350-356 / hifigan.py:320-323)
+  const int n_fft = c.gen_istft_n_fft, hop = c.gen_istft_hop_size;
+  const int L2 = istft ? (int)(Lw / hop) + 1 : 0;
+  const int ldh = 32;
+  const float* hs = o.har_source;
+  float* har = nullptr;
+  if (istft) har = ar.alloc<float>((int64_t)B * L2 * ldh);
+  if (istft && o.har) {
+    RUN(launch_ncl_to_cl(o.har, n_fft + 2, L2, har, ldh, B, st));
+  } else {
+    if (!hs) {
+      float* ph = ar.alloc<float>((int64_t)B * 9 * T);
+      float* hsw = ar.alloc<float>((int64_t)B * Lw);
+      RUN(launch_phase_scan(f0, B, T, spf, ph, st));
+      RUN(launch_har_source(f0, ph, o.noise, o.seed, W<float>(h->lin_w), h->lin_b, B, T, spf, hsw, st));
+      hs = hsw;
+    }
+    if (istft) RUN(launch_stft(hs, B, (int)Lw, har, ldh, st));
+  }
+  if (o.har_source_out && hs)
+    RUN(cudaMemcpyAsync(o.har_source_out, hs, (size_t)B * Lw * 4, cudaMemcpyDeviceToDevice, st) == cudaSuccess ? ST2_OK : ST2_ECUDA);
+  if (o.har_out && istft) RUN(launch_cl_to_ncl(har, ldh, n_fft + 2, L2, o.har_out, B, st));
+
+  // ---- generator stages (istftnet.py:358-374 / hifigan.py:327-341)
+  Act<AT> x = xg;
+  const int nk = c.n_resblock_kernels;
+  for (int i = 0; i < c.n_ups; ++i) {
+    const UpW& up = h->ups[i];
+    const bool lastst = i == c.n_ups - 1;
+    const int Lin = x.L, C = up.cout;
+    const int pad_rows = (istft && lastst) ? 1 : 0;  // ReflectionPad1d((1,0)), istftnet.py:364-365
+    const int Ls = Lin * up.rate + pad_rows;
+    Act<AT> xs = new_act(Ls, C), xm = new_act(Ls, C), tmp = new_act(Ls, C), runb = new_act(Ls, C),
+            outb = new_act(Ls, C);
+    // x_source = noise_res[i](noise_convs[i](har | har_source))
+    {
+      const ConvW& nc = h->noise_convs[i];
+      ConvIO io;
+      if (istft) { io.x = har; io.x_bstride = (int64_t)L2 * ldh; io.ldx = ldh; io.Lin = L2; }
+      else { io.x = hs; io.x_bstride = Lw; io.ldx = 1; io.Lin = (int)Lw; }
+      io.x_dtype = ST2_DT_F32;
+      io.y = xs.p; io.y_dtype = DT<AT>::id; io.y_bstride = xs.bstride; io.ldy = xs.ld; io.Lout = Ls;
+      io.want_stats = true;
+      const int64_t m = ar.mark();
+      int rc = conv(nc, io);
+      if (rc) return rc;
+      rc = finalize(last_partials, last_tiles, last_cols, C, Ls, h->noise_res[i].n1[0], 0);
+      if (rc) return rc;
+      ar.release(m);
+      rc = resblock1(h->noise_res[i], xs, xs, tmp, xs, 1.f, 0);
+      if (rc) return rc;
+    }
+    // x = ups[i](act(x)) (+ reflection pad) + x_source, with statistics for the three resblocks
+    {
+      ConvIO io;
+      io.x = x.p; io.x_dtype = DT<AT>::id; io.x_bstride = x.bstride; io.ldx = x.ld; io.Lin = Lin;
+      if (istft) { io.act = ST2_ACT_LRELU; io.slope = 0.1f; }
+      else { io.act = ST2_ACT_SNAKE; io.alpha = W<float>(h->alphas[i]); }
+      io.y = xm.p + (int64_t)pad_rows * C; io.y_dtype = DT<AT>::id; io.y_bstride = xm.bstride;
+      io.ldy = up.rate * C; io.Lout = Lin;
+      io.res = xs.p + (int64_t)pad_rows * C; io.res_bstride = xs.bstride; io.ldres = up.rate * C;
+      io.want_stats = true; io.extra_stat_tiles = pad_rows;
+      const int64_t m = ar.mark();
+      int rc = conv(up.conv, io);
+      if (rc) return rc;
+      if (pad_rows) {
+        float* slot = last_partials + (int64_t)(last_tiles - 1) * last_cols * 2;
+        RUN(launch_reflect_row0<AT>(x.p, x.bstride, x.ld, 0.1f, W<float>(up.row0_tap), W<float>(up.conv.bias),
+                                    xs.p, xs.bstride, xm.p, xm.bstride, C, slot,
+                                    (int64_t)last_tiles * last_cols * 2, B, st));
+      }
+      for (int j = 0; j < nk; ++j) {
+        rc = finalize(last_partials, last_tiles, last_cols, C, Ls, h->resblocks[i * nk + j].n1[0], 0);
+        if (rc) return rc;
+      }
+      ar.release(m);
+    }
+    for (int j = 0; j < nk; ++j) {
+      int rc = resblock1(h->resblocks[i * nk + j], xm, runb, tmp, outb, 1.f / (float)nk, j > 0 ? 1 : 0);
+      if (rc) return rc;
+    }
+    x = outb;
+  }
+
+  // ---- output head
+  if (istft) {
+    float* cp = ar.alloc<float>((int64_t)B * L2 * ldh);
+    ConvIO io;
+    io.x = x.p; io.x_dtype = DT<AT>::id; io.x_bstride = x.bstride; io.ldx = x.ld; io.Lin = x.L;
+    io.act = ST2_ACT_LRELU; io.slope = 0.01f;  // F.leaky_relu default slope, istftnet.py:375
+    io.y = cp; io.y_dtype = ST2_DT_F32; io.y_bstride = (int64_t)L2 * ldh; io.ldy = ldh; io.Lout = L2;
+    int rc = conv(h->conv_post, io);
+    if (rc) return rc;
+    RUN(launch_istft(cp, ldh, B, L2, wav, st));
+  } else {
+    ConvIO io;
+    io.x = x.p; io.x_dtype = DT<AT>::id; io.x_bstride = x.bstride; io.ldx = x.ld; io.Lin = x.L;
+    io.act = ST2_ACT_SNAKE; io.alpha = W<float>(h->alphas[c.n_ups]);  // hifigan.py:342
+    io.y = wav; io.y_dtype = ST2_DT_F32; io.y_bstride = Lw; io.ldy = 1; io.Lout = (int)Lw;
+    int rc = conv(h->conv_post, io);
+    if (rc) return rc;
+    RUN(launch_tanh_inplace(wav, (int64_t)B * Lw, st));
+  }
+  return ST2_OK;
+#undef RUN
+}
+
+}  // namespace st2
+
+// ============================================================================ C ABI
+using namespace st2;
+
+static int validate_cfg(const St2Config& c) {
+  ST2_REQUIRE(c.kind == ST2_KIND_ISTFTNET || c.kind == ST2_KIND_HIFIGAN, "kind");
+  ST2_REQUIRE(c.dim_in == 512, "dim_in must be 512 (asr_res is Conv1d(512, 64), istftnet.py:490)");
+  ST2_REQUIRE(c.style_dim > 0 && c.style_dim <= 192, "style_dim");
+  ST2_REQUIRE(c.upsample_initial_channel == 512, "upsample_initial_channel must equal decode.3's 512 outputs");
+  ST2_REQUIRE(c.n_ups >= 1 && c.n_ups <= ST2_MAX_UPS, "n_ups");
+  ST2_REQUIRE(c.n_resblock_kernels >= 1 && c.n_resblock_kernels <= ST2_MAX_RESK, "n_resblock_kernels");
+  for (int i = 0; i < c.n_ups; ++i) {
+    const int u = c.upsample_rates[i], k = c.upsample_kernel_sizes[i];
+    ST2_REQUIRE(u >= 1 && k >= u, "upsample rate / kernel");
+    if (c.kind == ST2_KIND_ISTFTNET) ST2_REQUIRE((k - u) % 2 == 0, "istftnet needs (kernel - rate) even so that Lout = rate * Lin");
+    else ST2_REQUIRE(k == 2 * u, "hifigan upsample kernels must be 2 * rate");
+  }
+  for (int j = 0; j < c.n_resblock_kernels; ++j) {
+    ST2_REQUIRE(c.resblock_kernel_sizes[j] % 2 == 1, "resblock kernel sizes must be odd");
+    for (int d = 0; d < 3; ++d) ST2_REQUIRE(c.resblock_dilations[j][d] >= 1, "dilation");
+  }
+  if (c.kind == ST2_KIND_ISTFTNET)
+    ST2_REQUIRE(c.gen_istft_n_fft == 20 && c.gen_istft_hop_size == 5,
+                "only the shipped n_fft 20 / hop 5 inverse STFT is implemented (Configs/config.yml:59-60)");
+  return ST2_OK;
+}
+
+extern "C" int st2_decoder_create(const St2Config* cfg, St2Decoder** out) {
+  if (!cfg || !out) {
+    set_error("st2_decoder_create: null argument");
+    return ST2_EINVAL;
+  }
+  int rc = validate_cfg(*cfg);
+  if (rc) return rc;
+  St2Decoder* h = new St2Decoder();
+  h->cfg = *cfg;
+  h->spf = 1;
+  for (int i = 0; i < cfg->n_ups; ++i) h->spf *= cfg->upsample_rates[i];
+  if (cfg->kind == ST2_KIND_ISTFTNET) h->spf *= cfg->gen_istft_hop_size;
+  build_keys(h);
+  if (cudaGetDevice(&h->device) != cudaSuccess) h->device = -1;  // reported at load()
+  (void)cudaGetLastError();
+  *out = h;
+  return ST2_OK;
+}
+
+extern "C" int st2_decoder_num_keys(const St2Decoder* h) { return h ? (int)h->key_names.size() : 0; }
+
+extern "C" int st2_decoder_key(const St2Decoder* h, int i, const char** name, int* ndim, int64_t shape[4]) {
+  if (!h || i < 0 || i >= (int)h->key_names.size()) {
+    set_error("st2_decoder_key: index");
+    return ST2_EINVAL;
+  }
+  if (name) *name = h->key_names[i].c_str();
+  if (ndim) *ndim = (int)h->key_shapes[i].size();
+  if (shape)
+    for (size_t d = 0; d < 4; ++d) shape[d] = d < h->key_shapes[i].size() ? h->key_shapes[i][d] : 1;
+  return ST2_OK;
+}
+
+extern "C" int st2_decoder_samples_per_frame(const St2Decoder* h) { return h ? h->spf : 0; }
+
+extern "C" int st2_decoder_load(St2Decoder* h, const St2Tensor* tensors, int n) {
+  if (!h || !tensors || n <= 0) {
+    set_error("st2_decoder_load: null argument");
+    return ST2_EINVAL;
+  }
+  int ndev = 0;
+  if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0) {
+    (void)cudaGetLastError();
+    set_error("st2_decoder_load: no CUDA device (this library has no CPU fallback)");
+    return ST2_ECUDA;
+  }
+  if (h->device < 0) ST2_CUDA_OK(cudaGetDevice(&h->device));
+  cudaDeviceProp prop;
+  ST2_CUDA_OK(cudaGetDeviceProperties(&prop, h->device));
+  if (prop.major != 10) {
+    set_error("st2_decoder_load: device is sm_" + std::to_string(prop.major) + std::to_string(prop.minor) +
+              ", this library is built for sm_100a only");
+    return ST2_ECUDA;
+  }
+  return do_load(h, tensors, n);
+}
+
+template <typename AT>
+static int forward_t(St2Decoder* h, const float* asr, const float* f0, const float* n, const float* s,
+                     float* wav, void* ws, int64_t ws_bytes, int B, int T, const St2ForwardOpts& o,
+                     cudaStream_t st, bool dry, int64_t* peak) {
+  Fwd<AT> f;
+  f.h = h; f.st = st; f.B = B; f.T = T; f.dry = dry;
+  f.ar.base = reinterpret_cast<uint8_t*>(ws); f.ar.cap = ws_bytes; f.ar.dry = dry;
+  int rc = f.run(asr, f0, n, s, wav, o);
+  if (peak) *peak = f.ar.peak;
+  return rc;
+}
+
+static int plan_bytes(St2Decoder* h, int B, int T, const St2ForwardOpts& o, int64_t* bytes) {
+  int64_t peak = 0;
+  int rc;
+  if (o.precision == ST2_PREC_BF16)
+    rc = forward_t<__nv_bfloat16>(h, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, 0, B, T, o, 0, true, &peak);
+  else
+    rc = forward_t<float>(h, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, 0, B, T, o, 0, true, &peak);
+  *bytes = round_up(peak, 256) + 256;
+  return rc;
+}
+
+extern "C" int64_t st2_decoder_workspace_bytes(const St2Decoder* hc, int B, int T, int precision) {
+  St2Decoder* h = const_cast<St2Decoder*>(hc);
+  if (!h || !h->loaded || B < 1 || T < 2 || (T & 1) || (precision != ST2_PREC_FP32 && precision != ST2_PREC_BF16)) {
+    set_error("st2_decoder_workspace_bytes: bad argument or weights not loaded");
+    return ST2_EINVAL;
+  }
+  St2ForwardOpts o;
+  memset(&o, 0, sizeof(o));
+  o.precision = precision;  // no injected excitation = the largest plan
+  int64_t bytes = 0;
+  int rc = plan_bytes(h, B, T, o, &bytes);
+  return rc ? rc : bytes;
+}
+
+extern "C" int st2_decoder_forward(St2Decoder* h, const float* asr, const float* f0, const float* n,
+                                   const float* s, float* wav_out, void* workspace, int64_t workspace_bytes,
+                                   int B, int T, const St2ForwardOpts* opts, void* stream) {
+  if (!h || !asr || !f0 || !n || !s || !wav_out || !workspace) {
+    set_error("st2_decoder_forward: null argument");
+    return ST2_EINVAL;
+  }
+  if (!h->loaded) {
+    set_error("st2_decoder_forward: weights not loaded");
+    return ST2_ESTATE;
+  }
+  ST2_REQUIRE(B >= 1 && T >= 2, "batch / length");
+  ST2_REQUIRE((T & 1) == 0, "len(F0_curve) must equal 2 * asr.shape[-1] (istftnet.py:513)");
+  ST2_REQUIRE(B <= 65535, "batch too large for one call");
+  St2ForwardOpts o;
+  memset(&o, 0, sizeof(o));
+  if (opts) o = *opts;
+  ST2_REQUIRE(o.precision == ST2_PREC_FP32 || o.precision == ST2_PREC_BF16, "precision");
+  ST2_REQUIRE(!(o.har && h->cfg.kind != ST2_KIND_ISTFTNET), "har injection is istftnet-only");
+  ST2_REQUIRE(((uintptr_t)workspace & 255) == 0, "workspace must be 256-byte aligned");
+  int dev = -1;
+  ST2_CUDA_OK(cudaGetDevice(&dev));
+  ST2_REQUIRE(dev == h->device, "handle belongs to another device");
+  int64_t need = 0;
+  int rc = plan_bytes(h, B, T, o, &need);
+  if (rc) return rc;
+  if (need > workspace_bytes) {
+    set_error("st2_decoder_forward: workspace too small (" + std::to_string(workspace_bytes) + " < " +
+              std::to_string(need) + ")");
+    return ST2_ENOMEM;
+  }
+  const int64_t before = launch_counter();
+  cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+  if (o.precision == ST2_PREC_BF16)
+    rc = forward_t<__nv_bfloat16>(h, asr, f0, n, s, wav_out, workspace, workspace_bytes, B, T, o, st, false, nullptr);
+  else
+    rc = forward_t<float>(h, asr, f0, n, s, wav_out, workspace, workspace_bytes, B, T, o, st, false, nullptr);
+  h->last_launches = launch_counter() - before;
+  return rc;
+}
+
+extern "C" int64_t st2_decoder_last_launches(const St2Decoder* h) { return h ? h->last_launches : 0; }
+
+extern "C" void st2_decoder_destroy(St2Decoder* h) {
+  if (!h) return;
+  if (h->dev) {
+    cudaFree(h->dev);
+  }
+  delete h;
+}
+
+extern "C" const char* st2_last_error(void) { return g_err.c_str(); }
+extern "C" const char* st2_version(void) { return "st2dec 0.1 (sm_100a)"; }
+
+// ---- single-kernel entry points
+extern "C" int st2_conv_simt(const St2ConvParams* p, void* stream) {
+  if (!p) return ST2_EINVAL;
+  return launch_conv_simt(*p, reinterpret_cast<cudaStream_t>(stream));
+}
+extern "C" int st2_conv_umma(const St2ConvParams* p, void* stream) {
+  if (!p) return ST2_EINVAL;
+  return launch_conv_umma(*p, reinterpret_cast<cudaStream_t>(stream));
+}
+extern "C" int st2_conv_tile_rows(int use_umma) { return conv_tile_rows(use_umma != 0); }
+
+extern "C" int st2_source_har(const float* f0, const float* noise, uint64_t seed, const float* lin_w9,
+                              float lin_b, int B, int T, int spf, float* phase_scratch, float* har_source,
+                              void* stream) {
+  cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+  int rc = launch_phase_scan(f0, B, T, spf, phase_scratch, st);
+  if (rc) return rc;
+  return launch_har_source(f0, phase_scratch, noise, seed, lin_w9, lin_b, B, T, spf, har_source, st);
+}
+extern "C" int st2_stft_har(const float* har_source, int B, int Lw, float* har_cl32, void* stream) {
+  return launch_stft(har_source, B, Lw, har_cl32, 32, reinterpret_cast<cudaStream_t>(stream));
+}
+extern "C" int st2_istft_head(const float* x_cl32, int B, int frames, float* wav, void* stream) {
+  return launch_istft(x_cl32, 32, B, frames, wav, reinterpret_cast<cudaStream_t>(stream));
+}
+
+// ---- host-only test hook: fold weight-norm and repack one conv exactly as load() does.
+// transposed = 0: Conv1d prefix (weight_g/weight_v/bias);  1: ConvTranspose1d (K, stride, padding).
+// Writes the fp32 [k][cin][n_cols] weights and [n_cols] bias; returns k / pad / cin / n_cols.
+extern "C" int st2_debug_pack_conv(const St2Tensor* tensors, int n, const char* prefix, int transposed,
+                                   int K, int stride, int padding, float* w_out, int64_t w_cap,
+                                   float* bias_out, int* k_out, int* pad_out, int* cin_out, int* ncols_out) {
+  Loader L;
+  for (int i = 0; i < n; ++i) L.by_name[tensors[i].name] = &tensors[i];
+  ConvW c;
+  UpW u;
+  bool ok;
+  if (transposed) {
+    ok = L.conv_transpose(u, prefix, K, stride, padding);
+    c = u.conv;
+  } else {
+    ok = L.conv1d(c, prefix, true, true, K, 1, padding, stride, false);
+  }
+  ST2_REQUIRE(ok, L.err);
+  const int64_t elems = (int64_t)c.k * c.cin * c.n;
+  ST2_REQUIRE(elems <= w_cap, "output buffer too small");
+  memcpy(w_out, L.blob.data.data() + c.w32, elems * 4);
+  if (bias_out && c.bias >= 0) memcpy(bias_out, L.blob.data.data() + c.bias, (size_t)c.n * 4);
+  *k_out = c.k; *pad_out = c.pad; *cin_out = c.cin; *ncols_out = c.n;
+  return ST2_OK;
+}

@@ -1,0 +1,341 @@
+// elementwise.cu — the small memory-bound kernels around the convolutions:
+//   style_fc        all AdaIN1d.fc layers as one [sum 2C, style] x [style, B] product (istftnet.py:19,22)
+//   stats_finalize  InstanceNorm1d statistics (biased var, eps 1e-5, istftnet.py:18) from per-tile
+//                   partial sums -> per-(b,c) (scale, shift) with the style affine folded in (:25)
+//   colstats        partial sums of a channels-last tensor that no conv epilogue produced
+//   prep_inputs     NCL -> channels-last transpose of asr, F0_conv / N_conv (istftnet.py:510-513)
+//   pool_up2        AdaIN + LeakyReLU(0.2) + depthwise ConvTranspose1d(k3,s2,p1,op1) (:441-443, :423)
+//   reflect_row0    row 0 of ReflectionPad1d((1,0)) after the last upsampling (:364-367)
+//   layout helpers  NCL <-> channels-last for the injected / exported `har`
+#include "common.cuh"
+
+namespace st2 {
+
+// ------------------------------------------------------------------------- style fc
+// one warp per output row j; the style vectors of up to 64 batch items sit in smem.
+__global__ void __launch_bounds__(256)
+style_fc_kernel(const float* __restrict__ s, const float* __restrict__ W,
+                const float* __restrict__ bvec, float* __restrict__ h, int B, int style, int rows) {
+  extern __shared__ float ssm[];  // [nb][style]
+  const int b0 = blockIdx.y * 64;
+  const int nb = min(64, B - b0);
+  for (int i = threadIdx.x; i < nb * style; i += blockDim.x) ssm[i] = s[(int64_t)b0 * style + i];
+  __syncthreads();
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int j = blockIdx.x * 8 + warp;
+  if (j >= rows) return;
+  const float* wr = W + (int64_t)j * style;
+  const float bj = bvec[j];
+  for (int b = 0; b < nb; ++b) {
+    float a = 0.f;
+    for (int i = lane; i < style; i += 32) a = fmaf(wr[i], ssm[b * style + i], a);
+    a = warp_sum(a);
+    if (lane == 0) h[(int64_t)(b0 + b) * rows + j] = a + bj;
+  }
+}
+
+int launch_style_fc(const float* s, const float* W, const float* bvec, float* h, int B, int style,
+                    int rows, cudaStream_t st) {
+  dim3 grid(ceil_div(rows, 8), ceil_div(B, 64));
+  size_t smem = (size_t)64 * style * sizeof(float);
+  ST2_REQUIRE(smem <= 48 * 1024, "style_dim too large");
+  style_fc_kernel<<<grid, 256, smem, st>>>(s, W, bvec, h, B, style, rows);
+  ST2_LAUNCH_OK("style_fc");
+  return ST2_OK;
+}
+
+// ------------------------------------------------------------------- stats finalize
+// thread per (b, c).  Partials are [B][n_tiles][n_cols][2]; channel c owns columns c, c+C, ...
+// (n_cols = phases*C for a polyphase transposed conv).  Sums run in fp64 in a fixed order, so
+// the result is deterministic and independent of how the grid was scheduled.
+__global__ void __launch_bounds__(128)
+stats_finalize_kernel(const float* __restrict__ partials, int n_tiles, int n_cols, int C,
+                      double inv_count, const float* __restrict__ hg, int h_stride, int Cn,
+                      float* __restrict__ ss, int ss_stride, int c_off) {
+  const int c = blockIdx.x * blockDim.x + threadIdx.x;
+  const int b = blockIdx.y;
+  if (c >= C) return;
+  const float2* pp = reinterpret_cast<const float2*>(partials) + (int64_t)b * n_tiles * n_cols;
+  double s = 0.0, q = 0.0;
+  for (int t = 0; t < n_tiles; ++t)
+    for (int col = c; col < n_cols; col += C) {
+      const float2 v = pp[(int64_t)t * n_cols + col];
+      s += (double)v.x;
+      q += (double)v.y;
+    }
+  const double mean = s * inv_count;
+  double var = q * inv_count - mean * mean;
+  if (var < 0.0) var = 0.0;
+  const double rstd = 1.0 / sqrt(var + 1e-5);
+  const double gamma = hg[(int64_t)b * h_stride + c_off + c];
+  const double beta = hg[(int64_t)b * h_stride + Cn + c_off + c];
+  const double scale = (1.0 + gamma) * rstd;
+  float* o = ss + ((int64_t)b * ss_stride + c_off + c) * 2;
+  o[0] = (float)scale;
+  o[1] = (float)(beta - mean * scale);
+}
+
+// hg points at this norm layer's gamma block inside the concatenated fc output; the layer
+// normalises Cn channels, of which [c_off, c_off + C) are finalised by this launch.
+int launch_stats_finalize(const float* partials, int n_tiles, int n_cols, int C, int64_t count,
+                          const float* hg, int h_stride, int Cn, float* ss, int ss_stride,
+                          int c_off, int B, cudaStream_t st) {
+  dim3 grid(ceil_div(C, 128), B);
+  stats_finalize_kernel<<<grid, 128, 0, st>>>(partials, n_tiles, n_cols, C, 1.0 / (double)count, hg,
+                                              h_stride, Cn, ss, ss_stride, c_off);
+  ST2_LAUNCH_OK("stats_finalize");
+  return ST2_OK;
+}
+
+// ------------------------------------------------------------------------- colstats
+constexpr int CS_ROWS = 256;
+int colstats_tiles(int L) { return ceil_div(L, CS_ROWS); }
+
+template <typename T>
+__global__ void __launch_bounds__(256)
+colstats_kernel(const T* __restrict__ x, int64_t bstride, int ld, int L, int c0, int ncols,
+                float* __restrict__ partials, int n_tiles) {
+  __shared__ float red[2][4][64];
+  const int tx = threadIdx.x & 63, ty = threadIdx.x >> 6;
+  const int tile = blockIdx.x, b = blockIdx.z;
+  const int col = blockIdx.y * 64 + tx;
+  float s = 0.f, q = 0.f;
+  if (col < ncols) {
+    const T* xb = x + (int64_t)b * bstride + c0 + col;
+    const int r1 = min(L, (tile + 1) * CS_ROWS);
+    for (int r = tile * CS_ROWS + ty; r < r1; r += 4) {
+      const float v = ld_f<T>(xb + (int64_t)r * ld);
+      s += v;
+      q += v * v;
+    }
+  }
+  red[0][ty][tx] = s;
+  red[1][ty][tx] = q;
+  __syncthreads();
+  if (ty == 0 && col < ncols) {
+    float* o = partials + (((int64_t)b * n_tiles + tile) * ncols + col) * 2;
+    o[0] = red[0][0][tx] + red[0][1][tx] + red[0][2][tx] + red[0][3][tx];
+    o[1] = red[1][0][tx] + red[1][1][tx] + red[1][2][tx] + red[1][3][tx];
+  }
+}
+
+template <typename T>
+int launch_colstats(const T* x, int64_t bstride, int ld, int L, int c0, int ncols, float* partials,
+                    int B, cudaStream_t st) {
+  const int nt = colstats_tiles(L);
+  dim3 grid(nt, ceil_div(ncols, 64), B);
+  colstats_kernel<T><<<grid, 256, 0, st>>>(x, bstride, ld, L, c0, ncols, partials, nt);
+  ST2_LAUNCH_OK("colstats");
+  return ST2_OK;
+}
+template int launch_colstats<float>(const float*, int64_t, int, int, int, int, float*, int, cudaStream_t);
+template int launch_colstats<__nv_bfloat16>(const __nv_bfloat16*, int64_t, int, int, int, int, float*,
+                                            int, cudaStream_t);
+
+// ---------------------------------------------------------------------- prep inputs
+// grid (ceil(T2/32), ceil(ld0/32), B), block (32, 8).  f0w / nw = {w0, w1, w2, bias} (folded).
+template <typename T>
+__global__ void __launch_bounds__(256)
+prep_inputs_kernel(const float* __restrict__ asr, const float* __restrict__ f0,
+                   const float* __restrict__ nn, const float* __restrict__ f0w,
+                   const float* __restrict__ nw, T* __restrict__ x0, int ld0, T* __restrict__ ca,
+                   T* __restrict__ cb, int ldc, int c_f0, int dim_in, int T2) {
+  __shared__ float tile[32][33];
+  const int b = blockIdx.z;
+  const int t0 = blockIdx.x * 32, ch0 = blockIdx.y * 32;
+  const int tx = threadIdx.x, ty = threadIdx.y;
+  // read: channel rows, time contiguous
+  for (int i = ty; i < 32; i += 8) {
+    const int ch = ch0 + i, t = t0 + tx;
+    float v = 0.f;
+    if (t < T2) {
+      if (ch < dim_in) {
+        v = asr[((int64_t)b * dim_in + ch) * T2 + t];
+      } else if (ch == dim_in || ch == dim_in + 1) {
+        const float* src = (ch == dim_in ? f0 : nn) + (int64_t)b * 2 * T2;
+        const float* w = ch == dim_in ? f0w : nw;
+        float a = w[3];
+#pragma unroll
+        for (int j = 0; j < 3; ++j) {
+          const int ti = 2 * t + j - 1;
+          if (ti >= 0 && ti < 2 * T2) a = fmaf(w[j], src[ti], a);
+        }
+        v = a;
+      }
+    }
+    tile[i][tx] = v;
+  }
+  __syncthreads();
+  // write: time rows, channels contiguous
+  for (int i = ty; i < 32; i += 8) {
+    const int t = t0 + i, ch = ch0 + tx;
+    if (t >= T2 || ch >= ld0) continue;
+    const float v = tile[tx][i];
+    st_f<T>(x0 + ((int64_t)b * T2 + t) * ld0 + ch, v);
+    if (ch >= dim_in) {  // F0 / N / zero padding of the concat buffers
+      const int cc = c_f0 + (ch - dim_in);
+      if (cc < ldc) {
+        st_f<T>(ca + ((int64_t)b * T2 + t) * ldc + cc, v);
+        st_f<T>(cb + ((int64_t)b * T2 + t) * ldc + cc, v);
+      }
+    }
+  }
+}
+
+template <typename T>
+int launch_prep_inputs(const float* asr, const float* f0, const float* n, const float* f0w,
+                       const float* nw, T* x0, int ld0, T* ca, T* cb, int ldc, int c_f0, int B,
+                       int dim_in, int T2, cudaStream_t st) {
+  ST2_REQUIRE(ld0 - dim_in >= ldc - c_f0, "prep_inputs: x0 padding must cover the concat padding");
+  dim3 grid(ceil_div(T2, 32), ceil_div(ld0, 32), B), block(32, 8);
+  prep_inputs_kernel<T><<<grid, block, 0, st>>>(asr, f0, n, f0w, nw, x0, ld0, ca, cb, ldc, c_f0, dim_in, T2);
+  ST2_LAUNCH_OK("prep_inputs");
+  return ST2_OK;
+}
+template int launch_prep_inputs<float>(const float*, const float*, const float*, const float*,
+                                       const float*, float*, int, float*, float*, int, int, int, int,
+                                       int, cudaStream_t);
+template int launch_prep_inputs<__nv_bfloat16>(const float*, const float*, const float*, const float*,
+                                               const float*, __nv_bfloat16*, int, __nv_bfloat16*,
+                                               __nv_bfloat16*, int, int, int, int, int, cudaStream_t);
+
+// -------------------------------------------------------------------------- pool x2
+// y[2q]   = w[c][1] * a[q] + bias[c]
+// y[2q+1] = w[c][2] * a[q] + w[c][0] * a[q+1] + bias[c],   a = lrelu(x*scale+shift), a[Lin] = 0
+// (ConvTranspose1d: y[t] = sum_i a[i] w[t + 1 - 2i], 0 <= t+1-2i < 3.)
+template <typename T>
+__global__ void __launch_bounds__(256)
+pool_up2_kernel(const T* __restrict__ x, int64_t x_bstride, int ldx, const float* __restrict__ ss,
+                int ss_stride, float slope, const float* __restrict__ w3,
+                const float* __restrict__ bias, T* __restrict__ y, int64_t y_bstride, int ldy,
+                int Lin, int C, int Cpad) {
+  const int c = blockIdx.x * blockDim.x + threadIdx.x;
+  const int q = blockIdx.y, b = blockIdx.z;
+  if (c >= Cpad) return;
+  T* y0 = y + (int64_t)b * y_bstride + (int64_t)(2 * q) * ldy + c;
+  if (c >= C) {
+    st_f<T>(y0, 0.f);
+    st_f<T>(y0 + ldy, 0.f);
+    return;
+  }
+  const float sc = ss[((int64_t)b * ss_stride + c) * 2], sh = ss[((int64_t)b * ss_stride + c) * 2 + 1];
+  const T* xp = x + (int64_t)b * x_bstride + (int64_t)q * ldx + c;
+  float a0 = fmaf(ld_f<T>(xp), sc, sh);
+  a0 = a0 > 0.f ? a0 : a0 * slope;
+  float a1 = 0.f;
+  if (q + 1 < Lin) {
+    a1 = fmaf(ld_f<T>(xp + ldx), sc, sh);
+    a1 = a1 > 0.f ? a1 : a1 * slope;
+  }
+  const float w0 = w3[c * 3], w1 = w3[c * 3 + 1], w2 = w3[c * 3 + 2], bb = bias[c];
+  st_f<T>(y0, fmaf(w1, a0, bb));
+  st_f<T>(y0 + ldy, fmaf(w2, a0, fmaf(w0, a1, bb)));
+}
+
+template <typename T>
+int launch_pool_up2(const T* x, int64_t x_bstride, int ldx, const float* ss, int ss_stride,
+                    float slope, const float* w3, const float* bias, T* y, int64_t y_bstride, int ldy,
+                    int B, int Lin, int C, int Cpad, cudaStream_t st) {
+  ST2_REQUIRE(Lin <= 65535, "pool_up2: sequence too long for grid.y");
+  dim3 grid(ceil_div(Cpad, 256), Lin, B);
+  pool_up2_kernel<T><<<grid, 256, 0, st>>>(x, x_bstride, ldx, ss, ss_stride, slope, w3, bias, y,
+                                           y_bstride, ldy, Lin, C, Cpad);
+  ST2_LAUNCH_OK("pool_up2");
+  return ST2_OK;
+}
+template int launch_pool_up2<float>(const float*, int64_t, int, const float*, int, float, const float*,
+                                    const float*, float*, int64_t, int, int, int, int, int, cudaStream_t);
+template int launch_pool_up2<__nv_bfloat16>(const __nv_bfloat16*, int64_t, int, const float*, int, float,
+                                            const float*, const float*, __nv_bfloat16*, int64_t, int,
+                                            int, int, int, int, cudaStream_t);
+
+// --------------------------------------------------------------------- reflect row 0
+// ReflectionPad1d((1,0)) after ups[-1]: padded row 0 = ups output at t = 1 = phase 1 of q = 0,
+// which only sees input row 0 through tap (1 + padding):  y0[co] = b[co] + sum_ci a[0,ci] w[ci,co],
+// then + x_source[0].  One block per batch item, one thread per output channel.
+template <typename T>
+__global__ void reflect_row0_kernel(const T* __restrict__ xin, int64_t xin_bstride, int cin,
+                                    float slope, const float* __restrict__ w_tap,
+                                    const float* __restrict__ bias, const T* __restrict__ xs,
+                                    int64_t xs_bstride, T* __restrict__ y, int64_t y_bstride, int cout,
+                                    float* __restrict__ stats_slot, int64_t stats_bstride) {
+  const int b = blockIdx.x, co = threadIdx.x;
+  if (co >= cout) return;
+  const T* xr = xin + (int64_t)b * xin_bstride;
+  float a = bias[co];
+  for (int ci = 0; ci < cin; ++ci) {
+    float v = ld_f<T>(xr + ci);
+    v = v > 0.f ? v : v * slope;
+    a = fmaf(v, w_tap[(int64_t)ci * cout + co], a);
+  }
+  a += ld_f<T>(xs + (int64_t)b * xs_bstride + co);
+  st_f<T>(y + (int64_t)b * y_bstride + co, a);
+  if (stats_slot) {
+    const float r = round_to<T>(a);
+    float* o = stats_slot + (int64_t)b * stats_bstride + co * 2;
+    o[0] = r;
+    o[1] = r * r;
+  }
+}
+
+template <typename T>
+int launch_reflect_row0(const T* xin, int64_t xin_bstride, int cin, float slope, const float* w_tap,
+                        const float* bias, const T* xs, int64_t xs_bstride, T* y, int64_t y_bstride,
+                        int cout, float* stats_slot, int64_t stats_bstride, int B, cudaStream_t st) {
+  ST2_REQUIRE(cout <= 1024, "reflect_row0: cout");
+  reflect_row0_kernel<T><<<B, round_up(cout, 32), 0, st>>>(xin, xin_bstride, cin, slope, w_tap, bias, xs,
+                                                           xs_bstride, y, y_bstride, cout, stats_slot,
+                                                           stats_bstride);
+  ST2_LAUNCH_OK("reflect_row0");
+  return ST2_OK;
+}
+template int launch_reflect_row0<float>(const float*, int64_t, int, float, const float*, const float*,
+                                        const float*, int64_t, float*, int64_t, int, float*, int64_t,
+                                        int, cudaStream_t);
+template int launch_reflect_row0<__nv_bfloat16>(const __nv_bfloat16*, int64_t, int, float, const float*,
+                                                const float*, const __nv_bfloat16*, int64_t,
+                                                __nv_bfloat16*, int64_t, int, float*, int64_t, int,
+                                                cudaStream_t);
+
+// ------------------------------------------------------------------- layout helpers
+__global__ void cl_to_ncl_kernel(const float* __restrict__ cl, int ld, int C, int L,
+                                 float* __restrict__ ncl) {
+  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;  // over C*L of item b
+  const int b = blockIdx.y;
+  if (i >= (int64_t)C * L) return;
+  const int c = (int)(i / L), t = (int)(i - (int64_t)c * L);
+  ncl[(int64_t)b * C * L + i] = cl[((int64_t)b * L + t) * ld + c];
+}
+__global__ void ncl_to_cl_kernel(const float* __restrict__ ncl, int C, int L, float* __restrict__ cl,
+                                 int ld) {
+  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;  // over L*ld of item b
+  const int b = blockIdx.y;
+  if (i >= (int64_t)L * ld) return;
+  const int t = (int)(i / ld), c = (int)(i - (int64_t)t * ld);
+  cl[(int64_t)b * L * ld + i] = c < C ? ncl[((int64_t)b * C + c) * L + t] : 0.f;
+}
+int launch_cl_to_ncl(const float* cl, int ld, int C, int L, float* ncl, int B, cudaStream_t st) {
+  dim3 grid((unsigned)(((int64_t)C * L + 255) / 256), B);
+  cl_to_ncl_kernel<<<grid, 256, 0, st>>>(cl, ld, C, L, ncl);
+  ST2_LAUNCH_OK("cl_to_ncl");
+  return ST2_OK;
+}
+int launch_ncl_to_cl(const float* ncl, int C, int L, float* cl, int ld, int B, cudaStream_t st) {
+  dim3 grid((unsigned)(((int64_t)L * ld + 255) / 256), B);
+  ncl_to_cl_kernel<<<grid, 256, 0, st>>>(ncl, C, L, cl, ld);
+  ST2_LAUNCH_OK("ncl_to_cl");
+  return ST2_OK;
+}
+
+// tanh head of the HiFi-GAN generator (hifigan.py:344), in place on the fp32 waveform
+__global__ void tanh_kernel(float* __restrict__ x, int64_t n) {
+  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) x[i] = tanhf(x[i]);
+}
+int launch_tanh_inplace(float* x, int64_t n, cudaStream_t st) {
+  tanh_kernel<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(x, n);
+  ST2_LAUNCH_OK("tanh");
+  return ST2_OK;
+}
+
+}  // namespace st2

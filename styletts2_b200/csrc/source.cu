@@ -1,0 +1,302 @@
+// source.cu — harmonic excitation, forward STFT and the inverse-STFT output head.
+//
+//   phase_scan   SineGen._f02sine up to the frame-rate phase (istftnet.py:152,174,183-184):
+//                rad = (f0*h/24000) % 1 per frame, block-level inclusive scan in fp64 (ATen's CPU
+//                cumsum accumulates float in double), then *2*pi*spf with fp32 rounding points
+//                identical to the reference expression order.
+//   har_source   linear x spf resampling of the phase with ATen's exact fp32 arithmetic
+//                (src = fma(1/spf, n+0.5, -0.5); out = fma(1-l, p[i0], l*p[i1])), sin, *0.1, uv mask,
+//                additive noise (injected or Philox), Linear(9->1) + tanh (istftnet.py:186,230-246,292).
+//   stft         torch.stft(n_fft 20, hop 5, hann periodic, center/reflect) -> |X|, angle(X) as 22
+//                channels-last columns (istftnet.py:91-97,355-356): a register-resident 20-point DFT.
+//   istft        exp / sin heads, inverse 20-point DFT, windowed overlap-add, envelope division and
+//                trimming (istftnet.py:377-379, 99-104); writes the final waveform.
+// All four are memory-bound; bytes per unit are listed in DESIGN.md.
+#include "common.cuh"
+
+namespace st2 {
+
+constexpr int NH = 9;  // fundamental + 8 overtones (istftnet.py:312)
+constexpr float F_PI = 3.14159265358979323846f;
+
+__constant__ float c_cos20[20];
+__constant__ float c_sin20[20];
+__constant__ float c_hann20[20];
+static bool g_tables_ready[64] = {};
+
+static int ensure_tables() {
+  int dev = 0;
+  ST2_CUDA_OK(cudaGetDevice(&dev));
+  if (dev < 64 && g_tables_ready[dev]) return ST2_OK;
+  float c[20], s[20], w[20];
+  const double pi = 3.14159265358979323846;
+  for (int m = 0; m < 20; ++m) {
+    double cv = cos(2.0 * pi * m / 20.0), sv = sin(2.0 * pi * m / 20.0);
+    if (fabs(cv) < 1e-12) cv = 0.0;
+    if (fabs(sv) < 1e-12) sv = 0.0;
+    c[m] = (float)cv;
+    s[m] = (float)sv;
+    w[m] = (float)(0.5 - 0.5 * cos(2.0 * pi * m / 20.0));  // scipy get_window('hann', 20, fftbins=True)
+  }
+  ST2_CUDA_OK(cudaMemcpyToSymbol(c_cos20, c, sizeof(c)));
+  ST2_CUDA_OK(cudaMemcpyToSymbol(c_sin20, s, sizeof(s)));
+  ST2_CUDA_OK(cudaMemcpyToSymbol(c_hann20, w, sizeof(w)));
+  if (dev < 64) g_tables_ready[dev] = true;
+  return ST2_OK;
+}
+
+// ----------------------------------------------------------------------- phase scan
+// grid B, block 256.  phase layout [B][9][T] (harmonic-major).
+__global__ void __launch_bounds__(256)
+phase_scan_kernel(const float* __restrict__ f0, int T, float spf_f, float* __restrict__ phase) {
+  __shared__ double part[NH][256];
+  const int b = blockIdx.x, tid = threadIdx.x;
+  const int per = (T + 255) / 256;
+  const int q0 = min(T, tid * per), q1 = min(T, q0 + per);
+  const float* f = f0 + (int64_t)b * T;
+  double loc[NH];
+#pragma unroll
+  for (int h = 0; h < NH; ++h) loc[h] = 0.0;
+  for (int q = q0; q < q1; ++q) {
+    const float fv = f[q];
+#pragma unroll
+    for (int h = 0; h < NH; ++h) {
+      float r = __fdiv_rn(__fmul_rn(fv, (float)(h + 1)), 24000.f);
+      r = r - floorf(r);  // torch `% 1` (python modulo)
+      loc[h] += (double)r;
+    }
+  }
+#pragma unroll
+  for (int h = 0; h < NH; ++h) part[h][tid] = loc[h];
+  __syncthreads();
+  if (tid < NH) {  // exclusive scan over the 256 chunk sums
+    double run = 0.0;
+    for (int i = 0; i < 256; ++i) {
+      const double v = part[tid][i];
+      part[tid][i] = run;
+      run += v;
+    }
+  }
+  __syncthreads();
+#pragma unroll
+  for (int h = 0; h < NH; ++h) loc[h] = part[h][tid];
+  for (int q = q0; q < q1; ++q) {
+    const float fv = f[q];
+#pragma unroll
+    for (int h = 0; h < NH; ++h) {
+      float r = __fdiv_rn(__fmul_rn(fv, (float)(h + 1)), 24000.f);
+      r = r - floorf(r);
+      loc[h] += (double)r;
+      float p = (float)loc[h];               // cumsum result, fp32
+      p = __fmul_rn(__fmul_rn(p, 2.f), F_PI);  // * 2 * np.pi
+      p = __fmul_rn(p, spf_f);                 // * upsample_scale (istftnet.py:184)
+      phase[((int64_t)b * NH + h) * T + q] = p;
+    }
+  }
+}
+
+int launch_phase_scan(const float* f0, int B, int T, int spf, float* phase, cudaStream_t st) {
+  phase_scan_kernel<<<B, 256, 0, st>>>(f0, T, (float)spf, phase);
+  ST2_LAUNCH_OK("phase_scan");
+  return ST2_OK;
+}
+
+// ---------------------------------------------------------------- Philox4x32-10 + normal
+__device__ __forceinline__ void philox4x32(uint32_t c0, uint32_t c1, uint32_t c2, uint32_t c3,
+                                           uint32_t k0, uint32_t k1, uint32_t out[4]) {
+#pragma unroll
+  for (int r = 0; r < 10; ++r) {
+    const uint32_t hi0 = __umulhi(0xD2511F53u, c0), lo0 = 0xD2511F53u * c0;
+    const uint32_t hi1 = __umulhi(0xCD9E8D57u, c2), lo1 = 0xCD9E8D57u * c2;
+    c0 = hi1 ^ c1 ^ k0;
+    c1 = lo1;
+    c2 = hi0 ^ c3 ^ k1;
+    c3 = lo0;
+    k0 += 0x9E3779B9u;
+    k1 += 0xBB67AE85u;
+  }
+  out[0] = c0; out[1] = c1; out[2] = c2; out[3] = c3;
+}
+__device__ __forceinline__ void box_muller(uint32_t a, uint32_t b, float& z0, float& z1) {
+  const float u1 = ((float)a + 1.f) * 2.3283064365386963e-10f;  // (0,1]
+  const float u2 = (float)b * 2.3283064365386963e-10f;
+  const float r = sqrtf(-2.f * __logf(u1));
+  float s, c;
+  __sincosf(2.f * F_PI * u2, &s, &c);
+  z0 = r * c;
+  z1 = r * s;
+}
+
+// ----------------------------------------------------------------------- har source
+__global__ void __launch_bounds__(256)
+har_source_kernel(const float* __restrict__ f0, const float* __restrict__ phase,
+                  const float* __restrict__ noise, uint64_t seed, const float* __restrict__ lin_w,
+                  float lin_b, int T, int spf, float ratio, float* __restrict__ out) {
+  const int b = blockIdx.y;
+  const int64_t Lw = (int64_t)T * spf;
+  const int64_t n = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (n >= Lw) return;
+  float src = fmaf(ratio, (float)n + 0.5f, -0.5f);
+  src = src < 0.f ? 0.f : src;
+  int i0 = (int)src;
+  i0 = min(i0, T - 1);
+  const int i1 = min(i0 + 1, T - 1);
+  const float l1 = __fsub_rn(src, (float)i0);
+  const float l0 = __fsub_rn(1.f, l1);
+  const float fv = f0[(int64_t)b * T + (int)(n / spf)];
+  const float uv = fv > 10.f ? 1.f : 0.f;                         // voiced_threshold 10 (istftnet.py:312)
+  const float namp = uv > 0.f ? 0.003f : __fdiv_rn(0.1f, 3.f);   // istftnet.py:240
+  float z[12];
+  if (noise) {
+    const float* np_ = noise + ((int64_t)b * Lw + n) * NH;
+#pragma unroll
+    for (int h = 0; h < NH; ++h) z[h] = np_[h];
+  } else {
+    const uint64_t ctr = (uint64_t)b * (uint64_t)Lw + (uint64_t)n;
+#pragma unroll
+    for (int g = 0; g < 3; ++g) {
+      uint32_t r[4];
+      philox4x32((uint32_t)ctr, (uint32_t)(ctr >> 32), (uint32_t)g, 0x5742u, (uint32_t)seed,
+                 (uint32_t)(seed >> 32), r);
+      box_muller(r[0], r[1], z[4 * g], z[4 * g + 1]);
+      box_muller(r[2], r[3], z[4 * g + 2], z[4 * g + 3]);
+    }
+  }
+  const float* pb = phase + (int64_t)b * NH * T;
+  float acc = 0.f;
+#pragma unroll
+  for (int h = 0; h < NH; ++h) {
+    const float p0 = pb[(int64_t)h * T + i0], p1 = pb[(int64_t)h * T + i1];
+    const float ph = fmaf(l0, p0, __fmul_rn(l1, p1));
+    const float sv = __fmul_rn(sinf(ph), 0.1f);  // sine_amp
+    const float sw = __fadd_rn(__fmul_rn(sv, uv), __fmul_rn(namp, z[h]));
+    acc = fmaf(lin_w[h], sw, acc);
+  }
+  out[(int64_t)b * Lw + n] = tanhf(acc + lin_b);
+}
+
+int launch_har_source(const float* f0, const float* phase, const float* noise, uint64_t seed,
+                      const float* lin_w9, float lin_b, int B, int T, int spf, float* out,
+                      cudaStream_t st) {
+  const int64_t Lw = (int64_t)T * spf;
+  dim3 grid((unsigned)((Lw + 255) / 256), B);
+  const float ratio = (float)(1.0 / (double)spf);
+  har_source_kernel<<<grid, 256, 0, st>>>(f0, phase, noise, seed, lin_w9, lin_b, T, spf, ratio, out);
+  ST2_LAUNCH_OK("har_source");
+  return ST2_OK;
+}
+
+// ----------------------------------------------------------------------------- STFT
+// thread per (b, frame).  har_cl row = [|X_0..10|, angle(X_0..10), zero padding to ld].
+__global__ void __launch_bounds__(128)
+stft_kernel(const float* __restrict__ hs, int Lw, int frames, float* __restrict__ har, int ld) {
+  const int b = blockIdx.y;
+  const int f = blockIdx.x * blockDim.x + threadIdx.x;
+  if (f >= frames) return;
+  const float* x = hs + (int64_t)b * Lw;
+  float xw[20];
+#pragma unroll
+  for (int n = 0; n < 20; ++n) {
+    int idx = 5 * f + n - 10;
+    if (idx < 0) idx = -idx;                      // reflect, center=True
+    if (idx >= Lw) idx = 2 * (Lw - 1) - idx;
+    xw[n] = x[idx] * c_hann20[n];
+  }
+  float* o = har + ((int64_t)b * frames + f) * ld;
+#pragma unroll
+  for (int k = 0; k <= 10; ++k) {
+    float re = 0.f, im = 0.f;
+#pragma unroll
+    for (int n = 0; n < 20; ++n) {
+      const int m = (k * n) % 20;
+      re = fmaf(xw[n], c_cos20[m], re);
+      im = fmaf(xw[n], -c_sin20[m], im);
+    }
+    if (k == 0 || k == 10) im = 0.f;  // r2c: DC / Nyquist have Im == +0 -> angle in {0, +pi}
+    o[k] = sqrtf(re * re + im * im);
+    o[11 + k] = atan2f(im, re);
+  }
+  for (int c = 22; c < ld; ++c) o[c] = 0.f;
+}
+
+int launch_stft(const float* hs, int B, int Lw, float* har_cl, int ld, cudaStream_t st) {
+  int rc = ensure_tables();
+  if (rc) return rc;
+  ST2_REQUIRE(Lw % 5 == 0 && Lw >= 20 && ld >= 22, "stft: shape");
+  const int frames = Lw / 5 + 1;
+  dim3 grid(ceil_div(frames, 128), B);
+  stft_kernel<<<grid, 128, 0, st>>>(hs, Lw, frames, har_cl, ld);
+  ST2_LAUNCH_OK("stft");
+  return ST2_OK;
+}
+
+// ---------------------------------------------------------------------------- iSTFT
+constexpr int IS_NS = 1024;            // output samples per block
+constexpr int IS_MAXF = IS_NS / 5 + 8; // frames touching them
+
+__global__ void __launch_bounds__(256)
+istft_kernel(const float* __restrict__ x, int ld, int frames, float* __restrict__ wav) {
+  __shared__ float Re[IS_MAXF][11];
+  __shared__ float Im[IS_MAXF][11];
+  const int b = blockIdx.y;
+  const int Lw = 5 * (frames - 1);
+  const int i0 = blockIdx.x * IS_NS;
+  const int i1 = min(Lw, i0 + IS_NS);
+  __shared__ float s_cos[20], s_sin[20], s_win[20];
+  if (threadIdx.x < 20) {
+    s_cos[threadIdx.x] = c_cos20[threadIdx.x];
+    s_sin[threadIdx.x] = c_sin20[threadIdx.x];
+    s_win[threadIdx.x] = c_hann20[threadIdx.x];
+  }
+  // frames f with 0 <= (i+10) - 5f <= 19 for some i in [i0, i1): f in [(i+10)/5 - 3, (i+10)/5]
+  const int fmin = max(0, (i0 + 10) / 5 - 3);
+  const int fmax = min(frames - 1, (i1 - 1 + 10) / 5);
+  const int nf = fmax - fmin + 1;
+  for (int idx = threadIdx.x; idx < nf * 11; idx += blockDim.x) {
+    const int fr = idx / 11, k = idx - fr * 11;
+    const float* row = x + ((int64_t)b * frames + fmin + fr) * ld;
+    const float spec = expf(row[k]);        // istftnet.py:377
+    const float ph = sinf(row[11 + k]);     // istftnet.py:378
+    float s, c;
+    sincosf(ph, &s, &c);
+    const float ck = (k == 0 || k == 10) ? 0.05f : 0.1f;  // c_k / n_fft
+    Re[fr][k] = spec * c * ck;
+    Im[fr][k] = spec * s * ck;
+  }
+  __syncthreads();
+  for (int i = i0 + threadIdx.x; i < i1; i += blockDim.x) {
+    const int m = i + 10;
+    const int fq = m / 5, r = m - 5 * fq;
+    float val = 0.f, env = 0.f;
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      const int f = fq - j, n = r + 5 * j;
+      if (f < 0 || f >= frames) continue;
+      const int fr = f - fmin;
+      float a = 0.f;
+#pragma unroll
+      for (int k = 0; k <= 10; ++k) {
+        const int mm = (k * n) % 20;
+        a = fmaf(Re[fr][k], s_cos[mm], a);
+        a = fmaf(-Im[fr][k], s_sin[mm], a);
+      }
+      const float w = s_win[n];
+      val = fmaf(a, w, val);
+      env = fmaf(w, w, env);
+    }
+    wav[(int64_t)b * Lw + i] = val / env;
+  }
+}
+
+int launch_istft(const float* x_cl, int ld, int B, int frames, float* wav, cudaStream_t st) {
+  int rc = ensure_tables();
+  if (rc) return rc;
+  ST2_REQUIRE(frames >= 5 && ld >= 22, "istft: shape");
+  const int Lw = 5 * (frames - 1);
+  dim3 grid(ceil_div(Lw, IS_NS), B);
+  istft_kernel<<<grid, 256, 0, st>>>(x_cl, ld, frames, wav);
+  ST2_LAUNCH_OK("istft");
+  return ST2_OK;
+}
+
+}  // namespace st2

@@ -1,0 +1,280 @@
+"""Drop-in ``Decoder`` modules backed by libst2dec.so (hand-written sm_100a CUDA).
+
+Mirrors the reference boundary:
+  * constructor kwargs   /root/reference/Modules/istftnet.py:467-473, Modules/hifigan.py:416-421
+  * ``forward(asr, F0_curve, N, s) -> [B, 1, 300*T]``   istftnet.py:498-527, hifigan.py:445-474
+  * ``state_dict`` keys  old-style weight_norm ``*.weight_g`` / ``*.weight_v`` (istftnet.py:5)
+so ``models.py:1006`` / ``:1021`` can import this class instead.  Weight-norm is folded when the
+weights are (re)loaded into the native handle, not on every forward (the reference recomputes it
+70 times per call).  Forward-only: ``.train()`` mode raises (the reference's training branch at
+istftnet.py:499-507 hard-codes ``.to('cuda')`` smoothing filters and needs autograd).
+
+No torch / CPU fallback exists: tensors must live on a CUDA device of compute capability 10.x.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import math
+from typing import Dict, List, Optional, Sequence
+
+import torch
+import torch.nn as nn
+
+from . import _cabi
+from ._cabi import lib, check, ptr
+
+_HANDLES: Dict[int, "_DecoderBase"] = {}
+_NEXT_ID = [1]
+
+
+def _mk_config(kind: int, dim_in, style_dim, dim_out, resblock_kernel_sizes, upsample_rates,
+               upsample_initial_channel, resblock_dilation_sizes, upsample_kernel_sizes,
+               gen_istft_n_fft=0, gen_istft_hop_size=0) -> _cabi.St2Config:
+    cfg = _cabi.St2Config()
+    cfg.kind = kind
+    cfg.dim_in, cfg.style_dim, cfg.dim_out = int(dim_in), int(style_dim), int(dim_out)
+    ks = list(resblock_kernel_sizes)
+    if len(ks) > _cabi.MAX_RESK or len(upsample_rates) > _cabi.MAX_UPS:
+        raise ValueError("too many resblock kernels / upsample stages")
+    if len(upsample_rates) != len(upsample_kernel_sizes):
+        raise ValueError("upsample_rates and upsample_kernel_sizes differ in length")
+    cfg.n_resblock_kernels = len(ks)
+    for i, k in enumerate(ks):
+        cfg.resblock_kernel_sizes[i] = int(k)
+        d = list(resblock_dilation_sizes[i])
+        if len(d) != 3:
+            raise ValueError("AdaINResBlock1 takes exactly three dilations")
+        for j in range(3):
+            cfg.resblock_dilations[i][j] = int(d[j])
+    cfg.n_ups = len(upsample_rates)
+    for i, (u, k) in enumerate(zip(upsample_rates, upsample_kernel_sizes)):
+        cfg.upsample_rates[i] = int(u)
+        cfg.upsample_kernel_sizes[i] = int(k)
+    cfg.upsample_initial_channel = int(upsample_initial_channel)
+    cfg.gen_istft_n_fft, cfg.gen_istft_hop_size = int(gen_istft_n_fft), int(gen_istft_hop_size)
+    return cfg
+
+
+class _Node(nn.Module):
+    """anonymous container so that parameters get the reference's dotted names."""
+
+
+class _DecoderBase(nn.Module):
+    KIND = -1
+
+    def _setup(self, cfg: _cabi.St2Config):
+        self._cfg = cfg
+        h = C.c_void_p()
+        check(lib.st2_decoder_create(C.byref(cfg), C.byref(h)), "st2_decoder_create")
+        try:
+            n = lib.st2_decoder_num_keys(h)
+            self._keys: List[str] = []
+            name, ndim, shape = C.c_char_p(), C.c_int(), (C.c_int64 * 4)()
+            for i in range(n):
+                check(lib.st2_decoder_key(h, i, C.byref(name), C.byref(ndim), shape))
+                key, shp = name.value.decode(), tuple(int(shape[d]) for d in range(ndim.value))
+                self._keys.append(key)
+                self._register(key, shp)
+            self.samples_per_frame = lib.st2_decoder_samples_per_frame(h)
+        finally:
+            lib.st2_decoder_destroy(h)
+        self._reset_parameters()
+        self._native: Dict[int, C.c_void_p] = {}     # device index -> handle
+        self._native_version: Dict[int, int] = {}
+        self._id = _NEXT_ID[0]
+        _NEXT_ID[0] += 1
+        self.precision = "bf16"
+        self.seed = 0
+        self.eval()
+
+    # ------------------------------------------------------------------ parameters
+    def _register(self, key: str, shape):
+        mod = self
+        parts = key.split(".")
+        for p in parts[:-1]:
+            if p not in mod._modules:
+                mod.add_module(p, _Node())
+            mod = mod._modules[p]
+        mod.register_parameter(parts[-1], nn.Parameter(torch.empty(shape), requires_grad=False))
+
+    @torch.no_grad()
+    def _reset_parameters(self):
+        """Same distributions as the reference's constructors: torch default U(+-1/sqrt(fan_in))
+        everywhere, N(0, 0.01) where ``init_weights`` is applied (Modules/utils.py:1-4 via
+        istftnet.py:38,48,343-344), weight_g = ||v||, Snake alpha = 1."""
+        sd = dict(self.named_parameters())
+        for key, p in sd.items():
+            leaf = key.rsplit(".", 1)[-1]
+            if leaf.startswith("alpha") or ".alphas." in key or ".alpha1." in key or ".alpha2." in key:
+                p.fill_(1.0)
+            elif leaf == "weight_v":
+                init01 = any(t in key for t in (".ups.", ".conv_post", ".convs1.", ".convs2."))
+                fan_in = p.shape[1] * p.shape[2]
+                if init01:
+                    p.normal_(0.0, 0.01)
+                else:
+                    p.uniform_(-1 / math.sqrt(fan_in), 1 / math.sqrt(fan_in))
+            elif leaf == "weight":
+                fan_in = p[0].numel()
+                p.uniform_(-1 / math.sqrt(fan_in), 1 / math.sqrt(fan_in))
+        for key, p in sd.items():
+            leaf = key.rsplit(".", 1)[-1]
+            if leaf == "weight_g":
+                v = sd[key[:-1] + "v"]
+                p.copy_(v.reshape(v.shape[0], -1).norm(dim=1).reshape(p.shape))
+            elif leaf == "bias":
+                base = key[: -len("bias")]
+                w = sd.get(base + "weight_v", sd.get(base + "weight"))
+                fan_in = w[0].numel() if w is not None and w.dim() > 1 else 1
+                p.uniform_(-1 / math.sqrt(fan_in), 1 / math.sqrt(fan_in))
+
+    def _load_from_state_dict(self, state_dict, prefix, *args, **kwargs):
+        # tolerate the DDP "module." prefix like models.py:1126-1142 / the notebooks' k[7:]
+        pref = prefix + "module."
+        for k in [k for k in state_dict if k.startswith(pref)]:
+            state_dict[prefix + k[len(pref):]] = state_dict.pop(k)
+        return super()._load_from_state_dict(state_dict, prefix, *args, **kwargs)
+
+    def _weights_version(self) -> int:
+        return sum(p._version for p in self.parameters())
+
+    def _handle_for(self, device: torch.device) -> C.c_void_p:
+        idx = device.index if device.index is not None else torch.cuda.current_device()
+        ver = self._weights_version()
+        h = self._native.get(idx)
+        if h is not None and self._native_version.get(idx) == ver:
+            return h
+        with torch.cuda.device(idx):
+            if h is None:
+                h = C.c_void_p()
+                check(lib.st2_decoder_create(C.byref(self._cfg), C.byref(h)), "st2_decoder_create")
+                self._native[idx] = h
+            sd = {k: v.detach().to("cpu", torch.float32).contiguous() for k, v in self.state_dict().items()}
+            arr = (_cabi.St2Tensor * len(sd))()
+            keep = []
+            for i, (k, v) in enumerate(sd.items()):
+                kb = k.encode()
+                keep.append(kb)
+                arr[i].name = kb
+                arr[i].data = v.data_ptr()
+                arr[i].ndim = v.dim()
+                for d in range(v.dim()):
+                    arr[i].shape[d] = v.shape[d]
+            check(lib.st2_decoder_load(h, arr, len(sd)), "st2_decoder_load")
+        self._native_version[idx] = ver
+        return h
+
+    def __del__(self):
+        try:
+            for h in getattr(self, "_native", {}).values():
+                lib.st2_decoder_destroy(h)
+        except Exception:
+            pass
+
+    # --------------------------------------------------------------------- forward
+    def forward(self, asr: torch.Tensor, F0_curve: torch.Tensor, N: torch.Tensor, s: torch.Tensor, *,
+                noise: Optional[torch.Tensor] = None, har_source: Optional[torch.Tensor] = None,
+                har: Optional[torch.Tensor] = None, precision: Optional[str] = None,
+                return_excitation: bool = False):
+        """Reference signature plus keyword-only extras; dispatches through the registered custom
+        op ``torch.ops.styletts2_b200.decoder_forward`` (see :meth:`_forward_native`)."""
+        if return_excitation:
+            return self._forward_native(asr, F0_curve, N, s, noise=noise, har_source=har_source, har=har,
+                                        precision=precision, return_excitation=True)
+        from . import ops
+        return torch.ops.styletts2_b200.decoder_forward(asr, F0_curve, N, s, noise, har_source, har,
+                                                        ops.register_module(self),
+                                                        precision or self.precision)
+
+    def _forward_native(self, asr: torch.Tensor, F0_curve: torch.Tensor, N: torch.Tensor, s: torch.Tensor, *,
+                        noise: Optional[torch.Tensor] = None, har_source: Optional[torch.Tensor] = None,
+                        har: Optional[torch.Tensor] = None, precision: Optional[str] = None,
+                        return_excitation: bool = False):
+        """``Decoder.forward(asr, F0_curve, N, s)`` (istftnet.py:498).  Extra keyword-only inputs
+        inject the excitation for reproducibility: ``noise`` [B, 300T, 9] (the randn_like draw of
+        SineGen), ``har_source`` [B, 300T] (output of m_source) or ``har`` [B, 22, 60T+1]."""
+        if self.training:
+            raise RuntimeError("styletts2_b200.Decoder is forward-only: call .eval() first")
+        if not asr.is_cuda:
+            raise RuntimeError("styletts2_b200.Decoder needs CUDA tensors (sm_100a); there is no CPU path")
+        if asr.dim() != 3 or F0_curve.dim() != 2 or N.dim() != 2 or s.dim() != 2:
+            raise RuntimeError("expected asr [B,C,T/2], F0_curve [B,T], N [B,T], s [B,style]")
+        B, Cin, T2 = asr.shape
+        T = F0_curve.shape[1]
+        if T != 2 * T2 or N.shape != F0_curve.shape or F0_curve.shape[0] != B or s.shape[0] != B:
+            # the reference fails in torch.cat at istftnet.py:513 with a size error
+            raise RuntimeError(f"Sizes of tensors must match: asr has {T2} frames, F0_curve/N have "
+                               f"{T} and {N.shape[1]} (need 2x), batch {B}")
+        if Cin != self._cfg.dim_in or s.shape[1] != self._cfg.style_dim:
+            raise RuntimeError("channel / style dimension mismatch")
+        prec = precision or self.precision
+        prec_id = {"fp32": _cabi.PREC_FP32, "bf16": _cabi.PREC_BF16}[prec]
+        dev = asr.device
+        f32 = lambda t: None if t is None else t.to(dev, torch.float32).contiguous()
+        asr_, f0_, n_, s_ = f32(asr), f32(F0_curve), f32(N), f32(s)
+        noise_, hs_, har_ = f32(noise), f32(har_source), f32(har)
+        spf = self.samples_per_frame
+        Lw = T * spf
+        if noise_ is not None and tuple(noise_.shape) != (B, Lw, 9):
+            raise RuntimeError(f"noise must be [B, {Lw}, 9]")
+        if hs_ is not None and tuple(hs_.shape) != (B, Lw):
+            raise RuntimeError(f"har_source must be [B, {Lw}]")
+        if har_ is not None and (self.KIND != _cabi.KIND_ISTFTNET or tuple(har_.shape) != (B, 22, Lw // 5 + 1)):
+            raise RuntimeError("har must be [B, 22, 60T+1] (istftnet only)")
+        h = self._handle_for(dev)
+        with torch.cuda.device(dev):
+            need = lib.st2_decoder_workspace_bytes(h, B, T, prec_id)
+            if need < 0:
+                check(int(need), "st2_decoder_workspace_bytes")
+            ws = torch.empty(int(need), dtype=torch.uint8, device=dev)
+            wav = torch.empty(B, 1, Lw, dtype=torch.float32, device=dev)
+            opts = _cabi.St2ForwardOpts()
+            opts.precision = prec_id
+            opts.noise, opts.har_source, opts.har = (t.data_ptr() if t is not None else None
+                                                     for t in (noise_, hs_, har_))
+            opts.seed = int(self.seed)
+            exc = {}
+            if return_excitation:
+                if har_ is None:
+                    exc["har_source"] = torch.empty(B, Lw, dtype=torch.float32, device=dev)
+                    opts.har_source_out = exc["har_source"].data_ptr()
+                if self.KIND == _cabi.KIND_ISTFTNET:
+                    exc["har"] = torch.empty(B, 22, Lw // 5 + 1, dtype=torch.float32, device=dev)
+                    opts.har_out = exc["har"].data_ptr()
+            stream = torch.cuda.current_stream(dev).cuda_stream
+            check(lib.st2_decoder_forward(h, ptr(asr_), ptr(f0_), ptr(n_), ptr(s_), ptr(wav), ptr(ws),
+                                          int(need), B, T, C.byref(opts), C.c_void_p(stream)),
+                  "st2_decoder_forward")
+            self.seed += 1 if noise_ is None and hs_ is None and har_ is None else 0
+            self.last_launches = int(lib.st2_decoder_last_launches(h))
+            # ws / inputs are only recycled by torch's caching allocator in stream order
+        if return_excitation:
+            return wav, exc
+        return wav
+
+
+class IstftnetDecoder(_DecoderBase):
+    """``Modules.istftnet.Decoder`` (istftnet.py:466-527)."""
+    KIND = _cabi.KIND_ISTFTNET
+
+    def __init__(self, dim_in=512, F0_channel=512, style_dim=64, dim_out=80,
+                 resblock_kernel_sizes=[3, 7, 11], upsample_rates=[10, 6], upsample_initial_channel=512,
+                 resblock_dilation_sizes=[[1, 3, 5], [1, 3, 5], [1, 3, 5]], upsample_kernel_sizes=[20, 12],
+                 gen_istft_n_fft=20, gen_istft_hop_size=5):
+        super().__init__()
+        self._setup(_mk_config(self.KIND, dim_in, style_dim, dim_out, resblock_kernel_sizes, upsample_rates,
+                               upsample_initial_channel, resblock_dilation_sizes, upsample_kernel_sizes,
+                               gen_istft_n_fft, gen_istft_hop_size))
+
+
+class HifiganDecoder(_DecoderBase):
+    """``Modules.hifigan.Decoder`` (hifigan.py:415-474)."""
+    KIND = _cabi.KIND_HIFIGAN
+
+    def __init__(self, dim_in=512, F0_channel=512, style_dim=64, dim_out=80,
+                 resblock_kernel_sizes=[3, 7, 11], upsample_rates=[10, 5, 3, 2], upsample_initial_channel=512,
+                 resblock_dilation_sizes=[[1, 3, 5], [1, 3, 5], [1, 3, 5]],
+                 upsample_kernel_sizes=[20, 10, 6, 4]):
+        super().__init__()
+        self._setup(_mk_config(self.KIND, dim_in, style_dim, dim_out, resblock_kernel_sizes, upsample_rates,
+                               upsample_initial_channel, resblock_dilation_sizes, upsample_kernel_sizes))

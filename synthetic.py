@@ -1,8 +1,9 @@
 """Synthetic weights and inputs for the StyleTTS2 waveform-decoder path.
 
-TEST INFRASTRUCTURE ONLY.  Nothing under ``oracle/`` is imported by the product
-(``styletts2_b200``); only ``tests/``, ``__graft_entry__.smoke()`` and the
-``cpu_baseline`` / ``--impl reference`` legs of ``bench.py`` may use it.
+Neutral data generator: it contains no decoder arithmetic.  ``bench.py``, ``tests/``,
+``__graft_entry__.smoke()`` and ``oracle/make_golden.py`` use it to build the same random-init
+state dict and seeded inputs on both sides of a comparison; the product package
+(``styletts2_b200``) does not import it.
 
 Why synthetic weights: the reference ships no checkpoints
 (``/root/reference/.MISSING_LARGE_BLOBS``) and BASELINE.json asks for random-init

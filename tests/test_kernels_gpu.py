@@ -1,0 +1,221 @@
+"""GPU parity tests of the single kernels, called through the C ABI (include/st2_decoder.h).
+
+fp32 FFMA conv: against a float64 torch restatement of conv_params.h (tolerance 2e-5 relative).
+tcgen05 conv : against the same restatement fed with bf16-rounded operands (what the tensor core
+               multiplies), tolerance = one bf16 ulp of the output + fp32 accumulation noise.
+source/STFT/iSTFT: against the oracle (oracle/decoder_oracle.py), which is pinned to the reference.
+"""
+import ctypes as C
+import math
+
+import numpy as np
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+
+from styletts2_b200 import _cabi  # noqa: E402
+from styletts2_b200._cabi import lib, check  # noqa: E402
+from tests.util import conv_reference, run_conv, snr_db, wrap_phase_err  # noqa: E402
+
+
+def _mk_case(B, Lin, cin, n, k, seed, ld=None, with_ss=True, act=_cabi.ACT_SNAKE):
+    g = torch.Generator().manual_seed(seed)
+    ld = ld or cin
+    x = torch.randn(B, Lin, ld, generator=g)
+    w = torch.randn(k, cin, n, generator=g) / math.sqrt(cin * k)
+    bias = torch.randn(n, generator=g) * 0.1
+    ss = None
+    if with_ss:
+        ss = torch.stack([1 + 0.5 * (torch.rand(B, ld, generator=g) - 0.5),
+                          0.5 * (torch.rand(B, ld, generator=g) - 0.5)], dim=-1)
+    alpha = 1 + 0.4 * (torch.rand(ld, generator=g) - 0.5) if act == _cabi.ACT_SNAKE else None
+    return x, w, bias, ss, alpha
+
+
+SIMT_CASES = [
+    # B, Lin, cin, n, k, dil, stride, act
+    (2, 100, 16, 64, 3, 1, 1, _cabi.ACT_SNAKE),
+    (2, 150, 22, 40, 12, 1, 6, _cabi.ACT_NONE),      # noise_convs[0]: 22 -> C, k12 s6 p3
+    (1, 301, 128, 22, 7, 1, 1, _cabi.ACT_LRELU),     # conv_post
+    (2, 77, 130, 100, 11, 5, 1, _cabi.ACT_SNAKE),    # ragged everything, widest halo
+    (1, 600, 1, 16, 60, 1, 30, _cabi.ACT_NONE),      # hifigan noise_convs[0]: 1 -> C, k60 s30
+    (2, 64, 514, 96, 3, 1, 1, _cabi.ACT_LRELU),      # encode.conv1 width
+]
+
+
+@pytest.mark.parametrize("case", SIMT_CASES)
+def test_conv_simt_fp32(case):
+    B, Lin, cin, n, k, dil, stride, act = case
+    x, w, bias, ss, alpha = _mk_case(B, Lin, cin, n, k, seed=hash(case) & 0xffff, act=act)
+    pad = (stride + 1) // 2 if stride > 1 else dil * (k - 1) // 2
+    Lout = (Lin + 2 * pad - dil * (k - 1) - 1) // stride + 1
+    g = torch.Generator().manual_seed(7)
+    res = torch.randn(B, Lout, n, generator=g)
+    ref = conv_reference(x, ss, act, 0.2, alpha, w, bias, k, dil, pad, stride, Lout, res, 0, 0.75, None)
+    y, st = run_conv("simt", x.cuda(), w, bias, k=k, dil=dil, pad=pad, stride=stride, ss=ss, act=act,
+                     slope=0.2, alpha=alpha, res=res, out_scale=0.75, want_stats=True)
+    err = (y.cpu().double() - ref).abs().max().item()
+    assert err < 2e-5 * max(1.0, ref.abs().max().item()), err
+    s_ref = torch.stack([ref.sum(1), (ref ** 2).sum(1)], dim=-1)
+    assert torch.allclose(st.cpu().double(), s_ref, rtol=1e-4, atol=1e-3)
+
+
+def test_conv_simt_accumulate_and_upsampled_residual():
+    B, Lin, cin, n, k = 2, 90, 32, 48, 3
+    x, w, bias, ss, alpha = _mk_case(B, Lin, cin, n, k, seed=5, act=_cabi.ACT_LRELU)
+    g = torch.Generator().manual_seed(9)
+    res = torch.randn(B, Lin // 2, n, generator=g)
+    y_old = torch.randn(B, Lin, n, generator=g)
+    ref = conv_reference(x, ss, _cabi.ACT_LRELU, 0.2, None, w, bias, k, 1, 1, 1, Lin, res, 1,
+                         1 / math.sqrt(2), y_old)
+    y, _ = run_conv("simt", x.cuda(), w, bias, k=k, pad=1, ss=ss, act=_cabi.ACT_LRELU, slope=0.2, res=res,
+                    res_shift=1, out_scale=1 / math.sqrt(2), y_old=y_old)
+    assert (y.cpu().double() - ref).abs().max().item() < 2e-5
+
+
+def _bf16_round(t):
+    return t.to(torch.bfloat16).to(torch.float32)
+
+
+def _umma_reference(xb, ss, act, slope, alpha, w, bias, k, dil, pad, Lout, res, res_shift, out_scale, y_old):
+    """what the tensor-core path computes: bf16(act(affine(x_bf16))) x bf16(w), fp32-ish accumulate."""
+    x = xb.float()
+    if ss is not None:
+        x = x * ss[:, None, :, 0] + ss[:, None, :, 1]
+    if act == _cabi.ACT_LRELU:
+        x = torch.where(x > 0, x, x * slope)
+    elif act == _cabi.ACT_SNAKE:
+        a = alpha[None, None, :]
+        x = x + (1 / a) * torch.sin(a * x) ** 2
+    x = _bf16_round(x)
+    return conv_reference(x, None, _cabi.ACT_NONE, 0.0, None, _bf16_round(w), bias, k, dil, pad, 1, Lout,
+                          res, res_shift, out_scale, y_old)
+
+
+UMMA_CASES = [
+    # B, Lin, cin, n, k, dil, act, with_res
+    (1, 256, 64, 128, 1, 1, _cabi.ACT_NONE, False),    # single tile, single stage, plain GEMM
+    (1, 256, 128, 128, 3, 1, _cabi.ACT_NONE, False),   # taps = row shifts of one smem tile
+    (2, 700, 128, 128, 7, 3, _cabi.ACT_SNAKE, True),   # stage-2 resblock conv, ragged length
+    (2, 1030, 128, 128, 11, 5, _cabi.ACT_SNAKE, True), # widest halo (50 rows)
+    (1, 513, 256, 256, 3, 5, _cabi.ACT_SNAKE, True),   # stage-1 width, two N tiles
+    (2, 130, 576, 1024, 3, 1, _cabi.ACT_LRELU, False), # encode.conv1: 9 chunks, 8 N tiles
+    (3, 40, 1152, 512, 1, 1, _cabi.ACT_NONE, False),   # conv1x1 shortcut
+    (1, 1200, 512, 2560, 3, 1, _cabi.ACT_LRELU, True), # ups[0] in polyphase form (N = 10*256)
+]
+
+
+@pytest.mark.parametrize("case", UMMA_CASES)
+def test_conv_umma_bf16(case):
+    B, Lin, cin, n, k, dil, act, with_res = case
+    x, w, bias, ss, alpha = _mk_case(B, Lin, cin, n, k, seed=hash(case) & 0xffff, act=act,
+                                     with_ss=act != _cabi.ACT_NONE)
+    pad = dil * (k - 1) // 2
+    xb = x.to(torch.bfloat16)
+    g = torch.Generator().manual_seed(11)
+    res = torch.randn(B, Lin, n, generator=g).to(torch.bfloat16) if with_res else None
+    ref = _umma_reference(xb, ss, act, 0.2, alpha, w, bias, k, dil, pad, Lin, res, 0, 0.5, None)
+    y, st = run_conv("umma", xb.cuda(), w, bias, k=k, dil=dil, pad=pad, ss=ss, act=act, slope=0.2,
+                     alpha=alpha, res=res, out_scale=0.5, want_stats=True)
+    yd = y.cpu().double()
+    assert torch.isfinite(yd).all()
+    tol = 2.0 ** -7 * ref.abs() + 3e-3  # one bf16 ulp of the result + rounding flips of the operands
+    bad = ((yd - ref).abs() > tol).sum().item()
+    assert bad == 0, (bad, (yd - ref).abs().max().item(), snr_db(ref, yd))
+    assert snr_db(ref, yd) > 45.0
+    s_ref = torch.stack([yd.sum(1), (yd ** 2).sum(1)], dim=-1)  # statistics are of the stored values
+    assert torch.allclose(st.cpu().double(), s_ref, rtol=2e-3, atol=2e-2)
+
+
+def test_conv_umma_accumulate_matches_simt():
+    B, Lin, cin, n, k, dil = 2, 900, 128, 128, 7, 1
+    x, w, bias, ss, alpha = _mk_case(B, Lin, cin, n, k, seed=21)
+    xb = x.to(torch.bfloat16).cuda()
+    g = torch.Generator().manual_seed(3)
+    res = torch.randn(B, Lin, n, generator=g).to(torch.bfloat16)
+    y_old = torch.randn(B, Lin, n, generator=g).to(torch.bfloat16)
+    kw = dict(k=k, dil=dil, pad=3, ss=ss, act=_cabi.ACT_SNAKE, alpha=alpha, res=res, out_scale=1 / 3,
+              y_old=y_old)
+    yu, _ = run_conv("umma", xb, w, bias, **kw)
+    ys, _ = run_conv("simt", xb, w, bias, **kw)
+    assert snr_db(ys.float(), yu.float()) > 40.0
+
+
+# ------------------------------------------------------------------ source / STFT / iSTFT
+def _oracle():
+    from oracle import decoder_oracle as orc
+    import synthetic as synth
+    return orc, synth
+
+
+@pytest.mark.parametrize("T", [8, 40, 400])
+def test_har_source_matches_oracle(T):
+    orc, synth = _oracle()
+    cfg = synth.ISTFTNET_CFG
+    inp = synth.synth_inputs(cfg, 2, T, seed=77 + T)
+    sd = {"generator.m_source.l_linear.weight": torch.tensor([[0.3, -0.2, 0.25, 0.1, -0.15, 0.2, 0.05, -0.1, 0.12]]),
+          "generator.m_source.l_linear.bias": torch.tensor([0.03])}
+    P = orc.Params(sd)
+    ref = orc.source_module(inp["F0_curve"], inp["noise"], P, 300)
+    f0 = inp["F0_curve"].cuda().contiguous(); nz = inp["noise"].cuda().contiguous()
+    lw = sd["generator.m_source.l_linear.weight"].reshape(-1).cuda().contiguous()
+    ph = torch.empty(2 * 9 * T, device="cuda"); out = torch.empty(2, T * 300, device="cuda")
+    check(lib.st2_source_har(f0.data_ptr(), nz.data_ptr(), 0, lw.data_ptr(), 0.03, 2, T, 300, ph.data_ptr(),
+                             out.data_ptr(), None))
+    torch.cuda.synchronize()
+    d = (out.cpu() - ref).abs()
+    # the phase reaches ~8e4 rad at T=400 (ulp 8e-3): identical fp32 rounding points are required
+    assert d.max().item() < 2e-5, (d.max().item(), (d > 1e-5).float().mean().item())
+
+
+def test_har_source_philox_is_normal_and_seeded():
+    T = 40
+    f0 = torch.zeros(2, T, device="cuda")  # unvoiced: output = tanh(sum w_h * (0.1/3) * z_h + b)
+    lw = torch.zeros(9, device="cuda"); lw[0] = 1.0
+    ph = torch.empty(2 * 9 * T, device="cuda")
+    outs = []
+    for seed in (1, 1, 2):
+        out = torch.empty(2, T * 300, device="cuda")
+        check(lib.st2_source_har(f0.data_ptr(), None, seed, lw.data_ptr(), 0.0, 2, T, 300, ph.data_ptr(),
+                                 out.data_ptr(), None))
+        outs.append(out.clone())
+    torch.cuda.synchronize()
+    assert torch.equal(outs[0], outs[1]) and not torch.equal(outs[0], outs[2])
+    z = torch.atanh(outs[0]) / (0.1 / 3)
+    assert abs(z.mean().item()) < 0.02 and abs(z.std().item() - 1) < 0.02
+    assert (outs[0][0] - outs[0][1]).abs().max().item() > 0  # items draw different noise
+
+
+@pytest.mark.parametrize("T", [8, 40])
+def test_stft_matches_oracle(T):
+    orc, synth = _oracle()
+    g = torch.Generator().manual_seed(T)
+    hs = torch.tanh(torch.randn(2, T * 300, generator=g) * 0.3)
+    mag, ph = orc.stft_transform(hs, 20, 5)
+    L2 = T * 60 + 1
+    out = torch.empty(2, L2, 32, device="cuda")
+    check(lib.st2_stft_har(hs.cuda().contiguous().data_ptr(), 2, T * 300, out.data_ptr(), None))
+    torch.cuda.synchronize()
+    o = out.cpu()
+    assert (o[:, :, :11].transpose(1, 2) - mag).abs().max().item() < 2e-6
+    # torch.angle is discontinuous at +-pi: compare on the circle, weighted by the magnitude
+    perr = wrap_phase_err(o[:, :, 11:22].transpose(1, 2), ph) * mag.double()
+    assert perr.max().item() < 5e-6
+    assert (o[:, :, 22:] == 0).all()
+    # DC / Nyquist: Im == +0 -> angle in {0, +pi}, never -pi (probed reference behaviour)
+    assert (o[:, :, 11] >= 0).all() and (o[:, :, 21] >= 0).all()
+
+
+@pytest.mark.parametrize("frames", [5, 481, 2401])
+def test_istft_head_matches_oracle(frames):
+    orc, _ = _oracle()
+    g = torch.Generator().manual_seed(frames)
+    x = torch.randn(2, 22, frames, generator=g) * 0.7
+    ref = orc.istft_inverse(torch.exp(x[:, :11]), torch.sin(x[:, 11:]), 20, 5)
+    xcl = torch.zeros(2, frames, 32)
+    xcl[:, :, :22] = x.transpose(1, 2)
+    wav = torch.empty(2, 5 * (frames - 1), device="cuda")
+    check(lib.st2_istft_head(xcl.cuda().contiguous().data_ptr(), 2, frames, wav.data_ptr(), None))
+    torch.cuda.synchronize()
+    assert (wav.cpu() - ref[:, 0]).abs().max().item() < 5e-6 * max(1.0, ref.abs().max().item())

@@ -1,0 +1,112 @@
+"""CPU: the oracle restatement against the golden vectors the REAL reference produced
+(oracle/make_golden.py, run where /root/reference exists).  This is what pins the oracle."""
+import json
+import os
+
+import numpy as np
+import pytest
+import torch
+
+from oracle import decoder_oracle as orc
+import synthetic as synth
+from tests.util_cpu import wrap_phase_err
+
+GOLD = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
+CFGS = {"istftnet": synth.ISTFTNET_CFG, "hifigan": synth.HIFIGAN_CFG}
+_SD = {}
+
+
+def sd_of(kind):
+    if kind not in _SD:
+        _SD[kind] = synth.synth_state_dict(CFGS[kind], seed=0)
+    return _SD[kind]
+
+
+def gold(kind, T):
+    g = np.load(os.path.join(GOLD, f"{kind}_T{T}.npz"))
+    return {k: torch.from_numpy(g[k]) for k in g.files}
+
+
+@pytest.mark.parametrize("kind", ["istftnet", "hifigan"])
+def test_param_spec_matches_reference_keys(kind):
+    ref = json.load(open(os.path.join(GOLD, f"keys_{kind}.json")))
+    mine = {n: list(s) for n, s, *_ in synth.param_spec(CFGS[kind])}
+    assert mine == ref
+    assert len(ref) == (375 if kind == "istftnet" else 678)
+
+
+@pytest.mark.parametrize("T", [8, 40])
+def test_istftnet_oracle_vs_reference_har_injected(T):
+    g = gold("istftnet", T)
+    out = orc.decoder_forward(sd_of("istftnet"), CFGS["istftnet"], g["asr"], g["F0_curve"], g["N"], g["s"],
+                              har=g["tap_har"])
+    assert out.shape == g["wav"].shape
+    assert (out - g["wav"]).abs().max().item() < 2e-6
+
+
+def test_istftnet_oracle_taps_vs_reference():
+    g = gold("istftnet", 8)
+    taps = {}
+    orc.decoder_forward(sd_of("istftnet"), CFGS["istftnet"], g["asr"], g["F0_curve"], g["N"], g["s"],
+                        noise=g["noise"], taps=taps)
+    for name in ("encode", "decode0", "decode1", "decode2", "decode3"):
+        assert (taps[name] - g["tap_" + name]).abs().max().item() < 1e-4, name
+    assert (taps["har_source"] - g["har_source"]).abs().max().item() < 2e-6
+    har, ref = taps["har"], g["tap_har"]
+    assert (har[:, :11] - ref[:, :11]).abs().max().item() < 5e-6
+    assert (wrap_phase_err(har[:, 11:], ref[:, 11:]) * ref[:, :11].double()).max().item() < 5e-6
+    # real bins: angle is 0 or +pi, never -pi
+    assert (har[:, 11] >= 0).all() and (har[:, 21] >= 0).all()
+    assert (ref[:, 11] >= 0).all() and (ref[:, 21] >= 0).all()
+
+
+@pytest.mark.parametrize("T", [8, 40])
+def test_hifigan_oracle_vs_reference(T):
+    g = gold("hifigan", T)
+    out = orc.decoder_forward(sd_of("hifigan"), CFGS["hifigan"], g["asr"], g["F0_curve"], g["N"], g["s"],
+                              noise=g["noise"])
+    assert (out - g["wav"]).abs().max().item() < 1e-5
+    out2 = orc.decoder_forward(sd_of("hifigan"), CFGS["hifigan"], g["asr"], g["F0_curve"], g["N"], g["s"],
+                               har_source=g["har_source"])
+    assert (out2 - g["wav"]).abs().max().item() < 1e-5
+
+
+def test_explicit_linear_resample_is_bit_exact_vs_aten():
+    """the fp32 rounding points the CUDA source kernel mirrors (fma(ratio, i+.5, -.5), fma(l0,x0,l1*x1))"""
+    import torch.nn.functional as F
+    T = 200
+    inp = synth.synth_inputs(CFGS["istftnet"], 1, T, with_noise=False)
+    harm = torch.arange(1, 10, dtype=torch.float32)
+    rad = ((inp["F0_curve"][:, :, None] * harm) / 24000) % 1
+    pt = (torch.cumsum(rad, dim=1) * 2 * np.pi).transpose(1, 2) * 300
+    up = F.interpolate(pt, scale_factor=300, mode="linear").numpy()
+    ex = orc.linear_resample_explicit(pt.contiguous().numpy(), 300 * T, np.float32(1.0 / 300.0))
+    assert np.array_equal(up, ex)
+    cs = np.cumsum(rad.numpy().astype(np.float64), axis=1).astype(np.float32)  # ATen CPU: double accumulate
+    assert np.array_equal((cs * np.float32(2) * np.float32(np.pi)).astype(np.float32),
+                          (torch.cumsum(rad, dim=1) * 2 * np.pi).numpy())
+
+
+def test_stft_istft_roundtrip_and_envelope():
+    g = torch.Generator().manual_seed(0)
+    x = torch.randn(2, 600, generator=g, dtype=torch.float64)
+    mag, ph = orc.stft_transform(x, 20, 5)
+    assert mag.shape == (2, 11, 121)
+    y = orc.istft_inverse(mag, ph, 20, 5)
+    assert y.shape == (2, 1, 600)
+    assert (y[:, 0] - x).abs().max().item() < 1e-9  # hann/hop-5 satisfies NOLA: exact reconstruction
+
+
+def test_fp64_oracle_close_to_fp32_oracle_with_har():
+    g = gold("istftnet", 8)
+    a = orc.decoder_forward(sd_of("istftnet"), CFGS["istftnet"], g["asr"], g["F0_curve"], g["N"], g["s"],
+                            har=g["tap_har"], dtype=torch.float64)
+    assert (a.float() - g["wav"]).abs().max().item() < 1e-4
+
+
+def test_metrics():
+    g = torch.Generator().manual_seed(0)
+    a = torch.randn(1, 1, 24000, generator=g)
+    assert orc.snr_db(a, a + 0.01 * torch.randn(1, 1, 24000, generator=g)) == pytest.approx(40, abs=0.5)
+    assert orc.log_mel_l1(a, a) == 0.0
+    assert orc.log_mel(a).shape == (1, 80, 81)
