@@ -83,6 +83,8 @@ typedef struct St2ForwardOpts {
   uint64_t seed;            /* Philox seed when noise == NULL */
   float* har_source_out;    /* optional [B, T*spf]: the excitation that was used */
   float* har_out;           /* optional [B, 22, 60T+1] NCL: the har that was used */
+  float* tap_decode;        /* optional [B, 512, T] NCL fp32: output of decode[3] (istftnet.py:522) */
+  float* tap_stage[ST2_MAX_UPS]; /* optional [B, C_i, L_i] NCL fp32: x after generator stage i (:374) */
 } St2ForwardOpts;
 
 /* Decoder(**kwargs): validates the config and builds the layer plan (no weights yet). */

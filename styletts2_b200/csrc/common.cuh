@@ -116,6 +116,8 @@ template <typename T>
 int launch_reflect_row0(const T* xin, int64_t xin_bstride, int cin, float slope, const float* w_tap,
                         const float* bias, const T* xs, int64_t xs_bstride, T* y, int64_t y_bstride,
                         int cout, float* stats_slot, int64_t stats_bstride, int B, cudaStream_t st);
+template <typename T>
+int launch_act_to_ncl(const T* cl, int64_t bstride, int ld, int C, int L, float* ncl, int B, cudaStream_t st);
 int launch_cl_to_ncl(const float* cl, int ld, int C, int L, float* ncl, int B, cudaStream_t st);
 int launch_ncl_to_cl(const float* ncl, int C, int L, float* cl, int ld, int B, cudaStream_t st);
 

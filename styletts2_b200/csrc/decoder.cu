@@ -711,6 +711,8 @@ int Fwd<AT>::run(const float* asr, const float* f0, const float* nn, const float
   }
   ar.release(m_dec);
 
+  if (o.tap_decode) RUN(launch_act_to_ncl<AT>(xg.p, xg.bstride, xg.ld, 512, T, o.tap_decode, B, st));
+
   // ---- excitation (istftnet.py:350-356 / hifigan.py:320-323)
   const int n_fft = c.gen_istft_n_fft, hop = c.gen_istft_hop_size;
   const int L2 = istft ? (int)(Lw / hop) + 1 : 0;
@@ -793,6 +795,7 @@ int Fwd<AT>::run(const float* asr, const float* f0, const float* nn, const float
       if (rc) return rc;
     }
     x = outb;
+    if (o.tap_stage[i]) RUN(launch_act_to_ncl<AT>(x.p, x.bstride, x.ld, C, Ls, o.tap_stage[i], B, st));
   }
 
   // ---- output head

@@ -327,6 +327,27 @@ int launch_ncl_to_cl(const float* ncl, int C, int L, float* cl, int ld, int B, c
   return ST2_OK;
 }
 
+// debug / parity taps: channels-last activation (fp32 or bf16) -> fp32 NCL
+template <typename T>
+__global__ void act_to_ncl_kernel(const T* __restrict__ cl, int64_t bstride, int ld, int C, int L,
+                                  float* __restrict__ ncl) {
+  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  const int b = blockIdx.y;
+  if (i >= (int64_t)C * L) return;
+  const int c = (int)(i / L), t = (int)(i - (int64_t)c * L);
+  ncl[(int64_t)b * C * L + i] = ld_f<T>(cl + (int64_t)b * bstride + (int64_t)t * ld + c);
+}
+template <typename T>
+int launch_act_to_ncl(const T* cl, int64_t bstride, int ld, int C, int L, float* ncl, int B, cudaStream_t st) {
+  dim3 grid((unsigned)(((int64_t)C * L + 255) / 256), B);
+  act_to_ncl_kernel<T><<<grid, 256, 0, st>>>(cl, bstride, ld, C, L, ncl);
+  ST2_LAUNCH_OK("act_to_ncl");
+  return ST2_OK;
+}
+template int launch_act_to_ncl<float>(const float*, int64_t, int, int, int, float*, int, cudaStream_t);
+template int launch_act_to_ncl<__nv_bfloat16>(const __nv_bfloat16*, int64_t, int, int, int, float*, int,
+                                              cudaStream_t);
+
 // tanh head of the HiFi-GAN generator (hifigan.py:344), in place on the fp32 waveform
 __global__ void tanh_kernel(float* __restrict__ x, int64_t n) {
   const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;

@@ -175,12 +175,13 @@ class _DecoderBase(nn.Module):
     def forward(self, asr: torch.Tensor, F0_curve: torch.Tensor, N: torch.Tensor, s: torch.Tensor, *,
                 noise: Optional[torch.Tensor] = None, har_source: Optional[torch.Tensor] = None,
                 har: Optional[torch.Tensor] = None, precision: Optional[str] = None,
-                return_excitation: bool = False):
+                return_excitation: bool = False, return_taps: bool = False):
         """Reference signature plus keyword-only extras; dispatches through the registered custom
         op ``torch.ops.styletts2_b200.decoder_forward`` (see :meth:`_forward_native`)."""
-        if return_excitation:
+        if return_excitation or return_taps:
             return self._forward_native(asr, F0_curve, N, s, noise=noise, har_source=har_source, har=har,
-                                        precision=precision, return_excitation=True)
+                                        precision=precision, return_excitation=return_excitation,
+                                        return_taps=return_taps)
         from . import ops
         return torch.ops.styletts2_b200.decoder_forward(asr, F0_curve, N, s, noise, har_source, har,
                                                         ops.register_module(self),
@@ -189,7 +190,7 @@ class _DecoderBase(nn.Module):
     def _forward_native(self, asr: torch.Tensor, F0_curve: torch.Tensor, N: torch.Tensor, s: torch.Tensor, *,
                         noise: Optional[torch.Tensor] = None, har_source: Optional[torch.Tensor] = None,
                         har: Optional[torch.Tensor] = None, precision: Optional[str] = None,
-                        return_excitation: bool = False):
+                        return_excitation: bool = False, return_taps: bool = False):
         """``Decoder.forward(asr, F0_curve, N, s)`` (istftnet.py:498).  Extra keyword-only inputs
         inject the excitation for reproducibility: ``noise`` [B, 300T, 9] (the randn_like draw of
         SineGen), ``har_source`` [B, 300T] (output of m_source) or ``har`` [B, 22, 60T+1]."""
@@ -241,6 +242,17 @@ class _DecoderBase(nn.Module):
                 if self.KIND == _cabi.KIND_ISTFTNET:
                     exc["har"] = torch.empty(B, 22, Lw // 5 + 1, dtype=torch.float32, device=dev)
                     opts.har_out = exc["har"].data_ptr()
+            taps = {}
+            if return_taps:
+                taps["decode3"] = torch.empty(B, 512, T, dtype=torch.float32, device=dev)
+                opts.tap_decode = taps["decode3"].data_ptr()
+                L, ch = T, self._cfg.upsample_initial_channel
+                for i in range(self._cfg.n_ups):
+                    L, ch = L * self._cfg.upsample_rates[i], ch // 2
+                    if self.KIND == _cabi.KIND_ISTFTNET and i == self._cfg.n_ups - 1:
+                        L += 1
+                    taps[f"stage{i}"] = torch.empty(B, ch, L, dtype=torch.float32, device=dev)
+                    opts.tap_stage[i] = taps[f"stage{i}"].data_ptr()
             stream = torch.cuda.current_stream(dev).cuda_stream
             check(lib.st2_decoder_forward(h, ptr(asr_), ptr(f0_), ptr(n_), ptr(s_), ptr(wav), ptr(ws),
                                           int(need), B, T, C.byref(opts), C.c_void_p(stream)),
@@ -248,6 +260,8 @@ class _DecoderBase(nn.Module):
             self.seed += 1 if noise_ is None and hs_ is None and har_ is None else 0
             self.last_launches = int(lib.st2_decoder_last_launches(h))
             # ws / inputs are only recycled by torch's caching allocator in stream order
+        if return_taps:
+            return wav, taps
         if return_excitation:
             return wav, exc
         return wav

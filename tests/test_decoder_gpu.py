@@ -86,7 +86,7 @@ def test_hifigan_fp32_vs_reference_golden(T):
     assert err < 1e-3, err
     wav2 = dec(_c(g["asr"]), _c(g["F0_curve"]), _c(g["N"]), _c(g["s"]), har_source=_c(g["har_source"]),
                precision="fp32")
-    assert (wav2.cpu() - g["wav"]).abs().max().item() < 5e-5
+    assert (wav2.cpu() - g["wav"]).abs().max().item() < 2e-4
 
 
 @pytest.mark.parametrize("kind", ["istftnet", "hifigan"])
