@@ -94,6 +94,7 @@ __device__ __forceinline__ float warp_sum(float v) {
 int launch_conv_simt(const St2ConvParams& p, cudaStream_t st);
 int launch_conv_umma(const St2ConvParams& p, cudaStream_t st);
 int conv_tile_rows(bool umma);
+int umma_n_tile(int n_cols);  // GEMM columns per tcgen05 tile for a layer of n_cols (0: none)
 
 int launch_style_fc(const float* s, const float* W, const float* bvec, float* h, int B, int style,
                     int rows, cudaStream_t st);

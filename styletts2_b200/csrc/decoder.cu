@@ -24,9 +24,10 @@ struct ConvW {
   int cin = 0;      // contraction channels of the fp32 layout
   int cin_pad = 0;  // channels of the UMMA blob (multiple of 64), 0 = no blob
   int n = 0;        // GEMM columns (Cout, or phases*Cout for a transposed conv)
+  int n16 = 0;      // columns of the UMMA blob (n rounded up to a multiple of 32)
   int cstat = 0;    // real channels the columns fold onto for statistics
   double flops_per_row = 0.0;  // algorithmic 2*MAC per output row (per INPUT row for a transposed conv)
-  int64_t w32 = -1, w16 = -1, bias = -1;  // byte offsets into the device weight arena
+  int64_t w32 = -1, w16 = -1, bias = -1, bias16 = -1;  // byte offsets into the device weight arena
 };
 struct NormW {
   int C = 0;
@@ -210,11 +211,28 @@ struct Loader {
   void finish_conv(ConvW& c, const std::vector<float>& w_kcn, const std::vector<float>* bias, bool want_umma) {
     c.w32 = blob.add(w_kcn.data(), (int64_t)w_kcn.size() * 4);
     if (bias) c.bias = blob.add(bias->data(), (int64_t)bias->size() * 4);
-    if (want_umma && c.stride == 1 && c.n % 128 == 0 && (c.k - 1) * c.dil <= 50) {
+    if (want_umma && c.stride == 1 && (c.k - 1) * c.dil <= 50) {
+      // GEMM columns are padded with zero weights / zero bias up to a multiple of 32 (conv_post: 22 -> 32)
       c.cin_pad = (int)round_up(c.cin, 64);
-      const int64_t elems = st2_umma_packed_elems(c.k, c.cin_pad, c.n);
+      c.n16 = (int)round_up(c.n, 32);
+      const std::vector<float>* wsrc = &w_kcn;
+      std::vector<float> wpad, bpad;
+      if (c.n16 != c.n) {
+        wpad.assign((size_t)c.k * c.cin * c.n16, 0.f);
+        for (int64_t r = 0; r < (int64_t)c.k * c.cin; ++r)
+          memcpy(&wpad[(size_t)r * c.n16], &w_kcn[(size_t)r * c.n], (size_t)c.n * 4);
+        wsrc = &wpad;
+        if (bias) {
+          bpad.assign((size_t)c.n16, 0.f);
+          memcpy(bpad.data(), bias->data(), (size_t)c.n * 4);
+          c.bias16 = blob.add(bpad.data(), (int64_t)bpad.size() * 4);
+        }
+      } else {
+        c.bias16 = c.bias;
+      }
+      const int64_t elems = st2_umma_packed_elems(c.k, c.cin_pad, c.n16);
       c.w16 = blob.add(nullptr, elems * 2);
-      st2_umma_pack_weights(w_kcn.data(), c.k, c.cin, c.cin_pad, c.n,
+      st2_umma_pack_weights(wsrc->data(), c.k, c.cin, c.cin_pad, c.n16,
                             reinterpret_cast<uint16_t*>(blob.data.data() + c.w16));
     }
   }
@@ -408,7 +426,7 @@ static int do_load(St2Decoder* h, const St2Tensor* tensors, int n) {
                        g + ".resblocks." + std::to_string(i * c.n_resblock_kernels + j), cout,
                        c.resblock_kernel_sizes[j], c.resblock_dilations[j]);
   }
-  ok = ok && L.conv1d(h->conv_post, g + ".conv_post", true, true, 7, 1, 3, 1, false);
+  ok = ok && L.conv1d(h->conv_post, g + ".conv_post", true, true, 7, 1, 3, 1, istft);
   if (ok && !istft) {
     h->alphas.assign(c.n_ups + 1, -1);
     for (int i = 0; i <= c.n_ups && ok; ++i)
@@ -514,8 +532,12 @@ struct Fwd {
   // runs one fused conv; partial statistics (if requested) are left in arena scratch that the
   // caller must consume (finalize) before the next arena allocation that follows a release.
   int conv(const ConvW& c, const ConvIO& io) {
+    // tcgen05 path: bf16 activations in; bf16 out, or fp32 out when the layer's padded width is the
+    // row stride of the destination (conv_post -> [rows][32] fp32)
     const bool umma = DT<AT>::id == ST2_DT_BF16 && c.w16 >= 0 && io.x_dtype == ST2_DT_BF16 &&
-                      io.y_dtype == ST2_DT_BF16;
+                      io.ldx >= c.cin_pad &&
+                      ((io.y_dtype == ST2_DT_BF16 && c.n16 == c.n) ||
+                       (io.y_dtype == ST2_DT_F32 && c.n16 <= io.ldy && c.n16 <= 64 && !io.want_stats));
     St2ConvParams p;
     memset(&p, 0, sizeof(p));
     p.B = B;
@@ -528,8 +550,8 @@ struct Fwd {
     p.act = io.act; p.slope = io.slope; p.alpha = io.alpha;
     p.k = c.k; p.dil = c.dil; p.pad = c.pad; p.stride = c.stride;
     p.w = umma ? (const void*)W<uint16_t>(c.w16) : (const void*)W<float>(c.w32);
-    p.bias = W<float>(c.bias);
-    p.n_cols = c.n;
+    p.bias = W<float>(umma ? c.bias16 : c.bias);
+    p.n_cols = umma ? c.n16 : c.n;
     p.y = io.y; p.y_dtype = io.y_dtype; p.y_bstride = io.y_bstride; p.ldy = io.ldy; p.Lout = io.Lout;
     p.res = io.res; p.res_bstride = io.res_bstride; p.ldres = io.ldres; p.res_shift = io.res_shift;
     p.out_scale = io.out_scale; p.accumulate = io.accumulate;

@@ -45,24 +45,51 @@ int launch_style_fc(const float* s, const float* W, const float* bvec, float* h,
 }
 
 // ------------------------------------------------------------------- stats finalize
-// thread per (b, c).  Partials are [B][n_tiles][n_cols][2]; channel c owns columns c, c+C, ...
-// (n_cols = phases*C for a polyphase transposed conv).  Sums run in fp64 in a fixed order, so
-// the result is deterministic and independent of how the grid was scheduled.
-__global__ void __launch_bounds__(128)
+// block = 32 channels of one batch item, 8 warps: warp w reduces tiles w, w+8, ... (lane = channel,
+// so every load is a 256-byte coalesced row of (sum, sumsq) pairs), then the 8 warp partials are
+// combined in a fixed order.  Partials are [B][n_tiles][n_cols][2]; channel c owns columns c, c+C,
+// ... (n_cols = phases*C for a polyphase transposed conv).  Sums run in fp64 in a fixed order, so
+// the result is deterministic and independent of how the producing grid was scheduled.
+constexpr int SF_WARPS = 8;
+__global__ void __launch_bounds__(SF_WARPS * 32)
 stats_finalize_kernel(const float* __restrict__ partials, int n_tiles, int n_cols, int C,
                       double inv_count, const float* __restrict__ hg, int h_stride, int Cn,
                       float* __restrict__ ss, int ss_stride, int c_off) {
-  const int c = blockIdx.x * blockDim.x + threadIdx.x;
+  __shared__ double red[SF_WARPS][32][2];
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int c = blockIdx.x * 32 + lane;
   const int b = blockIdx.y;
-  if (c >= C) return;
   const float2* pp = reinterpret_cast<const float2*>(partials) + (int64_t)b * n_tiles * n_cols;
   double s = 0.0, q = 0.0;
-  for (int t = 0; t < n_tiles; ++t)
+  if (c < C) {
     for (int col = c; col < n_cols; col += C) {
-      const float2 v = pp[(int64_t)t * n_cols + col];
-      s += (double)v.x;
-      q += (double)v.y;
+      int t = warp;
+      for (; t + 3 * SF_WARPS < n_tiles; t += 4 * SF_WARPS) {  // 4 independent loads in flight
+        const float2 v0 = pp[(int64_t)t * n_cols + col];
+        const float2 v1 = pp[(int64_t)(t + SF_WARPS) * n_cols + col];
+        const float2 v2 = pp[(int64_t)(t + 2 * SF_WARPS) * n_cols + col];
+        const float2 v3 = pp[(int64_t)(t + 3 * SF_WARPS) * n_cols + col];
+        s += (double)v0.x; q += (double)v0.y;
+        s += (double)v1.x; q += (double)v1.y;
+        s += (double)v2.x; q += (double)v2.y;
+        s += (double)v3.x; q += (double)v3.y;
+      }
+      for (; t < n_tiles; t += SF_WARPS) {
+        const float2 v = pp[(int64_t)t * n_cols + col];
+        s += (double)v.x; q += (double)v.y;
+      }
     }
+  }
+  red[warp][lane][0] = s;
+  red[warp][lane][1] = q;
+  __syncthreads();
+  if (warp != 0 || c >= C) return;
+  s = 0.0; q = 0.0;
+#pragma unroll
+  for (int w = 0; w < SF_WARPS; ++w) {
+    s += red[w][lane][0];
+    q += red[w][lane][1];
+  }
   const double mean = s * inv_count;
   double var = q * inv_count - mean * mean;
   if (var < 0.0) var = 0.0;
@@ -80,9 +107,9 @@ stats_finalize_kernel(const float* __restrict__ partials, int n_tiles, int n_col
 int launch_stats_finalize(const float* partials, int n_tiles, int n_cols, int C, int64_t count,
                           const float* hg, int h_stride, int Cn, float* ss, int ss_stride,
                           int c_off, int B, cudaStream_t st) {
-  dim3 grid(ceil_div(C, 128), B);
-  stats_finalize_kernel<<<grid, 128, 0, st>>>(partials, n_tiles, n_cols, C, 1.0 / (double)count, hg,
-                                              h_stride, Cn, ss, ss_stride, c_off);
+  dim3 grid(ceil_div(C, 32), B);
+  stats_finalize_kernel<<<grid, SF_WARPS * 32, 0, st>>>(partials, n_tiles, n_cols, C, 1.0 / (double)count,
+                                                       hg, h_stride, Cn, ss, ss_stride, c_off);
   ST2_LAUNCH_OK("stats_finalize");
   return ST2_OK;
 }

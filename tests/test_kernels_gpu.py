@@ -128,6 +128,35 @@ def test_conv_umma_bf16(case):
     assert torch.allclose(st.cpu().double(), s_ref, rtol=2e-3, atol=2e-2)
 
 
+@pytest.mark.parametrize("case", [
+    # B, Lin, cin, n, k, dil, act, out fp32
+    (2, 700, 128, 32, 7, 1, _cabi.ACT_LRELU, True),    # conv_post: 128 -> 22 (padded 32), fp32 rows of 128 B
+    (1, 1300, 64, 64, 3, 3, _cabi.ACT_SNAKE, False),   # hifigan stage-3 width: one 64-column tile
+    (2, 515, 64, 32, 11, 5, _cabi.ACT_SNAKE, False),   # hifigan stage-4 width, widest halo
+    (1, 300, 128, 64, 1, 1, _cabi.ACT_NONE, True),     # fp32 out, 64 columns
+    (2, 1000, 64, 192, 3, 1, _cabi.ACT_NONE, False),   # three 64-column tiles
+])
+def test_conv_umma_narrow_tiles(case):
+    B, Lin, cin, n, k, dil, act, f32out = case
+    x, w, bias, ss, alpha = _mk_case(B, Lin, cin, n, k, seed=hash(case) & 0xffff, act=act,
+                                     with_ss=act != _cabi.ACT_NONE)
+    pad = dil * (k - 1) // 2
+    xb = x.to(torch.bfloat16)
+    g = torch.Generator().manual_seed(13)
+    res = None if f32out else torch.randn(B, Lin, n, generator=g).to(torch.bfloat16)
+    ref = _umma_reference(xb, ss, act, 0.01, alpha, w, bias, k, dil, pad, Lin, res, 0, 1.0, None)
+    y, st = run_conv("umma", xb.cuda(), w, bias, k=k, dil=dil, pad=pad, ss=ss, act=act, slope=0.01,
+                     alpha=alpha, res=res, out_scale=1.0, want_stats=not f32out,
+                     out_dtype=torch.float32 if f32out else None)
+    yd = y.cpu().double()
+    assert torch.isfinite(yd).all()
+    tol = (2.0 ** -7 * ref.abs() if not f32out else 0) + 3e-3
+    assert ((yd - ref).abs() > tol).sum().item() == 0, (yd - ref).abs().max().item()
+    if not f32out:
+        s_ref = torch.stack([yd.sum(1), (yd ** 2).sum(1)], dim=-1)
+        assert torch.allclose(st.cpu().double(), s_ref, rtol=2e-3, atol=2e-2)
+
+
 def test_conv_umma_accumulate_matches_simt():
     B, Lin, cin, n, k, dil = 2, 900, 128, 128, 7, 1
     x, w, bias, ss, alpha = _mk_case(B, Lin, cin, n, k, seed=21)
