@@ -15,20 +15,27 @@
 // Persistent, warp-specialised CTA (1 per SM, 448 threads):
 //   warp 0      MMA issuer (one lane) + TMEM allocation (512 columns: 2 tiles x 2 accumulators)
 //   warp 1      weight producer (one lane, bulk copies through a 3-deep ring)
-//   warps 2-5   epilogue: tcgen05.ld -> (+residual) * scale + bias (+ y_old) -> staging tile in smem
-//               -> one bulk store per output row (coalesced, asynchronous), and per-column
-//               sum / sum-of-squares of the stored values for the next InstanceNorm, read back
-//               from the staging tile (2 columns per thread, conflict free)
+//   warps 2-5   epilogue: tcgen05.ld -> * scale + bias -> 128B-swizzled staging tile in smem -> one TMA
+//               tensor store per 128-byte column segment (coalesced, asynchronous, clipped at Lout by
+//               the tensor map), and per-column sum / sum-of-squares of the stored values for the
+//               next InstanceNorm, read back from the staging tile (2 columns per thread)
 //   warps 6-13  activation producers (the fused conv prologue): cp.async (LDGSTS) the raw bf16 tile
 //               straight into its final place in the A ring D chunks ahead, then normalise (AdaIN
 //               scale/shift), activate (Snake / LeakyReLU) and convert IN PLACE
+// The residual (and the running mean over resblocks, `accumulate`) never touch the epilogue: their
+// rows are staged like one more 64-channel activation chunk (plain cp.async, no arithmetic) and
+// added by the tensor core through an identity weight block (x 1/out_scale for y_old), which is
+// exact for bf16 data in an fp32 accumulator.
 // Pipelines: A ring (3-4 stages: loading / transforming / feeding the MMAs), W ring, TMEM double
 // buffer (MMA <-> epilogue): the prologue of tile i+1 and the epilogue of tile i-1 overlap the
 // MMAs of tile i.  No thread of this kernel waits on a global load it has just issued.
 //
 // Reference semantics: conv_params.h (Modules/istftnet.py:66-75, 440-453, 358-374).
+#include <cuda.h>
 #include <string.h>
 
+#include <map>
+#include <mutex>
 #include <vector>
 
 #include "common.cuh"
@@ -54,9 +61,11 @@ struct UmLayout {
   int na;             // A stages in use
   int dist;           // prefetch distance of the producers, in chunks (na - 2)
   int w_bytes;        // bytes per weight stage (= 8 * n_tile * 16)
-  int stg_row;        // bytes per row of the epilogue staging tile (row + 16 B pad)
-  int out_row;        // bytes per output row segment (n_tile * element size)
-  uint32_t off_w, off_stg, off_misc, total;
+  int out_row;        // bytes per output row segment (n_tile * element size), multiple of 128
+  int n_res, n_acc;   // extra 64-channel chunks per tile: residual rows, y_old rows
+  const uint8_t* ident_res;  // n_tile/64 identity weight blobs (x 1)
+  const uint8_t* ident_acc;  // n_tile/64 identity weight blobs (x 1/out_scale)
+  uint32_t off_a, off_w, off_misc, total;  // the staging tile sits at offset 0 (1024-byte aligned)
   uint32_t idesc;
 };
 
@@ -120,10 +129,11 @@ __device__ __forceinline__ void bulk_g2s(void* smem_dst, const void* gsrc, uint3
                "l"(gsrc), "r"(bytes), "r"(smem_u32(bar))
                : "memory");
 }
-// smem -> global bulk store (TMA engine), tracked by the issuing thread's bulk async-group
-__device__ __forceinline__ void bulk_s2g(void* gdst, const void* smem_src, uint32_t bytes) {
-  asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(gdst),
-               "r"(smem_u32(smem_src)), "r"(bytes)
+// smem -> global TMA tensor store (3-D map: column, row, batch), tracked by the issuing thread's
+// bulk async-group; rows / columns outside the tensor are clipped by the hardware
+__device__ __forceinline__ void tma_store_3d(const CUtensorMap* map, uint32_t smem_src, int c0, int c1, int c2) {
+  asm volatile("cp.async.bulk.tensor.3d.global.shared::cta.bulk_group [%0, {%2, %3, %4}], [%1];" ::"l"(map),
+               "r"(smem_src), "r"(c0), "r"(c1), "r"(c2)
                : "memory");
 }
 __device__ __forceinline__ void bulk_commit() { asm volatile("cp.async.bulk.commit_group;" ::: "memory"); }
@@ -180,7 +190,19 @@ static inline uint32_t um_idesc(int n_tile) {
   return (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(n_tile >> 3) << 17) | ((uint32_t)(128 >> 4) << 24);
 }
 
-__device__ __forceinline__ void tmem_ld32(uint32_t taddr, uint32_t (&v)[32]) {
+__device__ __forceinline__ void tmem_ld_wait() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
+// empty asm that "modifies" the loaded registers: their uses cannot be scheduled above the wait
+__device__ __forceinline__ void tmem_ld_fence(uint32_t (&v)[32]) {
+  asm volatile(""
+               : "+r"(v[0]), "+r"(v[1]), "+r"(v[2]), "+r"(v[3]), "+r"(v[4]), "+r"(v[5]), "+r"(v[6]), "+r"(v[7]),
+                 "+r"(v[8]), "+r"(v[9]), "+r"(v[10]), "+r"(v[11]), "+r"(v[12]), "+r"(v[13]), "+r"(v[14]),
+                 "+r"(v[15]), "+r"(v[16]), "+r"(v[17]), "+r"(v[18]), "+r"(v[19]), "+r"(v[20]), "+r"(v[21]),
+                 "+r"(v[22]), "+r"(v[23]), "+r"(v[24]), "+r"(v[25]), "+r"(v[26]), "+r"(v[27]), "+r"(v[28]),
+                 "+r"(v[29]), "+r"(v[30]), "+r"(v[31])
+               :
+               : "memory");
+}
+__device__ __forceinline__ void tmem_ld32_nowait(uint32_t taddr, uint32_t (&v)[32]) {
   asm volatile(
       "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
       "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
@@ -192,7 +214,6 @@ __device__ __forceinline__ void tmem_ld32(uint32_t taddr, uint32_t (&v)[32]) {
         "=r"(v[30]), "=r"(v[31])
       : "r"(taddr)
       : "memory");
-  asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
 }
 __device__ __forceinline__ void named_bar_sync(int id, int nthreads) {
   asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(nthreads) : "memory");
@@ -260,26 +281,63 @@ __device__ __forceinline__ void um_produce(const St2ConvParams& p, const UmLayou
                                            int n_ntiles, int nchunks) {
   const int v = ptid & 7, rbase = ptid >> 3;
   const int r_tot = UM_TM + (p.k - 1) * p.dil;
+  const int nct = nchunks + lay.n_res + lay.n_acc;  // chunks per tile incl. residual / y_old rows
   const __nv_bfloat16* xg = reinterpret_cast<const __nv_bfloat16*>(p.x);
-  const uint32_t a0 = smem_u32(smem) + (uint32_t)v * (uint32_t)(lay.rpad * 16);
+  const uint32_t a0 = smem_u32(smem + lay.off_a) + (uint32_t)v * (uint32_t)(lay.rpad * 16);
   constexpr bool IDENT = (ACT == ST2_ACT_NONE) && !HAS_SS;
 
   auto issue_loads = [&](const UmCur& q) {
     mbar_wait(&misc->a_empty[q.stage], q.ph ^ 1u, 0);
     const UmTile tl = um_tile(q.tile, n_ttiles, n_ntiles);
-    const int row0 = tl.t0 - p.pad;
-    const __nv_bfloat16* xb = xg + (int64_t)tl.b * p.x_bstride + (q.c * UM_CK + v * 8);
     const uint32_t dst = a0 + (uint32_t)q.stage * (uint32_t)lay.a_bytes;
+    if (q.c < nchunks) {
+      const int row0 = tl.t0 - p.pad;
+      const __nv_bfloat16* xb = xg + (int64_t)tl.b * p.x_bstride + (q.c * UM_CK + v * 8);
 #pragma unroll
-    for (int i = 0; i < UM_NI; ++i) {
-      const int r = rbase + 32 * i;
-      const int tin = row0 + r;
-      if (r < r_tot && tin >= 0 && tin < p.Lin) cp_async16(dst + (uint32_t)r * 16u, xb + (int64_t)tin * p.ldx);
+      for (int i = 0; i < UM_NI; ++i) {
+        const int r = rbase + 32 * i;
+        const int tin = row0 + r;
+        if (r < r_tot && tin >= 0 && tin < p.Lin) cp_async16(dst + (uint32_t)r * 16u, xb + (int64_t)tin * p.ldx);
+      }
+    } else {
+      // residual rows (row t >> res_shift of res) or y_old rows (row t of y): 64 columns of this N tile
+      const int e = q.c - nchunks;
+      const bool is_res = e < lay.n_res;
+      const int hh = is_res ? e : e - lay.n_res;
+      const __nv_bfloat16* sb;
+      int ld, shift;
+      if (is_res) {
+        sb = reinterpret_cast<const __nv_bfloat16*>(p.res) + (int64_t)tl.b * p.res_bstride;
+        ld = p.ldres; shift = p.res_shift;
+      } else {
+        sb = reinterpret_cast<const __nv_bfloat16*>(p.y) + (int64_t)tl.b * p.y_bstride;
+        ld = p.ldy; shift = 0;
+      }
+      sb += tl.nt * lay.n_tile + hh * UM_CK + v * 8;
+#pragma unroll
+      for (int i = 0; i < UM_TM / 32; ++i) {
+        const int r = rbase + 32 * i;
+        const int t = tl.t0 + r;
+        if (t < p.Lout) cp_async16(dst + (uint32_t)r * 16u, sb + (int64_t)(t >> shift) * ld);
+      }
     }
   };
 
   auto transform = [&](const UmCur& q) {
     const UmTile tl = um_tile(q.tile, n_ttiles, n_ntiles);
+    const uint32_t dst = a0 + (uint32_t)q.stage * (uint32_t)lay.a_bytes;
+    if (q.c >= nchunks) {
+      if (lay.dist == 2) cp_async_wait<2>();
+      else cp_async_wait<1>();
+#pragma unroll
+      for (int i = 0; i < UM_TM / 32; ++i) {
+        const int r = rbase + 32 * i;
+        if (tl.t0 + r >= p.Lout) sts128(dst + (uint32_t)r * 16u, make_uint4(0u, 0u, 0u, 0u));
+      }
+      fence_proxy_async_smem();
+      mbar_arrive(&misc->a_full[q.stage]);
+      return;
+    }
     const int row0 = tl.t0 - p.pad;
     const int ch0 = q.c * UM_CK + v * 8;
     float sc[8], sh[8], wsc[8], wsh[8], hia[8];
@@ -301,7 +359,6 @@ __device__ __forceinline__ void um_produce(const St2ConvParams& p, const UmLayou
     // chunk q's LDGSTS group is complete once at most `dist` newer groups are pending
     if (lay.dist == 2) cp_async_wait<2>();
     else cp_async_wait<1>();
-    const uint32_t dst = a0 + (uint32_t)q.stage * (uint32_t)lay.a_bytes;
 #pragma unroll
     for (int i = 0; i < UM_NI; ++i) {
       const int r = rbase + 32 * i;
@@ -335,176 +392,138 @@ __device__ __forceinline__ void um_produce(const St2ConvParams& p, const UmLayou
   for (int d = 0; d < lay.dist; ++d) {
     if (lc.tile < total_tiles) {
       issue_loads(lc);
-      um_advance(lc, nchunks, lay.na);
+      um_advance(lc, nct, lay.na);
     }
     cp_async_commit();
   }
   while (tc.tile < total_tiles) {
     if (lc.tile < total_tiles) {
       issue_loads(lc);
-      um_advance(lc, nchunks, lay.na);
+      um_advance(lc, nct, lay.na);
     }
     cp_async_commit();
     transform(tc);
-    um_advance(tc, nchunks, lay.na);
+    um_advance(tc, nct, lay.na);
   }
   cp_async_wait<0>();
 }
 
-// epilogue output conversion + staging store of 32 consecutive columns of one row
+// Staging tile: 128 rows x out_row bytes as out_row/128 column segments of [128 rows][128 B], each in
+// the TMA SWIZZLE_128B pattern (16-byte chunk index ^ (row & 7)), so that row-per-thread 16-byte
+// stores and the column reads of the statistics pass are both bank-conflict free.
+__device__ __forceinline__ uint32_t um_stg_addr(uint32_t stg, int row, int byte_in_row) {
+  const int seg = byte_in_row >> 7, chunk = (byte_in_row >> 4) & 7;
+  return stg + (uint32_t)seg * 16384u + (uint32_t)row * 128u + (uint32_t)((chunk ^ (row & 7)) << 4) +
+         (uint32_t)(byte_in_row & 15);
+}
+
+// scale / bias one 32-column block of this thread's row and write it to the staging tile
 template <bool OUT_F32>
-__device__ __forceinline__ void um_stage32(uint32_t addr, const float (&o)[32]) {
+__device__ __forceinline__ void um_stage32(uint32_t stg, int row, int cb, const uint32_t (&v)[32],
+                                           const float* bias_s, float scale) {
+  float o[32];
+#pragma unroll
+  for (int g = 0; g < 8; ++g) {
+    const float4 b4 = *reinterpret_cast<const float4*>(bias_s + cb * 32 + g * 4);
+    o[4 * g] = fmaf(__uint_as_float(v[4 * g]), scale, b4.x);
+    o[4 * g + 1] = fmaf(__uint_as_float(v[4 * g + 1]), scale, b4.y);
+    o[4 * g + 2] = fmaf(__uint_as_float(v[4 * g + 2]), scale, b4.z);
+    o[4 * g + 3] = fmaf(__uint_as_float(v[4 * g + 3]), scale, b4.w);
+  }
   if (OUT_F32) {
 #pragma unroll
     for (int g = 0; g < 8; ++g)
-      sts128(addr + g * 16, make_uint4(__float_as_uint(o[4 * g]), __float_as_uint(o[4 * g + 1]),
-                                       __float_as_uint(o[4 * g + 2]), __float_as_uint(o[4 * g + 3])));
+      sts128(um_stg_addr(stg, row, cb * 128 + g * 16),
+             make_uint4(__float_as_uint(o[4 * g]), __float_as_uint(o[4 * g + 1]), __float_as_uint(o[4 * g + 2]),
+                        __float_as_uint(o[4 * g + 3])));
   } else {
 #pragma unroll
     for (int g = 0; g < 4; ++g)
-      sts128(addr + g * 16, make_uint4(pack_bf16x2(o[8 * g], o[8 * g + 1]), pack_bf16x2(o[8 * g + 2], o[8 * g + 3]),
-                                       pack_bf16x2(o[8 * g + 4], o[8 * g + 5]), pack_bf16x2(o[8 * g + 6], o[8 * g + 7])));
+      sts128(um_stg_addr(stg, row, cb * 64 + g * 16),
+             make_uint4(pack_bf16x2(o[8 * g], o[8 * g + 1]), pack_bf16x2(o[8 * g + 2], o[8 * g + 3]),
+                        pack_bf16x2(o[8 * g + 4], o[8 * g + 5]), pack_bf16x2(o[8 * g + 6], o[8 * g + 7])));
   }
 }
 
 template <bool OUT_F32>
-__device__ __forceinline__ void um_epilogue(const St2ConvParams& p, const UmLayout& lay, uint8_t* smem,
-                                            UmMisc* misc, uint32_t tmem_base, int warp, int lane,
+__device__ __forceinline__ void um_epilogue(const St2ConvParams& p, const UmLayout& lay, const CUtensorMap* ymap,
+                                            uint8_t* smem, UmMisc* misc, uint32_t tmem_base, int warp, int lane,
                                             int total_tiles, int n_ttiles, int n_ntiles) {
   const int q = warp & 3;                          // TMEM lane group this warp may access
   const int et = threadIdx.x - UM_EPI_WARP0 * 32;  // 0..127
   const int rl = q * 32 + lane;                    // row inside an accumulator = TMEM lane
   const int n_tile = lay.n_tile, ncb = n_tile >> 5;
-  const int esz = OUT_F32 ? 4 : 2;
-  uint8_t* stg = smem + lay.off_stg;
-  const uint32_t my_stg = smem_u32(stg) + (uint32_t)rl * (uint32_t)lay.stg_row;
+  const uint32_t stg = smem_u32(smem);
+  const int nseg = lay.out_row >> 7;               // 128-byte column segments per row
+  const int seg_cols = OUT_F32 ? 32 : 64;
   // statistics pass: ncp column pairs x (128 / ncp) row groups of ncp rows
   const int ncp = n_tile >> 1;
   const int cp = et % ncp, grp = et / ncp;
-  const bool has_res = p.res != nullptr, has_acc = p.accumulate != 0;
-  uint8_t* yg = reinterpret_cast<uint8_t*>(p.y);
-  const uint8_t* rg = reinterpret_cast<const uint8_t*>(p.res);
+  const float scale = p.out_scale;
   uint32_t t_it = 0;
   for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, ++t_it) {
     const UmTile tl = um_tile(tile, n_ttiles, n_ntiles);
     const uint32_t tb = t_it & 1, tph = (t_it >> 1) & 1;
     float* bias_s = misc->bias[tb];
-    if (et < n_tile) bias_s[et] = (p.bias ? p.bias[tl.nt * n_tile + et] : 0.f) * p.out_scale;
-    named_bar_sync(1, UM_EPI_THREADS);
+    if (et < n_tile) bias_s[et] = (p.bias ? p.bias[tl.nt * n_tile + et] : 0.f) * scale;
     float s0 = 0.f, s1 = 0.f, q0 = 0.f, q1 = 0.f;
-
-    // residual / y_old of block g = acc * ncb + cb of this thread's row (16-byte pieces of 32 bf16)
-    auto row_of = [&](int acc) { return tl.t0 + acc * 128 + rl; };
-    auto load_blk = [&](int g, uint4 (&rr)[4], uint4 (&yy)[4]) {
-      const int acc = g / ncb, cb = g - acc * ncb;
-      const int row = row_of(acc);
-      if (row >= p.Lout) return;
-      if (has_res) {
-        const uint8_t* rp = rg + ((int64_t)tl.b * p.res_bstride + (int64_t)(row >> p.res_shift) * p.ldres +
-                                  tl.nt * n_tile + cb * 32) * 2;
-#pragma unroll
-        for (int i = 0; i < 4; ++i) rr[i] = ldg_nc16(rp + i * 16);
-      }
-      if (has_acc) {
-        const uint8_t* yp = yg + ((int64_t)tl.b * p.y_bstride + (int64_t)row * p.ldy + tl.nt * n_tile + cb * 32) * 2;
-#pragma unroll
-        for (int i = 0; i < 4; ++i) yy[i] = ldg_nc16(yp + i * 16);
-      }
-    };
-    uint4 rr[4], yy[4];
-#pragma unroll
-    for (int i = 0; i < 4; ++i) rr[i] = yy[i] = make_uint4(0u, 0u, 0u, 0u);
-    if (!OUT_F32) load_blk(0, rr, yy);
-
     mbar_wait(&misc->t_full[tb], tph, 5);
     tc_fence_after();
 #pragma unroll 1
     for (int acc = 0; acc < UM_NACC; ++acc) {
-      const int row = row_of(acc);
-      const bool valid = row < p.Lout;
-      // the staging tile is free once this thread's bulk store has read its row and every thread has
-      // finished the statistics pass over the previous contents
-      bulk_wait_read0();
-      if (p.stats) named_bar_sync(2, UM_EPI_THREADS);
-#pragma unroll 1
-      for (int cb = 0; cb < ncb; ++cb) {
+      // the staging tile is free once the previous TMA store has read it (issued by thread 0) and
+      // every thread has finished its statistics pass; this barrier also publishes bias_s
+      if (et == 0) bulk_wait_read0();
+      named_bar_sync(2, UM_EPI_THREADS);
+      const uint32_t tcol = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)((tb * UM_NACC + acc) * n_tile);
+      if (ncb == 1) {
         uint32_t v[32];
-        tmem_ld32(tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)((tb * UM_NACC + acc) * n_tile + cb * 32), v);
-        uint4 rn[4], yn[4];
-#pragma unroll
-        for (int i = 0; i < 4; ++i) rn[i] = yn[i] = make_uint4(0u, 0u, 0u, 0u);
-        const int gnext = acc * ncb + cb + 1;
-        if (!OUT_F32 && gnext < UM_NACC * ncb) load_blk(gnext, rn, yn);
-        float o[32];
-#pragma unroll
-        for (int i = 0; i < 32; ++i) o[i] = __uint_as_float(v[i]);
-        if (!OUT_F32 && has_res) {
-#pragma unroll
-          for (int g = 0; g < 4; ++g) {
-            const uint32_t rw[4] = {rr[g].x, rr[g].y, rr[g].z, rr[g].w};
-#pragma unroll
-            for (int e = 0; e < 4; ++e) {
-              o[g * 8 + 2 * e] += bf16lo(rw[e]);
-              o[g * 8 + 2 * e + 1] += bf16hi(rw[e]);
-            }
-          }
-        }
-#pragma unroll
-        for (int g = 0; g < 8; ++g) {
-          const float4 b4 = *reinterpret_cast<const float4*>(bias_s + cb * 32 + g * 4);
-          o[4 * g] = fmaf(o[4 * g], p.out_scale, b4.x);
-          o[4 * g + 1] = fmaf(o[4 * g + 1], p.out_scale, b4.y);
-          o[4 * g + 2] = fmaf(o[4 * g + 2], p.out_scale, b4.z);
-          o[4 * g + 3] = fmaf(o[4 * g + 3], p.out_scale, b4.w);
-        }
-        if (!OUT_F32 && has_acc) {
-#pragma unroll
-          for (int g = 0; g < 4; ++g) {
-            const uint32_t yw[4] = {yy[g].x, yy[g].y, yy[g].z, yy[g].w};
-#pragma unroll
-            for (int e = 0; e < 4; ++e) {
-              o[g * 8 + 2 * e] += bf16lo(yw[e]);
-              o[g * 8 + 2 * e + 1] += bf16hi(yw[e]);
-            }
-          }
-        }
-        if (!valid) {
-#pragma unroll
-          for (int i = 0; i < 32; ++i) o[i] = 0.f;
-        }
-        um_stage32<OUT_F32>(my_stg + (uint32_t)(cb * 32 * esz), o);
-#pragma unroll
-        for (int i = 0; i < 4; ++i) {
-          rr[i] = rn[i];
-          yy[i] = yn[i];
+        tmem_ld32_nowait(tcol, v);
+        tmem_ld_wait();
+        tmem_ld_fence(v);
+        um_stage32<OUT_F32>(stg, rl, 0, v, bias_s, scale);
+      } else {
+#pragma unroll 1
+        for (int cb = 0; cb < ncb; cb += 2) {
+          uint32_t v0[32], v1[32];
+          tmem_ld32_nowait(tcol + (uint32_t)(cb * 32), v0);
+          tmem_ld32_nowait(tcol + (uint32_t)(cb * 32 + 32), v1);
+          tmem_ld_wait();
+          tmem_ld_fence(v0);
+          tmem_ld_fence(v1);
+          um_stage32<OUT_F32>(stg, rl, cb, v0, bias_s, scale);
+          um_stage32<OUT_F32>(stg, rl, cb + 1, v1, bias_s, scale);
         }
       }
       if (acc == UM_NACC - 1) {
-        // all TMEM reads of this buffer are complete (tcgen05.wait::ld inside tmem_ld32)
+        // all TMEM reads of this buffer are complete (tcgen05.wait::ld above)
         tc_fence_before();
         mbar_arrive(&misc->t_empty[tb]);
       }
-      // this thread's row: staging (generic proxy) -> bulk store (async proxy)
+      // staging (generic proxy) -> TMA store (async proxy), one store per 128-byte column segment
       fence_proxy_async_smem();
-      if (valid) {
-        uint8_t* yrow = yg + ((int64_t)tl.b * p.y_bstride + (int64_t)row * p.ldy + tl.nt * n_tile) * esz;
-        bulk_s2g(yrow, stg + (size_t)rl * lay.stg_row, (uint32_t)lay.out_row);
+      named_bar_sync(1, UM_EPI_THREADS);
+      const int row0 = tl.t0 + acc * 128;
+      if (et == 0 && row0 < p.Lout) {
+        for (int sgi = 0; sgi < nseg; ++sgi)
+          tma_store_3d(ymap, stg + (uint32_t)sgi * 16384u, tl.nt * n_tile + sgi * seg_cols, row0, tl.b);
+        bulk_commit();
       }
-      bulk_commit();
-      if (p.stats) {
-        named_bar_sync(1, UM_EPI_THREADS);  // every row of the staging tile is written
-        const uint32_t base = smem_u32(stg) + (uint32_t)(grp * ncp) * (uint32_t)lay.stg_row + (uint32_t)cp * 4u;
-#pragma unroll 8
-        for (int r = 0; r < ncp; ++r) {
-          const uint32_t w = lds32(base + (uint32_t)r * (uint32_t)lay.stg_row);
+      if (!OUT_F32 && p.stats) {
+        int r1 = p.Lout - row0;  // valid rows of this accumulator
+        r1 = r1 > (grp + 1) * ncp ? (grp + 1) * ncp : r1;
+#pragma unroll 4
+        for (int r = grp * ncp; r < r1; ++r) {
+          const uint32_t w = lds32(um_stg_addr(stg, r, cp * 4));
           const float a = bf16lo(w), b = bf16hi(w);
           s0 += a; q0 = fmaf(a, a, q0);
           s1 += b; q1 = fmaf(b, b, q1);
         }
       }
     }
-    if (p.stats) {
-      // combine the row groups: sred[grp * n_tile + col]
+    if (!OUT_F32 && p.stats) {
+      // combine the row groups: sred[grp * n_tile + col] (reads of the previous tile's sums finished
+      // before that tile's threads passed the barriers above)
       misc->sred[grp * n_tile + 2 * cp][0] = s0;
       misc->sred[grp * n_tile + 2 * cp][1] = q0;
       misc->sred[grp * n_tile + 2 * cp + 1][0] = s1;
@@ -523,10 +542,11 @@ __device__ __forceinline__ void um_epilogue(const St2ConvParams& p, const UmLayo
       }
     }
   }
-  bulk_wait_all0();
+  if (et == 0) bulk_wait_all0();
 }
 
 __global__ void __launch_bounds__(UM_THREADS, 1) conv_umma_kernel(const St2ConvParams p, const UmLayout lay,
+                                                                   const __grid_constant__ CUtensorMap ymap,
                                                                    int total_tiles, int n_ttiles, int n_ntiles) {
   extern __shared__ __align__(1024) uint8_t smem_raw[];
   UmMisc* misc = reinterpret_cast<UmMisc*>(smem_raw + lay.off_misc);
@@ -534,6 +554,7 @@ __global__ void __launch_bounds__(UM_THREADS, 1) conv_umma_kernel(const St2ConvP
   const int nchunks = p.cin / UM_CK;
 
   if (threadIdx.x == 0) {
+    asm volatile("prefetch.tensormap [%0];" ::"l"(&ymap) : "memory");
     for (int i = 0; i < UM_MAX_A; ++i) {
       mbar_init(&misc->a_full[i], UM_PROD_THREADS);
       mbar_init(&misc->a_empty[i], 1);
@@ -563,7 +584,8 @@ __global__ void __launch_bounds__(UM_THREADS, 1) conv_umma_kernel(const St2ConvP
   if (warp == 0) {
     // ===================================================================== MMA issuer
     if (lane == 0) {
-      const uint32_t a_base = smem_u32(smem_raw), w_base = smem_u32(smem_raw + lay.off_w);
+      const uint32_t a_base = smem_u32(smem_raw + lay.off_a), w_base = smem_u32(smem_raw + lay.off_w);
+      const int nct = nchunks + lay.n_res + lay.n_acc;
       const uint32_t a_lbo = (uint32_t)lay.rpad * 16u, w_lbo = (uint32_t)lay.n_tile * 16u;
       int as = 0, ws = 0;
       uint32_t aph = 0, wph = 0, t_it = 0;
@@ -571,11 +593,14 @@ __global__ void __launch_bounds__(UM_THREADS, 1) conv_umma_kernel(const St2ConvP
         const uint32_t tb = t_it & 1, tph = (t_it >> 1) & 1;
         mbar_wait(&misc->t_empty[tb], tph ^ 1, 1);
         tc_fence_after();
-        for (int c = 0; c < nchunks; ++c) {
+        for (int c = 0; c < nct; ++c) {
           mbar_wait(&misc->a_full[as], aph, 2);
           tc_fence_after();
           const uint32_t a_addr = a_base + (uint32_t)as * (uint32_t)lay.a_bytes;
-          for (int j = 0; j < p.k; ++j) {
+          // residual / y_old chunks: one identity "tap" at row offset 0
+          const int taps = c < nchunks ? p.k : 1;
+          const int dil = c < nchunks ? p.dil : 0;
+          for (int j = 0; j < taps; ++j) {
             mbar_wait(&misc->w_full[ws], wph, 3);
             tc_fence_after();
             const uint32_t w_addr = w_base + (uint32_t)ws * (uint32_t)lay.w_bytes;
@@ -585,7 +610,7 @@ __global__ void __launch_bounds__(UM_THREADS, 1) conv_umma_kernel(const St2ConvP
 #pragma unroll
               for (int ks = 0; ks < UM_CK / 16; ++ks) {
                 const uint64_t ad =
-                    umma_desc(a_addr + (uint32_t)(2 * ks) * a_lbo + (uint32_t)(acc * 128 + j * p.dil) * 16u, a_lbo, 128);
+                    umma_desc(a_addr + (uint32_t)(2 * ks) * a_lbo + (uint32_t)(acc * 128 + j * dil) * 16u, a_lbo, 128);
                 const uint64_t bd = umma_desc(w_addr + (uint32_t)(2 * ks) * w_lbo, w_lbo, 128);
                 umma_bf16(d_tmem, ad, bd, lay.idesc, (c | j | ks) != 0 ? 1u : 0u);
               }
@@ -610,19 +635,24 @@ __global__ void __launch_bounds__(UM_THREADS, 1) conv_umma_kernel(const St2ConvP
       for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
         const UmTile tl = um_tile(tile, n_ttiles, n_ntiles);
         const uint8_t* src = wg + (int64_t)tl.nt * per_nt * lay.w_bytes;
-        for (int s = 0; s < per_nt; ++s) {
+        for (int s = 0; s < per_nt + lay.n_res + lay.n_acc; ++s) {
+          const uint8_t* blob = src + (int64_t)s * lay.w_bytes;
+          if (s >= per_nt) {  // identity blocks that add the residual / y_old rows
+            const int e = s - per_nt;
+            blob = e < lay.n_res ? lay.ident_res + (int64_t)e * lay.w_bytes
+                                 : lay.ident_acc + (int64_t)(e - lay.n_res) * lay.w_bytes;
+          }
           mbar_wait(&misc->w_empty[ws], wph ^ 1u, 4);
           mbar_arrive_expect_tx(&misc->w_full[ws], (uint32_t)lay.w_bytes);
-          bulk_g2s(wsm + (size_t)ws * lay.w_bytes, src + (int64_t)s * lay.w_bytes, (uint32_t)lay.w_bytes,
-                   &misc->w_full[ws]);
+          bulk_g2s(wsm + (size_t)ws * lay.w_bytes, blob, (uint32_t)lay.w_bytes, &misc->w_full[ws]);
           if (++ws == UM_W_STAGES) { ws = 0; wph ^= 1u; }
         }
       }
     }
   } else if (warp < UM_PROD_WARP0) {
     // ======================================================================= epilogue
-    if (p.y_dtype == ST2_DT_F32) um_epilogue<true>(p, lay, smem_raw, misc, tmem_base, warp, lane, total_tiles, n_ttiles, n_ntiles);
-    else um_epilogue<false>(p, lay, smem_raw, misc, tmem_base, warp, lane, total_tiles, n_ttiles, n_ntiles);
+    if (p.y_dtype == ST2_DT_F32) um_epilogue<true>(p, lay, &ymap, smem_raw, misc, tmem_base, warp, lane, total_tiles, n_ttiles, n_ntiles);
+    else um_epilogue<false>(p, lay, &ymap, smem_raw, misc, tmem_base, warp, lane, total_tiles, n_ttiles, n_ntiles);
   } else {
     // ============================================================ activation producers
     const int ptid = threadIdx.x - UM_PROD_WARP0 * 32;
@@ -657,7 +687,52 @@ int umma_n_tile(int n_cols) {
   return 0;
 }
 
-static int um_layout(const St2ConvParams& p, UmLayout& lay) {
+static inline uint16_t f32_to_bf16_rn(float f) {
+  uint32_t u;
+  memcpy(&u, &f, 4);
+  if ((u & 0x7fffffffu) > 0x7f800000u) return (uint16_t)((u >> 16) | 0x40);
+  u += 0x7fffu + ((u >> 16) & 1u);
+  return (uint16_t)(u >> 16);
+}
+static inline float bf16_to_f32(uint16_t h) {
+  uint32_t u = (uint32_t)h << 16;
+  float f;
+  memcpy(&f, &u, 4);
+  return f;
+}
+
+// Identity weight blobs (n_tile/64 of them, one per 64-channel chunk of the residual row):
+// blob h, element (v, n, e) = mult if n == h*64 + v*8 + e else 0.  Built once per (device, n_tile,
+// mult) on first use (never inside a stream capture: the first forward of a handle is eager).
+static std::mutex g_ident_mu;
+static std::map<uint64_t, uint8_t*> g_ident;
+static int um_ident(int dev, int n_tile, float mult, const uint8_t** out) {
+  const uint16_t mb = f32_to_bf16_rn(mult);
+  const uint64_t key = ((uint64_t)dev << 40) | ((uint64_t)n_tile << 16) | mb;
+  std::lock_guard<std::mutex> lk(g_ident_mu);
+  auto it = g_ident.find(key);
+  if (it != g_ident.end()) {
+    *out = it->second;
+    return ST2_OK;
+  }
+  const int nb = n_tile / 64;
+  const size_t blob_elems = (size_t)8 * n_tile * 8;
+  std::vector<uint16_t> h(nb * blob_elems, 0);
+  for (int hh = 0; hh < nb; ++hh)
+    for (int v = 0; v < 8; ++v)
+      for (int e = 0; e < 8; ++e) {
+        const int n = hh * 64 + v * 8 + e;
+        h[hh * blob_elems + ((size_t)v * n_tile + n) * 8 + e] = mb;
+      }
+  uint8_t* d = nullptr;
+  ST2_CUDA_OK(cudaMalloc(&d, h.size() * 2));
+  ST2_CUDA_OK(cudaMemcpy(d, h.data(), h.size() * 2, cudaMemcpyHostToDevice));
+  g_ident[key] = d;
+  *out = d;
+  return ST2_OK;
+}
+
+static int um_layout(const St2ConvParams& p, int dev, UmLayout& lay) {
   lay.n_tile = umma_n_tile(p.n_cols);
   ST2_REQUIRE(lay.n_tile != 0, "conv_umma: n_cols must be a multiple of 32");
   const int halo = (p.k - 1) * p.dil;
@@ -666,8 +741,8 @@ static int um_layout(const St2ConvParams& p, UmLayout& lay) {
   lay.w_bytes = 8 * lay.n_tile * 16;
   const int esz = p.y_dtype == ST2_DT_F32 ? 4 : 2;
   lay.out_row = lay.n_tile * esz;
-  lay.stg_row = lay.out_row + 16;
-  const int stg_bytes = (int)round_up((int64_t)128 * lay.stg_row, 128);
+  ST2_REQUIRE(lay.out_row % 128 == 0, "conv_umma: an output row segment must be a multiple of 128 bytes");
+  const int stg_bytes = (lay.out_row / 128) * 16384;
   const int misc_bytes = (int)round_up((int64_t)sizeof(UmMisc), 128);
   const int fixed = UM_W_STAGES * lay.w_bytes + stg_bytes + misc_bytes;
   int na = (UM_SMEM_LIMIT - fixed) / lay.a_bytes;
@@ -675,11 +750,62 @@ static int um_layout(const St2ConvParams& p, UmLayout& lay) {
   ST2_REQUIRE(na >= 3, "conv_umma: tile does not fit shared memory");
   lay.na = na;
   lay.dist = na - 2;
-  lay.off_w = (uint32_t)(na * lay.a_bytes);
-  lay.off_stg = lay.off_w + (uint32_t)(UM_W_STAGES * lay.w_bytes);
-  lay.off_misc = lay.off_stg + (uint32_t)stg_bytes;
+  lay.off_a = (uint32_t)stg_bytes;
+  lay.off_w = lay.off_a + (uint32_t)(na * lay.a_bytes);
+  lay.off_misc = lay.off_w + (uint32_t)(UM_W_STAGES * lay.w_bytes);
   lay.total = lay.off_misc + (uint32_t)misc_bytes;
   lay.idesc = um_idesc(lay.n_tile);
+  lay.n_res = lay.n_acc = 0;
+  if (p.res) {
+    ST2_REQUIRE(lay.n_tile >= 64, "conv_umma: residual needs a 64- or 128-column tile");
+    lay.n_res = lay.n_tile / 64;
+    int rc = um_ident(dev, lay.n_tile, 1.f, &lay.ident_res);
+    if (rc) return rc;
+  }
+  if (p.accumulate) {
+    ST2_REQUIRE(lay.n_tile >= 64, "conv_umma: accumulate needs a 64- or 128-column tile");
+    const float mult = 1.f / p.out_scale;
+    const float mr = bf16_to_f32(f32_to_bf16_rn(mult));
+    ST2_REQUIRE(fabsf(mr - mult) <= 1e-6f * fabsf(mult),
+                "conv_umma: accumulate needs 1/out_scale representable in bf16 (mean over 1, 2, 3, 4 ... resblocks)");
+    lay.n_acc = lay.n_tile / 64;
+    int rc = um_ident(dev, lay.n_tile, mr, &lay.ident_acc);
+    if (rc) return rc;
+  }
+  return ST2_OK;
+}
+
+// cuTensorMapEncodeTiled through the runtime (no link-time dependency on libcuda)
+typedef CUresult (*UmEncodeTiled)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                  const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
+                                  CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+static UmEncodeTiled g_encode = nullptr;
+static int um_encode_fn() {
+  if (g_encode) return ST2_OK;
+  void* fn = nullptr;
+  cudaDriverEntryPointQueryResult qres;
+  ST2_CUDA_OK(cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &fn, cudaEnableDefault, &qres));
+  ST2_REQUIRE(fn != nullptr && qres == cudaDriverEntryPointSuccess, "cuTensorMapEncodeTiled is not available");
+  g_encode = reinterpret_cast<UmEncodeTiled>(fn);
+  return ST2_OK;
+}
+// output view [B][Lout][n_cols] (row stride ldy, batch stride y_bstride); box = 128 bytes x 128 rows
+static int um_ymap(const St2ConvParams& p, CUtensorMap* map) {
+  int rc = um_encode_fn();
+  if (rc) return rc;
+  const bool f32 = p.y_dtype == ST2_DT_F32;
+  const uint64_t esz = f32 ? 4 : 2;
+  const cuuint64_t gdim[3] = {(cuuint64_t)p.n_cols, (cuuint64_t)p.Lout, (cuuint64_t)p.B};
+  const cuuint64_t gstr[2] = {(cuuint64_t)p.ldy * esz, (cuuint64_t)(p.B > 1 ? p.y_bstride : (int64_t)p.ldy * p.Lout) * esz};
+  const cuuint32_t box[3] = {(cuuint32_t)(128 / esz), 128u, 1u};
+  const cuuint32_t estr[3] = {1u, 1u, 1u};
+  const CUresult r = g_encode(map, f32 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT32 : CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 3, p.y,
+                              gdim, gstr, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
+                              CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) {
+    set_error("conv_umma: cuTensorMapEncodeTiled failed with code " + std::to_string((int)r));
+    return ST2_ECUDA;
+  }
   return ST2_OK;
 }
 
@@ -716,16 +842,19 @@ int launch_conv_umma(const St2ConvParams& p, cudaStream_t st) {
   ST2_REQUIRE(!(p.stats && p.accumulate), "conv_umma: stats with accumulate");
   ST2_REQUIRE(p.act != ST2_ACT_SNAKE || p.alpha, "conv_umma: snake needs alpha");
   ST2_REQUIRE(p.act != ST2_ACT_LRELU || (p.slope >= 0.f && p.slope <= 1.f), "conv_umma: LeakyReLU slope in [0, 1]");
+  int dev = 0;
+  ST2_CUDA_OK(cudaGetDevice(&dev));
   UmLayout lay;
   memset(&lay, 0, sizeof(lay));
-  int rc = um_layout(p, lay);
+  int rc = um_layout(p, dev, lay);
+  if (rc) return rc;
+  CUtensorMap ymap;
+  rc = um_ymap(p, &ymap);
   if (rc) return rc;
   const int n_ttiles = ceil_div(p.Lout, UM_TM), n_ntiles = p.n_cols / lay.n_tile;
   ST2_REQUIRE(!p.stats || p.n_tiles >= n_ttiles, "conv_umma: n_tiles");
   const int64_t total = (int64_t)p.B * n_ttiles * n_ntiles;
   ST2_REQUIRE(total < (1ll << 31), "conv_umma: too many tiles");
-  int dev = 0;
-  ST2_CUDA_OK(cudaGetDevice(&dev));
   if (dev >= 64 || g_num_sms[dev] == 0) {
     int n = 0;
     ST2_CUDA_OK(cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev));
@@ -750,7 +879,7 @@ int launch_conv_umma(const St2ConvParams& p, cudaStream_t st) {
     g_prof.flops += p.algo_flops;
     ST2_CUDA_OK(cudaEventRecord(e0, st));
   }
-  conv_umma_kernel<<<grid, UM_THREADS, lay.total, st>>>(p, lay, (int)total, n_ttiles, n_ntiles);
+  conv_umma_kernel<<<grid, UM_THREADS, lay.total, st>>>(p, lay, ymap, (int)total, n_ttiles, n_ntiles);
   ST2_LAUNCH_OK("conv_umma");
   if (e1) ST2_CUDA_OK(cudaEventRecord(e1, st));
   return ST2_OK;
@@ -787,13 +916,7 @@ extern "C" int64_t st2_umma_packed_elems(int k, int cin_pad, int n) {
   return (int64_t)(n / nt) * (cin_pad / st2::UM_CK) * k * (8 * nt * 8);
 }
 
-static inline uint16_t f32_to_bf16_rn(float f) {
-  uint32_t u;
-  memcpy(&u, &f, 4);
-  if ((u & 0x7fffffffu) > 0x7f800000u) return (uint16_t)((u >> 16) | 0x40);
-  u += 0x7fffu + ((u >> 16) & 1u);
-  return (uint16_t)(u >> 16);
-}
+using st2::f32_to_bf16_rn;
 
 extern "C" int st2_umma_pack_weights(const float* w_kcn, int k, int cin, int cin_pad, int n,
                                      uint16_t* out) {

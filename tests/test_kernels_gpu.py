@@ -132,7 +132,7 @@ def test_conv_umma_bf16(case):
     # B, Lin, cin, n, k, dil, act, out fp32
     (2, 700, 128, 32, 7, 1, _cabi.ACT_LRELU, True),    # conv_post: 128 -> 22 (padded 32), fp32 rows of 128 B
     (1, 1300, 64, 64, 3, 3, _cabi.ACT_SNAKE, False),   # hifigan stage-3 width: one 64-column tile
-    (2, 515, 64, 32, 11, 5, _cabi.ACT_SNAKE, False),   # hifigan stage-4 width, widest halo
+    (2, 515, 64, 64, 11, 5, _cabi.ACT_SNAKE, False),   # 64-column tile, widest halo
     (1, 300, 128, 64, 1, 1, _cabi.ACT_NONE, True),     # fp32 out, 64 columns
     (2, 1000, 64, 192, 3, 1, _cabi.ACT_NONE, False),   # three 64-column tiles
 ])

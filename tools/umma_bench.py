@@ -1,0 +1,94 @@
+"""micro-benchmark of the tcgen05 conv kernel on the stage shapes of config C2 (CUDA events, warm).
+usage: python tools/umma_bench.py [--one k,res,stats] [--iters N]"""
+import ctypes as C
+import math
+import os
+import sys
+
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+import torch
+from styletts2_b200 import _cabi
+from styletts2_b200._cabi import lib, check
+
+
+def make(B, L, cin, n, k, dil, act, with_res, with_stats, accumulate=False, f32out=False):
+    dev = "cuda"
+    g = torch.Generator().manual_seed(1)
+    x = torch.randn(B, L, cin, generator=g).to(torch.bfloat16).to(dev)
+    w = (torch.randn(k, cin, n, generator=g) / math.sqrt(cin * k)).contiguous()
+    elems = lib.st2_umma_packed_elems(k, cin, n)
+    packed = torch.empty(elems, dtype=torch.int16)
+    check(lib.st2_umma_pack_weights(w.data_ptr(), k, cin, cin, n, packed.data_ptr()))
+    wd = packed.to(dev)
+    bias = torch.randn(n, generator=g).to(dev)
+    ss = torch.stack([1 + 0.1 * torch.randn(B, cin, generator=g), 0.1 * torch.randn(B, cin, generator=g)], -1).contiguous().to(dev)
+    alpha = torch.ones(cin, device=dev)
+    y = torch.zeros(B, L, n, device=dev, dtype=torch.float32 if f32out else torch.bfloat16)
+    res = torch.randn(B, L, n, generator=g).to(torch.bfloat16).to(dev) if with_res else None
+    tr = lib.st2_conv_tile_rows(1)
+    nt = (L + tr - 1) // tr
+    stats = torch.zeros(B, nt, n, 2, device=dev) if with_stats else None
+    p = _cabi.St2ConvParams()
+    p.B = B
+    p.x = x.data_ptr(); p.x_dtype = _cabi.DT_BF16; p.x_bstride = L * cin; p.ldx = cin; p.Lin = L; p.cin = cin
+    p.ss = ss.data_ptr(); p.ss_stride = cin; p.act = act; p.slope = 0.1; p.alpha = alpha.data_ptr()
+    p.k, p.dil, p.pad, p.stride = k, dil, dil * (k - 1) // 2, 1
+    p.w = wd.data_ptr(); p.bias = bias.data_ptr(); p.n_cols = n
+    p.y = y.data_ptr(); p.y_dtype = _cabi.DT_F32 if f32out else _cabi.DT_BF16; p.y_bstride = L * n; p.ldy = n; p.Lout = L
+    if res is not None:
+        p.res = res.data_ptr(); p.res_bstride = L * n; p.ldres = n
+    p.out_scale = 1.0
+    p.accumulate = 1 if accumulate else 0
+    if stats is not None:
+        p.stats = stats.data_ptr(); p.n_tiles = nt
+    p.algo_flops = 2.0 * B * L * cin * n * k
+    keep = (x, wd, bias, ss, alpha, y, res, stats)
+    return p, keep
+
+
+def time_it(p, iters):
+    for _ in range(2):
+        check(lib.st2_conv_umma(C.byref(p), None))
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(iters):
+        check(lib.st2_conv_umma(C.byref(p), None))
+    e1.record()
+    torch.cuda.synchronize()
+    return e0.elapsed_time(e1) / iters * 1e3  # us
+
+
+def main():
+    iters = 5
+    if "--iters" in sys.argv:
+        iters = int(sys.argv[sys.argv.index("--iters") + 1])
+    B = 32
+    cases = []
+    if "--one" in sys.argv:
+        k, r, s = sys.argv[sys.argv.index("--one") + 1].split(",")
+        cases = [("one", 48001, 128, 128, int(k), 1, _cabi.ACT_SNAKE, bool(int(r)), bool(int(s)), False, False)]
+    else:
+        for k in (3, 7, 11):
+            cases.append((f"s2 k{k} d1 c1(stats)", 48001, 128, 128, k, 1, _cabi.ACT_SNAKE, False, True, False, False))
+            cases.append((f"s2 k{k} d1 c2(res,stats)", 48001, 128, 128, k, 1, _cabi.ACT_SNAKE, True, True, False, False))
+        cases.append(("s2 k11 d5 c1(stats)", 48001, 128, 128, 11, 5, _cabi.ACT_SNAKE, False, True, False, False))
+        cases.append(("s2 k11 acc(res)", 48001, 128, 128, 11, 1, _cabi.ACT_SNAKE, True, False, True, False))
+        cases.append(("s2 k3 none", 48001, 128, 128, 3, 1, _cabi.ACT_SNAKE, False, False, False, False))
+        cases.append(("s2 k3 lrelu none", 48001, 128, 128, 3, 1, _cabi.ACT_LRELU, False, False, False, False))
+        cases.append(("s1 k3 c1", 8000, 256, 256, 3, 1, _cabi.ACT_SNAKE, False, True, False, False))
+        cases.append(("s1 k7 c2", 8000, 256, 256, 7, 1, _cabi.ACT_SNAKE, True, True, False, False))
+        cases.append(("s1 k11 c2", 8000, 256, 256, 11, 1, _cabi.ACT_SNAKE, True, True, False, False))
+        cases.append(("conv_post k7 n32 f32", 48001, 128, 32, 7, 1, _cabi.ACT_LRELU, False, False, False, True))
+    for name, L, cin, n, k, dil, act, r, s, acc, f32 in cases:
+        p, keep = make(B, L, cin, n, k, dil, act, r, s, acc, f32)
+        us = time_it(p, iters)
+        tf = p.algo_flops / us / 1e6
+        gb = (B * L * cin * 2 + B * L * n * (4 if f32 else 2) * (1 + (1 if r else 0) + (1 if acc else 0))) / 1e9
+        print(f"{name:28s} {us:9.1f} us  {tf:8.1f} TFLOP/s  {gb / (us * 1e-6):8.1f} GB/s (min traffic {gb:.2f} GB)")
+        del keep
+        torch.cuda.empty_cache()
+
+
+if __name__ == "__main__":
+    main()
