@@ -215,6 +215,12 @@ __device__ __forceinline__ void tmem_ld32_nowait(uint32_t taddr, uint32_t (&v)[3
       : "r"(taddr)
       : "memory");
 }
+// one lane of a converged warp (elect.sync)
+__device__ __forceinline__ bool elect_one() {
+  uint32_t pred;
+  asm volatile("{ .reg .pred p; elect.sync _|p, 0xffffffff; selp.u32 %0, 1, 0, p; }" : "=r"(pred));
+  return pred != 0;
+}
 __device__ __forceinline__ void named_bar_sync(int id, int nthreads) {
   asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(nthreads) : "memory");
 }
@@ -323,12 +329,35 @@ __device__ __forceinline__ void um_produce(const St2ConvParams& p, const UmLayou
     }
   };
 
-  auto transform = [&](const UmCur& q) {
+  // raw per-channel parameters of the chunk (scale, shift pairs and alpha), loaded one iteration early
+  auto load_params = [&](const UmCur& q, float2 (&ssr)[8], float (&alr)[8]) {
+    if (q.c >= nchunks || q.tile >= total_tiles) return;
+    const UmTile tl = um_tile(q.tile, n_ttiles, n_ntiles);
+    const int ch0 = q.c * UM_CK + v * 8;
+    if (HAS_SS) {
+      const float4* sp = reinterpret_cast<const float4*>(p.ss + ((int64_t)tl.b * p.ss_stride + ch0) * 2);
+#pragma unroll
+      for (int e = 0; e < 4; ++e) {
+        const float4 t = __ldg(sp + e);
+        ssr[2 * e] = make_float2(t.x, t.y);
+        ssr[2 * e + 1] = make_float2(t.z, t.w);
+      }
+    }
+    if (ACT == ST2_ACT_SNAKE) {
+      const float4* ap = reinterpret_cast<const float4*>(p.alpha + ch0);
+      const float4 t0 = __ldg(ap), t1 = __ldg(ap + 1);
+      alr[0] = t0.x; alr[1] = t0.y; alr[2] = t0.z; alr[3] = t0.w;
+      alr[4] = t1.x; alr[5] = t1.y; alr[6] = t1.z; alr[7] = t1.w;
+    }
+  };
+
+  auto transform = [&](const UmCur& q, const float2 (&ssr)[8], const float (&alr)[8]) {
     const UmTile tl = um_tile(q.tile, n_ttiles, n_ntiles);
     const uint32_t dst = a0 + (uint32_t)q.stage * (uint32_t)lay.a_bytes;
+    // chunk q's LDGSTS group is complete once at most dist-1 newer groups are pending
+    if (lay.dist == 2) cp_async_wait<1>();
+    else cp_async_wait<0>();
     if (q.c >= nchunks) {
-      if (lay.dist == 2) cp_async_wait<2>();
-      else cp_async_wait<1>();
 #pragma unroll
       for (int i = 0; i < UM_TM / 32; ++i) {
         const int r = rbase + 32 * i;
@@ -339,26 +368,21 @@ __device__ __forceinline__ void um_produce(const St2ConvParams& p, const UmLayou
       return;
     }
     const int row0 = tl.t0 - p.pad;
-    const int ch0 = q.c * UM_CK + v * 8;
     float sc[8], sh[8], wsc[8], wsh[8], hia[8];
 #pragma unroll
     for (int e = 0; e < 8; ++e) {
       sc[e] = 1.f; sh[e] = 0.f; wsc[e] = 0.f; wsh[e] = 0.f; hia[e] = 0.f;
       if (HAS_SS) {
-        const float2 t = __ldg(reinterpret_cast<const float2*>(p.ss + ((int64_t)tl.b * p.ss_stride + ch0 + e) * 2));
-        sc[e] = t.x; sh[e] = t.y;
+        sc[e] = ssr[e].x; sh[e] = ssr[e].y;
       }
       if (ACT == ST2_ACT_SNAKE) {
-        const float a = __ldg(p.alpha + ch0 + e);
+        const float a = alr[e];
         hia[e] = __fdividef(0.5f, a);
         wsc[e] = 2.f * a * sc[e];
         wsh[e] = 2.f * a * sh[e];
         sh[e] += hia[e];
       }
     }
-    // chunk q's LDGSTS group is complete once at most `dist` newer groups are pending
-    if (lay.dist == 2) cp_async_wait<2>();
-    else cp_async_wait<1>();
 #pragma unroll
     for (int i = 0; i < UM_NI; ++i) {
       const int r = rbase + 32 * i;
@@ -396,14 +420,23 @@ __device__ __forceinline__ void um_produce(const St2ConvParams& p, const UmLayou
     }
     cp_async_commit();
   }
+  float2 ssr[8];
+  float alr[8];
+#pragma unroll
+  for (int e = 0; e < 8; ++e) {
+    ssr[e] = make_float2(1.f, 0.f);
+    alr[e] = 1.f;
+  }
+  load_params(tc, ssr, alr);
   while (tc.tile < total_tiles) {
+    transform(tc, ssr, alr);
+    um_advance(tc, nct, lay.na);
+    load_params(tc, ssr, alr);  // next chunk's parameters: in flight across the stage wait below
     if (lc.tile < total_tiles) {
       issue_loads(lc);
       um_advance(lc, nct, lay.na);
     }
     cp_async_commit();
-    transform(tc);
-    um_advance(tc, nct, lay.na);
   }
   cp_async_wait<0>();
 }
@@ -583,46 +616,54 @@ __global__ void __launch_bounds__(UM_THREADS, 1) conv_umma_kernel(const St2ConvP
 
   if (warp == 0) {
     // ===================================================================== MMA issuer
-    if (lane == 0) {
-      const uint32_t a_base = smem_u32(smem_raw + lay.off_a), w_base = smem_u32(smem_raw + lay.off_w);
-      const int nct = nchunks + lay.n_res + lay.n_acc;
-      const uint32_t a_lbo = (uint32_t)lay.rpad * 16u, w_lbo = (uint32_t)lay.n_tile * 16u;
-      int as = 0, ws = 0;
-      uint32_t aph = 0, wph = 0, t_it = 0;
-      for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, ++t_it) {
-        const uint32_t tb = t_it & 1, tph = (t_it >> 1) & 1;
-        mbar_wait(&misc->t_empty[tb], tph ^ 1, 1);
+    // The whole warp runs the (warp-uniform) loop and waits on the barriers; one elected lane issues
+    // the MMAs and commits.  Descriptors are built once; per MMA only the 14-bit start-address field
+    // moves: + 2*rpad per 16-channel K step, + 128 rows per accumulator, + dil rows per tap.
+    const uint32_t a_base = smem_u32(smem_raw + lay.off_a), w_base = smem_u32(smem_raw + lay.off_w);
+    const uint32_t a_lbo = (uint32_t)lay.rpad * 16u, w_lbo = (uint32_t)lay.n_tile * 16u;
+    const uint64_t a_desc0 = umma_desc(0, a_lbo, 128), w_desc0 = umma_desc(0, w_lbo, 128);
+    const uint32_t a_kstep = 2u * (uint32_t)lay.rpad, w_kstep = 2u * (uint32_t)lay.n_tile;  // in 16-byte units
+    const int nct = nchunks + lay.n_res + lay.n_acc;
+    const bool leader = elect_one();
+    int as = 0, ws = 0;
+    uint32_t aph = 0, wph = 0, t_it = 0;
+    for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, ++t_it) {
+      const uint32_t tb = t_it & 1, tph = (t_it >> 1) & 1;
+      mbar_wait(&misc->t_empty[tb], tph ^ 1, 1);
+      tc_fence_after();
+      const uint32_t d0 = tmem_base + (uint32_t)(tb * UM_NACC * lay.n_tile);
+      for (int c = 0; c < nct; ++c) {
+        mbar_wait(&misc->a_full[as], aph, 2);
         tc_fence_after();
-        for (int c = 0; c < nct; ++c) {
-          mbar_wait(&misc->a_full[as], aph, 2);
+        const uint32_t a_u = (a_base + (uint32_t)as * (uint32_t)lay.a_bytes) >> 4;
+        // residual / y_old chunks: one identity "tap" at row offset 0
+        const int taps = c < nchunks ? p.k : 1;
+        const uint32_t dil = c < nchunks ? (uint32_t)p.dil : 0u;
+        for (int j = 0; j < taps; ++j) {
+          mbar_wait(&misc->w_full[ws], wph, 3);
           tc_fence_after();
-          const uint32_t a_addr = a_base + (uint32_t)as * (uint32_t)lay.a_bytes;
-          // residual / y_old chunks: one identity "tap" at row offset 0
-          const int taps = c < nchunks ? p.k : 1;
-          const int dil = c < nchunks ? p.dil : 0;
-          for (int j = 0; j < taps; ++j) {
-            mbar_wait(&misc->w_full[ws], wph, 3);
-            tc_fence_after();
-            const uint32_t w_addr = w_base + (uint32_t)ws * (uint32_t)lay.w_bytes;
+          if (leader) {
+            const uint64_t ad = a_desc0 + (uint64_t)(a_u + (uint32_t)j * dil);
+            const uint64_t bd = w_desc0 + (uint64_t)((w_base + (uint32_t)ws * (uint32_t)lay.w_bytes) >> 4);
+            const uint32_t first = (c | j) != 0 ? 1u : 0u;
 #pragma unroll
             for (int acc = 0; acc < UM_NACC; ++acc) {
-              const uint32_t d_tmem = tmem_base + (uint32_t)((tb * UM_NACC + acc) * lay.n_tile);
 #pragma unroll
-              for (int ks = 0; ks < UM_CK / 16; ++ks) {
-                const uint64_t ad =
-                    umma_desc(a_addr + (uint32_t)(2 * ks) * a_lbo + (uint32_t)(acc * 128 + j * dil) * 16u, a_lbo, 128);
-                const uint64_t bd = umma_desc(w_addr + (uint32_t)(2 * ks) * w_lbo, w_lbo, 128);
-                umma_bf16(d_tmem, ad, bd, lay.idesc, (c | j | ks) != 0 ? 1u : 0u);
-              }
+              for (int ks = 0; ks < UM_CK / 16; ++ks)
+                umma_bf16(d0 + (uint32_t)(acc * lay.n_tile), ad + (uint64_t)(acc * 128 + ks * a_kstep),
+                          bd + (uint64_t)(ks * w_kstep), lay.idesc, ks != 0 ? 1u : first);
             }
             umma_commit(&misc->w_empty[ws]);
-            if (++ws == UM_W_STAGES) { ws = 0; wph ^= 1u; }
           }
-          umma_commit(&misc->a_empty[as]);
-          if (++as == lay.na) { as = 0; aph ^= 1u; }
+          __syncwarp();
+          if (++ws == UM_W_STAGES) { ws = 0; wph ^= 1u; }
         }
-        umma_commit(&misc->t_full[tb]);
+        if (leader) umma_commit(&misc->a_empty[as]);
+        __syncwarp();
+        if (++as == lay.na) { as = 0; aph ^= 1u; }
       }
+      if (leader) umma_commit(&misc->t_full[tb]);
+      __syncwarp();
     }
   } else if (warp == 1) {
     // ================================================================ weight producer
