@@ -251,15 +251,25 @@ __device__ __forceinline__ UmTile um_tile(int tile, int n_ttiles, int n_ntiles) 
   return t;
 }
 
-// one producer cursor: which (tile, chunk) an operation is at, and the A stage / phase it maps to
+// one producer cursor: which (tile, chunk) an operation is at, the tile's coordinates, and the A
+// stage / phase the chunk maps to
 struct UmCur {
   int tile, c, stage;
   uint32_t ph;
+  int b, t0, nt;
 };
-__device__ __forceinline__ void um_advance(UmCur& q, int nchunks, int na) {
+__device__ __forceinline__ void um_cur_tile(UmCur& q, int total_tiles, int n_ttiles, int n_ntiles) {
+  if (q.tile < total_tiles) {
+    const UmTile t = um_tile(q.tile, n_ttiles, n_ntiles);
+    q.b = t.b; q.t0 = t.t0; q.nt = t.nt;
+  }
+}
+__device__ __forceinline__ void um_advance(UmCur& q, int nchunks, int na, int total_tiles, int n_ttiles,
+                                           int n_ntiles) {
   if (++q.c == nchunks) {
     q.c = 0;
     q.tile += gridDim.x;
+    um_cur_tile(q, total_tiles, n_ttiles, n_ntiles);
   }
   if (++q.stage == na) {
     q.stage = 0;
@@ -289,22 +299,22 @@ __device__ __forceinline__ void um_produce(const St2ConvParams& p, const UmLayou
   const int r_tot = UM_TM + (p.k - 1) * p.dil;
   const int nct = nchunks + lay.n_res + lay.n_acc;  // chunks per tile incl. residual / y_old rows
   const __nv_bfloat16* xg = reinterpret_cast<const __nv_bfloat16*>(p.x);
-  const uint32_t a0 = smem_u32(smem + lay.off_a) + (uint32_t)v * (uint32_t)(lay.rpad * 16);
+  // this thread's 16-byte slot of row rbase in stage 0; row rbase + 32 i is i * 512 bytes further
+  const uint32_t a0 = smem_u32(smem + lay.off_a) + (uint32_t)v * (uint32_t)(lay.rpad * 16) + (uint32_t)rbase * 16u;
+  const int64_t x_step = (int64_t)32 * p.ldx;
   constexpr bool IDENT = (ACT == ST2_ACT_NONE) && !HAS_SS;
 
   auto issue_loads = [&](const UmCur& q) {
     mbar_wait(&misc->a_empty[q.stage], q.ph ^ 1u, 0);
-    const UmTile tl = um_tile(q.tile, n_ttiles, n_ntiles);
     const uint32_t dst = a0 + (uint32_t)q.stage * (uint32_t)lay.a_bytes;
     if (q.c < nchunks) {
-      const int row0 = tl.t0 - p.pad;
-      const __nv_bfloat16* xb = xg + (int64_t)tl.b * p.x_bstride + (q.c * UM_CK + v * 8);
+      // tile row r holds input row t0 - pad + r; rows outside [0, Lin) stay untouched (zeroed later)
+      const int row0 = q.t0 - p.pad + rbase;
+      const int lo = -row0, hi = min(r_tot - rbase, p.Lin - row0);  // valid: lo <= 32 i < hi
+      const __nv_bfloat16* xb = xg + (int64_t)q.b * p.x_bstride + (int64_t)row0 * p.ldx + (q.c * UM_CK + v * 8);
 #pragma unroll
-      for (int i = 0; i < UM_NI; ++i) {
-        const int r = rbase + 32 * i;
-        const int tin = row0 + r;
-        if (r < r_tot && tin >= 0 && tin < p.Lin) cp_async16(dst + (uint32_t)r * 16u, xb + (int64_t)tin * p.ldx);
-      }
+      for (int i = 0; i < UM_NI; ++i)
+        if (32 * i >= lo && 32 * i < hi) cp_async16(dst + (uint32_t)i * 512u, xb + i * x_step);
     } else {
       // residual rows (row t >> res_shift of res) or y_old rows (row t of y): 64 columns of this N tile
       const int e = q.c - nchunks;
@@ -313,29 +323,26 @@ __device__ __forceinline__ void um_produce(const St2ConvParams& p, const UmLayou
       const __nv_bfloat16* sb;
       int ld, shift;
       if (is_res) {
-        sb = reinterpret_cast<const __nv_bfloat16*>(p.res) + (int64_t)tl.b * p.res_bstride;
+        sb = reinterpret_cast<const __nv_bfloat16*>(p.res) + (int64_t)q.b * p.res_bstride;
         ld = p.ldres; shift = p.res_shift;
       } else {
-        sb = reinterpret_cast<const __nv_bfloat16*>(p.y) + (int64_t)tl.b * p.y_bstride;
+        sb = reinterpret_cast<const __nv_bfloat16*>(p.y) + (int64_t)q.b * p.y_bstride;
         ld = p.ldy; shift = 0;
       }
-      sb += tl.nt * lay.n_tile + hh * UM_CK + v * 8;
+      sb += q.nt * lay.n_tile + hh * UM_CK + v * 8;
+      const int t = q.t0 + rbase;
 #pragma unroll
-      for (int i = 0; i < UM_TM / 32; ++i) {
-        const int r = rbase + 32 * i;
-        const int t = tl.t0 + r;
-        if (t < p.Lout) cp_async16(dst + (uint32_t)r * 16u, sb + (int64_t)(t >> shift) * ld);
-      }
+      for (int i = 0; i < UM_TM / 32; ++i)
+        if (t + 32 * i < p.Lout) cp_async16(dst + (uint32_t)i * 512u, sb + (int64_t)((t + 32 * i) >> shift) * ld);
     }
   };
 
   // raw per-channel parameters of the chunk (scale, shift pairs and alpha), loaded one iteration early
   auto load_params = [&](const UmCur& q, float2 (&ssr)[8], float (&alr)[8]) {
     if (q.c >= nchunks || q.tile >= total_tiles) return;
-    const UmTile tl = um_tile(q.tile, n_ttiles, n_ntiles);
     const int ch0 = q.c * UM_CK + v * 8;
     if (HAS_SS) {
-      const float4* sp = reinterpret_cast<const float4*>(p.ss + ((int64_t)tl.b * p.ss_stride + ch0) * 2);
+      const float4* sp = reinterpret_cast<const float4*>(p.ss + ((int64_t)q.b * p.ss_stride + ch0) * 2);
 #pragma unroll
       for (int e = 0; e < 4; ++e) {
         const float4 t = __ldg(sp + e);
@@ -352,22 +359,21 @@ __device__ __forceinline__ void um_produce(const St2ConvParams& p, const UmLayou
   };
 
   auto transform = [&](const UmCur& q, const float2 (&ssr)[8], const float (&alr)[8]) {
-    const UmTile tl = um_tile(q.tile, n_ttiles, n_ntiles);
     const uint32_t dst = a0 + (uint32_t)q.stage * (uint32_t)lay.a_bytes;
     // chunk q's LDGSTS group is complete once at most dist-1 newer groups are pending
     if (lay.dist == 2) cp_async_wait<1>();
     else cp_async_wait<0>();
     if (q.c >= nchunks) {
+      const int t = q.t0 + rbase;
 #pragma unroll
-      for (int i = 0; i < UM_TM / 32; ++i) {
-        const int r = rbase + 32 * i;
-        if (tl.t0 + r >= p.Lout) sts128(dst + (uint32_t)r * 16u, make_uint4(0u, 0u, 0u, 0u));
-      }
+      for (int i = 0; i < UM_TM / 32; ++i)
+        if (t + 32 * i >= p.Lout) sts128(dst + (uint32_t)i * 512u, make_uint4(0u, 0u, 0u, 0u));
       fence_proxy_async_smem();
       mbar_arrive(&misc->a_full[q.stage]);
       return;
     }
-    const int row0 = tl.t0 - p.pad;
+    const int row0 = q.t0 - p.pad + rbase;
+    const int lo = -row0, hi = min(r_tot - rbase, p.Lin - row0), tot = r_tot - rbase;
     float sc[8], sh[8], wsc[8], wsh[8], hia[8];
 #pragma unroll
     for (int e = 0; e < 8; ++e) {
@@ -385,22 +391,20 @@ __device__ __forceinline__ void um_produce(const St2ConvParams& p, const UmLayou
     }
 #pragma unroll
     for (int i = 0; i < UM_NI; ++i) {
-      const int r = rbase + 32 * i;
-      if (r >= r_tot) continue;
-      const int tin = row0 + r;
-      const uint32_t addr = dst + (uint32_t)r * 16u;
-      if (tin >= 0 && tin < p.Lin) {
+      if (32 * i >= tot) continue;
+      const uint32_t addr = dst + (uint32_t)i * 512u;
+      if (32 * i >= lo && 32 * i < hi) {
         if (!IDENT) {
           const uint4 raw = lds128(addr);
           const uint32_t w[4] = {raw.x, raw.y, raw.z, raw.w};
           uint32_t o[4];
 #pragma unroll
           for (int e2 = 0; e2 < 4; ++e2) {
-            const float lo = um_act<ACT>(bf16lo(w[e2]), sc[2 * e2], sh[2 * e2], wsc[2 * e2], wsh[2 * e2],
-                                         hia[2 * e2], p.slope);
-            const float hi = um_act<ACT>(bf16hi(w[e2]), sc[2 * e2 + 1], sh[2 * e2 + 1], wsc[2 * e2 + 1],
-                                         wsh[2 * e2 + 1], hia[2 * e2 + 1], p.slope);
-            o[e2] = pack_bf16x2(lo, hi);
+            const float lo_ = um_act<ACT>(bf16lo(w[e2]), sc[2 * e2], sh[2 * e2], wsc[2 * e2], wsh[2 * e2],
+                                          hia[2 * e2], p.slope);
+            const float hi_ = um_act<ACT>(bf16hi(w[e2]), sc[2 * e2 + 1], sh[2 * e2 + 1], wsc[2 * e2 + 1],
+                                          wsh[2 * e2 + 1], hia[2 * e2 + 1], p.slope);
+            o[e2] = pack_bf16x2(lo_, hi_);
           }
           sts128(addr, make_uint4(o[0], o[1], o[2], o[3]));
         }
@@ -412,11 +416,13 @@ __device__ __forceinline__ void um_produce(const St2ConvParams& p, const UmLayou
     mbar_arrive(&misc->a_full[q.stage]);
   };
 
-  UmCur lc{(int)blockIdx.x, 0, 0, 0u}, tc{(int)blockIdx.x, 0, 0, 0u};
+  UmCur lc{(int)blockIdx.x, 0, 0, 0u, 0, 0, 0};
+  um_cur_tile(lc, total_tiles, n_ttiles, n_ntiles);
+  UmCur tc = lc;
   for (int d = 0; d < lay.dist; ++d) {
     if (lc.tile < total_tiles) {
       issue_loads(lc);
-      um_advance(lc, nct, lay.na);
+      um_advance(lc, nct, lay.na, total_tiles, n_ttiles, n_ntiles);
     }
     cp_async_commit();
   }
@@ -430,11 +436,11 @@ __device__ __forceinline__ void um_produce(const St2ConvParams& p, const UmLayou
   load_params(tc, ssr, alr);
   while (tc.tile < total_tiles) {
     transform(tc, ssr, alr);
-    um_advance(tc, nct, lay.na);
+    um_advance(tc, nct, lay.na, total_tiles, n_ttiles, n_ntiles);
     load_params(tc, ssr, alr);  // next chunk's parameters: in flight across the stage wait below
     if (lc.tile < total_tiles) {
       issue_loads(lc);
-      um_advance(lc, nct, lay.na);
+      um_advance(lc, nct, lay.na, total_tiles, n_ttiles, n_ntiles);
     }
     cp_async_commit();
   }
@@ -450,9 +456,10 @@ __device__ __forceinline__ uint32_t um_stg_addr(uint32_t stg, int row, int byte_
          (uint32_t)(byte_in_row & 15);
 }
 
-// scale / bias one 32-column block of this thread's row and write it to the staging tile
+// scale / bias one 32-column block of this thread's row and write it to the staging tile.
+// chunk_addr[j] = address of 16-byte chunk j of this row in column segment 0 (swizzle applied).
 template <bool OUT_F32>
-__device__ __forceinline__ void um_stage32(uint32_t stg, int row, int cb, const uint32_t (&v)[32],
+__device__ __forceinline__ void um_stage32(const uint32_t (&chunk_addr)[8], int cb, const uint32_t (&v)[32],
                                            const float* bias_s, float scale) {
   float o[32];
 #pragma unroll
@@ -463,16 +470,19 @@ __device__ __forceinline__ void um_stage32(uint32_t stg, int row, int cb, const 
     o[4 * g + 2] = fmaf(__uint_as_float(v[4 * g + 2]), scale, b4.z);
     o[4 * g + 3] = fmaf(__uint_as_float(v[4 * g + 3]), scale, b4.w);
   }
-  if (OUT_F32) {
+  if (OUT_F32) {  // 32 columns = one 128-byte segment
+    const uint32_t seg = (uint32_t)cb * 16384u;
 #pragma unroll
     for (int g = 0; g < 8; ++g)
-      sts128(um_stg_addr(stg, row, cb * 128 + g * 16),
+      sts128(chunk_addr[g] + seg,
              make_uint4(__float_as_uint(o[4 * g]), __float_as_uint(o[4 * g + 1]), __float_as_uint(o[4 * g + 2]),
                         __float_as_uint(o[4 * g + 3])));
-  } else {
+  } else {        // 32 columns = half a segment
+    const uint32_t seg = (uint32_t)(cb >> 1) * 16384u;
+    const int half = (cb & 1) * 4;
 #pragma unroll
     for (int g = 0; g < 4; ++g)
-      sts128(um_stg_addr(stg, row, cb * 64 + g * 16),
+      sts128((half ? chunk_addr[4 + g] : chunk_addr[g]) + seg,
              make_uint4(pack_bf16x2(o[8 * g], o[8 * g + 1]), pack_bf16x2(o[8 * g + 2], o[8 * g + 3]),
                         pack_bf16x2(o[8 * g + 4], o[8 * g + 5]), pack_bf16x2(o[8 * g + 6], o[8 * g + 7])));
   }
@@ -493,6 +503,13 @@ __device__ __forceinline__ void um_epilogue(const St2ConvParams& p, const UmLayo
   const int ncp = n_tile >> 1;
   const int cp = et % ncp, grp = et / ncp;
   const float scale = p.out_scale;
+  uint32_t chunk_addr[8];   // this row's 16-byte chunks in segment 0
+  uint32_t col_addr[8];     // statistics pass: (row grp*ncp + i, column pair cp), i = 0..7
+#pragma unroll
+  for (int j = 0; j < 8; ++j) {
+    chunk_addr[j] = um_stg_addr(stg, rl, j * 16);
+    col_addr[j] = um_stg_addr(stg, grp * ncp + j, cp * 4);
+  }
   uint32_t t_it = 0;
   for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, ++t_it) {
     const UmTile tl = um_tile(tile, n_ttiles, n_ntiles);
@@ -514,7 +531,7 @@ __device__ __forceinline__ void um_epilogue(const St2ConvParams& p, const UmLayo
         tmem_ld32_nowait(tcol, v);
         tmem_ld_wait();
         tmem_ld_fence(v);
-        um_stage32<OUT_F32>(stg, rl, 0, v, bias_s, scale);
+        um_stage32<OUT_F32>(chunk_addr, 0, v, bias_s, scale);
       } else {
 #pragma unroll 1
         for (int cb = 0; cb < ncb; cb += 2) {
@@ -524,8 +541,8 @@ __device__ __forceinline__ void um_epilogue(const St2ConvParams& p, const UmLayo
           tmem_ld_wait();
           tmem_ld_fence(v0);
           tmem_ld_fence(v1);
-          um_stage32<OUT_F32>(stg, rl, cb, v0, bias_s, scale);
-          um_stage32<OUT_F32>(stg, rl, cb + 1, v1, bias_s, scale);
+          um_stage32<OUT_F32>(chunk_addr, cb, v0, bias_s, scale);
+          um_stage32<OUT_F32>(chunk_addr, cb + 1, v1, bias_s, scale);
         }
       }
       if (acc == UM_NACC - 1) {
@@ -543,14 +560,26 @@ __device__ __forceinline__ void um_epilogue(const St2ConvParams& p, const UmLayo
         bulk_commit();
       }
       if (!OUT_F32 && p.stats) {
-        int r1 = p.Lout - row0;  // valid rows of this accumulator
-        r1 = r1 > (grp + 1) * ncp ? (grp + 1) * ncp : r1;
-#pragma unroll 4
-        for (int r = grp * ncp; r < r1; ++r) {
-          const uint32_t w = lds32(um_stg_addr(stg, r, cp * 4));
-          const float a = bf16lo(w), b = bf16hi(w);
-          s0 += a; q0 = fmaf(a, a, q0);
-          s1 += b; q1 = fmaf(b, b, q1);
+        const int r1 = p.Lout - row0 - grp * ncp;  // valid rows of this thread's row group
+        if (r1 >= ncp) {
+          // rows grp*ncp + 8 m + i sit 1024 m bytes after col_addr[i] (the swizzle repeats every 8 rows)
+#pragma unroll 1
+          for (int m = 0; m < ncp; m += 8) {
+#pragma unroll
+            for (int i = 0; i < 8; ++i) {
+              const uint32_t w = lds32(col_addr[i] + (uint32_t)m * 128u);
+              const float a = bf16lo(w), b = bf16hi(w);
+              s0 += a; q0 = fmaf(a, a, q0);
+              s1 += b; q1 = fmaf(b, b, q1);
+            }
+          }
+        } else {
+          for (int r = 0; r < r1; ++r) {
+            const uint32_t w = lds32(col_addr[r & 7] + (uint32_t)(r >> 3) * 1024u);
+            const float a = bf16lo(w), b = bf16hi(w);
+            s0 += a; q0 = fmaf(a, a, q0);
+            s1 += b; q1 = fmaf(b, b, q1);
+          }
         }
       }
     }
