@@ -127,6 +127,9 @@ int launch_har_source(const float* f0, const float* phase, const float* noise, u
                       const float* lin_w9, float lin_b, int B, int T, int spf, float* out,
                       cudaStream_t st);
 int launch_stft(const float* hs, int B, int Lw, float* har_cl, int ld, cudaStream_t st);
+int launch_stft_hilo(const float* hs, int B, int Lw, int rows_pad, __nv_bfloat16* har, cudaStream_t st);
+int launch_ncl_to_hilo(const float* ncl, int C, int L, int rows_pad, __nv_bfloat16* har, int B, cudaStream_t st);
+int launch_hilo_to_ncl(const __nv_bfloat16* har, int rows_pad, int C, int L, float* ncl, int B, cudaStream_t st);
 int launch_istft(const float* x_cl, int ld, int B, int frames, float* wav, cudaStream_t st);
 int launch_tanh_inplace(float* x, int64_t n, cudaStream_t st);
 

@@ -76,6 +76,8 @@ struct St2Decoder {
   float lin_b = 0.f;
   std::vector<st2::UpW> ups;
   std::vector<st2::ConvW> noise_convs;
+  std::vector<st2::ConvW> noise_convs16;  // istftnet, bf16 path: grouped (hi, lo) form for tcgen05
+  std::vector<int> noise_group;           // har rows per wide row of noise_convs16[i] (stride of noise_convs[i])
   std::vector<st2::ResBlock1W> noise_res, resblocks;
   std::vector<int64_t> alphas;  // hifigan generator.alphas
   st2::ConvW conv_post;
@@ -303,6 +305,46 @@ struct Loader {
     u.row0_tap = blob.add(tap.data(), (int64_t)tap.size() * 4);
     return true;
   }
+  // Strided noise conv Conv1d(src_ch, C, k = 2*sf, stride sf, padding (sf+1)/2) over the bf16 (hi, lo)
+  // rows of `har` (64 columns per row, source.cu stft_hilo_kernel), regrouped so that the tensor
+  // core can run it with stride 1: sf consecutive har rows form one wide row of sf*64 channels and
+  //   y[q] = sum_{j<3} sum_{r<sf} W'[j][r*64 + c] har[sf*(q+j-1) + r][c],  tap = sf*(j-1) + r + pad
+  // (zero weight when the tap falls outside [0, k)); the lo half repeats the hi weights.
+  // sf == 1 is the plain 1x1 conv of the last stage.
+  bool noise_conv16(ConvW& c, const std::string& p, int sf, int src_ch) {
+    const St2Tensor* t = get(p + ".weight");
+    const St2Tensor* bt = get(p + ".bias");
+    if (!t || !bt) return false;
+    const int cout = (int)t->shape[0], K = (int)t->shape[2];
+    if ((int)t->shape[1] != src_ch || src_ch > 32) return false;
+    const int pd = sf > 1 ? (sf + 1) / 2 : 0;
+    c.k = sf > 1 ? 3 : 1; c.dil = 1; c.pad = sf > 1 ? 1 : 0; c.stride = 1;
+    c.cin = sf * 64; c.n = cout; c.cstat = cout;
+    c.flops_per_row = 2.0 * (double)cout * (double)src_ch * (double)K;
+    std::vector<float> kcn((size_t)c.k * c.cin * cout, 0.f);
+    for (int j = 0; j < c.k; ++j)
+      for (int r = 0; r < sf; ++r) {
+        const int tap = sf > 1 ? sf * (j - 1) + r + pd : 0;
+        if (tap < 0 || tap >= K) continue;
+        for (int ch = 0; ch < src_ch; ++ch)
+          for (int co = 0; co < cout; ++co) {
+            const float w = t->data[((size_t)co * src_ch + ch) * K + tap];
+            kcn[((size_t)j * c.cin + r * 64 + ch) * cout + co] = w;
+            kcn[((size_t)j * c.cin + r * 64 + 32 + ch) * cout + co] = w;
+          }
+      }
+    std::vector<float> b(bt->data, bt->data + cout);
+    // only the UMMA blob is kept (w32 stays -1: this record is never run on the fp32 path)
+    c.bias = blob.add(b.data(), (int64_t)b.size() * 4);
+    c.bias16 = c.bias;
+    c.cin_pad = c.cin; c.n16 = cout;
+    if (umma_n_tile(cout) == 0) return false;
+    const int64_t elems = st2_umma_packed_elems(c.k, c.cin_pad, c.n16);
+    c.w16 = blob.add(nullptr, elems * 2);
+    st2_umma_pack_weights(kcn.data(), c.k, c.cin, c.cin_pad, c.n16,
+                          reinterpret_cast<uint16_t*>(blob.data.data() + c.w16));
+    return true;
+  }
   bool norm(NormW& n, const std::string& p, int C) {
     const St2Tensor* w = get(p + ".fc.weight");
     const St2Tensor* b = get(p + ".fc.bias");
@@ -403,6 +445,8 @@ static int do_load(St2Decoder* h, const St2Tensor* tensors, int n) {
   const int c0 = c.upsample_initial_channel;
   h->ups.assign(c.n_ups, UpW());
   h->noise_convs.assign(c.n_ups, ConvW());
+  h->noise_convs16.assign(c.n_ups, ConvW());
+  h->noise_group.assign(c.n_ups, 1);
   h->noise_res.assign(c.n_ups, ResBlock1W());
   h->resblocks.assign(c.n_ups * c.n_resblock_kernels, ResBlock1W());
   const int d135[3] = {1, 3, 5};
@@ -419,6 +463,13 @@ static int do_load(St2Decoder* h, const St2Tensor* tensors, int n) {
       rk = 7;
     } else if (ok) {
       ok = L.conv1d(h->noise_convs[i], g + ".noise_convs." + si, false, true, 1, 1, 0, 1, false);
+    }
+    if (ok && istft) {
+      const int sf = i + 1 < c.n_ups ? prod_from(c.upsample_rates, i + 1, c.n_ups) : 1;
+      h->noise_group[i] = sf;
+      // best effort: a layer the grouped form cannot express keeps the fp32-input FFMA kernel
+      if (!L.noise_conv16(h->noise_convs16[i], g + ".noise_convs." + si, sf, c.gen_istft_n_fft + 2))
+        h->noise_convs16[i] = ConvW();
     }
     ok = ok && L.resblock1(h->noise_res[i], g + ".noise_res." + si, cout, rk, d135);
     for (int j = 0; j < c.n_resblock_kernels && ok; ++j)
@@ -740,10 +791,25 @@ int Fwd<AT>::run(const float* asr, const float* f0, const float* nn, const float
   const int L2 = istft ? (int)(Lw / hop) + 1 : 0;
   const int ldh = 32;
   const float* hs = o.har_source;
+  // bf16 path: `har` is kept as bf16 (hi, lo) rows and the noise convs run on the tensor cores
+  bool hilo = istft && DT<AT>::id == ST2_DT_BF16;
+  int rows_pad = L2;
+  if (hilo) {
+    int len = T;
+    for (int i = 0; i < c.n_ups; ++i) {
+      len = len * c.upsample_rates[i] + (i == c.n_ups - 1 ? 1 : 0);
+      hilo = hilo && h->noise_convs16[i].w16 >= 0;
+      const int need = h->noise_group[i] > 1 ? h->noise_group[i] * (len + 1) : len;
+      if (need > rows_pad) rows_pad = need;
+    }
+  }
   float* har = nullptr;
-  if (istft) har = ar.alloc<float>((int64_t)B * L2 * ldh);
+  __nv_bfloat16* har16 = nullptr;
+  if (istft && hilo) har16 = ar.alloc<__nv_bfloat16>((int64_t)B * rows_pad * 64);
+  else if (istft) har = ar.alloc<float>((int64_t)B * L2 * ldh);
   if (istft && o.har) {
-    RUN(launch_ncl_to_cl(o.har, n_fft + 2, L2, har, ldh, B, st));
+    if (hilo) RUN(launch_ncl_to_hilo(o.har, n_fft + 2, L2, rows_pad, har16, B, st));
+    else RUN(launch_ncl_to_cl(o.har, n_fft + 2, L2, har, ldh, B, st));
   } else {
     if (!hs) {
       float* ph = ar.alloc<float>((int64_t)B * 9 * T);
@@ -752,11 +818,15 @@ int Fwd<AT>::run(const float* asr, const float* f0, const float* nn, const float
       RUN(launch_har_source(f0, ph, o.noise, o.seed, W<float>(h->lin_w), h->lin_b, B, T, spf, hsw, st));
       hs = hsw;
     }
-    if (istft) RUN(launch_stft(hs, B, (int)Lw, har, ldh, st));
+    if (istft && hilo) RUN(launch_stft_hilo(hs, B, (int)Lw, rows_pad, har16, st));
+    else if (istft) RUN(launch_stft(hs, B, (int)Lw, har, ldh, st));
   }
   if (o.har_source_out && hs)
     RUN(cudaMemcpyAsync(o.har_source_out, hs, (size_t)B * Lw * 4, cudaMemcpyDeviceToDevice, st) == cudaSuccess ? ST2_OK : ST2_ECUDA);
-  if (o.har_out && istft) RUN(launch_cl_to_ncl(har, ldh, n_fft + 2, L2, o.har_out, B, st));
+  if (o.har_out && istft) {
+    if (hilo) RUN(launch_hilo_to_ncl(har16, rows_pad, n_fft + 2, L2, o.har_out, B, st));
+    else RUN(launch_cl_to_ncl(har, ldh, n_fft + 2, L2, o.har_out, B, st));
+  }
 
   // ---- generator stages (istftnet.py:358-374 / hifigan.py:327-341)
   Act<AT> x = xg;
@@ -771,11 +841,17 @@ int Fwd<AT>::run(const float* asr, const float* f0, const float* nn, const float
             outb = new_act(Ls, C);
     // x_source = noise_res[i](noise_convs[i](har | har_source))
     {
-      const ConvW& nc = h->noise_convs[i];
+      const ConvW& nc = hilo ? h->noise_convs16[i] : h->noise_convs[i];
       ConvIO io;
-      if (istft) { io.x = har; io.x_bstride = (int64_t)L2 * ldh; io.ldx = ldh; io.Lin = L2; }
-      else { io.x = hs; io.x_bstride = Lw; io.ldx = 1; io.Lin = (int)Lw; }
-      io.x_dtype = ST2_DT_F32;
+      if (hilo) {  // sf har rows = one wide row of sf * 64 channels
+        const int sf = h->noise_group[i];
+        io.x = har16; io.x_dtype = ST2_DT_BF16; io.x_bstride = (int64_t)rows_pad * 64; io.ldx = sf * 64;
+        io.Lin = sf > 1 ? Ls + 1 : L2;
+      } else if (istft) {
+        io.x = har; io.x_dtype = ST2_DT_F32; io.x_bstride = (int64_t)L2 * ldh; io.ldx = ldh; io.Lin = L2;
+      } else {
+        io.x = hs; io.x_dtype = ST2_DT_F32; io.x_bstride = Lw; io.ldx = 1; io.Lin = (int)Lw;
+      }
       io.y = xs.p; io.y_dtype = DT<AT>::id; io.y_bstride = xs.bstride; io.ldy = xs.ld; io.Lout = Ls;
       io.want_stats = true;
       const int64_t m = ar.mark();

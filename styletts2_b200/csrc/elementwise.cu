@@ -354,6 +354,42 @@ int launch_ncl_to_cl(const float* ncl, int C, int L, float* cl, int ld, int B, c
   return ST2_OK;
 }
 
+// injected / exported `har` <-> the bf16 (hi, lo) row layout of stft_hilo_kernel
+__global__ void ncl_to_hilo_kernel(const float* __restrict__ ncl, int C, int L, int rows_pad,
+                                   __nv_bfloat16* __restrict__ har) {
+  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;  // over rows_pad * 32 of item b
+  const int b = blockIdx.y;
+  if (i >= (int64_t)rows_pad * 32) return;
+  const int t = (int)(i >> 5), c = (int)(i & 31);
+  const float v = (c < C && t < L) ? ncl[((int64_t)b * C + c) * L + t] : 0.f;
+  const __nv_bfloat16 h = __float2bfloat16_rn(v);
+  __nv_bfloat16* row = har + ((int64_t)b * rows_pad + t) * 64;
+  row[c] = h;
+  row[32 + c] = __float2bfloat16_rn(v - __bfloat162float(h));
+}
+__global__ void hilo_to_ncl_kernel(const __nv_bfloat16* __restrict__ har, int rows_pad, int C, int L,
+                                   float* __restrict__ ncl) {
+  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;  // over C*L of item b
+  const int b = blockIdx.y;
+  if (i >= (int64_t)C * L) return;
+  const int c = (int)(i / L), t = (int)(i - (int64_t)c * L);
+  const __nv_bfloat16* row = har + ((int64_t)b * rows_pad + t) * 64;
+  ncl[(int64_t)b * C * L + i] = __bfloat162float(row[c]) + __bfloat162float(row[32 + c]);
+}
+int launch_ncl_to_hilo(const float* ncl, int C, int L, int rows_pad, __nv_bfloat16* har, int B, cudaStream_t st) {
+  ST2_REQUIRE(C <= 32 && rows_pad >= L, "ncl_to_hilo: shape");
+  dim3 grid((unsigned)(((int64_t)rows_pad * 32 + 255) / 256), B);
+  ncl_to_hilo_kernel<<<grid, 256, 0, st>>>(ncl, C, L, rows_pad, har);
+  ST2_LAUNCH_OK("ncl_to_hilo");
+  return ST2_OK;
+}
+int launch_hilo_to_ncl(const __nv_bfloat16* har, int rows_pad, int C, int L, float* ncl, int B, cudaStream_t st) {
+  dim3 grid((unsigned)(((int64_t)C * L + 255) / 256), B);
+  hilo_to_ncl_kernel<<<grid, 256, 0, st>>>(har, rows_pad, C, L, ncl);
+  ST2_LAUNCH_OK("hilo_to_ncl");
+  return ST2_OK;
+}
+
 // debug / parity taps: channels-last activation (fp32 or bf16) -> fp32 NCL
 template <typename T>
 __global__ void act_to_ncl_kernel(const T* __restrict__ cl, int64_t bstride, int ld, int C, int L,

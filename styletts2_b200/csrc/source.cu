@@ -219,6 +219,74 @@ stft_kernel(const float* __restrict__ hs, int Lw, int frames, float* __restrict_
   for (int c = 22; c < ld; ++c) o[c] = 0.f;
 }
 
+// Same transform written as bf16 (hi, lo) pairs for the tcgen05 noise convs: row = 64 bf16 =
+// [hi(22) | 0(10) | lo(22) | 0(10)] with hi = bf16(v), lo = bf16(v - hi), so hi + lo carries 16
+// mantissa bits of v.  Rows [frames, rows_pad) are zero (the strided noise conv reads whole groups
+// of rows as one wide row).
+__global__ void __launch_bounds__(128)
+stft_hilo_kernel(const float* __restrict__ hs, int Lw, int frames, int rows_pad,
+                 __nv_bfloat16* __restrict__ har) {
+  const int b = blockIdx.y;
+  const int f = blockIdx.x * blockDim.x + threadIdx.x;
+  if (f >= rows_pad) return;
+  uint4* o4 = reinterpret_cast<uint4*>(har + ((int64_t)b * rows_pad + f) * 64);
+  if (f >= frames) {
+#pragma unroll
+    for (int i = 0; i < 8; ++i) o4[i] = make_uint4(0u, 0u, 0u, 0u);
+    return;
+  }
+  const float* x = hs + (int64_t)b * Lw;
+  float xw[20];
+#pragma unroll
+  for (int n = 0; n < 20; ++n) {
+    int idx = 5 * f + n - 10;
+    if (idx < 0) idx = -idx;
+    if (idx >= Lw) idx = 2 * (Lw - 1) - idx;
+    xw[n] = x[idx] * c_hann20[n];
+  }
+  float val[32];
+#pragma unroll
+  for (int c = 22; c < 32; ++c) val[c] = 0.f;
+#pragma unroll
+  for (int k = 0; k <= 10; ++k) {
+    float re = 0.f, im = 0.f;
+#pragma unroll
+    for (int n = 0; n < 20; ++n) {
+      const int m = (k * n) % 20;
+      re = fmaf(xw[n], c_cos20[m], re);
+      im = fmaf(xw[n], -c_sin20[m], im);
+    }
+    if (k == 0 || k == 10) im = 0.f;
+    val[k] = sqrtf(re * re + im * im);
+    val[11 + k] = atan2f(im, re);
+  }
+  uint32_t hi[16], lo[16];
+#pragma unroll
+  for (int i = 0; i < 16; ++i) {
+    const __nv_bfloat16 h0 = __float2bfloat16_rn(val[2 * i]), h1 = __float2bfloat16_rn(val[2 * i + 1]);
+    const __nv_bfloat16 l0 = __float2bfloat16_rn(val[2 * i] - __bfloat162float(h0));
+    const __nv_bfloat16 l1 = __float2bfloat16_rn(val[2 * i + 1] - __bfloat162float(h1));
+    hi[i] = (uint32_t)__bfloat16_as_ushort(h0) | ((uint32_t)__bfloat16_as_ushort(h1) << 16);
+    lo[i] = (uint32_t)__bfloat16_as_ushort(l0) | ((uint32_t)__bfloat16_as_ushort(l1) << 16);
+  }
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    o4[i] = make_uint4(hi[4 * i], hi[4 * i + 1], hi[4 * i + 2], hi[4 * i + 3]);
+    o4[4 + i] = make_uint4(lo[4 * i], lo[4 * i + 1], lo[4 * i + 2], lo[4 * i + 3]);
+  }
+}
+
+int launch_stft_hilo(const float* hs, int B, int Lw, int rows_pad, __nv_bfloat16* har, cudaStream_t st) {
+  int rc = ensure_tables();
+  if (rc) return rc;
+  const int frames = Lw / 5 + 1;
+  ST2_REQUIRE(Lw % 5 == 0 && Lw >= 20 && rows_pad >= frames, "stft_hilo: shape");
+  dim3 grid(ceil_div(rows_pad, 128), B);
+  stft_hilo_kernel<<<grid, 128, 0, st>>>(hs, Lw, frames, rows_pad, har);
+  ST2_LAUNCH_OK("stft_hilo");
+  return ST2_OK;
+}
+
 int launch_stft(const float* hs, int B, int Lw, float* har_cl, int ld, cudaStream_t st) {
   int rc = ensure_tables();
   if (rc) return rc;
