@@ -55,7 +55,7 @@ class St2ConvParams(C.Structure):
         ("Lout", C.c_int),
         ("res", C.c_void_p), ("res_bstride", C.c_int64), ("ldres", C.c_int), ("res_shift", C.c_int),
         ("out_scale", C.c_float), ("accumulate", C.c_int),
-        ("stats", C.c_void_p), ("n_tiles", C.c_int), ("algo_flops", C.c_double),
+        ("stats", C.c_void_p), ("n_tiles", C.c_int), ("algo_flops", C.c_double), ("bias_bstride", C.c_int64),
     ]
 
 

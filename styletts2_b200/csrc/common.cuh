@@ -122,6 +122,9 @@ int launch_act_to_ncl(const T* cl, int64_t bstride, int ld, int C, int L, float*
 int launch_cl_to_ncl(const float* cl, int ld, int C, int L, float* ncl, int B, cudaStream_t st);
 int launch_ncl_to_cl(const float* ncl, int C, int L, float* cl, int ld, int B, cudaStream_t st);
 
+int launch_row_mean(const float* x, int64_t L, float* mean, int B, cudaStream_t st);
+int launch_noise_bias(const float* mean, const float* wsum, const float* bias_nc, const float* bias_c2,
+                      float* bias_nc_shift, float* bias_c2_add, int C, int B, cudaStream_t st);
 int launch_phase_scan(const float* f0, int B, int T, int spf, float* phase, cudaStream_t st);
 int launch_har_source(const float* f0, const float* phase, const float* noise, uint64_t seed,
                       const float* lin_w9, float lin_b, int B, int T, int spf, float* out,

@@ -4,7 +4,7 @@
 //   base + b * bstride + t * ld + c        (all in elements of the tensor's dtype)
 // so one conv tap is a row offset and the GEMM K dimension (channels) is contiguous.
 //
-//   y[b,t,n] = post( bias[n] + sum_{j<k} sum_{c<cin} W[j][c][n] * pre(x[b, t*stride + j*dil - pad, c]) )
+//   y[b,t,n] = post( bias[b*bias_bstride + n] + sum_{j<k} sum_{c<cin} W[j][c][n] * pre(x[b, t*stride + j*dil - pad, c]) )
 //   pre(v)   = act( v * scale[b,c] + shift[b,c] ),  0 for rows outside [0, Lin)   (conv zero padding
 //              applies AFTER the activation, exactly like AdaIN -> Snake -> Conv1d(padding=..))
 //   post(a)  = (a + res[b, t >> res_shift, n]) * out_scale (+ y_old[b,t,n] if accumulate)
@@ -61,6 +61,7 @@ typedef struct St2ConvParams {
   float* stats;       // [B][n_tiles][n_cols][2] partial (sum, sumsq), or NULL
   int n_tiles;        // ceil(Lout / tile_rows) of the implementation that is called
   double algo_flops;  // algorithmic FLOPs of this call (2*MAC, no padding), bookkeeping only
+  int64_t bias_bstride;  // elements between the bias rows of two batch items (0: one shared bias)
 } St2ConvParams;
 
 #endif

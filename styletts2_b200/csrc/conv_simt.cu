@@ -102,7 +102,7 @@ conv_simt_kernel(const St2ConvParams p, const int CK, const int KJ, const int ro
       const int col = n0 + tx * 4 + q;
       if (col >= p.n_cols) continue;
       float v = acc[i][q];
-      if (p.bias) v += p.bias[col];
+      if (p.bias) v += p.bias[(int64_t)b * p.bias_bstride + col];
       if (rb) v += ld_f<OutT>(rb + (int64_t)(t >> p.res_shift) * p.ldres + col);
       v *= p.out_scale;
       OutT* yp = yb + (int64_t)t * p.ldy + col;

@@ -175,6 +175,32 @@ __device__ __forceinline__ void umma_bf16(uint32_t tmem_d, uint64_t adesc, uint6
       "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate)
       : "memory");
 }
+// branch-free variants for the issuing warp: executed by all lanes, performed by the one with on != 0
+__device__ __forceinline__ void umma_commit_if(uint64_t* bar, uint32_t on) {
+  asm volatile(
+      "{ .reg .pred q; setp.ne.b32 q, %1, 0;\n"
+      "@q tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0]; }" ::"r"(smem_u32(bar)),
+      "r"(on)
+      : "memory");
+}
+__device__ __forceinline__ void umma_bf16_if(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc, uint32_t idesc,
+                                             uint32_t accumulate, uint32_t on) {
+  asm volatile(
+      "{ .reg .pred p, q; setp.ne.b32 p, %4, 0; setp.ne.b32 q, %5, 0;\n"
+      "@q tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p; }" ::"r"(tmem_d),
+      "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate), "r"(on)
+      : "memory");
+}
+// one non-blocking probe of an mbarrier phase
+__device__ __forceinline__ uint32_t mbar_try(uint64_t* bar, uint32_t parity) {
+  uint32_t done;
+  asm volatile(
+      "{ .reg .pred p; mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2; selp.u32 %0, 1, 0, p; }"
+      : "=r"(done)
+      : "r"(smem_u32(bar)), "r"(parity)
+      : "memory");
+  return done;
+}
 // K-major, SWIZZLE_NONE shared-memory matrix descriptor (cute::UMMA::SmemDescriptor, version 1):
 // [0,14) start>>4, [16,30) leading (K-direction core-matrix) byte offset>>4,
 // [32,46) stride (8-row group) byte offset>>4, [46,48) version=1, [61,64) layout type 0.
@@ -389,27 +415,38 @@ __device__ __forceinline__ void um_produce(const St2ConvParams& p, const UmLayou
         sh[e] += hia[e];
       }
     }
+    // rows in two batches of 5: all shared-memory reads of a batch are issued before its arithmetic
 #pragma unroll
-    for (int i = 0; i < UM_NI; ++i) {
-      if (32 * i >= tot) continue;
-      const uint32_t addr = dst + (uint32_t)i * 512u;
-      if (32 * i >= lo && 32 * i < hi) {
-        if (!IDENT) {
-          const uint4 raw = lds128(addr);
-          const uint32_t w[4] = {raw.x, raw.y, raw.z, raw.w};
-          uint32_t o[4];
+    for (int h = 0; h < 2; ++h) {
+      uint4 raw[UM_NI / 2];
+      if (!IDENT) {
 #pragma unroll
-          for (int e2 = 0; e2 < 4; ++e2) {
-            const float lo_ = um_act<ACT>(bf16lo(w[e2]), sc[2 * e2], sh[2 * e2], wsc[2 * e2], wsh[2 * e2],
-                                          hia[2 * e2], p.slope);
-            const float hi_ = um_act<ACT>(bf16hi(w[e2]), sc[2 * e2 + 1], sh[2 * e2 + 1], wsc[2 * e2 + 1],
-                                          wsh[2 * e2 + 1], hia[2 * e2 + 1], p.slope);
-            o[e2] = pack_bf16x2(lo_, hi_);
-          }
-          sts128(addr, make_uint4(o[0], o[1], o[2], o[3]));
+        for (int ii = 0; ii < UM_NI / 2; ++ii) {
+          const int i = h * (UM_NI / 2) + ii;
+          if (32 * i < tot) raw[ii] = lds128(dst + (uint32_t)i * 512u);
         }
-      } else {
-        sts128(addr, make_uint4(0u, 0u, 0u, 0u));  // conv zero padding applies after the activation
+      }
+#pragma unroll
+      for (int ii = 0; ii < UM_NI / 2; ++ii) {
+        const int i = h * (UM_NI / 2) + ii;
+        if (32 * i >= tot) continue;
+        const uint32_t addr = dst + (uint32_t)i * 512u;
+        const bool valid = 32 * i >= lo && 32 * i < hi;
+        if (IDENT) {
+          if (!valid) sts128(addr, make_uint4(0u, 0u, 0u, 0u));
+          continue;
+        }
+        const uint32_t w[4] = {raw[ii].x, raw[ii].y, raw[ii].z, raw[ii].w};
+        uint32_t o[4];
+#pragma unroll
+        for (int e2 = 0; e2 < 4; ++e2) {
+          const float lo_ = um_act<ACT>(bf16lo(w[e2]), sc[2 * e2], sh[2 * e2], wsc[2 * e2], wsh[2 * e2],
+                                        hia[2 * e2], p.slope);
+          const float hi_ = um_act<ACT>(bf16hi(w[e2]), sc[2 * e2 + 1], sh[2 * e2 + 1], wsc[2 * e2 + 1],
+                                        wsh[2 * e2 + 1], hia[2 * e2 + 1], p.slope);
+          o[e2] = valid ? pack_bf16x2(lo_, hi_) : 0u;  // conv zero padding applies after the activation
+        }
+        sts128(addr, make_uint4(o[0], o[1], o[2], o[3]));
       }
     }
     fence_proxy_async_smem();
@@ -435,9 +472,24 @@ __device__ __forceinline__ void um_produce(const St2ConvParams& p, const UmLayou
   }
   load_params(tc, ssr, alr);
   while (tc.tile < total_tiles) {
+    // next chunk's parameters: their global loads are in flight during this chunk's arithmetic
+    UmCur nx = tc;
+    um_advance(nx, nct, lay.na, total_tiles, n_ttiles, n_ntiles);
+    float2 ssn[8];
+    float aln[8];
+#pragma unroll
+    for (int e = 0; e < 8; ++e) {
+      ssn[e] = ssr[e];
+      aln[e] = alr[e];
+    }
+    load_params(nx, ssn, aln);
     transform(tc, ssr, alr);
-    um_advance(tc, nct, lay.na, total_tiles, n_ttiles, n_ntiles);
-    load_params(tc, ssr, alr);  // next chunk's parameters: in flight across the stage wait below
+#pragma unroll
+    for (int e = 0; e < 8; ++e) {
+      ssr[e] = ssn[e];
+      alr[e] = aln[e];
+    }
+    tc = nx;
     if (lc.tile < total_tiles) {
       issue_loads(lc);
       um_advance(lc, nct, lay.na, total_tiles, n_ttiles, n_ntiles);
@@ -515,7 +567,7 @@ __device__ __forceinline__ void um_epilogue(const St2ConvParams& p, const UmLayo
     const UmTile tl = um_tile(tile, n_ttiles, n_ntiles);
     const uint32_t tb = t_it & 1, tph = (t_it >> 1) & 1;
     float* bias_s = misc->bias[tb];
-    if (et < n_tile) bias_s[et] = (p.bias ? p.bias[tl.nt * n_tile + et] : 0.f) * scale;
+    if (et < n_tile) bias_s[et] = (p.bias ? p.bias[(int64_t)tl.b * p.bias_bstride + tl.nt * n_tile + et] : 0.f) * scale;
     float s0 = 0.f, s1 = 0.f, q0 = 0.f, q1 = 0.f;
     mbar_wait(&misc->t_full[tb], tph, 5);
     tc_fence_after();
@@ -653,46 +705,48 @@ __global__ void __launch_bounds__(UM_THREADS, 1) conv_umma_kernel(const St2ConvP
     const uint64_t a_desc0 = umma_desc(0, a_lbo, 128), w_desc0 = umma_desc(0, w_lbo, 128);
     const uint32_t a_kstep = 2u * (uint32_t)lay.rpad, w_kstep = 2u * (uint32_t)lay.n_tile;  // in 16-byte units
     const int nct = nchunks + lay.n_res + lay.n_acc;
-    const bool leader = elect_one();
+    const uint32_t leader = elect_one() ? 1u : 0u;
     int as = 0, ws = 0;
     uint32_t aph = 0, wph = 0, t_it = 0;
+    // The tensor-core queue is shallow, so everything between two groups of MMAs is on the critical
+    // path: the next weight stage's barrier is probed BEFORE the current group is issued (its
+    // latency hides behind the issue), and issue / commit are predicated instead of branched.
+    uint32_t w_ready = 0;
     for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, ++t_it) {
       const uint32_t tb = t_it & 1, tph = (t_it >> 1) & 1;
       mbar_wait(&misc->t_empty[tb], tph ^ 1, 1);
-      tc_fence_after();
       const uint32_t d0 = tmem_base + (uint32_t)(tb * UM_NACC * lay.n_tile);
       for (int c = 0; c < nct; ++c) {
         mbar_wait(&misc->a_full[as], aph, 2);
-        tc_fence_after();
         const uint32_t a_u = (a_base + (uint32_t)as * (uint32_t)lay.a_bytes) >> 4;
         // residual / y_old chunks: one identity "tap" at row offset 0
         const int taps = c < nchunks ? p.k : 1;
         const uint32_t dil = c < nchunks ? (uint32_t)p.dil : 0u;
         for (int j = 0; j < taps; ++j) {
-          mbar_wait(&misc->w_full[ws], wph, 3);
+          if (!w_ready) mbar_wait(&misc->w_full[ws], wph, 3);
           tc_fence_after();
-          if (leader) {
-            const uint64_t ad = a_desc0 + (uint64_t)(a_u + (uint32_t)j * dil);
-            const uint64_t bd = w_desc0 + (uint64_t)((w_base + (uint32_t)ws * (uint32_t)lay.w_bytes) >> 4);
-            const uint32_t first = (c | j) != 0 ? 1u : 0u;
+          int wn = ws + 1;
+          uint32_t wnph = wph;
+          if (wn == UM_W_STAGES) { wn = 0; wnph ^= 1u; }
+          w_ready = mbar_try(&misc->w_full[wn], wnph);  // consumed after the MMAs below
+          const uint64_t ad = a_desc0 + (uint64_t)(a_u + (uint32_t)j * dil);
+          const uint64_t bd = w_desc0 + (uint64_t)((w_base + (uint32_t)ws * (uint32_t)lay.w_bytes) >> 4);
+          const uint32_t first = (c | j) != 0 ? 1u : 0u;
 #pragma unroll
-            for (int acc = 0; acc < UM_NACC; ++acc) {
+          for (int acc = 0; acc < UM_NACC; ++acc) {
 #pragma unroll
-              for (int ks = 0; ks < UM_CK / 16; ++ks)
-                umma_bf16(d0 + (uint32_t)(acc * lay.n_tile), ad + (uint64_t)(acc * 128 + ks * a_kstep),
-                          bd + (uint64_t)(ks * w_kstep), lay.idesc, ks != 0 ? 1u : first);
-            }
-            umma_commit(&misc->w_empty[ws]);
+            for (int ks = 0; ks < UM_CK / 16; ++ks)
+              umma_bf16_if(d0 + (uint32_t)(acc * lay.n_tile), ad + (uint64_t)(acc * 128 + ks * a_kstep),
+                           bd + (uint64_t)(ks * w_kstep), lay.idesc, ks != 0 ? 1u : first, leader);
           }
-          __syncwarp();
-          if (++ws == UM_W_STAGES) { ws = 0; wph ^= 1u; }
+          umma_commit_if(&misc->w_empty[ws], leader);
+          ws = wn;
+          wph = wnph;
         }
-        if (leader) umma_commit(&misc->a_empty[as]);
-        __syncwarp();
+        umma_commit_if(&misc->a_empty[as], leader);
         if (++as == lay.na) { as = 0; aph ^= 1u; }
       }
-      if (leader) umma_commit(&misc->t_full[tb]);
-      __syncwarp();
+      umma_commit_if(&misc->t_full[tb], leader);
     }
   } else if (warp == 1) {
     // ================================================================ weight producer

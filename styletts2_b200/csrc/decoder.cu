@@ -77,6 +77,7 @@ struct St2Decoder {
   std::vector<st2::UpW> ups;
   std::vector<st2::ConvW> noise_convs;
   std::vector<st2::ConvW> noise_convs16;  // istftnet, bf16 path: grouped (hi, lo) form for tcgen05
+  std::vector<int64_t> noise_wsum;        // hifigan: [C] sum over taps of noise_convs[i].weight (fp32)
   std::vector<int> noise_group;           // har rows per wide row of noise_convs16[i] (stride of noise_convs[i])
   std::vector<st2::ResBlock1W> noise_res, resblocks;
   std::vector<int64_t> alphas;  // hifigan generator.alphas
@@ -447,6 +448,7 @@ static int do_load(St2Decoder* h, const St2Tensor* tensors, int n) {
   h->noise_convs.assign(c.n_ups, ConvW());
   h->noise_convs16.assign(c.n_ups, ConvW());
   h->noise_group.assign(c.n_ups, 1);
+  h->noise_wsum.assign(c.n_ups, -1);
   h->noise_res.assign(c.n_ups, ResBlock1W());
   h->resblocks.assign(c.n_ups * c.n_resblock_kernels, ResBlock1W());
   const int d135[3] = {1, 3, 5};
@@ -463,6 +465,20 @@ static int do_load(St2Decoder* h, const St2Tensor* tensors, int n) {
       rk = 7;
     } else if (ok) {
       ok = L.conv1d(h->noise_convs[i], g + ".noise_convs." + si, false, true, 1, 1, 0, 1, false);
+    }
+    if (ok && !istft) {  // sum of each output channel's taps (mean-free storage of x_source)
+      const St2Tensor* t = L.get(g + ".noise_convs." + si + ".weight");
+      ok = t != nullptr;
+      if (ok) {
+        const int64_t inner = t->shape[1] * t->shape[2];
+        std::vector<float> ws((size_t)cout);
+        for (int co = 0; co < cout; ++co) {
+          double a = 0.0;
+          for (int64_t q = 0; q < inner; ++q) a += (double)t->data[co * inner + q];
+          ws[co] = (float)a;
+        }
+        h->noise_wsum[i] = L.blob.add(ws.data(), (int64_t)ws.size() * 4);
+      }
     }
     if (ok && istft) {
       const int sf = i + 1 < c.n_ups ? prod_from(c.upsample_rates, i + 1, c.n_ups) : 1;
@@ -575,6 +591,7 @@ struct Fwd {
     float out_scale = 1.f; int accumulate = 0;
     bool want_stats = false;
     int extra_stat_tiles = 0;
+    const float* bias_b = nullptr;  // per-batch bias [B][n] replacing the layer's own
   };
   // stats result of the last conv() call
   float* last_partials = nullptr;
@@ -602,6 +619,10 @@ struct Fwd {
     p.k = c.k; p.dil = c.dil; p.pad = c.pad; p.stride = c.stride;
     p.w = umma ? (const void*)W<uint16_t>(c.w16) : (const void*)W<float>(c.w32);
     p.bias = W<float>(umma ? c.bias16 : c.bias);
+    if (io.bias_b) {
+      p.bias = io.bias_b;
+      p.bias_bstride = c.n;
+    }
     p.n_cols = umma ? c.n16 : c.n;
     p.y = io.y; p.y_dtype = io.y_dtype; p.y_bstride = io.y_bstride; p.ldy = io.ldy; p.Lout = io.Lout;
     p.res = io.res; p.res_bstride = io.res_bstride; p.ldres = io.ldres; p.res_shift = io.res_shift;
@@ -679,7 +700,7 @@ struct Fwd {
   // run: private running buffer (may alias x for the in-place noise_res), tmp: conv1 output.
   // final: destination of the last iteration; final_scale / final_acc implement mean over resblocks.
   int resblock1(const ResBlock1W& r, const Act<AT>& x, const Act<AT>& run, const Act<AT>& tmp,
-                const Act<AT>& fin, float final_scale, int final_acc) {
+                const Act<AT>& fin, float final_scale, int final_acc, const float* c2_bias0 = nullptr) {
     for (int it = 0; it < 3; ++it) {
       const Act<AT>& src = it == 0 ? x : run;
       const bool last = it == 2;
@@ -700,6 +721,7 @@ struct Fwd {
         io.pre_norm = &r.n2[it]; io.act = ST2_ACT_SNAKE; io.alpha = W<float>(r.a2[it]);
         io.res = src.p; io.res_bstride = src.bstride; io.ldres = src.ld;
         if (last) { io.out_scale = final_scale; io.accumulate = final_acc; }
+        if (it == 0) io.bias_b = c2_bias0;
         io.want_stats = !last;
         int rc = conv(r.c2[it], io);
         if (rc) return rc;
@@ -828,6 +850,14 @@ int Fwd<AT>::run(const float* asr, const float* f0, const float* nn, const float
     else RUN(launch_cl_to_ncl(har, ldh, n_fft + 2, L2, o.har_out, B, st));
   }
 
+  // hifigan, bf16 path: x_source is stored without its per-(b,c) constant (elementwise.cu, noise_bias)
+  const bool meanfree = !istft && DT<AT>::id == ST2_DT_BF16;
+  float* hs_mean = nullptr;
+  if (meanfree) {
+    hs_mean = ar.alloc<float>(B);
+    RUN(launch_row_mean(hs, Lw, hs_mean, B, st));
+  }
+
   // ---- generator stages (istftnet.py:358-374 / hifigan.py:327-341)
   Act<AT> x = xg;
   const int nk = c.n_resblock_kernels;
@@ -854,13 +884,21 @@ int Fwd<AT>::run(const float* asr, const float* f0, const float* nn, const float
       }
       io.y = xs.p; io.y_dtype = DT<AT>::id; io.y_bstride = xs.bstride; io.ldy = xs.ld; io.Lout = Ls;
       io.want_stats = true;
+      float* bias_c2 = nullptr;
+      if (meanfree) {
+        float* bias_nc = ar.alloc<float>((int64_t)B * C);
+        bias_c2 = ar.alloc<float>((int64_t)B * C);
+        RUN(launch_noise_bias(hs_mean, W<float>(h->noise_wsum[i]), W<float>(nc.bias),
+                              W<float>(h->noise_res[i].c2[0].bias), bias_nc, bias_c2, C, B, st));
+        io.bias_b = bias_nc;
+      }
       const int64_t m = ar.mark();
       int rc = conv(nc, io);
       if (rc) return rc;
       rc = finalize(last_partials, last_tiles, last_cols, C, Ls, h->noise_res[i].n1[0], 0);
       if (rc) return rc;
       ar.release(m);
-      rc = resblock1(h->noise_res[i], xs, xs, tmp, xs, 1.f, 0);
+      rc = resblock1(h->noise_res[i], xs, xs, tmp, xs, 1.f, 0, bias_c2);
       if (rc) return rc;
     }
     // x = ups[i](act(x)) (+ reflection pad) + x_source, with statistics for the three resblocks

@@ -390,6 +390,50 @@ int launch_hilo_to_ncl(const __nv_bfloat16* har, int rows_pad, int C, int L, flo
   return ST2_OK;
 }
 
+// ------------------------------------------------------- mean-free storage of x_source (hifigan)
+// The time-domain noise convs of the HiFi-GAN generator (hifigan.py:295-302) see a one-channel
+// source whose mean is far from zero, so each output channel is a small signal riding on a large
+// constant kappa[b,c] = bias[c] + mean_t(har_source[b]) * sum_taps w[c]; rounding that sum to bf16
+// and then instance-normalising it amplifies the rounding noise by |mean|/std (20-5000 here).
+// InstanceNorm ignores a per-(b,c) constant, so the bf16 path stores x_source - kappa and adds
+// kappa back where the un-normalised tensor is consumed (the residual of noise_res iteration 0).
+__global__ void __launch_bounds__(256) row_mean_kernel(const float* __restrict__ x, int64_t L, float* __restrict__ mean) {
+  __shared__ double red[256];
+  const float* xb = x + (int64_t)blockIdx.x * L;
+  double s = 0.0;
+  for (int64_t i = threadIdx.x; i < L; i += 256) s += (double)xb[i];
+  red[threadIdx.x] = s;
+  __syncthreads();
+  for (int o = 128; o > 0; o >>= 1) {
+    if (threadIdx.x < o) red[threadIdx.x] += red[threadIdx.x + o];
+    __syncthreads();
+  }
+  if (threadIdx.x == 0) mean[blockIdx.x] = (float)(red[0] / (double)L);
+}
+// bias_nc_shift[b,c] = -mean[b]*wsum[c]  (noise conv bias with kappa removed)
+// bias_c2_add[b,c]   = bias_c2[c] + bias_nc[c] + mean[b]*wsum[c]  (conv2 bias with kappa restored)
+__global__ void noise_bias_kernel(const float* __restrict__ mean, const float* __restrict__ wsum,
+                                  const float* __restrict__ bias_nc, const float* __restrict__ bias_c2,
+                                  float* __restrict__ bias_nc_shift, float* __restrict__ bias_c2_add, int C) {
+  const int c = blockIdx.x * blockDim.x + threadIdx.x, b = blockIdx.y;
+  if (c >= C) return;
+  const float k = mean[b] * wsum[c];
+  bias_nc_shift[(int64_t)b * C + c] = -k;
+  bias_c2_add[(int64_t)b * C + c] = bias_c2[c] + bias_nc[c] + k;
+}
+int launch_row_mean(const float* x, int64_t L, float* mean, int B, cudaStream_t st) {
+  row_mean_kernel<<<B, 256, 0, st>>>(x, L, mean);
+  ST2_LAUNCH_OK("row_mean");
+  return ST2_OK;
+}
+int launch_noise_bias(const float* mean, const float* wsum, const float* bias_nc, const float* bias_c2,
+                      float* bias_nc_shift, float* bias_c2_add, int C, int B, cudaStream_t st) {
+  dim3 grid(ceil_div(C, 128), B);
+  noise_bias_kernel<<<grid, 128, 0, st>>>(mean, wsum, bias_nc, bias_c2, bias_nc_shift, bias_c2_add, C);
+  ST2_LAUNCH_OK("noise_bias");
+  return ST2_OK;
+}
+
 // debug / parity taps: channels-last activation (fp32 or bf16) -> fp32 NCL
 template <typename T>
 __global__ void act_to_ncl_kernel(const T* __restrict__ cl, int64_t bstride, int ld, int C, int L,
