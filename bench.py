@@ -250,8 +250,13 @@ def run_ours(args):
     roof = None
     if umma_n.value > 0 and umma_ms.value > 0:
         ach = umma_fl.value / (umma_ms.value * 1e-3) / 1e12
+        traffic = None  # DRAM bytes per launch of this kernel, from the committed ncu capture (profiles/)
+        tp = os.path.join(ROOT, "profiles", "conv_umma_traffic.json")
+        if args.workload == "c2" and os.path.exists(tp):
+            traffic = round(json.load(open(tp))["dram_bytes_per_launch"])
         roof = {"bound": "tensor", "achieved": round(ach, 2), "peak": peaks["tf_sustained"], "unit": "TFLOP/s",
-                "frac": round(ach / peaks["tf_sustained"], 4), "traffic": None,
+                "frac": round(ach / peaks["tf_sustained"], 4), "traffic": traffic,
+                "traffic_unit": "bytes per launch (dram read+write, ncu, profiles/r1_ncu_conv_umma_step_c2_v3.csv)",
                 "kernel": "conv_umma_kernel (tcgen05 implicit-GEMM conv)",
                 "launches_per_step": umma_n.value // args.steps,
                 "kernel_ms_per_step": round(umma_ms.value / args.steps, 3),
