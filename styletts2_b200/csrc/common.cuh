@@ -100,7 +100,7 @@ int launch_style_fc(const float* s, const float* W, const float* bvec, float* h,
                     int rows, cudaStream_t st);
 int launch_stats_finalize(const float* partials, int n_tiles, int n_cols, int C, int64_t count,
                           const float* h, int h_stride, int gamma_off, float* ss, int ss_stride,
-                          int c_off, int B, cudaStream_t st);
+                          int c_off, int B, cudaStream_t st, int reps = 1);
 template <typename T>
 int launch_colstats(const T* x, int64_t bstride, int ld, int L, int c0, int ncols, float* partials,
                     int B, cudaStream_t st);
@@ -124,7 +124,8 @@ int launch_ncl_to_cl(const float* ncl, int C, int L, float* cl, int ld, int B, c
 
 int launch_row_mean(const float* x, int64_t L, float* mean, int B, cudaStream_t st);
 int launch_noise_bias(const float* mean, const float* wsum, const float* bias_nc, const float* bias_c2,
-                      float* bias_nc_shift, float* bias_c2_add, int C, int B, cudaStream_t st);
+                      float* bias_nc_shift, float* bias_c2_add, int C, int B, cudaStream_t st, int reps = 1);
+int launch_cols_tanh(const float* cp, int ld, int ncol, float* wav, int64_t n, cudaStream_t st);
 int launch_phase_scan(const float* f0, int B, int T, int spf, float* phase, cudaStream_t st);
 int launch_har_source(const float* f0, const float* phase, const float* noise, uint64_t seed,
                       const float* lin_w9, float lin_b, int B, int T, int spf, float* out,

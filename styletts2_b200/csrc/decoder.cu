@@ -39,6 +39,11 @@ struct ResBlock1W {  // AdaINResBlock1, istftnet.py:27-75
   ConvW c1[3], c2[3];
   NormW n1[3], n2[3];
   int64_t a1[3], a2[3];
+  // row-pair form of a 32-channel block (Loader::pair_conv): the [L][32] tensor is read as
+  // [L/2][64], so the tcgen05 kernel (64-channel chunks, 128-byte output rows) can run it
+  bool paired = false;
+  ConvW c1p[3], c2p[3];
+  int64_t a1p[3], a2p[3];
 };
 struct ResBlk1dW {  // AdainResBlk1d, istftnet.py:409-453
   int din = 0, dout = 0, din_pad = 0;
@@ -82,6 +87,8 @@ struct St2Decoder {
   std::vector<st2::ResBlock1W> noise_res, resblocks;
   std::vector<int64_t> alphas;  // hifigan generator.alphas
   st2::ConvW conv_post;
+  st2::ConvW conv_post_p;     // row-pair form of a 32-channel conv_post (hifigan)
+  int64_t alpha_post_p = -1;  // alphas[n_ups] repeated twice
   int64_t last_launches = 0;
 };
 
@@ -240,8 +247,44 @@ struct Loader {
     }
   }
   // Conv1d: torch [Cout][Cin][k] -> [k][Cin][Cout]
+  // Row-pair form of a stride-1 conv: with t = 2q + e, y[2q+e][o] = sum_j W[j][c][o] x[2q + e + j*dil - pad][c]
+  // and 2q + e + j*dil - pad = 2(q + m) + h, so on rows of (h, c) / (e, o) pairs it is the dense conv
+  //   Y[q][e*n + o] = sum_m W2[m][h*cin + c][e*n + o] X[q + m][h*cin + c],  m = floor((e + j*dil - pad) / 2)
+  // with dilation 1 (most 32x32 blocks of W2 are zero: 2k of them are not).
+  void pair_conv(ConvW& c2, const ConvW& c, const std::vector<float>& kcn, const std::vector<float>* bias) {
+    auto fl2 = [](int v) { return v >= 0 ? v / 2 : -((-v + 1) / 2); };
+    const int m_min = fl2(-c.pad), m_max = fl2(1 + (c.k - 1) * c.dil - c.pad);
+    c2 = ConvW();
+    c2.k = m_max - m_min + 1; c2.dil = 1; c2.pad = -m_min; c2.stride = 1;
+    c2.cin = 2 * c.cin; c2.n = 2 * c.n; c2.cstat = c.n;
+    c2.flops_per_row = 2.0 * c.flops_per_row;  // two original rows per pair row
+    std::vector<float> w2((size_t)c2.k * c2.cin * c2.n, 0.f);
+    for (int e = 0; e < 2; ++e)
+      for (int j = 0; j < c.k; ++j) {
+        const int s = e + j * c.dil - c.pad, m = fl2(s), hh = s - 2 * m;
+        for (int ci = 0; ci < c.cin; ++ci)
+          for (int o = 0; o < c.n; ++o)
+            w2[((size_t)(m - m_min) * c2.cin + hh * c.cin + ci) * c2.n + e * c.n + o] =
+                kcn[((size_t)j * c.cin + ci) * c.n + o];
+      }
+    std::vector<float> b2;
+    if (bias) {
+      b2.resize((size_t)c2.n);
+      for (int e = 0; e < 2; ++e)
+        for (int o = 0; o < c.n; ++o) b2[e * c.n + o] = (*bias)[o];
+    }
+    finish_conv(c2, w2, bias ? &b2 : nullptr, true);
+  }
+  bool vec2(int64_t& off, const std::string& name, int64_t n) {  // parameter vector repeated twice
+    const St2Tensor* t = get(name);
+    if (!t) return false;
+    std::vector<float> v((size_t)2 * n);
+    for (int64_t i = 0; i < n; ++i) v[i] = v[n + i] = t->data[i];
+    off = blob.add(v.data(), 2 * n * 4);
+    return true;
+  }
   bool conv1d(ConvW& c, const std::string& p, bool weight_norm, bool has_bias, int k, int dil, int pad,
-              int stride, bool want_umma) {
+              int stride, bool want_umma, ConvW* pair = nullptr) {
     std::vector<float> w;
     int64_t d0, d1, d2;
     if (weight_norm) {
@@ -266,6 +309,7 @@ struct Loader {
       b.assign(bt->data, bt->data + d0);
     }
     finish_conv(c, kcn, has_bias ? &b : nullptr, want_umma);
+    if (pair) pair_conv(*pair, c, kcn, has_bias ? &b : nullptr);
     return true;
   }
   // ConvTranspose1d [Cin][Cout][K] (stride s, padding p) -> polyphase conv over input offsets
@@ -384,13 +428,20 @@ struct Loader {
   }
   bool resblock1(ResBlock1W& r, const std::string& p, int C, int k, const int* dils) {
     r.C = C; r.k = k;
+    r.paired = C == 32;
     bool ok = true;
     for (int i = 0; i < 3 && ok; ++i) {
       const std::string si = std::to_string(i);
-      ok = conv1d(r.c1[i], p + ".convs1." + si, true, true, k, dils[i], dils[i] * (k - 1) / 2, 1, true) &&
-           conv1d(r.c2[i], p + ".convs2." + si, true, true, k, 1, (k - 1) / 2, 1, true) &&
+      ok = conv1d(r.c1[i], p + ".convs1." + si, true, true, k, dils[i], dils[i] * (k - 1) / 2, 1, true,
+                  r.paired ? &r.c1p[i] : nullptr) &&
+           conv1d(r.c2[i], p + ".convs2." + si, true, true, k, 1, (k - 1) / 2, 1, true,
+                  r.paired ? &r.c2p[i] : nullptr) &&
            norm(r.n1[i], p + ".adain1." + si, C) && norm(r.n2[i], p + ".adain2." + si, C) &&
            vec(r.a1[i], p + ".alpha1." + si, C) && vec(r.a2[i], p + ".alpha2." + si, C);
+      if (ok && r.paired) {
+        ok = vec2(r.a1p[i], p + ".alpha1." + si, C) && vec2(r.a2p[i], p + ".alpha2." + si, C);
+        if (r.c1p[i].w16 < 0 || r.c2p[i].w16 < 0) r.paired = false;  // halo too long for the tile
+      }
     }
     return ok;
   }
@@ -493,7 +544,10 @@ static int do_load(St2Decoder* h, const St2Tensor* tensors, int n) {
                        g + ".resblocks." + std::to_string(i * c.n_resblock_kernels + j), cout,
                        c.resblock_kernel_sizes[j], c.resblock_dilations[j]);
   }
-  ok = ok && L.conv1d(h->conv_post, g + ".conv_post", true, true, 7, 1, 3, 1, istft);
+  const bool post_pair = !istft && (c0 >> c.n_ups) == 32;
+  ok = ok && L.conv1d(h->conv_post, g + ".conv_post", true, true, 7, 1, 3, 1, istft,
+                      post_pair ? &h->conv_post_p : nullptr);
+  if (ok && post_pair) ok = L.vec2(h->alpha_post_p, g + ".alphas." + std::to_string(c.n_ups), 32);
   if (ok && !istft) {
     h->alphas.assign(c.n_ups + 1, -1);
     for (int i = 0; i <= c.n_ups && ok; ++i)
@@ -577,9 +631,9 @@ struct Fwd {
 
   // finalize InstanceNorm statistics of channels [c_off, c_off+C) of norm layer n
   int finalize(const float* partials, int n_tiles, int n_cols, int C, int64_t count, const NormW& n,
-               int c_off) {
+               int c_off, int reps = 1) {
     RUN(launch_stats_finalize(partials, n_tiles, n_cols, C, count, hall + n.h_off, h->fc_rows, n.C,
-                              ss + (int64_t)n.ss_off * 2, h->ss_pairs, c_off, B, st));
+                              ss + (int64_t)n.ss_off * 2, h->ss_pairs, c_off, B, st, reps));
     return ST2_OK;
   }
 
@@ -699,34 +753,37 @@ struct Fwd {
   // AdaINResBlock1 (istftnet.py:66-75).  x: block input whose adain1[0] scale/shift are finalized.
   // run: private running buffer (may alias x for the in-place noise_res), tmp: conv1 output.
   // final: destination of the last iteration; final_scale / final_acc implement mean over resblocks.
+  // pr: the views are row pairs ([L/2][2C]) and the block runs in its row-pair form (Loader::pair_conv).
   int resblock1(const ResBlock1W& r, const Act<AT>& x, const Act<AT>& run, const Act<AT>& tmp,
-                const Act<AT>& fin, float final_scale, int final_acc, const float* c2_bias0 = nullptr) {
+                const Act<AT>& fin, float final_scale, int final_acc, const float* c2_bias0 = nullptr,
+                bool pr = false) {
+    const int reps = pr ? 2 : 1;
     for (int it = 0; it < 3; ++it) {
       const Act<AT>& src = it == 0 ? x : run;
       const bool last = it == 2;
       const int64_t m = ar.mark();
       {
         ConvIO io = io_of(src, tmp);
-        io.pre_norm = &r.n1[it]; io.act = ST2_ACT_SNAKE; io.alpha = W<float>(r.a1[it]);
+        io.pre_norm = &r.n1[it]; io.act = ST2_ACT_SNAKE; io.alpha = W<float>(pr ? r.a1p[it] : r.a1[it]);
         io.want_stats = true;
-        int rc = conv(r.c1[it], io);
+        int rc = conv(pr ? r.c1p[it] : r.c1[it], io);
         if (rc) return rc;
-        rc = finalize(last_partials, last_tiles, last_cols, r.C, tmp.L, r.n2[it], 0);
+        rc = finalize(last_partials, last_tiles, last_cols, r.C, (int64_t)tmp.L * reps, r.n2[it], 0, reps);
         if (rc) return rc;
         ar.release(m);
       }
       {
         const Act<AT>& dst = last ? fin : run;
         ConvIO io = io_of(tmp, dst);
-        io.pre_norm = &r.n2[it]; io.act = ST2_ACT_SNAKE; io.alpha = W<float>(r.a2[it]);
+        io.pre_norm = &r.n2[it]; io.act = ST2_ACT_SNAKE; io.alpha = W<float>(pr ? r.a2p[it] : r.a2[it]);
         io.res = src.p; io.res_bstride = src.bstride; io.ldres = src.ld;
         if (last) { io.out_scale = final_scale; io.accumulate = final_acc; }
         if (it == 0) io.bias_b = c2_bias0;
         io.want_stats = !last;
-        int rc = conv(r.c2[it], io);
+        int rc = conv(pr ? r.c2p[it] : r.c2[it], io);
         if (rc) return rc;
         if (!last) {
-          rc = finalize(last_partials, last_tiles, last_cols, r.C, dst.L, r.n1[it + 1], 0);
+          rc = finalize(last_partials, last_tiles, last_cols, r.C, (int64_t)dst.L * reps, r.n1[it + 1], 0, reps);
           if (rc) return rc;
         }
         ar.release(m);
@@ -869,6 +926,17 @@ int Fwd<AT>::run(const float* asr, const float* f0, const float* nn, const float
     const int Ls = Lin * up.rate + pad_rows;
     Act<AT> xs = new_act(Ls, C), xm = new_act(Ls, C), tmp = new_act(Ls, C), runb = new_act(Ls, C),
             outb = new_act(Ls, C);
+    // a 32-channel stage runs on row pairs ([Ls/2][64] views of the same memory) so that its convs
+    // fit the tcgen05 kernel's 64-channel chunks (Loader::pair_conv)
+    bool pr = DT<AT>::id == ST2_DT_BF16 && C == 32 && pad_rows == 0 && Ls % 2 == 0 && up.rate % 2 == 0 &&
+              h->noise_res[i].paired;
+    for (int j = 0; j < nk; ++j) pr = pr && h->resblocks[i * nk + j].paired;
+    const int reps = pr ? 2 : 1;
+    auto vw = [pr](const Act<AT>& a) {
+      Act<AT> v = a;
+      if (pr) { v.L = a.L / 2; v.ld = a.ld * 2; }
+      return v;
+    };
     // x_source = noise_res[i](noise_convs[i](har | har_source))
     {
       const ConvW& nc = hilo ? h->noise_convs16[i] : h->noise_convs[i];
@@ -887,18 +955,18 @@ int Fwd<AT>::run(const float* asr, const float* f0, const float* nn, const float
       float* bias_c2 = nullptr;
       if (meanfree) {
         float* bias_nc = ar.alloc<float>((int64_t)B * C);
-        bias_c2 = ar.alloc<float>((int64_t)B * C);
+        bias_c2 = ar.alloc<float>((int64_t)B * C * reps);
         RUN(launch_noise_bias(hs_mean, W<float>(h->noise_wsum[i]), W<float>(nc.bias),
-                              W<float>(h->noise_res[i].c2[0].bias), bias_nc, bias_c2, C, B, st));
+                              W<float>(h->noise_res[i].c2[0].bias), bias_nc, bias_c2, C, B, st, reps));
         io.bias_b = bias_nc;
       }
       const int64_t m = ar.mark();
       int rc = conv(nc, io);
       if (rc) return rc;
-      rc = finalize(last_partials, last_tiles, last_cols, C, Ls, h->noise_res[i].n1[0], 0);
+      rc = finalize(last_partials, last_tiles, last_cols, C, Ls, h->noise_res[i].n1[0], 0, reps);
       if (rc) return rc;
       ar.release(m);
-      rc = resblock1(h->noise_res[i], xs, xs, tmp, xs, 1.f, 0, bias_c2);
+      rc = resblock1(h->noise_res[i], vw(xs), vw(xs), vw(tmp), vw(xs), 1.f, 0, bias_c2, pr);
       if (rc) return rc;
     }
     // x = ups[i](act(x)) (+ reflection pad) + x_source, with statistics for the three resblocks
@@ -921,13 +989,14 @@ int Fwd<AT>::run(const float* asr, const float* f0, const float* nn, const float
                                     (int64_t)last_tiles * last_cols * 2, B, st));
       }
       for (int j = 0; j < nk; ++j) {
-        rc = finalize(last_partials, last_tiles, last_cols, C, Ls, h->resblocks[i * nk + j].n1[0], 0);
+        rc = finalize(last_partials, last_tiles, last_cols, C, Ls, h->resblocks[i * nk + j].n1[0], 0, reps);
         if (rc) return rc;
       }
       ar.release(m);
     }
     for (int j = 0; j < nk; ++j) {
-      int rc = resblock1(h->resblocks[i * nk + j], xm, runb, tmp, outb, 1.f / (float)nk, j > 0 ? 1 : 0);
+      int rc = resblock1(h->resblocks[i * nk + j], vw(xm), vw(runb), vw(tmp), vw(outb), 1.f / (float)nk,
+                         j > 0 ? 1 : 0, nullptr, pr);
       if (rc) return rc;
     }
     x = outb;
@@ -944,6 +1013,17 @@ int Fwd<AT>::run(const float* asr, const float* f0, const float* nn, const float
     int rc = conv(h->conv_post, io);
     if (rc) return rc;
     RUN(launch_istft(cp, ldh, B, L2, wav, st));
+  } else if (DT<AT>::id == ST2_DT_BF16 && h->conv_post_p.w16 >= 0 && x.ld == 32 && x.L % 2 == 0) {
+    // row-pair form on the tensor cores: fp32 rows of 32 columns, columns 0/1 = samples 2q / 2q+1
+    const int Lp = x.L / 2, ldp = h->conv_post_p.n16;
+    float* cp = ar.alloc<float>((int64_t)B * Lp * ldp);
+    ConvIO io;
+    io.x = x.p; io.x_dtype = DT<AT>::id; io.x_bstride = x.bstride; io.ldx = 2 * x.ld; io.Lin = Lp;
+    io.act = ST2_ACT_SNAKE; io.alpha = W<float>(h->alpha_post_p);  // hifigan.py:342
+    io.y = cp; io.y_dtype = ST2_DT_F32; io.y_bstride = (int64_t)Lp * ldp; io.ldy = ldp; io.Lout = Lp;
+    int rc = conv(h->conv_post_p, io);
+    if (rc) return rc;
+    RUN(launch_cols_tanh(cp, ldp, 2, wav, (int64_t)B * Lw, st));
   } else {
     ConvIO io;
     io.x = x.p; io.x_dtype = DT<AT>::id; io.x_bstride = x.bstride; io.ldx = x.ld; io.Lin = x.L;

@@ -54,7 +54,7 @@ constexpr int SF_WARPS = 8;
 __global__ void __launch_bounds__(SF_WARPS * 32)
 stats_finalize_kernel(const float* __restrict__ partials, int n_tiles, int n_cols, int C,
                       double inv_count, const float* __restrict__ hg, int h_stride, int Cn,
-                      float* __restrict__ ss, int ss_stride, int c_off) {
+                      float* __restrict__ ss, int ss_stride, int c_off, int reps) {
   __shared__ double red[SF_WARPS][32][2];
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int c = blockIdx.x * 32 + lane;
@@ -97,19 +97,23 @@ stats_finalize_kernel(const float* __restrict__ partials, int n_tiles, int n_col
   const double gamma = hg[(int64_t)b * h_stride + c_off + c];
   const double beta = hg[(int64_t)b * h_stride + Cn + c_off + c];
   const double scale = (1.0 + gamma) * rstd;
-  float* o = ss + ((int64_t)b * ss_stride + c_off + c) * 2;
-  o[0] = (float)scale;
-  o[1] = (float)(beta - mean * scale);
+  // reps > 1: the consumer reads the tensor as rows of reps*C columns (row-pair view of a
+  // 32-channel stage), so the pair is repeated at c, c + C, ...
+  for (int r = 0; r < reps; ++r) {
+    float* o = ss + ((int64_t)b * ss_stride + c_off + c + r * C) * 2;
+    o[0] = (float)scale;
+    o[1] = (float)(beta - mean * scale);
+  }
 }
 
 // hg points at this norm layer's gamma block inside the concatenated fc output; the layer
 // normalises Cn channels, of which [c_off, c_off + C) are finalised by this launch.
 int launch_stats_finalize(const float* partials, int n_tiles, int n_cols, int C, int64_t count,
                           const float* hg, int h_stride, int Cn, float* ss, int ss_stride,
-                          int c_off, int B, cudaStream_t st) {
+                          int c_off, int B, cudaStream_t st, int reps) {
   dim3 grid(ceil_div(C, 32), B);
   stats_finalize_kernel<<<grid, SF_WARPS * 32, 0, st>>>(partials, n_tiles, n_cols, C, 1.0 / (double)count,
-                                                       hg, h_stride, Cn, ss, ss_stride, c_off);
+                                                       hg, h_stride, Cn, ss, ss_stride, c_off, reps);
   ST2_LAUNCH_OK("stats_finalize");
   return ST2_OK;
 }
@@ -414,12 +418,14 @@ __global__ void __launch_bounds__(256) row_mean_kernel(const float* __restrict__
 // bias_c2_add[b,c]   = bias_c2[c] + bias_nc[c] + mean[b]*wsum[c]  (conv2 bias with kappa restored)
 __global__ void noise_bias_kernel(const float* __restrict__ mean, const float* __restrict__ wsum,
                                   const float* __restrict__ bias_nc, const float* __restrict__ bias_c2,
-                                  float* __restrict__ bias_nc_shift, float* __restrict__ bias_c2_add, int C) {
+                                  float* __restrict__ bias_nc_shift, float* __restrict__ bias_c2_add, int C,
+                                  int reps) {
   const int c = blockIdx.x * blockDim.x + threadIdx.x, b = blockIdx.y;
   if (c >= C) return;
   const float k = mean[b] * wsum[c];
   bias_nc_shift[(int64_t)b * C + c] = -k;
-  bias_c2_add[(int64_t)b * C + c] = bias_c2[c] + bias_nc[c] + k;
+  for (int r = 0; r < reps; ++r)  // repeated for the row-pair view (rows of reps*C columns)
+    bias_c2_add[((int64_t)b * reps + r) * C + c] = bias_c2[c] + bias_nc[c] + k;
 }
 int launch_row_mean(const float* x, int64_t L, float* mean, int B, cudaStream_t st) {
   row_mean_kernel<<<B, 256, 0, st>>>(x, L, mean);
@@ -427,9 +433,9 @@ int launch_row_mean(const float* x, int64_t L, float* mean, int B, cudaStream_t 
   return ST2_OK;
 }
 int launch_noise_bias(const float* mean, const float* wsum, const float* bias_nc, const float* bias_c2,
-                      float* bias_nc_shift, float* bias_c2_add, int C, int B, cudaStream_t st) {
+                      float* bias_nc_shift, float* bias_c2_add, int C, int B, cudaStream_t st, int reps) {
   dim3 grid(ceil_div(C, 128), B);
-  noise_bias_kernel<<<grid, 128, 0, st>>>(mean, wsum, bias_nc, bias_c2, bias_nc_shift, bias_c2_add, C);
+  noise_bias_kernel<<<grid, 128, 0, st>>>(mean, wsum, bias_nc, bias_c2, bias_nc_shift, bias_c2_add, C, reps);
   ST2_LAUNCH_OK("noise_bias");
   return ST2_OK;
 }
@@ -463,6 +469,18 @@ __global__ void tanh_kernel(float* __restrict__ x, int64_t n) {
 int launch_tanh_inplace(float* x, int64_t n, cudaStream_t st) {
   tanh_kernel<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(x, n);
   ST2_LAUNCH_OK("tanh");
+  return ST2_OK;
+}
+
+// HiFi-GAN head on the tensor-core path: conv_post ran on row pairs and left fp32 rows of ld columns
+// whose first ncol entries are consecutive samples; wav[i] = tanh(cp[i / ncol][i % ncol]).
+__global__ void cols_tanh_kernel(const float* __restrict__ cp, int ld, int ncol, float* __restrict__ wav, int64_t n) {
+  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) wav[i] = tanhf(cp[(i / ncol) * ld + (i % ncol)]);
+}
+int launch_cols_tanh(const float* cp, int ld, int ncol, float* wav, int64_t n, cudaStream_t st) {
+  cols_tanh_kernel<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(cp, ld, ncol, wav, n);
+  ST2_LAUNCH_OK("cols_tanh");
   return ST2_OK;
 }
 
