@@ -38,6 +38,7 @@ WORKLOADS = {
     "c2": ("istftnet", 32, 800, "BASELINE config 1: LJSpeech iSTFTNet B=32 x 800 frames (10 s each)"),
     "c3": ("istftnet", 64, 800, "BASELINE config 2: multispeaker B=64 x 800 frames, one style row per item"),
     "c4": ("hifigan", 32, 800, "BASELINE config 3: HiFi-GAN decoder B=32 x 800 frames"),
+    "c5": ("istftnet", 512, 2400, "BASELINE config 4 on one GPU: B=512 x 2400 frames, decoded in micro-batches"),
     "c5shard": ("istftnet", 64, 2400, "BASELINE config 4 per-GPU shard at 8 GPUs: B=64 x 2400 frames (30 s each)"),
 }
 MFLOP_PER_FRAME = {"istftnet": 649.05, "hifigan": 873.90}  # SURVEY.md section 8d (2*MAC, convs + linears)

@@ -85,6 +85,8 @@ typedef struct St2ForwardOpts {
   float* har_out;           /* optional [B, 22, 60T+1] NCL: the har that was used */
   float* tap_decode;        /* optional [B, 512, T] NCL fp32: output of decode[3] (istftnet.py:522) */
   float* tap_stage[ST2_MAX_UPS]; /* optional [B, C_i, L_i] NCL fp32: x after generator stage i (:374) */
+  int64_t item_offset;      /* global index of row 0 (Philox counter = (item, sample)): a shard or a
+                               micro-batch of a larger batch draws the noise the full batch would */
 } St2ForwardOpts;
 
 /* Decoder(**kwargs): validates the config and builds the layer plan (no weights yet). */

@@ -85,6 +85,9 @@ class _DecoderBase(nn.Module):
         _NEXT_ID[0] += 1
         self.precision = "bf16"
         self.seed = 0
+        # a batch whose workspace would exceed this is decoded in micro-batches (utterances are
+        # independent, SURVEY 8d: config C5 is 512 x 2400 frames); 0 = never split
+        self.workspace_limit_bytes = 48 << 30
         self.eval()
 
     # ------------------------------------------------------------------ parameters
@@ -175,22 +178,24 @@ class _DecoderBase(nn.Module):
     def forward(self, asr: torch.Tensor, F0_curve: torch.Tensor, N: torch.Tensor, s: torch.Tensor, *,
                 noise: Optional[torch.Tensor] = None, har_source: Optional[torch.Tensor] = None,
                 har: Optional[torch.Tensor] = None, precision: Optional[str] = None,
-                return_excitation: bool = False, return_taps: bool = False):
+                return_excitation: bool = False, return_taps: bool = False, item_offset: int = 0):
         """Reference signature plus keyword-only extras; dispatches through the registered custom
-        op ``torch.ops.styletts2_b200.decoder_forward`` (see :meth:`_forward_native`)."""
+        op ``torch.ops.styletts2_b200.decoder_forward`` (see :meth:`_forward_native`).
+        ``item_offset`` is the global index of row 0 when the call decodes a slice of a larger batch
+        (the in-kernel noise is keyed by (seed, global item, sample))."""
         if return_excitation or return_taps:
             return self._forward_native(asr, F0_curve, N, s, noise=noise, har_source=har_source, har=har,
                                         precision=precision, return_excitation=return_excitation,
-                                        return_taps=return_taps)
+                                        return_taps=return_taps, item_offset=item_offset)
         from . import ops
         return torch.ops.styletts2_b200.decoder_forward(asr, F0_curve, N, s, noise, har_source, har,
                                                         ops.register_module(self),
-                                                        precision or self.precision)
+                                                        precision or self.precision, item_offset)
 
     def _forward_native(self, asr: torch.Tensor, F0_curve: torch.Tensor, N: torch.Tensor, s: torch.Tensor, *,
                         noise: Optional[torch.Tensor] = None, har_source: Optional[torch.Tensor] = None,
                         har: Optional[torch.Tensor] = None, precision: Optional[str] = None,
-                        return_excitation: bool = False, return_taps: bool = False):
+                        return_excitation: bool = False, return_taps: bool = False, item_offset: int = 0):
         """``Decoder.forward(asr, F0_curve, N, s)`` (istftnet.py:498).  Extra keyword-only inputs
         inject the excitation for reproducibility: ``noise`` [B, 300T, 9] (the randn_like draw of
         SineGen), ``har_source`` [B, 300T] (output of m_source) or ``har`` [B, 22, 60T+1]."""
@@ -227,10 +232,30 @@ class _DecoderBase(nn.Module):
             need = lib.st2_decoder_workspace_bytes(h, B, T, prec_id)
             if need < 0:
                 check(int(need), "st2_decoder_workspace_bytes")
+            limit = int(self.workspace_limit_bytes)
+            if limit and need > limit and B > 1 and not (return_excitation or return_taps):
+                # micro-batches: rows are independent, results are identical to the one-shot call
+                mb = max(1, min(B - 1, int(B * limit // need)))
+                while mb > 1 and lib.st2_decoder_workspace_bytes(h, mb, T, prec_id) > limit:
+                    mb -= 1
+                wav = torch.empty(B, 1, Lw, dtype=torch.float32, device=dev)
+                seed0, launches = self.seed, 0
+                sl = lambda t, a, b: None if t is None else t[a:b]
+                for lo in range(0, B, mb):
+                    hi = min(B, lo + mb)
+                    self.seed = seed0
+                    wav[lo:hi] = self._forward_native(
+                        asr_[lo:hi], f0_[lo:hi], n_[lo:hi], s_[lo:hi], noise=sl(noise_, lo, hi),
+                        har_source=sl(hs_, lo, hi), har=sl(har_, lo, hi), precision=prec,
+                        item_offset=item_offset + lo)
+                    launches += self.last_launches
+                self.last_launches = launches
+                return wav
             ws = torch.empty(int(need), dtype=torch.uint8, device=dev)
             wav = torch.empty(B, 1, Lw, dtype=torch.float32, device=dev)
             opts = _cabi.St2ForwardOpts()
             opts.precision = prec_id
+            opts.item_offset = int(item_offset)
             opts.noise, opts.har_source, opts.har = (t.data_ptr() if t is not None else None
                                                      for t in (noise_, hs_, har_))
             opts.seed = int(self.seed)

@@ -40,6 +40,8 @@ def decode_sharded(forward: Callable[..., torch.Tensor], asr, F0_curve, N, s, *,
     lo, hi = shard_range(B, world, rank)
     kw = {k: (v[lo:hi] if isinstance(v, torch.Tensor) and v.dim() > 0 and v.shape[0] == B else v) for k, v in kw.items()}
     if hi > lo:
+        if getattr(forward, "samples_per_frame", None) is not None:  # a Decoder module: same noise as the full batch
+            kw.setdefault("item_offset", lo)
         out = forward(asr[lo:hi], F0_curve[lo:hi], N[lo:hi], s[lo:hi], **kw)
     else:
         out = None

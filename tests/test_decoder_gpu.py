@@ -131,6 +131,32 @@ def test_batch_rows_are_independent_bitwise():
         assert torch.equal(full, again), prec  # deterministic: no atomics on the path
 
 
+@pytest.mark.parametrize("kind", ["istftnet", "hifigan"])
+def test_micro_batches_and_shards_draw_the_same_noise(kind):
+    """A batch decoded in micro-batches (workspace limit, config C5) or as shards with
+    ``item_offset`` equals the one-shot batch bit for bit, in-kernel Philox noise included."""
+    import synthetic as synth
+    from styletts2_b200.shard import decode_sharded
+    dec, sd, cfg = _get(kind)
+    inp = synth.synth_inputs(cfg, 5, 40, seed=21, with_noise=False)
+    a = {k: v.cuda() for k, v in inp.items()}
+    dec.seed = 77
+    full = dec(a["asr"], a["F0_curve"], a["N"], a["s"])
+    old = dec.workspace_limit_bytes
+    try:
+        dec.workspace_limit_bytes = 1  # forces micro-batches of one utterance
+        dec.seed = 77
+        chunked = dec(a["asr"], a["F0_curve"], a["N"], a["s"])
+    finally:
+        dec.workspace_limit_bytes = old
+    assert torch.equal(full, chunked)
+    parts = []
+    for r in range(2):
+        dec.seed = 77
+        parts.append(decode_sharded(dec, a["asr"], a["F0_curve"], a["N"], a["s"], world=2, rank=r))
+    assert torch.equal(full, torch.cat(parts, 0))
+
+
 def test_philox_excitation_runs_and_is_seeded():
     import synthetic as synth
     dec, sd, cfg = _get("istftnet")
