@@ -4,13 +4,14 @@
 //
 // for every (64-channel chunk, tap, 16-channel K step); NT (columns per tile) is 128, 64 or 32.
 // Activations are channels-last, so a conv tap is a ROW OFFSET into one staged activation tile: the
-// tile (256 output rows + (k-1)*dil halo) lives in the UMMA no-swizzle K-major core-matrix layout
-//      byte(row r, 16-byte channel group v) = v * (RPAD*16) + r * 16
-// in which every row shift keeps the layout canonical (core matrix = 8 consecutive rows x 16 B,
-// SBO = 128 B, LBO = RPAD*16 B), so all k taps read the same smem tile through descriptors that
-// differ only in their start address.  RPAD is odd, which makes 16-byte accesses of 8 planes
-// bank-conflict free.  Weights are pre-packed at load time into the same core-matrix layout, one
-// blob per (N tile, channel chunk, tap), streamed with cp.async.bulk (mbarrier complete_tx).
+// tile (256 output rows + (k-1)*dil halo, 64 channels) lives in the UMMA K-major SWIZZLE_128B layout
+//      byte(row r, 16-byte channel group v) = r * 128 + ((v ^ (r & 7)) << 4)      (1024-byte aligned)
+// i.e. one 128-byte row per time step, so the 8 lanes that fetch one row's 128 bytes from global
+// memory also write 128 contiguous bytes of shared memory (one wavefront; a plane-per-channel-group
+// layout costs LDGSTS eight).  The swizzle is a function of the absolute address, so all k taps read
+// the same smem tile through descriptors that differ only in their start address (+ dil rows per
+// tap).  Weights are pre-packed at load time into the no-swizzle core-matrix layout, one blob per
+// (N tile, channel chunk, tap), streamed with cp.async.bulk (mbarrier complete_tx).
 //
 // Persistent, warp-specialised CTA (1 per SM, 448 threads):
 //   warp 0      MMA issuer (one lane) + TMEM allocation (512 columns: 2 tiles x 2 accumulators)
@@ -57,8 +58,7 @@ constexpr int UM_SMEM_LIMIT = 227 * 1024;
 
 struct UmLayout {
   int n_tile;         // GEMM columns per tile (128 / 64 / 32)
-  int rpad;           // rows per plane of an A stage (odd)
-  int a_bytes;        // bytes per A stage (8 planes)
+  int a_bytes;        // bytes per A stage (rows x 128 B, multiple of 1024)
   int na;             // A stages in use
   int dist;           // prefetch distance of the producers, in chunks (na - 2)
   int w_bytes;        // bytes per weight stage (= 8 * n_tile * 16)
@@ -202,14 +202,17 @@ __device__ __forceinline__ uint32_t mbar_try(uint64_t* bar, uint32_t parity) {
       : "memory");
   return done;
 }
-// K-major, SWIZZLE_NONE shared-memory matrix descriptor (cute::UMMA::SmemDescriptor, version 1):
+// K-major shared-memory matrix descriptor (cute::UMMA::SmemDescriptor, version 1):
 // [0,14) start>>4, [16,30) leading (K-direction core-matrix) byte offset>>4,
-// [32,46) stride (8-row group) byte offset>>4, [46,48) version=1, [61,64) layout type 0.
-__device__ __forceinline__ uint64_t umma_desc(uint32_t saddr, uint32_t lbo_bytes, uint32_t sbo_bytes) {
+// [32,46) stride (8-row group) byte offset>>4, [46,48) version=1, [49,52) base offset,
+// [61,64) layout type (0 = no swizzle, 2 = SWIZZLE_128B).
+__device__ __forceinline__ uint64_t umma_desc(uint32_t saddr, uint32_t lbo_bytes, uint32_t sbo_bytes,
+                                              uint32_t layout_type = 0) {
   uint64_t d = (uint64_t)((saddr >> 4) & 0x3FFF);
   d |= (uint64_t)((lbo_bytes >> 4) & 0x3FFF) << 16;
   d |= (uint64_t)((sbo_bytes >> 4) & 0x3FFF) << 32;
   d |= (uint64_t)1 << 46;
+  d |= (uint64_t)layout_type << 61;
   return d;
 }
 // instruction descriptor (cute::UMMA::InstrDescriptor): D fp32, A/B bf16, both K-major, M 128, N n_tile
@@ -326,8 +329,9 @@ __device__ __forceinline__ void um_produce(const St2ConvParams& p, const UmLayou
   const int r_tot = UM_TM + (p.k - 1) * p.dil;
   const int nct = nchunks + lay.n_res + lay.n_acc;  // chunks per tile incl. residual / y_old rows
   const __nv_bfloat16* xg = reinterpret_cast<const __nv_bfloat16*>(p.x);
-  // this thread's 16-byte slot of row rbase in stage 0; row rbase + 32 i is i * 512 bytes further
-  const uint32_t a0 = smem_u32(smem + lay.off_a) + (uint32_t)v * (uint32_t)(lay.rpad * 16) + (uint32_t)rbase * 16u;
+  // this thread's 16-byte slot of row rbase in stage 0; row rbase + 32 i is i * 4096 bytes further
+  // (same row & 7, hence the same swizzled slot)
+  const uint32_t a0 = smem_u32(smem + lay.off_a) + (uint32_t)rbase * 128u + (uint32_t)((v ^ (rbase & 7)) << 4);
   const int64_t x_step = (int64_t)32 * p.ldx;
   constexpr bool IDENT = (ACT == ST2_ACT_NONE) && !HAS_SS;
 
@@ -341,7 +345,7 @@ __device__ __forceinline__ void um_produce(const St2ConvParams& p, const UmLayou
       const __nv_bfloat16* xb = xg + (int64_t)q.b * p.x_bstride + (int64_t)row0 * p.ldx + (q.c * UM_CK + v * 8);
 #pragma unroll
       for (int i = 0; i < UM_NI; ++i)
-        if (32 * i >= lo && 32 * i < hi) cp_async16(dst + (uint32_t)i * 512u, xb + i * x_step);
+        if (32 * i >= lo && 32 * i < hi) cp_async16(dst + (uint32_t)i * 4096u, xb + i * x_step);
     } else {
       // residual rows (row t >> res_shift of res) or y_old rows (row t of y): 64 columns of this N tile
       const int e = q.c - nchunks;
@@ -360,7 +364,7 @@ __device__ __forceinline__ void um_produce(const St2ConvParams& p, const UmLayou
       const int t = q.t0 + rbase;
 #pragma unroll
       for (int i = 0; i < UM_TM / 32; ++i)
-        if (t + 32 * i < p.Lout) cp_async16(dst + (uint32_t)i * 512u, sb + (int64_t)((t + 32 * i) >> shift) * ld);
+        if (t + 32 * i < p.Lout) cp_async16(dst + (uint32_t)i * 4096u, sb + (int64_t)((t + 32 * i) >> shift) * ld);
     }
   };
 
@@ -397,7 +401,7 @@ __device__ __forceinline__ void um_produce(const St2ConvParams& p, const UmLayou
       const int t = q.t0 + rbase;
 #pragma unroll
       for (int i = 0; i < UM_TM / 32; ++i)
-        if (t + 32 * i >= p.Lout) sts128(dst + (uint32_t)i * 512u, make_uint4(0u, 0u, 0u, 0u));
+        if (t + 32 * i >= p.Lout) sts128(dst + (uint32_t)i * 4096u, make_uint4(0u, 0u, 0u, 0u));
       fence_proxy_async_smem();
       mbar_arrive(&misc->a_full[q.stage]);
       return;
@@ -427,14 +431,14 @@ __device__ __forceinline__ void um_produce(const St2ConvParams& p, const UmLayou
 #pragma unroll
         for (int ii = 0; ii < UM_NI / 2; ++ii) {
           const int i = h * (UM_NI / 2) + ii;
-          if (32 * i < tot) raw[ii] = lds128(dst + (uint32_t)i * 512u);
+          if (32 * i < tot) raw[ii] = lds128(dst + (uint32_t)i * 4096u);
         }
       }
 #pragma unroll
       for (int ii = 0; ii < UM_NI / 2; ++ii) {
         const int i = h * (UM_NI / 2) + ii;
         if (32 * i >= tot) continue;
-        const uint32_t addr = dst + (uint32_t)i * 512u;
+        const uint32_t addr = dst + (uint32_t)i * 4096u;
         const bool valid = 32 * i >= lo && 32 * i < hi;
         if (IDENT) {
           if (!valid) sts128(addr, make_uint4(0u, 0u, 0u, 0u));
@@ -721,11 +725,12 @@ __global__ void __launch_bounds__(UM_THREADS, 1) conv_umma_kernel(const St2ConvP
     // ===================================================================== MMA issuer
     // The whole warp runs the (warp-uniform) loop and waits on the barriers; one elected lane issues
     // the MMAs and commits.  Descriptors are built once; per MMA only the 14-bit start-address field
-    // moves: + 2*rpad per 16-channel K step, + 128 rows per accumulator, + dil rows per tap.
+    // moves (16-byte units): A (SWIZZLE_128B rows of 128 B) + 2 per 16-channel K step, + 8 per row
+    // (128 rows per accumulator, dil rows per tap); W (core matrices) + 2*n_tile per K step.
     const uint32_t a_base = smem_u32(smem_raw + lay.off_a), w_base = smem_u32(smem_raw + lay.off_w);
-    const uint32_t a_lbo = (uint32_t)lay.rpad * 16u, w_lbo = (uint32_t)lay.n_tile * 16u;
-    const uint64_t a_desc0 = umma_desc(0, a_lbo, 128), w_desc0 = umma_desc(0, w_lbo, 128);
-    const uint32_t a_kstep = 2u * (uint32_t)lay.rpad, w_kstep = 2u * (uint32_t)lay.n_tile;  // in 16-byte units
+    const uint32_t w_lbo = (uint32_t)lay.n_tile * 16u;
+    const uint64_t a_desc0 = umma_desc(0, 16, 1024, 2), w_desc0 = umma_desc(0, w_lbo, 128);
+    const uint32_t a_kstep = 2u, w_kstep = 2u * (uint32_t)lay.n_tile;  // in 16-byte units
     const int nct = nchunks + lay.n_res + lay.n_acc;
     const uint32_t leader = elect_one() ? 1u : 0u;
     int as = 0, ws = 0;
@@ -751,14 +756,17 @@ __global__ void __launch_bounds__(UM_THREADS, 1) conv_umma_kernel(const St2ConvP
           uint32_t wnph = wph;
           if (wn == UM_W_STAGES) { wn = 0; wnph ^= 1u; }
           w_ready = mbar_try(&misc->w_full[wn], wnph);  // consumed after the MMAs below
-          const uint64_t ad = a_desc0 + (uint64_t)(a_u + (uint32_t)j * dil);
+          const uint32_t shift = (uint32_t)j * dil;  // rows
+          // the swizzle is a function of the absolute smem address: a start that is not a multiple of
+          // 8 rows needs no base offset (measured: base-offset variants fail the parity tests)
+          const uint64_t ad = a_desc0 + (uint64_t)(a_u + shift * 8u);
           const uint64_t bd = w_desc0 + (uint64_t)((w_base + (uint32_t)ws * (uint32_t)lay.w_bytes) >> 4);
           const uint32_t first = (c | j) != 0 ? 1u : 0u;
 #pragma unroll
           for (int acc = 0; acc < UM_NACC; ++acc) {
 #pragma unroll
             for (int ks = 0; ks < UM_CK / 16; ++ks)
-              umma_bf16_if(d0 + (uint32_t)(acc * lay.n_tile), ad + (uint64_t)(acc * 128 + ks * a_kstep),
+              umma_bf16_if(d0 + (uint32_t)(acc * lay.n_tile), ad + (uint64_t)(acc * 1024 + ks * a_kstep),
                            bd + (uint64_t)(ks * w_kstep), lay.idesc, ks != 0 ? 1u : first, leader);
           }
           umma_commit_if(&misc->w_empty[ws], leader);
@@ -882,8 +890,7 @@ static int um_layout(const St2ConvParams& p, int dev, UmLayout& lay) {
   lay.n_tile = umma_n_tile(p.n_cols);
   ST2_REQUIRE(lay.n_tile != 0, "conv_umma: n_cols must be a multiple of 32");
   const int halo = (p.k - 1) * p.dil;
-  lay.rpad = (UM_TM + halo) | 1;  // >= rows staged, odd
-  lay.a_bytes = (int)round_up((int64_t)8 * lay.rpad * 16, 128);
+  lay.a_bytes = (int)round_up((int64_t)(UM_TM + halo) * 128, 1024);
   lay.w_bytes = 8 * lay.n_tile * 16;
   const int esz = p.y_dtype == ST2_DT_F32 ? 4 : 2;
   lay.out_row = lay.n_tile * esz;
