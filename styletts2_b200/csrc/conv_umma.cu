@@ -423,7 +423,11 @@ __device__ __forceinline__ void um_produce(const St2ConvParams& p, const UmLayou
         sh[e] += hia[e];
       }
     }
-    // rows in two batches of 5: all shared-memory reads of a batch are issued before its arithmetic
+    // Rows in two batches of 5: all shared-memory reads of a batch are issued before its arithmetic,
+    // and the arithmetic is branch-free (one basic block per batch: 40 independent chains for the
+    // scheduler to interleave behind the MUFU latency).  Rows outside [0, Lin) are computed on
+    // whatever the slot holds and masked to zero (the conv's zero padding applies after the
+    // activation); only the halo rows i >= UM_TM/32 can lie outside the tile and are predicated.
 #pragma unroll
     for (int h = 0; h < 2; ++h) {
       uint4 raw[UM_NI / 2];
@@ -431,17 +435,18 @@ __device__ __forceinline__ void um_produce(const St2ConvParams& p, const UmLayou
 #pragma unroll
         for (int ii = 0; ii < UM_NI / 2; ++ii) {
           const int i = h * (UM_NI / 2) + ii;
-          if (32 * i < tot) raw[ii] = lds128(dst + (uint32_t)i * 4096u);
+          raw[ii] = make_uint4(0u, 0u, 0u, 0u);
+          if (i < UM_TM / 32 || 32 * i < tot) raw[ii] = lds128(dst + (uint32_t)i * 4096u);
         }
       }
 #pragma unroll
       for (int ii = 0; ii < UM_NI / 2; ++ii) {
         const int i = h * (UM_NI / 2) + ii;
-        if (32 * i >= tot) continue;
+        const bool in_tile = i < UM_TM / 32 || 32 * i < tot;
         const uint32_t addr = dst + (uint32_t)i * 4096u;
-        const bool valid = 32 * i >= lo && 32 * i < hi;
+        const uint32_t mask = (32 * i >= lo && 32 * i < hi) ? 0xFFFFFFFFu : 0u;
         if (IDENT) {
-          if (!valid) sts128(addr, make_uint4(0u, 0u, 0u, 0u));
+          if (in_tile && mask == 0u) sts128(addr, make_uint4(0u, 0u, 0u, 0u));
           continue;
         }
         const uint32_t w[4] = {raw[ii].x, raw[ii].y, raw[ii].z, raw[ii].w};
@@ -452,9 +457,9 @@ __device__ __forceinline__ void um_produce(const St2ConvParams& p, const UmLayou
                                         hia[2 * e2], p.slope);
           const float hi_ = um_act<ACT>(bf16hi(w[e2]), sc[2 * e2 + 1], sh[2 * e2 + 1], wsc[2 * e2 + 1],
                                         wsh[2 * e2 + 1], hia[2 * e2 + 1], p.slope);
-          o[e2] = valid ? pack_bf16x2(lo_, hi_) : 0u;  // conv zero padding applies after the activation
+          o[e2] = pack_bf16x2(lo_, hi_) & mask;
         }
-        sts128(addr, make_uint4(o[0], o[1], o[2], o[3]));
+        if (in_tile) sts128(addr, make_uint4(o[0], o[1], o[2], o[3]));
       }
     }
     fence_proxy_async_smem();
@@ -594,7 +599,8 @@ __device__ __forceinline__ void um_epilogue(const St2ConvParams& p, const UmLayo
     const uint32_t tb = t_it & 1, tph = (t_it >> 1) & 1;
     float* bias_s = misc->bias[tb];
     if (et < n_tile) bias_s[et] = (p.bias ? p.bias[(int64_t)tl.b * p.bias_bstride + tl.nt * n_tile + et] : 0.f) * scale;
-    float s0 = 0.f, s1 = 0.f, q0 = 0.f, q1 = 0.f;
+    // two independent accumulator sets (even / odd rows) halve the dependent FADD/FFMA chains
+    float s0 = 0.f, s1 = 0.f, q0 = 0.f, q1 = 0.f, s0b = 0.f, s1b = 0.f, q0b = 0.f, q1b = 0.f;
     mbar_wait(&misc->t_full[tb], tph, 5);
     tc_fence_after();
 #pragma unroll 1
@@ -644,11 +650,14 @@ __device__ __forceinline__ void um_epilogue(const St2ConvParams& p, const UmLayo
 #pragma unroll 1
           for (int m = 0; m < ncp; m += 8) {
 #pragma unroll
-            for (int i = 0; i < 8; ++i) {
+            for (int i = 0; i < 8; i += 2) {
               const uint32_t w = lds32(col_addr[i] + (uint32_t)m * 128u);
-              const float a = bf16lo(w), b = bf16hi(w);
+              const uint32_t w2 = lds32(col_addr[i + 1] + (uint32_t)m * 128u);
+              const float a = bf16lo(w), b = bf16hi(w), a2 = bf16lo(w2), b2 = bf16hi(w2);
               s0 += a; q0 = fmaf(a, a, q0);
               s1 += b; q1 = fmaf(b, b, q1);
+              s0b += a2; q0b = fmaf(a2, a2, q0b);
+              s1b += b2; q1b = fmaf(b2, b2, q1b);
             }
           }
         } else {
@@ -664,10 +673,10 @@ __device__ __forceinline__ void um_epilogue(const St2ConvParams& p, const UmLayo
     if (!OUT_F32 && p.stats) {
       // combine the row groups: sred[grp * n_tile + col] (reads of the previous tile's sums finished
       // before that tile's threads passed the barriers above)
-      misc->sred[grp * n_tile + 2 * cp][0] = s0;
-      misc->sred[grp * n_tile + 2 * cp][1] = q0;
-      misc->sred[grp * n_tile + 2 * cp + 1][0] = s1;
-      misc->sred[grp * n_tile + 2 * cp + 1][1] = q1;
+      misc->sred[grp * n_tile + 2 * cp][0] = s0 + s0b;
+      misc->sred[grp * n_tile + 2 * cp][1] = q0 + q0b;
+      misc->sred[grp * n_tile + 2 * cp + 1][0] = s1 + s1b;
+      misc->sred[grp * n_tile + 2 * cp + 1][1] = q1 + q1b;
       named_bar_sync(1, UM_EPI_THREADS);
       if (et < n_tile) {
         const int ngrp = 128 / ncp;
