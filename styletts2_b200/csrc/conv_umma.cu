@@ -75,7 +75,10 @@ struct UmMisc {
   uint64_t w_full[UM_W_STAGES], w_empty[UM_W_STAGES];
   uint64_t t_full[2], t_empty[2];
   uint32_t tmem_base, pad_;
-  alignas(16) float bias[2][128];
+  // bias through the tensor core: one K=16 step with A = ones_a (every row (1, 1, 0, ...)) and
+  // B = bias_b[tb] (per column (hi, lo, 0, ...) bf16 split of the fp32 bias), issued first for each tile
+  alignas(128) uint4 bias_b[2][128];
+  alignas(128) uint4 ones_a[16];   // core matrix k 0..7 = rows of (1, 1, 0, 0, 0, 0, 0, 0); k 8..15 = zeros
   alignas(16) float sred[256][2];
 };
 
@@ -265,6 +268,27 @@ __device__ __forceinline__ uint32_t pack_bf16x2(float lo, float hi) {
   __nv_bfloat162 t = __floats2bfloat162_rn(lo, hi);
   return *reinterpret_cast<uint32_t*>(&t);
 }
+// packed fp32x2 arithmetic (sm_100: FADD2 / FFMA2, one issue slot for two lanes of math)
+__device__ __forceinline__ uint64_t f2_pack(uint32_t lo, uint32_t hi) {
+  uint64_t r;
+  asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "r"(lo), "r"(hi));
+  return r;
+}
+__device__ __forceinline__ void f2_unpack(uint64_t v, float& lo, float& hi) {
+  asm("mov.b64 {%0, %1}, %2;" : "=f"(lo), "=f"(hi) : "l"(v));
+}
+__device__ __forceinline__ uint64_t f2_add(uint64_t a, uint64_t b) {
+  uint64_t d;
+  asm("add.rn.f32x2 %0, %1, %2;" : "=l"(d) : "l"(a), "l"(b));
+  return d;
+}
+__device__ __forceinline__ uint64_t f2_fma(uint64_t a, uint64_t b, uint64_t c) {
+  uint64_t d;
+  asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(d) : "l"(a), "l"(b), "l"(c));
+  return d;
+}
+// bf16x2 word -> its two values as a packed fp32x2 (low half first)
+__device__ __forceinline__ uint64_t f2_from_bf16x2(uint32_t w) { return f2_pack(w << 16, w & 0xFFFF0000u); }
 __device__ __forceinline__ float bf16lo(uint32_t u) { return __uint_as_float(u << 16); }
 __device__ __forceinline__ float bf16hi(uint32_t u) { return __uint_as_float(u & 0xFFFF0000u); }
 
@@ -530,6 +554,13 @@ __device__ __forceinline__ void um_produce(const St2ConvParams& p, const UmLayou
   cp_async_wait<0>();
 }
 
+// fp32 bias -> (hi, lo, 0, ...) bf16: one 16-byte K group of the bias operand
+__device__ __forceinline__ uint4 um_bias_split(float b) {
+  const __nv_bfloat16 hi = __float2bfloat16_rn(b);
+  const __nv_bfloat16 lo = __float2bfloat16_rn(b - __bfloat162float(hi));
+  return make_uint4((uint32_t)__bfloat16_as_ushort(hi) | ((uint32_t)__bfloat16_as_ushort(lo) << 16), 0u, 0u, 0u);
+}
+
 // Staging tile: 128 rows x out_row bytes as out_row/128 column segments of [128 rows][128 B], each in
 // the TMA SWIZZLE_128B pattern (16-byte chunk index ^ (row & 7)), so that row-per-thread 16-byte
 // stores and the column reads of the statistics pass are both bank-conflict free.
@@ -539,20 +570,14 @@ __device__ __forceinline__ uint32_t um_stg_addr(uint32_t stg, int row, int byte_
          (uint32_t)(byte_in_row & 15);
 }
 
-// scale / bias one 32-column block of this thread's row and write it to the staging tile.
+// scale one 32-column block of this thread's row and write it to the staging tile.
 // chunk_addr[j] = address of 16-byte chunk j of this row in column segment 0 (swizzle applied).
 template <bool OUT_F32>
 __device__ __forceinline__ void um_stage32(const uint32_t (&chunk_addr)[8], int cb, const uint32_t (&v)[32],
-                                           const float* bias_s, float scale) {
+                                           float scale) {
   float o[32];
 #pragma unroll
-  for (int g = 0; g < 8; ++g) {
-    const float4 b4 = *reinterpret_cast<const float4*>(bias_s + cb * 32 + g * 4);
-    o[4 * g] = fmaf(__uint_as_float(v[4 * g]), scale, b4.x);
-    o[4 * g + 1] = fmaf(__uint_as_float(v[4 * g + 1]), scale, b4.y);
-    o[4 * g + 2] = fmaf(__uint_as_float(v[4 * g + 2]), scale, b4.z);
-    o[4 * g + 3] = fmaf(__uint_as_float(v[4 * g + 3]), scale, b4.w);
-  }
+  for (int g = 0; g < 32; ++g) o[g] = __uint_as_float(v[g]) * scale;  // the bias is already in the accumulator
   if (OUT_F32) {  // 32 columns = one 128-byte segment
     const uint32_t seg = (uint32_t)cb * 16384u;
 #pragma unroll
@@ -597,16 +622,25 @@ __device__ __forceinline__ void um_epilogue(const St2ConvParams& p, const UmLayo
   for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, ++t_it) {
     const UmTile tl = um_tile(tile, n_ttiles, n_ntiles);
     const uint32_t tb = t_it & 1, tph = (t_it >> 1) & 1;
-    float* bias_s = misc->bias[tb];
-    if (et < n_tile) bias_s[et] = (p.bias ? p.bias[(int64_t)tl.b * p.bias_bstride + tl.nt * n_tile + et] : 0.f) * scale;
+    // bias of the tile that will use this TMEM buffer next (two tiles ahead), loaded early
+    const int tile2 = tile + 2 * (int)gridDim.x;
+    float bias2 = 0.f;
+    if (et < n_tile && tile2 < total_tiles && p.bias) {
+      const UmTile t2 = um_tile(tile2, n_ttiles, n_ntiles);
+      bias2 = __ldg(p.bias + (int64_t)t2.b * p.bias_bstride + t2.nt * n_tile + et);
+    }
     // two independent accumulator sets (even / odd rows) halve the dependent FADD/FFMA chains
-    float s0 = 0.f, s1 = 0.f, q0 = 0.f, q1 = 0.f, s0b = 0.f, s1b = 0.f, q0b = 0.f, q1b = 0.f;
+    // (sum, sum of squares) of this thread's two columns as packed fp32x2
+    uint64_t sa = 0ull, qa = 0ull, sb = 0ull, qb = 0ull;
     mbar_wait(&misc->t_full[tb], tph, 5);
     tc_fence_after();
+    // this tile's bias MMA has completed: its operand slot can take the next bias; the t_empty arrive
+    // below (after the fence) hands it to the MMA warp together with the TMEM buffer
+    if (et < n_tile) misc->bias_b[tb][et] = um_bias_split(bias2);
 #pragma unroll 1
     for (int acc = 0; acc < UM_NACC; ++acc) {
       // the staging tile is free once the previous TMA store has read it (issued by thread 0) and
-      // every thread has finished its statistics pass; this barrier also publishes bias_s
+      // every thread has finished its statistics pass
       if (et == 0) bulk_wait_read0();
       named_bar_sync(2, UM_EPI_THREADS);
       const uint32_t tcol = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)((tb * UM_NACC + acc) * n_tile);
@@ -615,7 +649,7 @@ __device__ __forceinline__ void um_epilogue(const St2ConvParams& p, const UmLayo
         tmem_ld32_nowait(tcol, v);
         tmem_ld_wait();
         tmem_ld_fence(v);
-        um_stage32<OUT_F32>(chunk_addr, 0, v, bias_s, scale);
+        um_stage32<OUT_F32>(chunk_addr, 0, v, scale);
       } else {
 #pragma unroll 1
         for (int cb = 0; cb < ncb; cb += 2) {
@@ -625,17 +659,17 @@ __device__ __forceinline__ void um_epilogue(const St2ConvParams& p, const UmLayo
           tmem_ld_wait();
           tmem_ld_fence(v0);
           tmem_ld_fence(v1);
-          um_stage32<OUT_F32>(chunk_addr, cb, v0, bias_s, scale);
-          um_stage32<OUT_F32>(chunk_addr, cb + 1, v1, bias_s, scale);
+          um_stage32<OUT_F32>(chunk_addr, cb, v0, scale);
+          um_stage32<OUT_F32>(chunk_addr, cb + 1, v1, scale);
         }
       }
+      // staging and bias_b (generic proxy) -> TMA store / next bias MMA (async proxy)
+      fence_proxy_async_smem();
       if (acc == UM_NACC - 1) {
         // all TMEM reads of this buffer are complete (tcgen05.wait::ld above)
         tc_fence_before();
         mbar_arrive(&misc->t_empty[tb]);
       }
-      // staging (generic proxy) -> TMA store (async proxy), one store per 128-byte column segment
-      fence_proxy_async_smem();
       named_bar_sync(1, UM_EPI_THREADS);
       const int row0 = tl.t0 + acc * 128;
       if (et == 0 && row0 < p.Lout) {
@@ -653,19 +687,16 @@ __device__ __forceinline__ void um_epilogue(const St2ConvParams& p, const UmLayo
             for (int i = 0; i < 8; i += 2) {
               const uint32_t w = lds32(col_addr[i] + (uint32_t)m * 128u);
               const uint32_t w2 = lds32(col_addr[i + 1] + (uint32_t)m * 128u);
-              const float a = bf16lo(w), b = bf16hi(w), a2 = bf16lo(w2), b2 = bf16hi(w2);
-              s0 += a; q0 = fmaf(a, a, q0);
-              s1 += b; q1 = fmaf(b, b, q1);
-              s0b += a2; q0b = fmaf(a2, a2, q0b);
-              s1b += b2; q1b = fmaf(b2, b2, q1b);
+              const uint64_t x = f2_from_bf16x2(w), x2 = f2_from_bf16x2(w2);
+              sa = f2_add(sa, x); qa = f2_fma(x, x, qa);
+              sb = f2_add(sb, x2); qb = f2_fma(x2, x2, qb);
             }
           }
         } else {
           for (int r = 0; r < r1; ++r) {
             const uint32_t w = lds32(col_addr[r & 7] + (uint32_t)(r >> 3) * 1024u);
-            const float a = bf16lo(w), b = bf16hi(w);
-            s0 += a; q0 = fmaf(a, a, q0);
-            s1 += b; q1 = fmaf(b, b, q1);
+            const uint64_t x = f2_from_bf16x2(w);
+            sa = f2_add(sa, x); qa = f2_fma(x, x, qa);
           }
         }
       }
@@ -673,10 +704,13 @@ __device__ __forceinline__ void um_epilogue(const St2ConvParams& p, const UmLayo
     if (!OUT_F32 && p.stats) {
       // combine the row groups: sred[grp * n_tile + col] (reads of the previous tile's sums finished
       // before that tile's threads passed the barriers above)
-      misc->sred[grp * n_tile + 2 * cp][0] = s0 + s0b;
-      misc->sred[grp * n_tile + 2 * cp][1] = q0 + q0b;
-      misc->sred[grp * n_tile + 2 * cp + 1][0] = s1 + s1b;
-      misc->sred[grp * n_tile + 2 * cp + 1][1] = q1 + q1b;
+      float s0, s1, q0, q1;
+      f2_unpack(f2_add(sa, sb), s0, s1);
+      f2_unpack(f2_add(qa, qb), q0, q1);
+      misc->sred[grp * n_tile + 2 * cp][0] = s0;
+      misc->sred[grp * n_tile + 2 * cp][1] = q0;
+      misc->sred[grp * n_tile + 2 * cp + 1][0] = s1;
+      misc->sred[grp * n_tile + 2 * cp + 1][1] = q1;
       named_bar_sync(1, UM_EPI_THREADS);
       if (et < n_tile) {
         const int ngrp = 128 / ncp;
@@ -718,6 +752,24 @@ __global__ void __launch_bounds__(UM_THREADS, 1) conv_umma_kernel(const St2ConvP
     }
     fence_barrier_init();
   }
+  {  // operands of the bias MMA: ones_a, and bias_b of this CTA's first two tiles
+    const int et0 = (int)threadIdx.x - UM_EPI_WARP0 * 32;
+    if (et0 >= 0 && et0 < UM_EPI_THREADS) {
+      if (et0 < 16) misc->ones_a[et0] = make_uint4(et0 < 8 ? 0x3F803F80u : 0u, 0u, 0u, 0u);
+      if (et0 < lay.n_tile) {
+        for (int i = 0; i < 2; ++i) {
+          const int tile = (int)blockIdx.x + i * (int)gridDim.x;
+          float b = 0.f;
+          if (tile < total_tiles && p.bias) {
+            const UmTile t = um_tile(tile, n_ttiles, n_ntiles);
+            b = __ldg(p.bias + (int64_t)t.b * p.bias_bstride + t.nt * lay.n_tile + et0);
+          }
+          misc->bias_b[i][et0] = um_bias_split(b);
+        }
+      }
+      fence_proxy_async_smem();
+    }
+  }
   if (warp == 0) {  // TMEM: all 512 columns (this CTA owns the SM: > 114 KB smem, 1 block/SM)
     asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(
                      smem_u32(&misc->tmem_base)),
@@ -752,6 +804,14 @@ __global__ void __launch_bounds__(UM_THREADS, 1) conv_umma_kernel(const St2ConvP
       const uint32_t tb = t_it & 1, tph = (t_it >> 1) & 1;
       mbar_wait(&misc->t_empty[tb], tph ^ 1, 1);
       const uint32_t d0 = tmem_base + (uint32_t)(tb * UM_NACC * lay.n_tile);
+      tc_fence_after();
+      {  // D = ones x bias: A rows all alias one core matrix (SBO 0), B's second K group aliases the first (LBO 0, x 0)
+        const uint64_t od = umma_desc(smem_u32(misc->ones_a), 128, 0);
+        const uint64_t bd = umma_desc(smem_u32(misc->bias_b[tb]), 0, 128);
+#pragma unroll
+        for (int acc = 0; acc < UM_NACC; ++acc)
+          umma_bf16_if(d0 + (uint32_t)(acc * lay.n_tile), od, bd, lay.idesc, 0u, leader);
+      }
       for (int c = 0; c < nct; ++c) {
         mbar_wait(&misc->a_full[as], aph, 2);
         const uint32_t a_u = (a_base + (uint32_t)as * (uint32_t)lay.a_bytes) >> 4;
@@ -770,13 +830,12 @@ __global__ void __launch_bounds__(UM_THREADS, 1) conv_umma_kernel(const St2ConvP
           // 8 rows needs no base offset (measured: base-offset variants fail the parity tests)
           const uint64_t ad = a_desc0 + (uint64_t)(a_u + shift * 8u);
           const uint64_t bd = w_desc0 + (uint64_t)((w_base + (uint32_t)ws * (uint32_t)lay.w_bytes) >> 4);
-          const uint32_t first = (c | j) != 0 ? 1u : 0u;
 #pragma unroll
           for (int acc = 0; acc < UM_NACC; ++acc) {
 #pragma unroll
             for (int ks = 0; ks < UM_CK / 16; ++ks)
               umma_bf16_if(d0 + (uint32_t)(acc * lay.n_tile), ad + (uint64_t)(acc * 1024 + ks * a_kstep),
-                           bd + (uint64_t)(ks * w_kstep), lay.idesc, ks != 0 ? 1u : first, leader);
+                           bd + (uint64_t)(ks * w_kstep), lay.idesc, 1u, leader);
           }
           umma_commit_if(&misc->w_empty[ws], leader);
           ws = wn;
