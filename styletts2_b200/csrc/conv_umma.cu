@@ -103,16 +103,29 @@ __device__ __noinline__ void mbar_timeout(int which, uint32_t parity) {
          (int)blockIdx.x, (int)threadIdx.x, which, parity);
   __trap();
 }
+__device__ __forceinline__ uint64_t global_timer_ns() {
+  uint64_t t;
+  asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+  return t;
+}
+// try_wait carries a suspend-time hint, so a waiting thread sleeps in hardware instead of spinning
+// through issue slots the working warps need; the 4 s deadline is checked every 64 wake-ups
 __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity, int which) {
   const uint32_t addr = smem_u32(bar);
-  uint32_t done = 0;
-  for (uint32_t spin = 0; !done; ++spin) {
+  uint32_t done = 0, spin = 0;
+  uint64_t t0 = 0;
+  while (true) {
     asm volatile(
-        "{ .reg .pred p; mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2; selp.u32 %0, 1, 0, p; }"
+        "{ .reg .pred p; mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2, %3; selp.u32 %0, 1, 0, p; }"
         : "=r"(done)
-        : "r"(addr), "r"(parity)
+        : "r"(addr), "r"(parity), "r"(0x989680u)
         : "memory");
-    if (!done && spin > (1u << 24)) mbar_timeout(which, parity);
+    if (done) break;
+    if ((++spin & 63u) == 0u) {
+      const uint64_t now = global_timer_ns();
+      if (t0 == 0) t0 = now;
+      else if (now - t0 > 4000000000ull) mbar_timeout(which, parity);
+    }
   }
 }
 __device__ __forceinline__ void fence_barrier_init() {
@@ -447,26 +460,31 @@ __device__ __forceinline__ void um_produce(const St2ConvParams& p, const UmLayou
         sh[e] += hia[e];
       }
     }
-    // Rows in two batches of 5: all shared-memory reads of a batch are issued before its arithmetic,
-    // and the arithmetic is branch-free (one basic block per batch: 40 independent chains for the
-    // scheduler to interleave behind the MUFU latency).  Rows outside [0, Lin) are computed on
-    // whatever the slot holds and masked to zero (the conv's zero padding applies after the
-    // activation); only the halo rows i >= UM_TM/32 can lie outside the tile and are predicated.
+    // Rows in batches of 4 (+ a tail of 2 halo rows): all shared-memory reads of a batch are issued
+    // before its arithmetic, and the arithmetic is branch-free (one basic block per batch: 32
+    // independent chains for the scheduler to interleave behind the MUFU latency).  Rows outside
+    // [0, Lin) are computed on whatever the slot holds and masked to zero (the conv's zero padding
+    // applies after the activation).  Only the tail rows i >= UM_TM/32 can lie outside the tile:
+    // the tail is skipped by a warp-uniform test and its rows are predicated.
+    constexpr int NB = UM_TM / 32 / 4;  // full batches
 #pragma unroll
-    for (int h = 0; h < 2; ++h) {
-      uint4 raw[UM_NI / 2];
+    for (int h = 0; h <= NB; ++h) {
+      const int i0 = h * 4, cnt = h < NB ? 4 : UM_NI - 4 * NB;
+      if (h == NB && 32 * i0 + 4 * (ptid >> 5) >= r_tot) break;  // no row of this warp reaches the tail
+      uint4 raw[4];
       if (!IDENT) {
 #pragma unroll
-        for (int ii = 0; ii < UM_NI / 2; ++ii) {
-          const int i = h * (UM_NI / 2) + ii;
+        for (int ii = 0; ii < 4; ++ii) {
+          const int i = i0 + ii;
           raw[ii] = make_uint4(0u, 0u, 0u, 0u);
-          if (i < UM_TM / 32 || 32 * i < tot) raw[ii] = lds128(dst + (uint32_t)i * 4096u);
+          if (ii < cnt && (h < NB || 32 * i < tot)) raw[ii] = lds128(dst + (uint32_t)i * 4096u);
         }
       }
 #pragma unroll
-      for (int ii = 0; ii < UM_NI / 2; ++ii) {
-        const int i = h * (UM_NI / 2) + ii;
-        const bool in_tile = i < UM_TM / 32 || 32 * i < tot;
+      for (int ii = 0; ii < 4; ++ii) {
+        if (ii >= cnt) continue;
+        const int i = i0 + ii;
+        const bool in_tile = h < NB || 32 * i < tot;
         const uint32_t addr = dst + (uint32_t)i * 4096u;
         const uint32_t mask = (32 * i >= lo && 32 * i < hi) ? 0xFFFFFFFFu : 0u;
         if (IDENT) {
