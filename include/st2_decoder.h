@@ -87,6 +87,8 @@ typedef struct St2ForwardOpts {
   float* tap_stage[ST2_MAX_UPS]; /* optional [B, C_i, L_i] NCL fp32: x after generator stage i (:374) */
   int64_t item_offset;      /* global index of row 0 (Philox counter = (item, sample)): a shard or a
                                micro-batch of a larger batch draws the noise the full batch would */
+  const uint64_t* seed_dev; /* optional DEVICE pointer to the Philox seed, read by the kernel instead of
+                               `seed`: lets a captured CUDA graph draw fresh noise on every replay */
 } St2ForwardOpts;
 
 /* Decoder(**kwargs): validates the config and builds the layer plan (no weights yet). */

@@ -39,7 +39,7 @@ class St2ForwardOpts(C.Structure):
         ("precision", C.c_int), ("noise", C.c_void_p), ("har_source", C.c_void_p), ("har", C.c_void_p),
         ("seed", C.c_uint64), ("har_source_out", C.c_void_p), ("har_out", C.c_void_p),
         ("tap_decode", C.c_void_p), ("tap_stage", C.c_void_p * MAX_UPS),
-        ("item_offset", C.c_int64),
+        ("item_offset", C.c_int64), ("seed_dev", C.c_void_p),
     ]
 
 

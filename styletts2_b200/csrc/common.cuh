@@ -129,7 +129,7 @@ int launch_cols_tanh(const float* cp, int ld, int ncol, float* wav, int64_t n, c
 int launch_phase_scan(const float* f0, int B, int T, int spf, float* phase, cudaStream_t st);
 int launch_har_source(const float* f0, const float* phase, const float* noise, uint64_t seed,
                       const float* lin_w9, float lin_b, int B, int T, int spf, float* out,
-                      cudaStream_t st, int64_t item0 = 0);
+                      cudaStream_t st, int64_t item0 = 0, const uint64_t* seed_dev = nullptr);
 int launch_stft(const float* hs, int B, int Lw, float* har_cl, int ld, cudaStream_t st);
 int launch_stft_hilo(const float* hs, int B, int Lw, int rows_pad, __nv_bfloat16* har, cudaStream_t st);
 int launch_ncl_to_hilo(const float* ncl, int C, int L, int rows_pad, __nv_bfloat16* har, int B, cudaStream_t st);

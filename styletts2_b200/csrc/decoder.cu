@@ -894,7 +894,7 @@ int Fwd<AT>::run(const float* asr, const float* f0, const float* nn, const float
       float* ph = ar.alloc<float>((int64_t)B * 9 * T);
       float* hsw = ar.alloc<float>((int64_t)B * Lw);
       RUN(launch_phase_scan(f0, B, T, spf, ph, st));
-      RUN(launch_har_source(f0, ph, o.noise, o.seed, W<float>(h->lin_w), h->lin_b, B, T, spf, hsw, st, o.item_offset));
+      RUN(launch_har_source(f0, ph, o.noise, o.seed, W<float>(h->lin_w), h->lin_b, B, T, spf, hsw, st, o.item_offset, o.seed_dev));
       hs = hsw;
     }
     if (istft && hilo) RUN(launch_stft_hilo(hs, B, (int)Lw, rows_pad, har16, st));

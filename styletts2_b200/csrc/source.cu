@@ -131,7 +131,9 @@ __device__ __forceinline__ void box_muller(uint32_t a, uint32_t b, float& z0, fl
 __global__ void __launch_bounds__(256)
 har_source_kernel(const float* __restrict__ f0, const float* __restrict__ phase,
                   const float* __restrict__ noise, uint64_t seed, const float* __restrict__ lin_w,
-                  float lin_b, int T, int spf, float ratio, float* __restrict__ out, int64_t item0) {
+                  float lin_b, int T, int spf, float ratio, float* __restrict__ out, int64_t item0,
+                  const uint64_t* __restrict__ seed_dev) {
+  if (seed_dev) seed = *seed_dev;
   const int b = blockIdx.y;
   const int64_t Lw = (int64_t)T * spf;
   const int64_t n = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
@@ -178,11 +180,11 @@ har_source_kernel(const float* __restrict__ f0, const float* __restrict__ phase,
 
 int launch_har_source(const float* f0, const float* phase, const float* noise, uint64_t seed,
                       const float* lin_w9, float lin_b, int B, int T, int spf, float* out,
-                      cudaStream_t st, int64_t item0) {
+                      cudaStream_t st, int64_t item0, const uint64_t* seed_dev) {
   const int64_t Lw = (int64_t)T * spf;
   dim3 grid((unsigned)((Lw + 255) / 256), B);
   const float ratio = (float)(1.0 / (double)spf);
-  har_source_kernel<<<grid, 256, 0, st>>>(f0, phase, noise, seed, lin_w9, lin_b, T, spf, ratio, out, item0);
+  har_source_kernel<<<grid, 256, 0, st>>>(f0, phase, noise, seed, lin_w9, lin_b, T, spf, ratio, out, item0, seed_dev);
   ST2_LAUNCH_OK("har_source");
   return ST2_OK;
 }

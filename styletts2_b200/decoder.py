@@ -88,6 +88,11 @@ class _DecoderBase(nn.Module):
         # a batch whose workspace would exceed this is decoded in micro-batches (utterances are
         # independent, SURVEY 8d: config C5 is 512 x 2400 frames); 0 = never split
         self.workspace_limit_bytes = 48 << 30
+        # replay the forward as a CUDA graph (one per device / batch shape / precision, static buffers;
+        # inputs are copied in, the waveform is copied out): removes ~150 launch gaps per forward
+        self.cuda_graphs = False
+        self.max_graphs = 4
+        self._graphs: Dict[tuple, dict] = {}
         self.eval()
 
     # ------------------------------------------------------------------ parameters
@@ -251,6 +256,9 @@ class _DecoderBase(nn.Module):
                     launches += self.last_launches
                 self.last_launches = launches
                 return wav
+            if (self.cuda_graphs and noise_ is None and hs_ is None and har_ is None
+                    and not (return_excitation or return_taps) and not torch.cuda.is_current_stream_capturing()):
+                return self._forward_graph(h, asr_, f0_, n_, s_, int(need), prec_id, int(item_offset))
             ws = torch.empty(int(need), dtype=torch.uint8, device=dev)
             wav = torch.empty(B, 1, Lw, dtype=torch.float32, device=dev)
             opts = _cabi.St2ForwardOpts()
@@ -290,6 +298,59 @@ class _DecoderBase(nn.Module):
         if return_excitation:
             return wav, exc
         return wav
+
+
+def _graph_forward_impl(self, h, asr_, f0_, n_, s_, need, prec_id, item_offset):
+    """CUDA-graph replay of one forward (in-kernel Philox noise, no taps).  The graph owns static copies
+    of the inputs, the workspace, the output and a device-side seed; weights are baked in, so a reload
+    (new handle version) invalidates the cache."""
+    dev = asr_.device
+    idx = dev.index if dev.index is not None else torch.cuda.current_device()
+    B, _, T2 = asr_.shape
+    T = 2 * T2
+    Lw = T * self.samples_per_frame
+    key = (idx, B, T, prec_id, item_offset, self._native_version.get(idx))
+    g = self._graphs.get(key)
+    if g is None:
+        for k in [k for k in self._graphs if k[0] == idx and k[-1] != key[-1]]:
+            del self._graphs[k]          # stale weights
+        while len(self._graphs) >= max(1, int(self.max_graphs)):
+            del self._graphs[next(iter(self._graphs))]
+        g = {"asr": torch.empty_like(asr_), "f0": torch.empty_like(f0_), "n": torch.empty_like(n_),
+             "s": torch.empty_like(s_), "ws": torch.empty(need, dtype=torch.uint8, device=dev),
+             "wav": torch.empty(B, 1, Lw, dtype=torch.float32, device=dev),
+             "seed": torch.zeros(1, dtype=torch.int64, device=dev)}
+        opts = _cabi.St2ForwardOpts()
+        opts.precision = prec_id
+        opts.item_offset = item_offset
+        opts.seed_dev = g["seed"].data_ptr()
+        g["opts"] = opts
+
+        def launch():
+            stream = torch.cuda.current_stream(dev).cuda_stream
+            check(lib.st2_decoder_forward(h, ptr(g["asr"]), ptr(g["f0"]), ptr(g["n"]), ptr(g["s"]), ptr(g["wav"]),
+                                          ptr(g["ws"]), need, B, T, C.byref(opts), C.c_void_p(stream)),
+                  "st2_decoder_forward")
+        for src, dst in ((asr_, g["asr"]), (f0_, g["f0"]), (n_, g["n"]), (s_, g["s"])):
+            dst.copy_(src)
+        launch()                          # eager warm-up: first-use allocations happen outside the capture
+        torch.cuda.current_stream(dev).synchronize()
+        graph = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(graph):
+            launch()
+        g["graph"] = graph
+        g["launches"] = int(lib.st2_decoder_last_launches(h))
+        self._graphs[key] = g
+    for src, dst in ((asr_, g["asr"]), (f0_, g["f0"]), (n_, g["n"]), (s_, g["s"])):
+        dst.copy_(src, non_blocking=True)
+    g["seed"].fill_(int(self.seed))
+    g["graph"].replay()
+    self.seed += 1
+    self.last_launches = g["launches"]
+    return g["wav"].clone()
+
+
+_DecoderBase._forward_graph = _graph_forward_impl
 
 
 class IstftnetDecoder(_DecoderBase):
