@@ -473,7 +473,7 @@ static int do_load(St2Decoder* h, const St2Tensor* tensors, int n) {
   for (int i = 0; i < 3 && ok; ++i) ok = L.resblk1d(h->decode[i], "decode." + std::to_string(i), 1090, 1024, false);
   ok = ok && L.resblk1d(h->decode[3], "decode.3", 1090, 512, true);
   ok = ok && L.resblk1d(h->encode, "encode", c.dim_in + 2, 1024, false);
-  ok = ok && L.conv1d(h->asr_res, "asr_res.0", true, true, 1, 1, 0, 1, false);
+  ok = ok && L.conv1d(h->asr_res, "asr_res.0", true, true, 1, 1, 0, 1, true);
   for (int which = 0; which < 2 && ok; ++which) {
     const std::string p = which == 0 ? "F0_conv" : "N_conv";
     std::vector<float> w;
