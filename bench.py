@@ -129,6 +129,50 @@ def _oracle_cpu_decoder(kind, B, T, steps, warmup, threads=None):
     return audio_s / statistics.median(times), statistics.median(times) * 1e3, torch.get_num_threads()
 
 
+def _hbm_kernels(B, T, dev, peaks):
+    """the memory-bound kernels of the path (north star: "report achieved HBM GB/s"), timed alone at the
+    workload's shape with CUDA events; L2 is flushed (256 MB memset) before every timed launch."""
+    import torch
+    from styletts2_b200._cabi import lib, check
+    Lw, L2 = T * 300, T * 60 + 1
+    g = torch.Generator().manual_seed(3)
+    f0 = (torch.rand(B, T, generator=g) * 300 + 80).to(dev)
+    lw = torch.randn(9, generator=g).to(dev)
+    ph = torch.empty(B * 9 * T, device=dev)
+    hs = torch.empty(B, Lw, device=dev)
+    har = torch.empty(B, L2, 32, device=dev)
+    x = (torch.randn(B, L2, 32, generator=g) * 0.3).to(dev)
+    wav = torch.empty(B, Lw, device=dev)
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
+    st = torch.cuda.current_stream(dev).cuda_stream
+    cases = [
+        ("phase_scan + har_source (SineGen + SourceModuleHnNSF, Philox noise)", B * Lw * 4 + B * T * 4,
+         lambda: check(lib.st2_source_har(f0.data_ptr(), None, 7, lw.data_ptr(), 0.0, B, T, 300, ph.data_ptr(),
+                                          hs.data_ptr(), st))),
+        ("stft_kernel (20-point DFT, |X| and angle)", B * Lw * 4 + B * L2 * 128,
+         lambda: check(lib.st2_stft_har(hs.data_ptr(), B, Lw, har.data_ptr(), st))),
+        ("istft_kernel (exp/sin heads, inverse DFT, overlap-add)", B * L2 * 88 + B * Lw * 4,
+         lambda: check(lib.st2_istft_head(x.data_ptr(), B, L2, wav.data_ptr(), st))),
+    ]
+    out = []
+    for name, nbytes, fn in cases:
+        fn()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        ms = []
+        for _ in range(5):
+            flush.zero_()
+            e0.record()
+            fn()
+            e1.record()
+            torch.cuda.synchronize()
+            ms.append(e0.elapsed_time(e1))
+        t = statistics.median(ms)
+        gbs = nbytes / (t * 1e-3) / 1e9
+        out.append({"kernel": name, "algorithmic_bytes": nbytes, "us": round(t * 1e3, 1), "achieved_GBs": round(gbs, 1),
+                    "frac_of_hbm_peak": round(gbs / peaks["hbm"], 4)})
+    return out
+
+
 def run_reference(args):
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
@@ -308,6 +352,7 @@ def run_ours(args):
                 "ms_per_step": round(ms_e2e, 3)},
         "gpu_launches": int(launches_per_step * args.steps),
         "roofline": roof, "cpu_baseline": cpu, "clocks": clocks,
+        "hbm_kernels": _hbm_kernels(B, T, dev, peaks) if (world == 1 and kind == "istftnet") else None,
     }
     print(json.dumps(line), flush=True)
     if world > 1:

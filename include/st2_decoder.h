@@ -36,6 +36,9 @@ extern "C" {
 
 #define ST2_KIND_ISTFTNET 0 /* Modules/istftnet.py */
 #define ST2_KIND_HIFIGAN 1  /* Modules/hifigan.py  */
+#define ST2_KIND_F0N 2      /* ProsodyPredictor.F0Ntrain (models.py:562-590, 638-654): the step before the decoder.
+                               St2Config: dim_in = d_hid (512), style_dim; the other fields are ignored.  Uses
+                               create / load / num_keys / key / destroy of the decoder API and st2_f0n_* below. */
 
 /* arithmetic of the dense contractions */
 #define ST2_PREC_FP32 0 /* fp32 FFMA kernels, fp32 activations: the parity path        */
@@ -117,6 +120,15 @@ int64_t st2_decoder_workspace_bytes(const St2Decoder* h, int B, int T, int preci
 int st2_decoder_forward(St2Decoder* h, const float* asr, const float* f0, const float* n,
                         const float* s, float* wav_out, void* workspace, int64_t workspace_bytes,
                         int B, int T, const St2ForwardOpts* opts, void* stream);
+
+/* ProsodyPredictor.F0Ntrain(x, s) (models.py:651-654) on a handle created with kind ST2_KIND_F0N:
+ *   x [B, d_hid + style_dim, T] fp32 NCL (duration-expanded prosody encoding `en`), s [B, style_dim]
+ *   f0_out, n_out [B, 2T] fp32: the F0 curve and energy the decoder consumes (F0_curve, N).
+ * bidirectional LSTM (input projection as one dense conv + a cluster-resident recurrence kernel),
+ * then per branch three AdainResBlk1d (the middle one upsamples x2) and a 1x1 projection. */
+int64_t st2_f0n_workspace_bytes(const St2Decoder* h, int B, int T, int precision);
+int st2_f0n_forward(St2Decoder* h, const float* x, const float* s, float* f0_out, float* n_out,
+                    void* workspace, int64_t workspace_bytes, int B, int T, int precision, void* stream);
 
 /* Number of kernel launches the last forward on this handle issued (bench bookkeeping). */
 int64_t st2_decoder_last_launches(const St2Decoder* h);

@@ -12,7 +12,7 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "_lib", "libst2dec.so")
 
 ST2_OK = 0
-KIND_ISTFTNET, KIND_HIFIGAN = 0, 1
+KIND_ISTFTNET, KIND_HIFIGAN, KIND_F0N = 0, 1, 2
 PREC_FP32, PREC_BF16 = 0, 1
 DT_F32, DT_BF16 = 0, 1
 ACT_NONE, ACT_LRELU, ACT_SNAKE = 0, 1, 2
@@ -72,6 +72,9 @@ SYMBOLS = {
     "st2_decoder_forward": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p,
                                       C.c_void_p, C.c_void_p, C.c_int64, C.c_int, C.c_int,
                                       C.POINTER(St2ForwardOpts), C.c_void_p]),
+    "st2_f0n_workspace_bytes": (C.c_int64, [C.c_void_p, C.c_int, C.c_int, C.c_int]),
+    "st2_f0n_forward": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p,
+                                  C.c_int64, C.c_int, C.c_int, C.c_int, C.c_void_p]),
     "st2_decoder_last_launches": (C.c_int64, [C.c_void_p]),
     "st2_decoder_destroy": (None, [C.c_void_p]),
     "st2_last_error": (C.c_char_p, []),

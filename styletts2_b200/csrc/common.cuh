@@ -121,6 +121,11 @@ template <typename T>
 int launch_act_to_ncl(const T* cl, int64_t bstride, int ld, int C, int L, float* ncl, int B, cudaStream_t st);
 int launch_cl_to_ncl(const float* cl, int ld, int C, int L, float* ncl, int B, cudaStream_t st);
 int launch_ncl_to_cl(const float* ncl, int C, int L, float* cl, int ld, int B, cudaStream_t st);
+// lstm.cu: NCL fp32 -> channels-last activations; recurrence of the bidirectional LSTM (hidden 256)
+template <typename AT>
+int launch_ncl_to_act(const float* ncl, int C, int L, AT* cl, int ld, int B, cudaStream_t st);
+template <typename AT>
+int launch_lstm_scan(const AT* pre, const float* whh, AT* out, int B, int T, cudaStream_t st);
 
 int launch_row_mean(const float* x, int64_t L, float* mean, int B, cudaStream_t st);
 int launch_noise_bias(const float* mean, const float* wsum, const float* bias_nc, const float* bias_c2,

@@ -87,6 +87,11 @@ struct St2Decoder {
   std::vector<st2::ResBlock1W> noise_res, resblocks;
   std::vector<int64_t> alphas;  // hifigan generator.alphas
   st2::ConvW conv_post;
+  // ST2_KIND_F0N: ProsodyPredictor.F0Ntrain
+  st2::ConvW lstm_ih;         // both directions' W_ih as one 1x1 conv (n = 2 * 4H), bias = b_ih + b_hh
+  int64_t lstm_whh = -1;      // [2][4H][H] fp32
+  st2::ResBlk1dW f0n_blk[2][3];
+  st2::ConvW f0n_proj[2];
   st2::ConvW conv_post_p;     // row-pair form of a 32-channel conv_post (hifigan)
   int64_t alpha_post_p = -1;  // alphas[n_ups] repeated twice
   int64_t last_launches = 0;
@@ -138,6 +143,25 @@ static int prod_from(const int* r, int from, int n) {
 static void build_keys(St2Decoder* h) {
   const St2Config& c = h->cfg;
   const int style = c.style_dim;
+  if (c.kind == ST2_KIND_F0N) {  // models.py:562-590
+    const int d = c.dim_in, hid = d / 2;
+    for (int r = 0; r < 2; ++r) {
+      const std::string sfx = r ? "_reverse" : "";
+      add_key(h, "shared.weight_ih_l0" + sfx, {4 * hid, d + style});
+      add_key(h, "shared.weight_hh_l0" + sfx, {4 * hid, hid});
+      add_key(h, "shared.bias_ih_l0" + sfx, {4 * hid});
+      add_key(h, "shared.bias_hh_l0" + sfx, {4 * hid});
+    }
+    for (int br = 0; br < 2; ++br) {
+      const std::string b = br ? "N" : "F0";
+      keys_resblk1d(h, b + ".0", d, d, style, false);
+      keys_resblk1d(h, b + ".1", d, hid, style, true);
+      keys_resblk1d(h, b + ".2", hid, hid, style, false);
+      add_key(h, b + "_proj.weight", {1, hid, 1});
+      add_key(h, b + "_proj.bias", {1});
+    }
+    return;
+  }
   for (int i = 0; i < 3; ++i) keys_resblk1d(h, "decode." + std::to_string(i), 1024 + 2 + 64, 1024, style, false);
   keys_resblk1d(h, "decode.3", 1024 + 2 + 64, 512, style, true);
   keys_resblk1d(h, "encode", c.dim_in + 2, 1024, style, false);
@@ -447,6 +471,22 @@ struct Loader {
   }
 };
 
+static int finish_load(St2Decoder* h, Loader& L) {
+  h->fc_rows = (int)L.fcB.size();
+  h->ss_pairs = L.ss_pairs;
+  h->fcW = L.blob.add(L.fcW.data(), (int64_t)L.fcW.size() * 4);
+  h->fcB = L.blob.add(L.fcB.data(), (int64_t)L.fcB.size() * 4);
+
+  ST2_CUDA_OK(cudaSetDevice(h->device));
+  if (h->dev) ST2_CUDA_OK(cudaFree(h->dev));
+  h->dev = nullptr;
+  h->dev_bytes = (int64_t)L.blob.data.size();
+  ST2_CUDA_OK(cudaMalloc(&h->dev, h->dev_bytes));
+  ST2_CUDA_OK(cudaMemcpy(h->dev, L.blob.data.data(), h->dev_bytes, cudaMemcpyHostToDevice));
+  h->loaded = true;
+  return ST2_OK;
+}
+
 static int do_load(St2Decoder* h, const St2Tensor* tensors, int n) {
   const St2Config& c = h->cfg;
   Loader L;
@@ -470,6 +510,41 @@ static int do_load(St2Decoder* h, const St2Tensor* tensors, int n) {
   ST2_REQUIRE(L.by_name.size() == h->key_names.size(), "unexpected keys in state dict");
 
   bool ok = true;
+  if (c.kind == ST2_KIND_F0N) {
+    const int d = c.dim_in, hid = d / 2, in = d + c.style_dim, g4 = 4 * hid;
+    // both directions' input projections as one GEMM: column dir * 4H + gate * H + unit
+    std::vector<float> kcn((size_t)in * 2 * g4), bsum((size_t)2 * g4), whh((size_t)2 * g4 * hid);
+    for (int r = 0; r < 2 && ok; ++r) {
+      const std::string sfx = r ? "_reverse" : "";
+      const St2Tensor* wih = L.get("shared.weight_ih_l0" + sfx);
+      const St2Tensor* whp = L.get("shared.weight_hh_l0" + sfx);
+      const St2Tensor* bi = L.get("shared.bias_ih_l0" + sfx);
+      const St2Tensor* bh = L.get("shared.bias_hh_l0" + sfx);
+      ok = wih && whp && bi && bh;
+      if (!ok) break;
+      for (int row = 0; row < g4; ++row) {
+        for (int ci = 0; ci < in; ++ci) kcn[(size_t)ci * 2 * g4 + r * g4 + row] = wih->data[(size_t)row * in + ci];
+        bsum[(size_t)r * g4 + row] = bi->data[row] + bh->data[row];
+      }
+      memcpy(&whh[(size_t)r * g4 * hid], whp->data, (size_t)g4 * hid * 4);
+    }
+    if (ok) {
+      ConvW& cw = h->lstm_ih;
+      cw.k = 1; cw.dil = 1; cw.pad = 0; cw.stride = 1;
+      cw.cin = in; cw.n = 2 * g4; cw.cstat = 2 * g4;
+      cw.flops_per_row = 2.0 * (double)in * (double)(2 * g4);
+      L.finish_conv(cw, kcn, &bsum, true);
+      h->lstm_whh = L.blob.add(whh.data(), (int64_t)whh.size() * 4);
+    }
+    for (int br = 0; br < 2 && ok; ++br) {
+      const std::string b = br ? "N" : "F0";
+      ok = L.resblk1d(h->f0n_blk[br][0], b + ".0", d, d, false) && L.resblk1d(h->f0n_blk[br][1], b + ".1", d, hid, true) &&
+           L.resblk1d(h->f0n_blk[br][2], b + ".2", hid, hid, false) &&
+           L.conv1d(h->f0n_proj[br], b + "_proj", false, true, 1, 1, 0, 1, false);
+    }
+    ST2_REQUIRE(ok, L.err);
+    return finish_load(h, L);
+  }
   for (int i = 0; i < 3 && ok; ++i) ok = L.resblk1d(h->decode[i], "decode." + std::to_string(i), 1090, 1024, false);
   ok = ok && L.resblk1d(h->decode[3], "decode.3", 1090, 512, true);
   ok = ok && L.resblk1d(h->encode, "encode", c.dim_in + 2, 1024, false);
@@ -554,19 +629,7 @@ static int do_load(St2Decoder* h, const St2Tensor* tensors, int n) {
       ok = L.vec(h->alphas[i], g + ".alphas." + std::to_string(i), i == 0 ? c0 : c0 >> i);
   }
   ST2_REQUIRE(ok, L.err);
-  h->fc_rows = (int)L.fcB.size();
-  h->ss_pairs = L.ss_pairs;
-  h->fcW = L.blob.add(L.fcW.data(), (int64_t)L.fcW.size() * 4);
-  h->fcB = L.blob.add(L.fcB.data(), (int64_t)L.fcB.size() * 4);
-
-  ST2_CUDA_OK(cudaSetDevice(h->device));
-  if (h->dev) ST2_CUDA_OK(cudaFree(h->dev));
-  h->dev = nullptr;
-  h->dev_bytes = (int64_t)L.blob.data.size();
-  ST2_CUDA_OK(cudaMalloc(&h->dev, h->dev_bytes));
-  ST2_CUDA_OK(cudaMemcpy(h->dev, L.blob.data.data(), h->dev_bytes, cudaMemcpyHostToDevice));
-  h->loaded = true;
-  return ST2_OK;
+  return finish_load(h, L);
 }
 
 }  // namespace st2
@@ -794,7 +857,70 @@ struct Fwd {
 
   int run(const float* asr, const float* f0, const float* nn, const float* s, float* wav,
           const St2ForwardOpts& o);
+  int run_f0n(const float* x, const float* s, float* f0_out, float* n_out);
 };
+
+// ProsodyPredictor.F0Ntrain (models.py:638-654): x [B, d_hid + style, T] NCL -> F0, N [B, 2T]
+template <typename AT>
+int Fwd<AT>::run_f0n(const float* x, const float* s, float* f0_out, float* n_out) {
+  const St2Config& c = h->cfg;
+  const int d = c.dim_in, hid = d / 2, in = d + c.style_dim;
+  float* hall_w = ar.alloc<float>((int64_t)B * h->fc_rows);
+  hall = hall_w;
+  ss = ar.alloc<float>((int64_t)B * h->ss_pairs * 2);
+  RUN(launch_style_fc(s, W<float>(h->fcW), W<float>(h->fcB), hall_w, B, c.style_dim, h->fc_rows, st));
+  RUN(cudaMemsetAsync(ss, 0, (size_t)B * h->ss_pairs * 8, st) == cudaSuccess ? ST2_OK : ST2_ECUDA);
+
+  // ---- x, _ = self.shared(x.transpose(-1, -2)) (models.py:639)
+  Act<AT> hx = new_act(T, d);  // LSTM output, channels-last [B][T][2H]
+  {
+    const int64_t m = ar.mark();
+    Act<AT> xc = new_act(T, in), pre = new_act(T, h->lstm_ih.n);
+    RUN(launch_ncl_to_act<AT>(x, in, T, xc.p, in, B, st));
+    int rc = conv(h->lstm_ih, io_of(xc, pre));  // W_ih x + b_ih + b_hh for every step and both directions
+    if (rc) return rc;
+    RUN(launch_lstm_scan<AT>(pre.p, W<float>(h->lstm_whh), hx.p, B, T, st));
+    ar.release(m);
+  }
+  // statistics of the LSTM output for norm1 of the first block of both branches
+  {
+    const int64_t m = ar.mark();
+    const int tiles = colstats_tiles(T);
+    float* part = ar.alloc<float>((int64_t)B * tiles * d * 2);
+    RUN(launch_colstats<AT>(hx.p, hx.bstride, hx.ld, T, 0, d, part, B, st));
+    for (int br = 0; br < 2; ++br) {
+      int rc = finalize(part, tiles, d, d, T, h->f0n_blk[br][0].n1, 0);
+      if (rc) return rc;
+    }
+    ar.release(m);
+  }
+  for (int br = 0; br < 2; ++br) {
+    const int64_t m = ar.mark();
+    Act<AT> a1 = new_act(T, d), a2 = new_act(2 * T, hid), a3 = new_act(2 * T, hid);
+    const Act<AT> ins[3] = {hx, a1, a2}, outs[3] = {a1, a2, a3};
+    for (int i = 0; i < 3; ++i) {
+      const int64_t m2 = ar.mark();
+      const bool more = i < 2;
+      int rc = resblk1d(h->f0n_blk[br][i], ins[i], outs[i], more);
+      if (rc) return rc;
+      if (more) {
+        rc = finalize(last_partials, last_tiles, last_cols, h->f0n_blk[br][i].dout, outs[i].L,
+                      h->f0n_blk[br][i + 1].n1, 0);
+        if (rc) return rc;
+      }
+      ar.release(m2);
+    }
+    // F0_proj / N_proj: Conv1d(hid, 1, 1) -> [B, 2T] fp32
+    ConvIO io;
+    io.x = a3.p; io.x_dtype = DT<AT>::id; io.x_bstride = a3.bstride; io.ldx = a3.ld; io.Lin = a3.L;
+    float* dst = br == 0 ? f0_out : n_out;
+    io.y = dst; io.y_dtype = ST2_DT_F32; io.y_bstride = 2 * T; io.ldy = 1; io.Lout = 2 * T;
+    int rc = conv(h->f0n_proj[br], io);
+    if (rc) return rc;
+    ar.release(m);
+  }
+  return ST2_OK;
+}
 
 template <typename AT>
 int Fwd<AT>::run(const float* asr, const float* f0, const float* nn, const float* s, float* wav,
@@ -1043,6 +1169,11 @@ int Fwd<AT>::run(const float* asr, const float* f0, const float* nn, const float
 using namespace st2;
 
 static int validate_cfg(const St2Config& c) {
+  if (c.kind == ST2_KIND_F0N) {
+    ST2_REQUIRE(c.dim_in == 512, "d_hid must be 512 (the LSTM kernel keeps 256 hidden units per direction)");
+    ST2_REQUIRE(c.style_dim > 0 && c.style_dim <= 192 && (c.dim_in + c.style_dim) % 64 == 0, "style_dim");
+    return ST2_OK;
+  }
   ST2_REQUIRE(c.kind == ST2_KIND_ISTFTNET || c.kind == ST2_KIND_HIFIGAN, "kind");
   ST2_REQUIRE(c.dim_in == 512, "dim_in must be 512 (asr_res is Conv1d(512, 64), istftnet.py:490)");
   ST2_REQUIRE(c.style_dim > 0 && c.style_dim <= 192, "style_dim");
@@ -1147,7 +1278,8 @@ static int plan_bytes(St2Decoder* h, int B, int T, const St2ForwardOpts& o, int6
 
 extern "C" int64_t st2_decoder_workspace_bytes(const St2Decoder* hc, int B, int T, int precision) {
   St2Decoder* h = const_cast<St2Decoder*>(hc);
-  if (!h || !h->loaded || B < 1 || T < 2 || (T & 1) || (precision != ST2_PREC_FP32 && precision != ST2_PREC_BF16)) {
+  if (!h || !h->loaded || h->cfg.kind == ST2_KIND_F0N || B < 1 || T < 2 || (T & 1) ||
+      (precision != ST2_PREC_FP32 && precision != ST2_PREC_BF16)) {
     set_error("st2_decoder_workspace_bytes: bad argument or weights not loaded");
     return ST2_EINVAL;
   }
@@ -1170,6 +1302,7 @@ extern "C" int st2_decoder_forward(St2Decoder* h, const float* asr, const float*
     set_error("st2_decoder_forward: weights not loaded");
     return ST2_ESTATE;
   }
+  ST2_REQUIRE(h->cfg.kind != ST2_KIND_F0N, "st2_decoder_forward: this handle is an F0/N predictor (use st2_f0n_forward)");
   ST2_REQUIRE(B >= 1 && T >= 2, "batch / length");
   ST2_REQUIRE((T & 1) == 0, "len(F0_curve) must equal 2 * asr.shape[-1] (istftnet.py:513)");
   ST2_REQUIRE(B <= 65535, "batch too large for one call");
@@ -1196,6 +1329,69 @@ extern "C" int st2_decoder_forward(St2Decoder* h, const float* asr, const float*
     rc = forward_t<__nv_bfloat16>(h, asr, f0, n, s, wav_out, workspace, workspace_bytes, B, T, o, st, false, nullptr);
   else
     rc = forward_t<float>(h, asr, f0, n, s, wav_out, workspace, workspace_bytes, B, T, o, st, false, nullptr);
+  h->last_launches = launch_counter() - before;
+  return rc;
+}
+
+template <typename AT>
+static int f0n_t(St2Decoder* h, const float* x, const float* s, float* f0, float* n, void* ws, int64_t ws_bytes,
+                 int B, int T, cudaStream_t st, bool dry, int64_t* peak) {
+  Fwd<AT> f;
+  f.h = h; f.st = st; f.B = B; f.T = T; f.dry = dry;
+  f.ar.base = reinterpret_cast<uint8_t*>(ws); f.ar.cap = ws_bytes; f.ar.dry = dry;
+  int rc = f.run_f0n(x, s, f0, n);
+  if (peak) *peak = f.ar.peak;
+  return rc;
+}
+static int f0n_plan(St2Decoder* h, int B, int T, int precision, int64_t* bytes) {
+  int64_t peak = 0;
+  int rc = precision == ST2_PREC_BF16
+               ? f0n_t<__nv_bfloat16>(h, nullptr, nullptr, nullptr, nullptr, nullptr, 0, B, T, 0, true, &peak)
+               : f0n_t<float>(h, nullptr, nullptr, nullptr, nullptr, nullptr, 0, B, T, 0, true, &peak);
+  *bytes = round_up(peak, 256) + 256;
+  return rc;
+}
+extern "C" int64_t st2_f0n_workspace_bytes(const St2Decoder* hc, int B, int T, int precision) {
+  St2Decoder* h = const_cast<St2Decoder*>(hc);
+  if (!h || !h->loaded || h->cfg.kind != ST2_KIND_F0N || B < 1 || T < 1 ||
+      (precision != ST2_PREC_FP32 && precision != ST2_PREC_BF16)) {
+    set_error("st2_f0n_workspace_bytes: bad argument, wrong handle kind or weights not loaded");
+    return ST2_EINVAL;
+  }
+  int64_t bytes = 0;
+  int rc = f0n_plan(h, B, T, precision, &bytes);
+  return rc ? rc : bytes;
+}
+extern "C" int st2_f0n_forward(St2Decoder* h, const float* x, const float* s, float* f0_out, float* n_out,
+                               void* workspace, int64_t workspace_bytes, int B, int T, int precision,
+                               void* stream) {
+  if (!h || !x || !s || !f0_out || !n_out || !workspace) {
+    set_error("st2_f0n_forward: null argument");
+    return ST2_EINVAL;
+  }
+  ST2_REQUIRE(h->cfg.kind == ST2_KIND_F0N, "st2_f0n_forward: handle was not created with ST2_KIND_F0N");
+  if (!h->loaded) {
+    set_error("st2_f0n_forward: weights not loaded");
+    return ST2_ESTATE;
+  }
+  ST2_REQUIRE(B >= 1 && B <= 65535 && T >= 1, "batch / length");
+  ST2_REQUIRE(precision == ST2_PREC_FP32 || precision == ST2_PREC_BF16, "precision");
+  ST2_REQUIRE(((uintptr_t)workspace & 255) == 0, "workspace must be 256-byte aligned");
+  int dev = -1;
+  ST2_CUDA_OK(cudaGetDevice(&dev));
+  ST2_REQUIRE(dev == h->device, "handle belongs to another device");
+  int64_t need = 0;
+  int rc = f0n_plan(h, B, T, precision, &need);
+  if (rc) return rc;
+  if (need > workspace_bytes) {
+    set_error("st2_f0n_forward: workspace too small (" + std::to_string(workspace_bytes) + " < " + std::to_string(need) + ")");
+    return ST2_ENOMEM;
+  }
+  const int64_t before = launch_counter();
+  cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+  rc = precision == ST2_PREC_BF16
+           ? f0n_t<__nv_bfloat16>(h, x, s, f0_out, n_out, workspace, workspace_bytes, B, T, st, false, nullptr)
+           : f0n_t<float>(h, x, s, f0_out, n_out, workspace, workspace_bytes, B, T, st, false, nullptr);
   h->last_launches = launch_counter() - before;
   return rc;
 }

@@ -220,3 +220,53 @@ def synth_inputs(cfg, B: int, T: int, seed: int = 1234, with_noise: bool = True)
     if with_noise:
         out["noise"] = torch.randn(B, T * samples_per_frame(cfg), 9, generator=g)
     return out
+
+
+# ------------------------------------------------------------- F0/N predictor
+F0N_CFG = {"style_dim": 128, "d_hid": 512}
+
+
+def f0n_param_spec(cfg) -> Spec:
+    """Names/shapes of the F0Ntrain part of ``ProsodyPredictor.state_dict()`` (models.py:562-590):
+    ``shared`` (bidirectional LSTM), ``F0.{0,1,2}``, ``N.{0,1,2}``, ``F0_proj``, ``N_proj``."""
+    spec: Spec = []
+    style, d = cfg["style_dim"], cfg["d_hid"]
+    hid = d // 2
+    for sfx in ("", "_reverse"):
+        spec.append((f"shared.weight_ih_l0{sfx}", (4 * hid, d + style), "w", hid))
+        spec.append((f"shared.weight_hh_l0{sfx}", (4 * hid, hid), "w", hid))
+        spec.append((f"shared.bias_ih_l0{sfx}", (4 * hid,), "bias", hid))
+        spec.append((f"shared.bias_hh_l0{sfx}", (4 * hid,), "bias", hid))
+    for br in ("F0", "N"):
+        _adain_resblk1d(spec, f"{br}.0", d, d, style, False)
+        _adain_resblk1d(spec, f"{br}.1", d, hid, style, True)
+        _adain_resblk1d(spec, f"{br}.2", hid, hid, style, False)
+        spec.append((f"{br}_proj.weight", (1, hid, 1), "w", hid))
+        spec.append((f"{br}_proj.bias", (1,), "bias", hid))
+    return spec
+
+
+def synth_f0n_state_dict(cfg, seed: int = 0) -> Dict[str, torch.Tensor]:
+    spec = f0n_param_spec(cfg)
+    sd: Dict[str, torch.Tensor] = {}
+    for name, shape, kind, fan_in in spec:
+        if kind == "g":
+            continue
+        g = _gen_for("f0n." + name, seed)
+        bound = 1.0 / math.sqrt(max(fan_in, 1))
+        sd[name] = ((torch.rand(shape, generator=g) * 2 - 1) * bound).float().contiguous()
+    for name, shape, kind, _ in spec:
+        if kind != "g":
+            continue
+        v = sd[name[:-1] + "v"]
+        nrm = v.reshape(v.shape[0], -1).norm(dim=1).reshape(shape)
+        pert = 1.0 + 0.1 * (torch.rand(shape, generator=_gen_for("f0n." + name, seed)) * 2 - 1)
+        sd[name] = (nrm * pert).float().contiguous()
+    return {name: sd[name] for name, *_ in spec}
+
+
+def synth_f0n_inputs(cfg, B: int, T: int, seed: int = 77):
+    """``en`` [B, d_hid + style, T] (duration-expanded prosody encoding) and ``s`` [B, style]."""
+    g = torch.Generator().manual_seed(seed)
+    return {"x": torch.randn(B, cfg["d_hid"] + cfg["style_dim"], T, generator=g),
+            "s": torch.randn(B, cfg["style_dim"], generator=g)}

@@ -110,3 +110,26 @@ def test_metrics():
     assert orc.snr_db(a, a + 0.01 * torch.randn(1, 1, 24000, generator=g)) == pytest.approx(40, abs=0.5)
     assert orc.log_mel_l1(a, a) == 0.0
     assert orc.log_mel(a).shape == (1, 80, 81)
+
+
+# ------------------------------------------------------------- F0/N predictor
+def test_f0n_spec_matches_reference_keys():
+    ref = json.load(open(os.path.join(GOLD, "keys_f0n.json")))
+    mine = {n: list(s) for n, s, *_ in synth.f0n_param_spec(synth.F0N_CFG)}
+    assert mine == ref and len(ref) == 82
+
+
+@pytest.mark.parametrize("T", [20, 51])
+def test_f0n_oracle_vs_reference(T):
+    """oracle/predictor_oracle.py against ProsodyPredictor.F0Ntrain of the real reference
+    (oracle/make_golden_f0n.py): LSTM output and both curves"""
+    from oracle import predictor_oracle as porc
+    g = np.load(os.path.join(GOLD, f"f0n_T{T}.npz"))
+    g = {k: torch.from_numpy(g[k]) for k in g.files}
+    sd = synth.synth_f0n_state_dict(synth.F0N_CFG, seed=0)
+    lstm = porc.shared_lstm(g["x"], porc.Params(sd))
+    assert (lstm - g["lstm"]).abs().max().item() < 2e-6
+    F0, N = porc.f0n_forward(sd, g["x"], g["s"])
+    assert F0.shape == g["F0"].shape == (g["x"].shape[0], 2 * T)
+    assert (F0 - g["F0"]).abs().max().item() < 5e-6
+    assert (N - g["N"]).abs().max().item() < 5e-6
