@@ -173,9 +173,150 @@ def _hbm_kernels(B, T, dev, peaks):
     return out
 
 
+def run_f0n(args):
+    """next-row workload: ProsodyPredictor.F0Ntrain at the C2 shape (B=32, 400 prosody
+    frames -> 800 F0/N frames = 10 s of audio per item).  Same line format as the decoder bench."""
+    import torch
+    import torch.distributed as dist
+    import styletts2_b200 as st2
+    import synthetic as synth
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a CUDA device: styletts2_b200 has no CPU fallback")
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+    B, T = 32, 400
+    cfg = synth.F0N_CFG
+    p = st2.F0NPredictor(**cfg)
+    sd = synth.synth_f0n_state_dict(cfg, seed=0)
+    p.load_state_dict(sd, strict=True)
+    p = p.to(dev).eval()
+    p.precision = args.precision
+    inp = synth.synth_f0n_inputs(cfg, B, T, seed=4321 + rank)
+    host = {k: v.pin_memory() for k, v in inp.items()}
+    d = {k: v.to(dev) for k, v in inp.items()}
+    audio_s = B * 2 * T * 300 / 24000.0
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def max_over_ranks(ms):
+        if world == 1:
+            return ms
+        t = torch.tensor([ms], device=dev, dtype=torch.float64)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+
+    for _ in range(max(3, args.warmup)):
+        f0, n = p.F0Ntrain(d["x"], d["s"])
+    barrier()
+    launches = p.last_launches
+    sampler = ClockSampler(local)
+    if sampler.ok:
+        sampler.start()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    barrier()
+    e0.record()
+    for _ in range(args.steps):
+        f0, n = p.F0Ntrain(d["x"], d["s"])
+    e1.record()
+    barrier()
+    clocks = sampler.stop()
+    ms_step = max_over_ranks(e0.elapsed_time(e1)) / args.steps
+    assert torch.isfinite(f0).all() and torch.isfinite(n).all()
+    out_host = torch.empty(2, B, 2 * T).pin_memory()
+
+    def e2e_step():
+        a = {k: host[k].to(dev, non_blocking=True) for k in ("x", "s")}
+        f0, n = p.F0Ntrain(a["x"], a["s"])
+        out_host[0].copy_(f0, non_blocking=True)
+        out_host[1].copy_(n, non_blocking=True)
+
+    for _ in range(2):
+        e2e_step()
+    barrier()
+    e0.record()
+    for _ in range(args.steps):
+        e2e_step()
+    e1.record()
+    barrier()
+    ms_e2e = max_over_ranks(e0.elapsed_time(e1)) / args.steps
+    if rank != 0:
+        if world > 1:
+            dist.destroy_process_group()
+        return 0
+    cpu = None
+    if world == 1 and not args.no_cpu_baseline:
+        from oracle import predictor_oracle as porc
+        torch.set_num_threads(os.cpu_count() or 1)
+        one = synth.synth_f0n_inputs(cfg, 1, T, seed=1)
+        ts = []
+        for i in range(3):
+            t0 = time.perf_counter()
+            porc.f0n_forward(sd, one["x"], one["s"])
+            ts.append(time.perf_counter() - t0)
+        tm = statistics.median(ts[1:])
+        cpu = {"value": round(2 * T * 300 / 24000.0 / tm, 3), "unit": UNIT, "cores": torch.get_num_threads(), "kind": "port",
+               "sample": f"1 item x {T} prosody frames, fp32, torch CPU (oracle port of models.py F0Ntrain), {tm * 1e3:.0f} ms"}
+    # algorithmic work: LSTM 2 dirs x (4H x (In + H)) + the six AdainResBlk1d convs + projections, 2*MAC per prosody frame
+    H, In, dd = 256, 640, 512
+    lstm = 2 * 2 * 4 * H * (In + H)
+    blk = lambda din, dout, up: 2 * 3 * (din * dout * (2 if up else 1) + dout * dout * (2 if up else 1)) + (2 * din * dout * (2 if up else 1) if din != dout else 0)
+    per_frame = lstm + 2 * (blk(dd, dd, False) + blk(dd, H, True) + blk(H, H, False) * 2 + 2 * H * 2)
+    line = {
+        "metric": "audio-sec/sec of F0/N curves predicted (ProsodyPredictor.F0Ntrain, bf16)", "value": round(world * audio_s / (ms_step * 1e-3), 2),
+        "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": max(3, args.warmup), "ms_per_step": round(ms_step, 3),
+        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": args.precision, "data": "synthetic",
+        "config": {"workload": "next row N1: F0Ntrain, B=32 x 400 prosody frames (800 F0 frames, 10 s each)", "batch_per_gpu": B,
+                   "frames": T, "weights": "random-init (synthetic.py, seed 0)", "l2": "working set 0.3 GB per step (> 126 MB L2)",
+                   "parallelism": f"dp{world} (independent batches, no collective)"},
+        "e2e": {"value": round(world * audio_s / (ms_e2e * 1e-3), 2), "unit": UNIT, "ms_per_step": round(ms_e2e, 3),
+                "h2d_bytes_per_step": sum(host[k].numel() * 4 for k in host), "d2h_bytes_per_step": out_host.numel() * 4},
+        "gpu_launches": int(launches * args.steps),
+        "roofline": {"bound": "tensor", "achieved": round(per_frame * B * T / (ms_step * 1e-3) / 1e12, 2), "peak": _peaks()["tf_sustained"],
+                     "unit": "TFLOP/s", "frac": round(per_frame * B * T / (ms_step * 1e-3) / 1e12 / _peaks()["tf_sustained"], 4),
+                     "traffic": None, "note": "whole forward (the LSTM recurrence is latency-bound: T dependent steps)"},
+        "cpu_baseline": cpu, "clocks": clocks,
+    }
+    print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+    return 0
+
+
 def run_reference(args):
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
+        return 0
+    if args.workload == "f0n":
+        import torch
+        import synthetic as synth
+        from oracle import predictor_oracle as porc
+        torch.set_num_threads(os.cpu_count() or 1)
+        sd = synth.synth_f0n_state_dict(synth.F0N_CFG, seed=0)
+        one = synth.synth_f0n_inputs(synth.F0N_CFG, 1, 400, seed=1)
+        ts = []
+        for i in range(max(1, args.warmup) + args.steps):
+            t0 = time.perf_counter()
+            porc.f0n_forward(sd, one["x"], one["s"])
+            ts.append(time.perf_counter() - t0)
+        tm = statistics.median(ts[max(1, args.warmup):])
+        v = 10.0 / tm
+        print(json.dumps({"impl": "reference", "metric": "audio-sec/sec of F0/N curves predicted (ProsodyPredictor.F0Ntrain, bf16)",
+                          "value": round(v, 3), "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps, "warmup": max(1, args.warmup),
+                          "ms_per_step": round(tm * 1e3, 2), "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+                          "dtype": "f32", "data": "synthetic",
+                          "config": {"workload": "next row N1: F0Ntrain", "sample": "B=1 x 400 prosody frames per step on the CPU"},
+                          "cpu_baseline": {"value": round(v, 3), "unit": UNIT, "cores": torch.get_num_threads(), "kind": "port",
+                                           "sample": "1 item x 400 prosody frames, fp32, torch CPU (oracle port of models.py F0Ntrain)"},
+                          "e2e": {"value": round(v, 3), "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+                          "gpu_launches": 0}), flush=True)
         return 0
     kind, B, T, desc = WORKLOADS[args.workload]
     sb, st = 1, T  # bounded sample: one utterance of the workload per step
@@ -366,7 +507,7 @@ def main():
     ap.add_argument("--steps", type=int, default=10)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--workload", default="c2", choices=sorted(WORKLOADS))
+    ap.add_argument("--workload", default="c2", choices=sorted(WORKLOADS) + ["f0n"])
     ap.add_argument("--precision", default="bf16", choices=["bf16", "fp32"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-graphs", action="store_true", help="launch every kernel eagerly instead of replaying a CUDA graph")
@@ -380,7 +521,7 @@ def main():
         cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={args.gpus}",
                "--master-addr", "127.0.0.1", "--master-port", "29541", os.path.abspath(__file__)] + sys.argv[1:]
         return subprocess.call(cmd)
-    return run_ours(args)
+    return run_f0n(args) if args.workload == "f0n" else run_ours(args)
 
 
 if __name__ == "__main__":
