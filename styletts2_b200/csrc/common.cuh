@@ -24,6 +24,30 @@ int64_t& launch_counter();               // decoder.cu (thread-local running cou
     }                                                                                  \
   } while (0)
 
+// Programmatic dependent launch: a kernel that starts with pdl_wait_then_trigger() may be launched with
+// the programmatic-stream-serialization attribute (launch_pdl below).  It is then scheduled while its
+// predecessor is still running (its launch latency hides behind the predecessor's tail), blocks in
+// griddepcontrol.wait until the predecessor has completed and flushed, and only then lets its own
+// successor be scheduled -- so nothing it reads can be stale, whatever the predecessor is.
+#ifdef __CUDACC__
+__device__ __forceinline__ void pdl_wait_then_trigger() {
+  asm volatile("griddepcontrol.wait;" ::: "memory");
+  asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+}
+#endif
+bool pdl_enabled();  // decoder.cu: ST2_PDL=0 turns the attribute off (A/B switch)
+template <typename... KArgs, typename... Args>
+static inline cudaError_t launch_pdl(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t st,
+                                     Args... args) {
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = grid; cfg.blockDim = block; cfg.dynamicSmemBytes = smem; cfg.stream = st;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[0].val.programmaticStreamSerializationAllowed = pdl_enabled() ? 1 : 0;
+  cfg.attrs = attr; cfg.numAttrs = 1;
+  return cudaLaunchKernelEx(&cfg, kernel, KArgs(args)...);
+}
+
 #define ST2_LAUNCH_OK(name)                                                            \
   do {                                                                                 \
     st2::launch_counter()++;                                                           \

@@ -61,6 +61,7 @@ struct UmLayout {
   int a_bytes;        // bytes per A stage (rows x 128 B, multiple of 1024)
   int na;             // A stages in use
   int dist;           // prefetch distance of the producers, in chunks (na - 2)
+  int dbg;            // ST2_UMMA_DBG experiments (bit 0: reuse the weight stages without reloading; wrong results)
   int w_bytes;        // bytes per weight stage (= 8 * n_tile * 16)
   int out_row;        // bytes per output row segment (n_tile * element size), multiple of 128
   int n_res, n_acc;   // extra 64-channel chunks per tile: residual rows, y_old rows
@@ -68,6 +69,7 @@ struct UmLayout {
   const uint8_t* ident_acc;  // n_tile/64 identity weight blobs (x 1/out_scale)
   uint32_t off_a, off_w, off_misc, total;  // the staging tile sits at offset 0 (1024-byte aligned)
   uint32_t idesc;
+  uint32_t idesc64;   // the same with N = 64 (identity chunks of a 128-column tile)
 };
 
 struct UmMisc {
@@ -750,6 +752,7 @@ __global__ void __launch_bounds__(UM_THREADS, 1) conv_umma_kernel(const St2ConvP
                                                                    const __grid_constant__ CUtensorMap ymap,
                                                                    int total_tiles, int n_ttiles, int n_ntiles) {
   extern __shared__ __align__(1024) uint8_t smem_raw[];
+  pdl_wait_then_trigger();  // launched with the programmatic-serialization attribute (common.cuh)
   UmMisc* misc = reinterpret_cast<UmMisc*>(smem_raw + lay.off_misc);
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int nchunks = p.cin / UM_CK;
@@ -847,13 +850,22 @@ __global__ void __launch_bounds__(UM_THREADS, 1) conv_umma_kernel(const St2ConvP
           // the swizzle is a function of the absolute smem address: a start that is not a multiple of
           // 8 rows needs no base offset (measured: base-offset variants fail the parity tests)
           const uint64_t ad = a_desc0 + (uint64_t)(a_u + shift * 8u);
-          const uint64_t bd = w_desc0 + (uint64_t)((w_base + (uint32_t)ws * (uint32_t)lay.w_bytes) >> 4);
+          uint64_t bd = w_desc0 + (uint64_t)((w_base + (uint32_t)ws * (uint32_t)lay.w_bytes) >> 4);
+          // identity chunk e of a 128-column tile only touches columns [64 e', 64 e' + 64): a 64-column MMA
+          uint32_t idesc = lay.idesc, dcol = 0;
+          if (c >= nchunks && lay.n_tile == 128) {
+            const int e = c - nchunks;
+            const uint32_t hh = (uint32_t)(e < lay.n_res ? e : e - lay.n_res);
+            idesc = lay.idesc64;
+            dcol = hh * 64u;
+            bd += (uint64_t)(hh * 64u);  // 64 columns x 16 bytes, in 16-byte units
+          }
 #pragma unroll
           for (int acc = 0; acc < UM_NACC; ++acc) {
 #pragma unroll
             for (int ks = 0; ks < UM_CK / 16; ++ks)
-              umma_bf16_if(d0 + (uint32_t)(acc * lay.n_tile), ad + (uint64_t)(acc * 1024 + ks * a_kstep),
-                           bd + (uint64_t)(ks * w_kstep), lay.idesc, 1u, leader);
+              umma_bf16_if(d0 + (uint32_t)(acc * lay.n_tile) + dcol, ad + (uint64_t)(acc * 1024 + ks * a_kstep),
+                           bd + (uint64_t)(ks * w_kstep), idesc, 1u, leader);
           }
           umma_commit_if(&misc->w_empty[ws], leader);
           ws = wn;
@@ -883,8 +895,12 @@ __global__ void __launch_bounds__(UM_THREADS, 1) conv_umma_kernel(const St2ConvP
                                  : lay.ident_acc + (int64_t)(e - lay.n_res) * lay.w_bytes;
           }
           mbar_wait(&misc->w_empty[ws], wph ^ 1u, 4);
-          mbar_arrive_expect_tx(&misc->w_full[ws], (uint32_t)lay.w_bytes);
-          bulk_g2s(wsm + (size_t)ws * lay.w_bytes, blob, (uint32_t)lay.w_bytes, &misc->w_full[ws]);
+          if ((lay.dbg & 1) && (tile != (int)blockIdx.x || s >= UM_W_STAGES)) {
+            mbar_arrive(&misc->w_full[ws]);  // timing experiment only
+          } else {
+            mbar_arrive_expect_tx(&misc->w_full[ws], (uint32_t)lay.w_bytes);
+            bulk_g2s(wsm + (size_t)ws * lay.w_bytes, blob, (uint32_t)lay.w_bytes, &misc->w_full[ws]);
+          }
           if (++ws == UM_W_STAGES) { ws = 0; wph ^= 1u; }
         }
       }
@@ -993,14 +1009,17 @@ static int um_layout(const St2ConvParams& p, int dev, UmLayout& lay) {
   lay.dist = na - 2;  // measured: fixed distance beats opportunistic issue by 5-10 % on residual convs
   if (const char* e = getenv("ST2_UMMA_DIST")) {
     lay.dist = atoi(e);
-    if (lay.dist > na - 2) lay.dist = na - 2;
+    if (lay.dist > na - 1) lay.dist = na - 1;
     if (lay.dist < 0) lay.dist = 0;
   }
+  lay.dbg = 0;
+  if (const char* e = getenv("ST2_UMMA_DBG")) lay.dbg = atoi(e);
   lay.off_a = (uint32_t)stg_bytes;
   lay.off_w = lay.off_a + (uint32_t)(na * lay.a_bytes);
   lay.off_misc = lay.off_w + (uint32_t)(UM_W_STAGES * lay.w_bytes);
   lay.total = lay.off_misc + (uint32_t)misc_bytes;
   lay.idesc = um_idesc(lay.n_tile);
+  lay.idesc64 = um_idesc(64);
   lay.n_res = lay.n_acc = 0;
   if (p.res) {
     ST2_REQUIRE(lay.n_tile >= 64, "conv_umma: residual needs a 64- or 128-column tile");
@@ -1125,7 +1144,8 @@ int launch_conv_umma(const St2ConvParams& p, cudaStream_t st) {
     g_prof.flops += p.algo_flops;
     ST2_CUDA_OK(cudaEventRecord(e0, st));
   }
-  conv_umma_kernel<<<grid, UM_THREADS, lay.total, st>>>(p, lay, ymap, (int)total, n_ttiles, n_ntiles);
+  ST2_CUDA_OK(launch_pdl(conv_umma_kernel, dim3(grid), dim3(UM_THREADS), (size_t)lay.total, st, p, lay, ymap, (int)total,
+                         n_ttiles, n_ntiles));
   ST2_LAUNCH_OK("conv_umma");
   if (e1) ST2_CUDA_OK(cudaEventRecord(e1, st));
   return ST2_OK;

@@ -15,6 +15,13 @@ namespace st2 {
 static thread_local std::string g_err;
 static thread_local int64_t g_launches = 0;
 void set_error(const std::string& msg) { g_err = msg; }
+bool pdl_enabled() {
+  static const bool on = [] {
+    const char* e = getenv("ST2_PDL");
+    return !(e && e[0] == '0');
+  }();
+  return on;
+}
 int64_t& launch_counter() { return g_launches; }
 int launch_tanh_inplace(float* x, int64_t n, cudaStream_t st);  // elementwise.cu
 

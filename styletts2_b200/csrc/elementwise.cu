@@ -56,6 +56,7 @@ stats_finalize_kernel(const float* __restrict__ partials, int n_tiles, int n_col
                       double inv_count, const float* __restrict__ hg, int h_stride, int Cn,
                       float* __restrict__ ss, int ss_stride, int c_off, int reps) {
   __shared__ double red[SF_WARPS][32][2];
+  pdl_wait_then_trigger();
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int c = blockIdx.x * 32 + lane;
   const int b = blockIdx.y;
@@ -112,8 +113,8 @@ int launch_stats_finalize(const float* partials, int n_tiles, int n_cols, int C,
                           const float* hg, int h_stride, int Cn, float* ss, int ss_stride,
                           int c_off, int B, cudaStream_t st, int reps) {
   dim3 grid(ceil_div(C, 32), B);
-  stats_finalize_kernel<<<grid, SF_WARPS * 32, 0, st>>>(partials, n_tiles, n_cols, C, 1.0 / (double)count,
-                                                       hg, h_stride, Cn, ss, ss_stride, c_off, reps);
+  ST2_CUDA_OK(launch_pdl(stats_finalize_kernel, grid, dim3(SF_WARPS * 32), 0, st, partials, n_tiles, n_cols, C,
+                         1.0 / (double)count, hg, h_stride, Cn, ss, ss_stride, c_off, reps));
   ST2_LAUNCH_OK("stats_finalize");
   return ST2_OK;
 }
