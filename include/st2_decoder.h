@@ -92,6 +92,11 @@ typedef struct St2ForwardOpts {
                                micro-batch of a larger batch draws the noise the full batch would */
   const uint64_t* seed_dev; /* optional DEVICE pointer to the Philox seed, read by the kernel instead of
                                `seed`: lets a captured CUDA graph draw fresh noise on every replay */
+  const int32_t* align_idx; /* optional [B, T/2] token index of every asr frame (st2_alignment_indices).  When set,
+                               the `asr` argument is the TOKEN-rate encoding t_en [B, dim_in, align_len] and the
+                               expansion asr = t_en @ pred_aln_trg (Inference_LJSpeech.ipynb cell 17) is fused
+                               into the decoder's input load; -1 = a zero frame */
+  int align_len;            /* tokens per item (Ltext) of t_en */
 } St2ForwardOpts;
 
 /* Decoder(**kwargs): validates the config and builds the layer plan (no weights yet). */
@@ -129,6 +134,21 @@ int st2_decoder_forward(St2Decoder* h, const float* asr, const float* f0, const 
 int64_t st2_f0n_workspace_bytes(const St2Decoder* h, int B, int T, int precision);
 int st2_f0n_forward(St2Decoder* h, const float* x, const float* s, float* f0_out, float* n_out,
                     void* workspace, int64_t workspace_bytes, int B, int T, int precision, void* stream);
+
+/* Duration-based alignment (next row N3; Demo/Inference_LJSpeech.ipynb cell 17, Inference_LibriTTS.ipynb cell 16).
+ *   dur [B, Ltext] int32 durations (frames per token, device) -> idx [B, frames] int32: the token shown by each
+ *   frame, -1 past the item's total; totals [B] (optional) = sum of durations.  shift_one != 0 applies the
+ *   HiFi-GAN one-frame right shift (frame 0 repeated).
+ * st2_expand_alignment materialises x @ one_hot: out[b, c, f] = x[b, c, idx[b, f]] (0 where idx < 0), NCL fp32. */
+int st2_alignment_indices(const int32_t* dur, int B, int Ltext, int frames, int shift_one, int32_t* idx,
+                          int32_t* totals, void* stream);
+int st2_expand_alignment(const float* x, const int32_t* idx, int B, int C, int Ltext, int frames, float* out,
+                         void* stream);
+
+/* Output stage (next row N4): wav [B, L] fp32 -> out [B, L - trim_tail] int16 PCM,
+ * clip(rint(x * 32767), -32768, 32767); trim_tail drops the last samples of every item (the LibriTTS
+ * notebook cuts 50: "weird pulse at the end of the model"). */
+int st2_wave_to_pcm16(const float* wav, int B, int64_t L, int64_t trim_tail, int16_t* out, void* stream);
 
 /* Number of kernel launches the last forward on this handle issued (bench bookkeeping). */
 int64_t st2_decoder_last_launches(const St2Decoder* h);

@@ -40,6 +40,7 @@ class St2ForwardOpts(C.Structure):
         ("seed", C.c_uint64), ("har_source_out", C.c_void_p), ("har_out", C.c_void_p),
         ("tap_decode", C.c_void_p), ("tap_stage", C.c_void_p * MAX_UPS),
         ("item_offset", C.c_int64), ("seed_dev", C.c_void_p),
+        ("align_idx", C.c_void_p), ("align_len", C.c_int),
     ]
 
 
@@ -75,6 +76,9 @@ SYMBOLS = {
     "st2_f0n_workspace_bytes": (C.c_int64, [C.c_void_p, C.c_int, C.c_int, C.c_int]),
     "st2_f0n_forward": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p,
                                   C.c_int64, C.c_int, C.c_int, C.c_int, C.c_void_p]),
+    "st2_wave_to_pcm16": (C.c_int, [C.c_void_p, C.c_int, C.c_int64, C.c_int64, C.c_void_p, C.c_void_p]),
+    "st2_alignment_indices": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p]),
+    "st2_expand_alignment": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_void_p]),
     "st2_decoder_last_launches": (C.c_int64, [C.c_void_p]),
     "st2_decoder_destroy": (None, [C.c_void_p]),
     "st2_last_error": (C.c_char_p, []),

@@ -132,7 +132,12 @@ int colstats_tiles(int L);
 template <typename T>
 int launch_prep_inputs(const float* asr, const float* f0, const float* n, const float* f0w,
                        const float* nw, T* x0, int ld0, T* ca, T* cb, int ldc, int c_f0, int B,
-                       int dim_in, int T2, cudaStream_t st);
+                       int dim_in, int T2, cudaStream_t st, const int* align_idx = nullptr, int align_len = 0);
+int launch_wave_to_pcm16(const float* wav, int B, int64_t L, int64_t trim, int16_t* out, cudaStream_t st);
+int launch_alignment_idx(const int* dur, int B, int Ltext, int frames, int shift, int* idx, int* totals,
+                         cudaStream_t st);
+int launch_expand_alignment(const float* x, const int* idx, int B, int C, int Ltext, int frames, float* out,
+                            cudaStream_t st);
 template <typename T>
 int launch_pool_up2(const T* x, int64_t x_bstride, int ldx, const float* ss, int ss_stride,
                     float slope, const float* w3, const float* bias, T* y, int64_t y_bstride, int ldy,

@@ -953,7 +953,7 @@ int Fwd<AT>::run(const float* asr, const float* f0, const float* nn, const float
   {
     Act<AT> x0 = new_act(T2, ld0), ca = new_act(T2, ldc), cb = new_act(T2, ldc);
     RUN(launch_prep_inputs<AT>(asr, f0, nn, W<float>(h->f0w), W<float>(h->nw), x0.p, ld0, ca.p, cb.p, ldc,
-                               c_f0, B, c.dim_in, T2, st));
+                               c_f0, B, c.dim_in, T2, st, o.align_idx, o.align_len));
     // asr_res = Conv1d(512 -> 64, k1)(asr) written into columns [1024, 1088) of both concat buffers
     for (int which = 0; which < 2; ++which) {
       Act<AT>& dstb = which == 0 ? ca : cb;
@@ -1318,6 +1318,7 @@ extern "C" int st2_decoder_forward(St2Decoder* h, const float* asr, const float*
   if (opts) o = *opts;
   ST2_REQUIRE(o.precision == ST2_PREC_FP32 || o.precision == ST2_PREC_BF16, "precision");
   ST2_REQUIRE(!(o.har && h->cfg.kind != ST2_KIND_ISTFTNET), "har injection is istftnet-only");
+  ST2_REQUIRE(!o.align_idx || o.align_len >= 1, "align_len must be the token count of t_en");
   ST2_REQUIRE(((uintptr_t)workspace & 255) == 0, "workspace must be 256-byte aligned");
   int dev = -1;
   ST2_CUDA_OK(cudaGetDevice(&dev));
@@ -1401,6 +1402,22 @@ extern "C" int st2_f0n_forward(St2Decoder* h, const float* x, const float* s, fl
            : f0n_t<float>(h, x, s, f0_out, n_out, workspace, workspace_bytes, B, T, st, false, nullptr);
   h->last_launches = launch_counter() - before;
   return rc;
+}
+
+extern "C" int st2_wave_to_pcm16(const float* wav, int B, int64_t L, int64_t trim_tail, int16_t* out, void* stream) {
+  ST2_REQUIRE(wav && out && B >= 1 && B <= 65535 && trim_tail >= 0 && L > trim_tail, "st2_wave_to_pcm16: bad argument");
+  return launch_wave_to_pcm16(wav, B, L, trim_tail, out, reinterpret_cast<cudaStream_t>(stream));
+}
+extern "C" int st2_alignment_indices(const int32_t* dur, int B, int Ltext, int frames, int shift_one, int32_t* idx,
+                                     int32_t* totals, void* stream) {
+  ST2_REQUIRE(dur && idx && B >= 1 && B <= 65535 && Ltext >= 1 && frames >= 1, "st2_alignment_indices: bad argument");
+  return launch_alignment_idx(dur, B, Ltext, frames, shift_one, idx, totals, reinterpret_cast<cudaStream_t>(stream));
+}
+extern "C" int st2_expand_alignment(const float* x, const int32_t* idx, int B, int C, int Ltext, int frames, float* out,
+                                    void* stream) {
+  ST2_REQUIRE(x && idx && out && B >= 1 && B <= 65535 && C >= 1 && C <= 65535 && Ltext >= 1 && frames >= 1,
+              "st2_expand_alignment: bad argument");
+  return launch_expand_alignment(x, idx, B, C, Ltext, frames, out, reinterpret_cast<cudaStream_t>(stream));
 }
 
 extern "C" int64_t st2_decoder_last_launches(const St2Decoder* h) { return h ? h->last_launches : 0; }

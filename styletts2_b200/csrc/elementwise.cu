@@ -171,7 +171,8 @@ __global__ void __launch_bounds__(256)
 prep_inputs_kernel(const float* __restrict__ asr, const float* __restrict__ f0,
                    const float* __restrict__ nn, const float* __restrict__ f0w,
                    const float* __restrict__ nw, T* __restrict__ x0, int ld0, T* __restrict__ ca,
-                   T* __restrict__ cb, int ldc, int c_f0, int dim_in, int T2) {
+                   T* __restrict__ cb, int ldc, int c_f0, int dim_in, int T2,
+                   const int* __restrict__ align_idx, int align_len) {
   __shared__ float tile[32][33];
   const int b = blockIdx.z;
   const int t0 = blockIdx.x * 32, ch0 = blockIdx.y * 32;
@@ -182,7 +183,12 @@ prep_inputs_kernel(const float* __restrict__ asr, const float* __restrict__ f0,
     float v = 0.f;
     if (t < T2) {
       if (ch < dim_in) {
-        v = asr[((int64_t)b * dim_in + ch) * T2 + t];
+        if (align_idx) {  // asr = t_en @ one-hot alignment, fused: frame t reads token align_idx[b][t]
+          const int tok = align_idx[(int64_t)b * T2 + t];
+          v = tok >= 0 ? asr[((int64_t)b * dim_in + ch) * align_len + tok] : 0.f;
+        } else {
+          v = asr[((int64_t)b * dim_in + ch) * T2 + t];
+        }
       } else if (ch == dim_in || ch == dim_in + 1) {
         const float* src = (ch == dim_in ? f0 : nn) + (int64_t)b * 2 * T2;
         const float* w = ch == dim_in ? f0w : nw;
@@ -217,19 +223,84 @@ prep_inputs_kernel(const float* __restrict__ asr, const float* __restrict__ f0,
 template <typename T>
 int launch_prep_inputs(const float* asr, const float* f0, const float* n, const float* f0w,
                        const float* nw, T* x0, int ld0, T* ca, T* cb, int ldc, int c_f0, int B,
-                       int dim_in, int T2, cudaStream_t st) {
+                       int dim_in, int T2, cudaStream_t st, const int* align_idx, int align_len) {
   ST2_REQUIRE(ld0 - dim_in >= ldc - c_f0, "prep_inputs: x0 padding must cover the concat padding");
   dim3 grid(ceil_div(T2, 32), ceil_div(ld0, 32), B), block(32, 8);
-  prep_inputs_kernel<T><<<grid, block, 0, st>>>(asr, f0, n, f0w, nw, x0, ld0, ca, cb, ldc, c_f0, dim_in, T2);
+  prep_inputs_kernel<T><<<grid, block, 0, st>>>(asr, f0, n, f0w, nw, x0, ld0, ca, cb, ldc, c_f0, dim_in, T2,
+                                                align_idx, align_len);
   ST2_LAUNCH_OK("prep_inputs");
   return ST2_OK;
 }
 template int launch_prep_inputs<float>(const float*, const float*, const float*, const float*,
                                        const float*, float*, int, float*, float*, int, int, int, int,
-                                       int, cudaStream_t);
+                                       int, cudaStream_t, const int*, int);
 template int launch_prep_inputs<__nv_bfloat16>(const float*, const float*, const float*, const float*,
                                                const float*, __nv_bfloat16*, int, __nv_bfloat16*,
-                                               __nv_bfloat16*, int, int, int, int, int, cudaStream_t);
+                                               __nv_bfloat16*, int, int, int, int, int, cudaStream_t,
+                                               const int*, int);
+
+// ------------------------------------------------------------------------ alignment
+// The reference expands token-rate features to frame rate with a one-hot matrix built on the host
+// (Demo/Inference_LJSpeech.ipynb cell 17: pred_aln_trg[i, c : c + dur[i]] = 1; asr = t_en @ pred_aln_trg).
+// Here: idx[b][f] = the token whose duration interval contains frame f (-1 past the item's total: the
+// matmul's zero columns); shift = HiFi-GAN's one-frame right shift (Inference_LibriTTS.ipynb cell 16:
+// asr_new[..., 0] = asr[..., 0]; asr_new[..., 1:] = asr[..., :-1]).  One block per item.
+__global__ void __launch_bounds__(256)
+alignment_idx_kernel(const int* __restrict__ dur, int Ltext, int frames, int shift, int* __restrict__ idx,
+                     int* __restrict__ totals) {
+  __shared__ int scan[256];
+  __shared__ int carry_s;
+  const int b = blockIdx.x, tid = threadIdx.x;
+  const int* d = dur + (int64_t)b * Ltext;
+  int* out = idx + (int64_t)b * frames;
+  for (int f = tid; f < frames; f += 256) out[f] = -1;
+  if (tid == 0) carry_s = 0;
+  __syncthreads();
+  for (int base = 0; base < Ltext; base += 256) {
+    const int i = base + tid;
+    const int v = i < Ltext ? max(d[i], 0) : 0;
+    scan[tid] = v;
+    __syncthreads();
+    for (int o = 1; o < 256; o <<= 1) {  // inclusive Hillis-Steele scan of one 256-token chunk
+      const int t = tid >= o ? scan[tid - o] : 0;
+      __syncthreads();
+      scan[tid] += t;
+      __syncthreads();
+    }
+    const int carry = carry_s;
+    const int end = carry + scan[tid], start = end - v;
+    for (int f = start; f < end; ++f) {
+      const int g = f + (shift ? 1 : 0);  // frame g shows what frame f held before the shift
+      if (g < frames) out[g] = i;
+      if (shift && f == 0) out[0] = i;
+    }
+    __syncthreads();
+    if (tid == 255) carry_s = carry + scan[255];
+    __syncthreads();
+  }
+  if (tid == 0 && totals) totals[b] = carry_s;
+}
+int launch_alignment_idx(const int* dur, int B, int Ltext, int frames, int shift, int* idx, int* totals,
+                         cudaStream_t st) {
+  alignment_idx_kernel<<<B, 256, 0, st>>>(dur, Ltext, frames, shift, idx, totals);
+  ST2_LAUNCH_OK("alignment_idx");
+  return ST2_OK;
+}
+// out[b][c][f] = idx[b][f] >= 0 ? x[b][c][idx[b][f]] : 0      (x NCL [B][C][Ltext], out NCL [B][C][frames])
+__global__ void expand_alignment_kernel(const float* __restrict__ x, const int* __restrict__ idx, int C, int Ltext,
+                                        int frames, float* __restrict__ out) {
+  const int f = blockIdx.x * blockDim.x + threadIdx.x, c = blockIdx.y, b = blockIdx.z;
+  if (f >= frames) return;
+  const int tok = idx[(int64_t)b * frames + f];
+  out[((int64_t)b * C + c) * frames + f] = tok >= 0 ? x[((int64_t)b * C + c) * Ltext + tok] : 0.f;
+}
+int launch_expand_alignment(const float* x, const int* idx, int B, int C, int Ltext, int frames, float* out,
+                            cudaStream_t st) {
+  dim3 grid(ceil_div(frames, 256), C, B);
+  expand_alignment_kernel<<<grid, 256, 0, st>>>(x, idx, C, Ltext, frames, out);
+  ST2_LAUNCH_OK("expand_alignment");
+  return ST2_OK;
+}
 
 // -------------------------------------------------------------------------- pool x2
 // y[2q]   = w[c][1] * a[q] + bias[c]
@@ -470,6 +541,23 @@ __global__ void tanh_kernel(float* __restrict__ x, int64_t n) {
 int launch_tanh_inplace(float* x, int64_t n, cudaStream_t st) {
   tanh_kernel<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(x, n);
   ST2_LAUNCH_OK("tanh");
+  return ST2_OK;
+}
+
+// Output stage (next row N4): drop the last trim samples of every item (Inference_LibriTTS.ipynb cell 16:
+// out[..., :-50]) and convert to 16-bit PCM: clip(rint(x * 32767), -32768, 32767), round half to even.
+__global__ void wave_to_pcm16_kernel(const float* __restrict__ wav, int64_t L, int64_t Lo, int16_t* __restrict__ out) {
+  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  const int b = blockIdx.y;
+  if (i >= Lo) return;
+  const float v = fminf(fmaxf(wav[(int64_t)b * L + i] * 32767.f, -32768.f), 32767.f);
+  out[(int64_t)b * Lo + i] = (int16_t)__float2int_rn(v);
+}
+int launch_wave_to_pcm16(const float* wav, int B, int64_t L, int64_t trim, int16_t* out, cudaStream_t st) {
+  const int64_t Lo = L - trim;
+  dim3 grid((unsigned)((Lo + 255) / 256), B);
+  wave_to_pcm16_kernel<<<grid, 256, 0, st>>>(wav, L, Lo, out);
+  ST2_LAUNCH_OK("wave_to_pcm16");
   return ST2_OK;
 }
 

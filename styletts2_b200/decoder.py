@@ -183,15 +183,18 @@ class _DecoderBase(nn.Module):
     def forward(self, asr: torch.Tensor, F0_curve: torch.Tensor, N: torch.Tensor, s: torch.Tensor, *,
                 noise: Optional[torch.Tensor] = None, har_source: Optional[torch.Tensor] = None,
                 har: Optional[torch.Tensor] = None, precision: Optional[str] = None,
-                return_excitation: bool = False, return_taps: bool = False, item_offset: int = 0):
+                return_excitation: bool = False, return_taps: bool = False, item_offset: int = 0,
+                alignment: Optional[torch.Tensor] = None):
         """Reference signature plus keyword-only extras; dispatches through the registered custom
         op ``torch.ops.styletts2_b200.decoder_forward`` (see :meth:`_forward_native`).
         ``item_offset`` is the global index of row 0 when the call decodes a slice of a larger batch
-        (the in-kernel noise is keyed by (seed, global item, sample))."""
-        if return_excitation or return_taps:
+        (the in-kernel noise is keyed by (seed, global item, sample)).  ``alignment`` (int32
+        ``[B, T/2]`` from :func:`styletts2_b200.alignment.alignment_indices`) fuses the reference's
+        ``asr = t_en @ pred_aln_trg``: the first argument is then the token-rate ``t_en``."""
+        if return_excitation or return_taps or alignment is not None:
             return self._forward_native(asr, F0_curve, N, s, noise=noise, har_source=har_source, har=har,
                                         precision=precision, return_excitation=return_excitation,
-                                        return_taps=return_taps, item_offset=item_offset)
+                                        return_taps=return_taps, item_offset=item_offset, alignment=alignment)
         from . import ops
         return torch.ops.styletts2_b200.decoder_forward(asr, F0_curve, N, s, noise, har_source, har,
                                                         ops.register_module(self),
@@ -200,7 +203,8 @@ class _DecoderBase(nn.Module):
     def _forward_native(self, asr: torch.Tensor, F0_curve: torch.Tensor, N: torch.Tensor, s: torch.Tensor, *,
                         noise: Optional[torch.Tensor] = None, har_source: Optional[torch.Tensor] = None,
                         har: Optional[torch.Tensor] = None, precision: Optional[str] = None,
-                        return_excitation: bool = False, return_taps: bool = False, item_offset: int = 0):
+                        return_excitation: bool = False, return_taps: bool = False, item_offset: int = 0,
+                        alignment: Optional[torch.Tensor] = None):
         """``Decoder.forward(asr, F0_curve, N, s)`` (istftnet.py:498).  Extra keyword-only inputs
         inject the excitation for reproducibility: ``noise`` [B, 300T, 9] (the randn_like draw of
         SineGen), ``har_source`` [B, 300T] (output of m_source) or ``har`` [B, 22, 60T+1]."""
@@ -211,6 +215,12 @@ class _DecoderBase(nn.Module):
         if asr.dim() != 3 or F0_curve.dim() != 2 or N.dim() != 2 or s.dim() != 2:
             raise RuntimeError("expected asr [B,C,T/2], F0_curve [B,T], N [B,T], s [B,style]")
         B, Cin, T2 = asr.shape
+        align_len = 0
+        if alignment is not None:  # asr is t_en [B, C, Ltext]; frames come from the alignment
+            if alignment.dim() != 2 or alignment.shape[0] != B or not alignment.is_cuda:
+                raise RuntimeError("alignment must be a CUDA int32 tensor [B, T/2] (alignment_indices)")
+            align_len, T2 = T2, alignment.shape[1]
+            alignment = alignment.to(asr.device, torch.int32).contiguous()
         T = F0_curve.shape[1]
         if T != 2 * T2 or N.shape != F0_curve.shape or F0_curve.shape[0] != B or s.shape[0] != B:
             # the reference fails in torch.cat at istftnet.py:513 with a size error
@@ -252,11 +262,11 @@ class _DecoderBase(nn.Module):
                     wav[lo:hi] = self._forward_native(
                         asr_[lo:hi], f0_[lo:hi], n_[lo:hi], s_[lo:hi], noise=sl(noise_, lo, hi),
                         har_source=sl(hs_, lo, hi), har=sl(har_, lo, hi), precision=prec,
-                        item_offset=item_offset + lo)
+                        item_offset=item_offset + lo, alignment=sl(alignment, lo, hi))
                     launches += self.last_launches
                 self.last_launches = launches
                 return wav
-            if (self.cuda_graphs and noise_ is None and hs_ is None and har_ is None
+            if (self.cuda_graphs and noise_ is None and hs_ is None and har_ is None and alignment is None
                     and not (return_excitation or return_taps) and not torch.cuda.is_current_stream_capturing()):
                 return self._forward_graph(h, asr_, f0_, n_, s_, int(need), prec_id, int(item_offset))
             ws = torch.empty(int(need), dtype=torch.uint8, device=dev)
@@ -264,6 +274,8 @@ class _DecoderBase(nn.Module):
             opts = _cabi.St2ForwardOpts()
             opts.precision = prec_id
             opts.item_offset = int(item_offset)
+            if alignment is not None:
+                opts.align_idx, opts.align_len = alignment.data_ptr(), int(align_len)
             opts.noise, opts.har_source, opts.har = (t.data_ptr() if t is not None else None
                                                      for t in (noise_, hs_, har_))
             opts.seed = int(self.seed)

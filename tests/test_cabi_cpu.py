@@ -33,7 +33,7 @@ def test_struct_layouts_match_header_sizes():
     # St2ConvParams: ints/pointers/int64 interleaved; ctypes applies the same natural alignment as C
     assert C.sizeof(_cabi.St2ConvParams) % 8 == 0
     assert C.sizeof(_cabi.St2Tensor) == 8 + 8 + 8 + 32
-    assert C.sizeof(_cabi.St2ForwardOpts) == 56 + 8 + 32 + 8 + 8  # + item_offset, seed_dev
+    assert C.sizeof(_cabi.St2ForwardOpts) == 56 + 8 + 32 + 8 + 8 + 8 + 8  # + item_offset, seed_dev, align_idx, align_len (+ padding)
 
 
 @pytest.mark.parametrize("kind", ["istftnet", "hifigan"])

@@ -270,3 +270,58 @@ def test_module_prefix_state_dict_and_custom_op():
                                                    None, None, _c(g["tap_har"]),
                                                    st2.ops.register_module(d2), "fp32")
     assert (out.cpu() - g["wav"]).abs().max().item() < 5e-5
+
+
+@pytest.mark.parametrize("shift", [False, True])
+def test_alignment_expansion_matches_the_notebook(shift):
+    """next row N3: device alignment indices + gather == the reference's one-hot matmul (bit exact: every
+    output is one input value), ragged totals, zero-length tokens, more than 256 tokens"""
+    from oracle import alignment_oracle as aorc
+    from styletts2_b200.alignment import alignment_indices, expand
+    g = torch.Generator().manual_seed(3)
+    B, C, L = 3, 40, 300
+    dur = torch.randint(0, 6, (B, L), generator=g)
+    dur[1, 200:] = 0          # a shorter item
+    dur[2, :5] = 0            # leading zero-length tokens
+    x = torch.randn(B, C, L, generator=g)
+    frames = int(dur.sum(1).max())
+    idx, totals = alignment_indices(dur.cuda(), shift=shift)
+    assert idx.shape == (B, frames) and totals.cpu().tolist() == dur.sum(1).tolist()
+    got = expand(x.cuda(), idx).cpu()
+    ref = aorc.expand(x, dur, frames, shift)
+    assert torch.equal(got, ref)
+
+
+@pytest.mark.parametrize("kind", ["istftnet", "hifigan"])
+def test_decoder_with_fused_alignment_equals_materialised_asr(kind):
+    import synthetic as synth
+    from oracle import alignment_oracle as aorc
+    from styletts2_b200.alignment import alignment_indices
+    dec, sd, cfg = _get(kind)
+    g = torch.Generator().manual_seed(11)
+    B, L = 2, 17
+    dur = torch.randint(1, 4, (B, L), generator=g)
+    dur[1, 12:] = 0
+    T2 = int(dur.sum(1).max())
+    t_en = torch.randn(B, 512, L, generator=g)
+    inp = synth.synth_inputs(cfg, B, 2 * T2, seed=2)
+    shift = kind == "hifigan"
+    asr = aorc.expand(t_en, dur, T2, shift)
+    idx, _ = alignment_indices(dur.cuda(), frames=T2, shift=shift)
+    a = {k: v.cuda() for k, v in inp.items()}
+    for prec in ("fp32", "bf16"):
+        ref = dec(asr.cuda(), a["F0_curve"], a["N"], a["s"], noise=a["noise"], precision=prec)
+        got = dec(t_en.cuda(), a["F0_curve"], a["N"], a["s"], noise=a["noise"], precision=prec, alignment=idx)
+        assert torch.equal(ref, got), prec
+
+
+def test_pcm16_output_stage():
+    """next row N4: trim + 16-bit PCM on the device == numpy's clip(rint(x * 32767)) of the trimmed wave"""
+    from styletts2_b200.output import to_pcm16
+    g = torch.Generator().manual_seed(5)
+    wav = torch.randn(3, 1, 1000, generator=g) * 0.7
+    wav[0, 0, :4] = torch.tensor([1.5, -1.5, 0.5 / 32767, 1.5 / 32767])  # clipping and ties
+    got = to_pcm16(wav.cuda(), trim_tail=50).cpu().numpy()
+    ref = np.clip(np.rint(wav.reshape(3, -1).numpy()[..., :-50] * np.float32(32767)), -32768, 32767).astype(np.int16)
+    assert got.shape == (3, 950) and got.dtype == np.int16
+    assert np.array_equal(got, ref)
