@@ -133,6 +133,9 @@ template <typename T>
 int launch_prep_inputs(const float* asr, const float* f0, const float* n, const float* f0w,
                        const float* nw, T* x0, int ld0, T* ca, T* cb, int ldc, int c_f0, int B,
                        int dim_in, int T2, cudaStream_t st, const int* align_idx = nullptr, int align_len = 0);
+int launch_norm_act_bf16(const __nv_bfloat16* x, int64_t x_bstride, int ldx, const float* ss, int ss_stride,
+                         float slope, __nv_bfloat16* y, int64_t y_bstride, int ldy, int B, int L, int C,
+                         cudaStream_t st);
 int launch_wave_to_pcm16(const float* wav, int B, int64_t L, int64_t trim, int16_t* out, cudaStream_t st);
 int launch_alignment_idx(const int* dur, int B, int Ltext, int frames, int shift, int* idx, int* totals,
                          cudaStream_t st);

@@ -776,6 +776,12 @@ struct Fwd {
     return a;
   }
 
+  // y = lrelu(AdaIN(x)) as its own pass (bf16 activations only)
+  int norm_act(const Act<AT>& x, const NormW& n, float slope, const Act<AT>& y, int C) {
+    return launch_norm_act_bf16(reinterpret_cast<const __nv_bfloat16*>(x.p), x.bstride, x.ld, ss_of(n), h->ss_pairs,
+                                slope, reinterpret_cast<__nv_bfloat16*>(y.p), y.bstride, y.ld, B, x.L, C, st);
+  }
+
   // AdainResBlk1d (istftnet.py:440-453).  `in` has r.din_pad columns; norm1 of `in` must already be
   // finalized.  Output goes to out (any ld).  want_out_stats leaves partials in last_*.
   int resblk1d(const ResBlk1dW& r, const Act<AT>& in, const Act<AT>& out, bool want_out_stats) {
@@ -788,9 +794,17 @@ struct Fwd {
                               W<float>(r.pool_b), cin1.p, cin1.bstride, cin1.ld, B, L, r.din, r.din_pad, st));
     }
     Act<AT> hbuf = new_act(Lo, r.dout);
+    // wide layers (N >= 512: every activation tile feeds >= 4 N tiles of the tcgen05 kernel): AdaIN +
+    // LeakyReLU are applied once by an elementwise pass instead of once per N tile in the conv prologue
+    const bool pre_act = DT<AT>::id == ST2_DT_BF16 && r.conv1.w16 >= 0 && r.dout >= 512;
     {
+      if (pre_act && !r.up) {
+        Act<AT> a1 = new_act(Lo, r.din_pad);
+        RUN(norm_act(cin1, r.n1, 0.2f, a1, r.din_pad));
+        cin1 = a1;
+      }
       ConvIO io = io_of(cin1, hbuf);
-      if (!r.up) { io.pre_norm = &r.n1; io.act = ST2_ACT_LRELU; io.slope = 0.2f; }
+      if (!r.up && !pre_act) { io.pre_norm = &r.n1; io.act = ST2_ACT_LRELU; io.slope = 0.2f; }
       io.want_stats = true;
       const int64_t m1 = ar.mark();
       int rc = conv(r.conv1, io);
@@ -807,8 +821,13 @@ struct Fwd {
       if (rc) return rc;
     }
     {
-      ConvIO io = io_of(hbuf, out);
-      io.pre_norm = &r.n2; io.act = ST2_ACT_LRELU; io.slope = 0.2f;
+      Act<AT> cin2 = hbuf;
+      if (pre_act) {
+        cin2 = new_act(Lo, r.dout);
+        RUN(norm_act(hbuf, r.n2, 0.2f, cin2, r.dout));
+      }
+      ConvIO io = io_of(cin2, out);
+      if (!pre_act) { io.pre_norm = &r.n2; io.act = ST2_ACT_LRELU; io.slope = 0.2f; }
       io.res = sc.p; io.res_bstride = sc.bstride; io.ldres = sc.ld; io.res_shift = r.up ? 1 : 0;
       io.out_scale = 0.70710678118654752440f;  // 1/sqrt(2), istftnet.py:452
       io.want_stats = want_out_stats;

@@ -302,6 +302,57 @@ int launch_expand_alignment(const float* x, const int* idx, int B, int C, int Lt
   return ST2_OK;
 }
 
+// ------------------------------------------------------------------------- norm + act
+// y = lrelu(x * scale[b,c] + shift[b,c]) on a bf16 channels-last tensor, 8 channels per thread.
+// Used where one activation tile feeds many N tiles (N >= 512: the decode / encode blocks and the
+// F0/N predictor): applying AdaIN + LeakyReLU once here is cheaper than once per N tile in the conv
+// prologue, which then degenerates to plain cp.async staging.
+constexpr int NA_ROWS = 8;
+__global__ void __launch_bounds__(256)
+norm_act_bf16_kernel(const __nv_bfloat16* __restrict__ x, int64_t x_bstride, int ldx, const float* __restrict__ ss,
+                     int ss_stride, float slope, __nv_bfloat16* __restrict__ y, int64_t y_bstride, int ldy,
+                     int L, int C8) {
+  const int g = blockIdx.x * blockDim.x + threadIdx.x;  // group of 8 channels
+  const int b = blockIdx.z;
+  if (g >= C8) return;
+  float sc[8], sh[8];
+  const float4* sp = reinterpret_cast<const float4*>(ss + ((int64_t)b * ss_stride + g * 8) * 2);
+#pragma unroll
+  for (int e = 0; e < 4; ++e) {
+    const float4 t = __ldg(sp + e);
+    sc[2 * e] = t.x; sh[2 * e] = t.y; sc[2 * e + 1] = t.z; sh[2 * e + 1] = t.w;
+  }
+  const int r0 = blockIdx.y * NA_ROWS;
+#pragma unroll
+  for (int i = 0; i < NA_ROWS; ++i) {
+    const int r = r0 + i;
+    if (r >= L) break;
+    const uint4 raw = *reinterpret_cast<const uint4*>(x + (int64_t)b * x_bstride + (int64_t)r * ldx + g * 8);
+    const uint32_t w[4] = {raw.x, raw.y, raw.z, raw.w};
+    uint32_t o[4];
+#pragma unroll
+    for (int e = 0; e < 4; ++e) {
+      float lo = fmaf(__uint_as_float(w[e] << 16), sc[2 * e], sh[2 * e]);
+      float hi = fmaf(__uint_as_float(w[e] & 0xFFFF0000u), sc[2 * e + 1], sh[2 * e + 1]);
+      lo = fmaxf(lo, lo * slope);
+      hi = fmaxf(hi, hi * slope);
+      const __nv_bfloat162 pk = __floats2bfloat162_rn(lo, hi);
+      o[e] = *reinterpret_cast<const uint32_t*>(&pk);
+    }
+    *reinterpret_cast<uint4*>(y + (int64_t)b * y_bstride + (int64_t)r * ldy + g * 8) = make_uint4(o[0], o[1], o[2], o[3]);
+  }
+}
+int launch_norm_act_bf16(const __nv_bfloat16* x, int64_t x_bstride, int ldx, const float* ss, int ss_stride,
+                         float slope, __nv_bfloat16* y, int64_t y_bstride, int ldy, int B, int L, int C,
+                         cudaStream_t st) {
+  ST2_REQUIRE(C % 8 == 0 && ldx % 8 == 0 && ldy % 8 == 0 && slope >= 0.f && slope <= 1.f, "norm_act: shape");
+  const int C8 = C / 8, threads = C8 < 128 ? 64 : 128;
+  dim3 grid(ceil_div(C8, threads), ceil_div(L, NA_ROWS), B);
+  norm_act_bf16_kernel<<<grid, threads, 0, st>>>(x, x_bstride, ldx, ss, ss_stride, slope, y, y_bstride, ldy, L, C8);
+  ST2_LAUNCH_OK("norm_act");
+  return ST2_OK;
+}
+
 // -------------------------------------------------------------------------- pool x2
 // y[2q]   = w[c][1] * a[q] + bias[c]
 // y[2q+1] = w[c][2] * a[q] + w[c][0] * a[q+1] + bias[c],   a = lrelu(x*scale+shift), a[Lin] = 0
