@@ -65,6 +65,7 @@ struct UmLayout {
   int w_bytes;        // bytes per weight stage (= 8 * n_tile * 16)
   int out_row;        // bytes per output row segment (n_tile * element size), multiple of 128
   int n_res, n_acc;   // extra 64-channel chunks per tile: residual rows, y_old rows
+  int res_tma, acc_tma;  // those rows come by TMA tensor loads (one thread) instead of 256 threads' cp.async
   const uint8_t* ident_res;  // n_tile/64 identity weight blobs (x 1)
   const uint8_t* ident_acc;  // n_tile/64 identity weight blobs (x 1/out_scale)
   uint32_t off_a, off_w, off_misc, total;  // the staging tile sits at offset 0 (1024-byte aligned)
@@ -154,6 +155,19 @@ __device__ __forceinline__ void tma_store_3d(const CUtensorMap* map, uint32_t sm
   asm volatile("cp.async.bulk.tensor.3d.global.shared::cta.bulk_group [%0, {%2, %3, %4}], [%1];" ::"l"(map),
                "r"(smem_src), "r"(c0), "r"(c1), "r"(c2)
                : "memory");
+}
+// global -> smem TMA tensor load (3-D map), completion reported as transaction bytes on an mbarrier;
+// elements outside the tensor are zero-filled
+__device__ __forceinline__ void tma_load_3d(const CUtensorMap* map, uint32_t smem_dst, int c0, int c1, int c2,
+                                            uint64_t* bar) {
+  asm volatile(
+      "cp.async.bulk.tensor.3d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5}], [%2];" ::"r"(
+          smem_dst),
+      "l"(map), "r"(smem_u32(bar)), "r"(c0), "r"(c1), "r"(c2)
+      : "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
+  asm volatile("mbarrier.expect_tx.relaxed.cta.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
 }
 __device__ __forceinline__ void bulk_commit() { asm volatile("cp.async.bulk.commit_group;" ::: "memory"); }
 __device__ __forceinline__ void bulk_wait_read0() {
@@ -361,7 +375,8 @@ __device__ __forceinline__ float um_act(float v, float sc, float sh, float wsc, 
 }
 
 template <int ACT, bool HAS_SS>
-__device__ __forceinline__ void um_produce(const St2ConvParams& p, const UmLayout& lay, uint8_t* smem,
+__device__ __forceinline__ void um_produce(const St2ConvParams& p, const UmLayout& lay, const CUtensorMap* ymap,
+                                           const CUtensorMap* rmap, uint8_t* smem,
                                            UmMisc* misc, int ptid, int total_tiles, int n_ttiles,
                                            int n_ntiles, int nchunks) {
   const int v = ptid & 7, rbase = ptid >> 3;
@@ -390,6 +405,20 @@ __device__ __forceinline__ void um_produce(const St2ConvParams& p, const UmLayou
       const int e = q.c - nchunks;
       const bool is_res = e < lay.n_res;
       const int hh = is_res ? e : e - lay.n_res;
+      if (is_res ? lay.res_tma : lay.acc_tma) {
+        // two 128-row boxes in the SWIZZLE_128B pattern of the A tile, zero-filled past Lout; the bytes
+        // are expected on a_full[stage] next to the producers' 256 arrivals
+        if (ptid == 0) {
+          const uint32_t base = smem_u32(smem + lay.off_a) + (uint32_t)q.stage * (uint32_t)lay.a_bytes;
+          const int col = q.nt * lay.n_tile + hh * UM_CK;
+          const bool two = q.t0 + 128 < p.Lout;
+          mbar_expect_tx(&misc->a_full[q.stage], two ? 32768u : 16384u);
+          const CUtensorMap* mp = is_res ? rmap : ymap;
+          tma_load_3d(mp, base, col, q.t0, q.b, &misc->a_full[q.stage]);
+          if (two) tma_load_3d(mp, base + 16384u, col, q.t0 + 128, q.b, &misc->a_full[q.stage]);
+        }
+        return;
+      }
       const __nv_bfloat16* sb;
       int ld, shift;
       if (is_res) {
@@ -437,11 +466,15 @@ __device__ __forceinline__ void um_produce(const St2ConvParams& p, const UmLayou
     else if (newer == 1) cp_async_wait<1>();
     else cp_async_wait<0>();
     if (q.c >= nchunks) {
-      const int t = q.t0 + rbase;
+      const bool tma = (q.c - nchunks) < lay.n_res ? lay.res_tma : lay.acc_tma;
+      if (!tma) {
+        const int t = q.t0 + rbase;
 #pragma unroll
-      for (int i = 0; i < UM_TM / 32; ++i)
-        if (t + 32 * i >= p.Lout) sts128(dst + (uint32_t)i * 4096u, make_uint4(0u, 0u, 0u, 0u));
-      fence_proxy_async_smem();
+        for (int i = 0; i < UM_TM / 32; ++i)
+          if (t + 32 * i >= p.Lout) sts128(dst + (uint32_t)i * 4096u, make_uint4(0u, 0u, 0u, 0u));
+        fence_proxy_async_smem();
+      }
+      // TMA rows: nothing to do (rows past Lout of a half-loaded tile are never stored or counted)
       mbar_arrive(&misc->a_full[q.stage]);
       return;
     }
@@ -750,6 +783,7 @@ __device__ __forceinline__ void um_epilogue(const St2ConvParams& p, const UmLayo
 
 __global__ void __launch_bounds__(UM_THREADS, 1) conv_umma_kernel(const St2ConvParams p, const UmLayout lay,
                                                                    const __grid_constant__ CUtensorMap ymap,
+                                                                   const __grid_constant__ CUtensorMap rmap,
                                                                    int total_tiles, int n_ttiles, int n_ntiles) {
   extern __shared__ __align__(1024) uint8_t smem_raw[];
   pdl_wait_then_trigger();  // launched with the programmatic-serialization attribute (common.cuh)
@@ -913,13 +947,13 @@ __global__ void __launch_bounds__(UM_THREADS, 1) conv_umma_kernel(const St2ConvP
     // ============================================================ activation producers
     const int ptid = threadIdx.x - UM_PROD_WARP0 * 32;
     if (p.ss) {
-      if (p.act == ST2_ACT_SNAKE) um_produce<ST2_ACT_SNAKE, true>(p, lay, smem_raw, misc, ptid, total_tiles, n_ttiles, n_ntiles, nchunks);
-      else if (p.act == ST2_ACT_LRELU) um_produce<ST2_ACT_LRELU, true>(p, lay, smem_raw, misc, ptid, total_tiles, n_ttiles, n_ntiles, nchunks);
-      else um_produce<ST2_ACT_NONE, true>(p, lay, smem_raw, misc, ptid, total_tiles, n_ttiles, n_ntiles, nchunks);
+      if (p.act == ST2_ACT_SNAKE) um_produce<ST2_ACT_SNAKE, true>(p, lay, &ymap, &rmap, smem_raw, misc, ptid, total_tiles, n_ttiles, n_ntiles, nchunks);
+      else if (p.act == ST2_ACT_LRELU) um_produce<ST2_ACT_LRELU, true>(p, lay, &ymap, &rmap, smem_raw, misc, ptid, total_tiles, n_ttiles, n_ntiles, nchunks);
+      else um_produce<ST2_ACT_NONE, true>(p, lay, &ymap, &rmap, smem_raw, misc, ptid, total_tiles, n_ttiles, n_ntiles, nchunks);
     } else {
-      if (p.act == ST2_ACT_SNAKE) um_produce<ST2_ACT_SNAKE, false>(p, lay, smem_raw, misc, ptid, total_tiles, n_ttiles, n_ntiles, nchunks);
-      else if (p.act == ST2_ACT_LRELU) um_produce<ST2_ACT_LRELU, false>(p, lay, smem_raw, misc, ptid, total_tiles, n_ttiles, n_ntiles, nchunks);
-      else um_produce<ST2_ACT_NONE, false>(p, lay, smem_raw, misc, ptid, total_tiles, n_ttiles, n_ntiles, nchunks);
+      if (p.act == ST2_ACT_SNAKE) um_produce<ST2_ACT_SNAKE, false>(p, lay, &ymap, &rmap, smem_raw, misc, ptid, total_tiles, n_ttiles, n_ntiles, nchunks);
+      else if (p.act == ST2_ACT_LRELU) um_produce<ST2_ACT_LRELU, false>(p, lay, &ymap, &rmap, smem_raw, misc, ptid, total_tiles, n_ttiles, n_ntiles, nchunks);
+      else um_produce<ST2_ACT_NONE, false>(p, lay, &ymap, &rmap, smem_raw, misc, ptid, total_tiles, n_ttiles, n_ntiles, nchunks);
     }
   }
 
@@ -1074,6 +1108,24 @@ static int um_ymap(const St2ConvParams& p, CUtensorMap* map) {
   return ST2_OK;
 }
 
+// residual view [B][Lout][n_cols] of p.res (row stride ldres), same box / swizzle as the output map
+static int um_rmap(const St2ConvParams& p, CUtensorMap* map) {
+  int rc = um_encode_fn();
+  if (rc) return rc;
+  const cuuint64_t gdim[3] = {(cuuint64_t)p.n_cols, (cuuint64_t)p.Lout, (cuuint64_t)p.B};
+  const cuuint64_t gstr[2] = {(cuuint64_t)p.ldres * 2, (cuuint64_t)(p.B > 1 ? p.res_bstride : (int64_t)p.ldres * p.Lout) * 2};
+  const cuuint32_t box[3] = {64u, 128u, 1u};
+  const cuuint32_t estr[3] = {1u, 1u, 1u};
+  const CUresult r = g_encode(map, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 3, const_cast<void*>(p.res), gdim, gstr, box, estr,
+                              CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
+                              CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) {
+    set_error("conv_umma: cuTensorMapEncodeTiled (residual) failed with code " + std::to_string((int)r));
+    return ST2_ECUDA;
+  }
+  return ST2_OK;
+}
+
 static int g_num_sms[64] = {};
 
 // optional per-launch event timing (st2_prof_enable / st2_prof_read)
@@ -1116,6 +1168,20 @@ int launch_conv_umma(const St2ConvParams& p, cudaStream_t st) {
   CUtensorMap ymap;
   rc = um_ymap(p, &ymap);
   if (rc) return rc;
+  // residual / y_old rows by TMA when the source is a plain [B][Lout][>= n_cols] bf16 view (not the x2-repeated
+  // shortcut of the upsampling block); ST2_UMMA_RES_TMA=0 keeps the cp.async path (A/B switch)
+  static const bool tma_ok = [] { const char* e = getenv("ST2_UMMA_RES_TMA"); return !(e && e[0] == '0'); }();
+  CUtensorMap rmap = ymap;
+  lay.res_tma = lay.acc_tma = 0;
+  if (tma_ok && p.y_dtype == ST2_DT_BF16) {
+    if (lay.n_acc) lay.acc_tma = 1;
+    if (lay.n_res && p.res_shift == 0 && (((uintptr_t)p.res) & 15) == 0 && (p.ldres % 8) == 0 &&
+        (p.res_bstride % 8) == 0) {
+      rc = um_rmap(p, &rmap);
+      if (rc) return rc;
+      lay.res_tma = 1;
+    }
+  }
   const int n_ttiles = ceil_div(p.Lout, UM_TM), n_ntiles = p.n_cols / lay.n_tile;
   ST2_REQUIRE(!p.stats || p.n_tiles >= n_ttiles, "conv_umma: n_tiles");
   const int64_t total = (int64_t)p.B * n_ttiles * n_ntiles;
@@ -1144,7 +1210,7 @@ int launch_conv_umma(const St2ConvParams& p, cudaStream_t st) {
     g_prof.flops += p.algo_flops;
     ST2_CUDA_OK(cudaEventRecord(e0, st));
   }
-  ST2_CUDA_OK(launch_pdl(conv_umma_kernel, dim3(grid), dim3(UM_THREADS), (size_t)lay.total, st, p, lay, ymap, (int)total,
+  ST2_CUDA_OK(launch_pdl(conv_umma_kernel, dim3(grid), dim3(UM_THREADS), (size_t)lay.total, st, p, lay, ymap, rmap, (int)total,
                          n_ttiles, n_ntiles));
   ST2_LAUNCH_OK("conv_umma");
   if (e1) ST2_CUDA_OK(cudaEventRecord(e1, st));
