@@ -66,6 +66,7 @@ struct UmLayout {
   int out_row;        // bytes per output row segment (n_tile * element size), multiple of 128
   int n_res, n_acc;   // extra 64-channel chunks per tile: residual rows, y_old rows
   int res_tma, acc_tma;  // those rows come by TMA tensor loads (one thread) instead of 256 threads' cp.async
+  int x_tma;          // the raw activation tile too: one 256-row box + ceil(halo / 8) boxes of 8 rows
   const uint8_t* ident_res;  // n_tile/64 identity weight blobs (x 1)
   const uint8_t* ident_acc;  // n_tile/64 identity weight blobs (x 1/out_scale)
   uint32_t off_a, off_w, off_misc, total;  // the staging tile sits at offset 0 (1024-byte aligned)
@@ -75,6 +76,7 @@ struct UmLayout {
 
 struct UmMisc {
   uint64_t a_full[UM_MAX_A], a_empty[UM_MAX_A];
+  uint64_t raw_full[UM_MAX_A];  // raw activation tile of the stage has landed (TMA transaction bytes)
   uint64_t w_full[UM_W_STAGES], w_empty[UM_W_STAGES];
   uint64_t t_full[2], t_empty[2];
   uint32_t tmem_base, pad_;
@@ -376,7 +378,8 @@ __device__ __forceinline__ float um_act(float v, float sc, float sh, float wsc, 
 
 template <int ACT, bool HAS_SS>
 __device__ __forceinline__ void um_produce(const St2ConvParams& p, const UmLayout& lay, const CUtensorMap* ymap,
-                                           const CUtensorMap* rmap, uint8_t* smem,
+                                           const CUtensorMap* rmap, const CUtensorMap* xmap,
+                                           const CUtensorMap* xmap8, uint8_t* smem,
                                            UmMisc* misc, int ptid, int total_tiles, int n_ttiles,
                                            int n_ntiles, int nchunks) {
   const int v = ptid & 7, rbase = ptid >> 3;
@@ -392,7 +395,23 @@ __device__ __forceinline__ void um_produce(const St2ConvParams& p, const UmLayou
   // the caller has seen a_empty[q.stage] complete for this round of the ring
   auto issue_loads = [&](const UmCur& q) {
     const uint32_t dst = a0 + (uint32_t)q.stage * (uint32_t)lay.a_bytes;
-    if (q.c < nchunks) {
+    if (q.c < nchunks && lay.x_tma) {
+      // tile row r holds input row t0 - pad + r: one 256-row box and the halo in 8-row boxes, all
+      // zero-filled outside [0, Lin).  A conv without prologue arithmetic (IDENT) hands the bytes
+      // straight to the MMA barrier; otherwise the producers wait for them on raw_full.
+      if (ptid == 0) {
+        uint64_t* bar = IDENT ? &misc->a_full[q.stage] : &misc->raw_full[q.stage];
+        const uint32_t base = smem_u32(smem + lay.off_a) + (uint32_t)q.stage * (uint32_t)lay.a_bytes;
+        const int nh = (r_tot - UM_TM + 7) >> 3;
+        const int row0 = q.t0 - p.pad, col = q.c * UM_CK;
+        const uint32_t bytes = (uint32_t)(UM_TM * 128 + nh * 1024);
+        if (IDENT) mbar_expect_tx(bar, bytes);      // next to the 256 producer arrivals
+        else mbar_arrive_expect_tx(bar, bytes);     // raw_full: this is its only arrival
+        tma_load_3d(xmap, base, col, row0, q.b, bar);
+        for (int i = 0; i < nh; ++i)
+          tma_load_3d(xmap8, base + (uint32_t)(UM_TM * 128 + i * 1024), col, row0 + UM_TM + 8 * i, q.b, bar);
+      }
+    } else if (q.c < nchunks) {
       // tile row r holds input row t0 - pad + r; rows outside [0, Lin) stay untouched (zeroed later)
       const int row0 = q.t0 - p.pad + rbase;
       const int lo = -row0, hi = min(r_tot - rbase, p.Lin - row0);  // valid: lo <= 32 i < hi
@@ -405,6 +424,8 @@ __device__ __forceinline__ void um_produce(const St2ConvParams& p, const UmLayou
       const int e = q.c - nchunks;
       const bool is_res = e < lay.n_res;
       const int hh = is_res ? e : e - lay.n_res;
+      // keep raw_full[stage] in step with the ring: this use of the stage has no raw tile
+      if (lay.x_tma && !IDENT && ptid == 0) mbar_arrive(&misc->raw_full[q.stage]);
       if (is_res ? lay.res_tma : lay.acc_tma) {
         // two 128-row boxes in the SWIZZLE_128B pattern of the A tile, zero-filled past Lout; the bytes
         // are expected on a_full[stage] next to the producers' 256 arrivals
@@ -477,6 +498,13 @@ __device__ __forceinline__ void um_produce(const St2ConvParams& p, const UmLayou
       // TMA rows: nothing to do (rows past Lout of a half-loaded tile are never stored or counted)
       mbar_arrive(&misc->a_full[q.stage]);
       return;
+    }
+    if (lay.x_tma) {
+      if (IDENT) {  // the TMA zero-fill is the conv's zero padding: nothing to touch
+        mbar_arrive(&misc->a_full[q.stage]);
+        return;
+      }
+      mbar_wait(&misc->raw_full[q.stage], q.ph, 6);
     }
     const int row0 = q.t0 - p.pad + rbase;
     const int lo = -row0, hi = min(r_tot - rbase, p.Lin - row0), tot = r_tot - rbase;
@@ -784,6 +812,8 @@ __device__ __forceinline__ void um_epilogue(const St2ConvParams& p, const UmLayo
 __global__ void __launch_bounds__(UM_THREADS, 1) conv_umma_kernel(const St2ConvParams p, const UmLayout lay,
                                                                    const __grid_constant__ CUtensorMap ymap,
                                                                    const __grid_constant__ CUtensorMap rmap,
+                                                                   const __grid_constant__ CUtensorMap xmap,
+                                                                   const __grid_constant__ CUtensorMap xmap8,
                                                                    int total_tiles, int n_ttiles, int n_ntiles) {
   extern __shared__ __align__(1024) uint8_t smem_raw[];
   pdl_wait_then_trigger();  // launched with the programmatic-serialization attribute (common.cuh)
@@ -796,6 +826,7 @@ __global__ void __launch_bounds__(UM_THREADS, 1) conv_umma_kernel(const St2ConvP
     for (int i = 0; i < UM_MAX_A; ++i) {
       mbar_init(&misc->a_full[i], UM_PROD_THREADS);
       mbar_init(&misc->a_empty[i], 1);
+      mbar_init(&misc->raw_full[i], 1);
     }
     for (int i = 0; i < UM_W_STAGES; ++i) {
       mbar_init(&misc->w_full[i], 1);
@@ -947,13 +978,13 @@ __global__ void __launch_bounds__(UM_THREADS, 1) conv_umma_kernel(const St2ConvP
     // ============================================================ activation producers
     const int ptid = threadIdx.x - UM_PROD_WARP0 * 32;
     if (p.ss) {
-      if (p.act == ST2_ACT_SNAKE) um_produce<ST2_ACT_SNAKE, true>(p, lay, &ymap, &rmap, smem_raw, misc, ptid, total_tiles, n_ttiles, n_ntiles, nchunks);
-      else if (p.act == ST2_ACT_LRELU) um_produce<ST2_ACT_LRELU, true>(p, lay, &ymap, &rmap, smem_raw, misc, ptid, total_tiles, n_ttiles, n_ntiles, nchunks);
-      else um_produce<ST2_ACT_NONE, true>(p, lay, &ymap, &rmap, smem_raw, misc, ptid, total_tiles, n_ttiles, n_ntiles, nchunks);
+      if (p.act == ST2_ACT_SNAKE) um_produce<ST2_ACT_SNAKE, true>(p, lay, &ymap, &rmap, &xmap, &xmap8, smem_raw, misc, ptid, total_tiles, n_ttiles, n_ntiles, nchunks);
+      else if (p.act == ST2_ACT_LRELU) um_produce<ST2_ACT_LRELU, true>(p, lay, &ymap, &rmap, &xmap, &xmap8, smem_raw, misc, ptid, total_tiles, n_ttiles, n_ntiles, nchunks);
+      else um_produce<ST2_ACT_NONE, true>(p, lay, &ymap, &rmap, &xmap, &xmap8, smem_raw, misc, ptid, total_tiles, n_ttiles, n_ntiles, nchunks);
     } else {
-      if (p.act == ST2_ACT_SNAKE) um_produce<ST2_ACT_SNAKE, false>(p, lay, &ymap, &rmap, smem_raw, misc, ptid, total_tiles, n_ttiles, n_ntiles, nchunks);
-      else if (p.act == ST2_ACT_LRELU) um_produce<ST2_ACT_LRELU, false>(p, lay, &ymap, &rmap, smem_raw, misc, ptid, total_tiles, n_ttiles, n_ntiles, nchunks);
-      else um_produce<ST2_ACT_NONE, false>(p, lay, &ymap, &rmap, smem_raw, misc, ptid, total_tiles, n_ttiles, n_ntiles, nchunks);
+      if (p.act == ST2_ACT_SNAKE) um_produce<ST2_ACT_SNAKE, false>(p, lay, &ymap, &rmap, &xmap, &xmap8, smem_raw, misc, ptid, total_tiles, n_ttiles, n_ntiles, nchunks);
+      else if (p.act == ST2_ACT_LRELU) um_produce<ST2_ACT_LRELU, false>(p, lay, &ymap, &rmap, &xmap, &xmap8, smem_raw, misc, ptid, total_tiles, n_ttiles, n_ntiles, nchunks);
+      else um_produce<ST2_ACT_NONE, false>(p, lay, &ymap, &rmap, &xmap, &xmap8, smem_raw, misc, ptid, total_tiles, n_ttiles, n_ntiles, nchunks);
     }
   }
 
@@ -1126,6 +1157,24 @@ static int um_rmap(const St2ConvParams& p, CUtensorMap* map) {
   return ST2_OK;
 }
 
+// input view [B][Lin][cin] of p.x (row stride ldx); rows = 256 for the body of a tile, 8 for its halo
+static int um_xmap(const St2ConvParams& p, int rows, CUtensorMap* map) {
+  int rc = um_encode_fn();
+  if (rc) return rc;
+  const cuuint64_t gdim[3] = {(cuuint64_t)p.cin, (cuuint64_t)p.Lin, (cuuint64_t)p.B};
+  const cuuint64_t gstr[2] = {(cuuint64_t)p.ldx * 2, (cuuint64_t)(p.B > 1 ? p.x_bstride : (int64_t)p.ldx * p.Lin) * 2};
+  const cuuint32_t box[3] = {64u, (cuuint32_t)rows, 1u};
+  const cuuint32_t estr[3] = {1u, 1u, 1u};
+  const CUresult r = g_encode(map, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 3, const_cast<void*>(p.x), gdim, gstr, box, estr,
+                              CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
+                              CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) {
+    set_error("conv_umma: cuTensorMapEncodeTiled (input) failed with code " + std::to_string((int)r));
+    return ST2_ECUDA;
+  }
+  return ST2_OK;
+}
+
 static int g_num_sms[64] = {};
 
 // optional per-launch event timing (st2_prof_enable / st2_prof_read)
@@ -1182,6 +1231,16 @@ int launch_conv_umma(const St2ConvParams& p, cudaStream_t st) {
       lay.res_tma = 1;
     }
   }
+  static const bool x_tma_ok = [] { const char* e = getenv("ST2_UMMA_X_TMA"); return !(e && e[0] == '0'); }();
+  CUtensorMap xmap = ymap, xmap8 = ymap;
+  lay.x_tma = 0;
+  if (x_tma_ok && (((uintptr_t)p.x) & 15) == 0 && (p.ldx % 8) == 0 && (p.x_bstride % 8) == 0) {
+    rc = um_xmap(p, UM_TM, &xmap);
+    if (rc) return rc;
+    rc = um_xmap(p, 8, &xmap8);
+    if (rc) return rc;
+    lay.x_tma = 1;
+  }
   const int n_ttiles = ceil_div(p.Lout, UM_TM), n_ntiles = p.n_cols / lay.n_tile;
   ST2_REQUIRE(!p.stats || p.n_tiles >= n_ttiles, "conv_umma: n_tiles");
   const int64_t total = (int64_t)p.B * n_ttiles * n_ntiles;
@@ -1210,7 +1269,7 @@ int launch_conv_umma(const St2ConvParams& p, cudaStream_t st) {
     g_prof.flops += p.algo_flops;
     ST2_CUDA_OK(cudaEventRecord(e0, st));
   }
-  ST2_CUDA_OK(launch_pdl(conv_umma_kernel, dim3(grid), dim3(UM_THREADS), (size_t)lay.total, st, p, lay, ymap, rmap, (int)total,
+  ST2_CUDA_OK(launch_pdl(conv_umma_kernel, dim3(grid), dim3(UM_THREADS), (size_t)lay.total, st, p, lay, ymap, rmap, xmap, xmap8, (int)total,
                          n_ttiles, n_ntiles));
   ST2_LAUNCH_OK("conv_umma");
   if (e1) ST2_CUDA_OK(cudaEventRecord(e1, st));
