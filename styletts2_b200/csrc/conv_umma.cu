@@ -67,6 +67,7 @@ struct UmLayout {
   int n_res, n_acc;   // extra 64-channel chunks per tile: residual rows, y_old rows
   int res_tma, acc_tma;  // those rows come by TMA tensor loads (one thread) instead of 256 threads' cp.async
   int x_tma;          // the raw activation tile too: one 256-row box + ceil(halo / 8) boxes of 8 rows
+  uint32_t nt_m, nt_l, tt_m, tt_l;  // multiply-shift division by n_ntiles / n_ttiles (um_tile)
   const uint8_t* ident_res;  // n_tile/64 identity weight blobs (x 1)
   const uint8_t* ident_acc;  // n_tile/64 identity weight blobs (x 1/out_scale)
   uint32_t off_a, off_w, off_misc, total;  // the staging tile sits at offset 0 (1024-byte aligned)
@@ -327,12 +328,21 @@ __device__ __forceinline__ float bf16hi(uint32_t u) { return __uint_as_float(u &
 struct UmTile {
   int b, t0, nt;
 };
-__device__ __forceinline__ UmTile um_tile(int tile, int n_ttiles, int n_ntiles) {
+// n / d for n < 2^31 with the host-computed (m, l) of um_fastdiv: no integer-division sequence in the
+// per-tile bookkeeping of 448 threads
+__device__ __forceinline__ uint32_t um_div(uint32_t n, uint32_t m, uint32_t l) {
+  if (l == 0) return n;
+  const uint32_t t = __umulhi(n, m);
+  return (t + ((n - t) >> 1)) >> (l - 1);
+}
+#define um_tile(tile, n_ttiles, n_ntiles) um_tile_(tile, n_ttiles, n_ntiles, lay)
+__device__ __forceinline__ UmTile um_tile_(int tile, int n_ttiles, int n_ntiles, const UmLayout& lay) {
   UmTile t;
-  t.nt = tile % n_ntiles;
-  const int bt = tile / n_ntiles;
-  t.t0 = (bt % n_ttiles) * UM_TM;
-  t.b = bt / n_ttiles;
+  const uint32_t bt = um_div((uint32_t)tile, lay.nt_m, lay.nt_l);
+  t.nt = tile - (int)bt * n_ntiles;
+  const uint32_t b = um_div(bt, lay.tt_m, lay.tt_l);
+  t.t0 = (int)(bt - b * (uint32_t)n_ttiles) * UM_TM;
+  t.b = (int)b;
   return t;
 }
 
@@ -343,14 +353,16 @@ struct UmCur {
   uint32_t ph;
   int b, t0, nt;
 };
-__device__ __forceinline__ void um_cur_tile(UmCur& q, int total_tiles, int n_ttiles, int n_ntiles) {
+#define um_cur_tile(q, total_tiles, n_ttiles, n_ntiles) um_cur_tile_(q, total_tiles, n_ttiles, n_ntiles, lay)
+#define um_advance(q, nchunks, na, total_tiles, n_ttiles, n_ntiles) um_advance_(q, nchunks, na, total_tiles, n_ttiles, n_ntiles, lay)
+__device__ __forceinline__ void um_cur_tile_(UmCur& q, int total_tiles, int n_ttiles, int n_ntiles, const UmLayout& lay) {
   if (q.tile < total_tiles) {
     const UmTile t = um_tile(q.tile, n_ttiles, n_ntiles);
     q.b = t.b; q.t0 = t.t0; q.nt = t.nt;
   }
 }
-__device__ __forceinline__ void um_advance(UmCur& q, int nchunks, int na, int total_tiles, int n_ttiles,
-                                           int n_ntiles) {
+__device__ __forceinline__ void um_advance_(UmCur& q, int nchunks, int na, int total_tiles, int n_ttiles,
+                                            int n_ntiles, const UmLayout& lay) {
   if (++q.c == nchunks) {
     q.c = 0;
     q.tile += gridDim.x;
@@ -1175,6 +1187,12 @@ static int um_xmap(const St2ConvParams& p, int rows, CUtensorMap* map) {
   return ST2_OK;
 }
 
+static void um_fastdiv(uint32_t d, uint32_t& m, uint32_t& l) {
+  l = 0;
+  while ((1u << l) < d) ++l;
+  m = (uint32_t)((((uint64_t)1 << 32) * (((uint64_t)1 << l) - d)) / d + 1);
+}
+
 static int g_num_sms[64] = {};
 
 // optional per-launch event timing (st2_prof_enable / st2_prof_read)
@@ -1243,6 +1261,8 @@ int launch_conv_umma(const St2ConvParams& p, cudaStream_t st) {
   }
   const int n_ttiles = ceil_div(p.Lout, UM_TM), n_ntiles = p.n_cols / lay.n_tile;
   ST2_REQUIRE(!p.stats || p.n_tiles >= n_ttiles, "conv_umma: n_tiles");
+  um_fastdiv((uint32_t)n_ntiles, lay.nt_m, lay.nt_l);
+  um_fastdiv((uint32_t)n_ttiles, lay.tt_m, lay.tt_l);
   const int64_t total = (int64_t)p.B * n_ttiles * n_ntiles;
   ST2_REQUIRE(total < (1ll << 31), "conv_umma: too many tiles");
   if (dev >= 64 || g_num_sms[dev] == 0) {
