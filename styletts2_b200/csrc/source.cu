@@ -171,7 +171,11 @@ har_source_kernel(const float* __restrict__ f0, const float* __restrict__ phase,
   for (int h = 0; h < NH; ++h) {
     const float p0 = pb[(int64_t)h * T + i0], p1 = pb[(int64_t)h * T + i1];
     const float ph = fmaf(l0, p0, __fmul_rn(l1, p1));
-    const float sv = __fmul_rn(sinf(ph), 0.1f);  // sine_amp
+    // sin of an fp32 phase that reaches 1e5 rad: reduce mod 2*pi in fp64 (exact to 1e-11), then MUFU.SIN on
+    // [-pi, pi] (abs error < 4e-7); libdevice sinf takes its slow Payne-Hanek path above 1e5 rad
+    const double rev = (double)ph * 0.15915494309189535;
+    const float red = (float)((rev - rint(rev)) * 6.283185307179586);
+    const float sv = __fmul_rn(__sinf(red), 0.1f);  // sine_amp
     const float sw = __fadd_rn(__fmul_rn(sv, uv), __fmul_rn(namp, z[h]));
     acc = fmaf(lin_w[h], sw, acc);
   }
