@@ -87,7 +87,7 @@ class _DecoderBase(nn.Module):
         self.seed = 0
         # a batch whose workspace would exceed this is decoded in micro-batches (utterances are
         # independent, SURVEY 8d: config C5 is 512 x 2400 frames); 0 = never split
-        self.workspace_limit_bytes = 48 << 30
+        self.workspace_limit_bytes = 32 << 30
         # replay the forward as a CUDA graph (one per device / batch shape / precision, static buffers;
         # inputs are copied in, the waveform is copied out): removes ~150 launch gaps per forward
         self.cuda_graphs = False
@@ -256,14 +256,18 @@ class _DecoderBase(nn.Module):
                 wav = torch.empty(B, 1, Lw, dtype=torch.float32, device=dev)
                 seed0, launches = self.seed, 0
                 sl = lambda t, a, b: None if t is None else t[a:b]
-                for lo in range(0, B, mb):
-                    hi = min(B, lo + mb)
-                    self.seed = seed0
-                    wav[lo:hi] = self._forward_native(
-                        asr_[lo:hi], f0_[lo:hi], n_[lo:hi], s_[lo:hi], noise=sl(noise_, lo, hi),
-                        har_source=sl(hs_, lo, hi), har=sl(har_, lo, hi), precision=prec,
-                        item_offset=item_offset + lo, alignment=sl(alignment, lo, hi))
-                    launches += self.last_launches
+                graphs, self.cuda_graphs = self.cuda_graphs, False  # a graph would pin one workspace per shape
+                try:
+                    for lo in range(0, B, mb):
+                        hi = min(B, lo + mb)
+                        self.seed = seed0
+                        wav[lo:hi] = self._forward_native(
+                            asr_[lo:hi], f0_[lo:hi], n_[lo:hi], s_[lo:hi], noise=sl(noise_, lo, hi),
+                            har_source=sl(hs_, lo, hi), har=sl(har_, lo, hi), precision=prec,
+                            item_offset=item_offset + lo, alignment=sl(alignment, lo, hi))
+                        launches += self.last_launches
+                finally:
+                    self.cuda_graphs = graphs
                 self.last_launches = launches
                 return wav
             if (self.cuda_graphs and noise_ is None and hs_ is None and har_ is None and alignment is None
