@@ -40,6 +40,15 @@ extern "C" {
                                St2Config: dim_in = d_hid (512), style_dim; the other fields are ignored.  Uses
                                create / load / num_keys / key / destroy of the decoder API and st2_f0n_* below. */
 
+#define ST2_KIND_SAMPLER 3  /* style sampler (next row N2): DiffusionSampler + ADPM2Sampler + KarrasSchedule over the
+                               KDiffusion denoiser StyleTransformer1d / Transformer1d (Modules/diffusion/sampler.py:480-585,
+                               Modules/diffusion/modules.py:40-426, built by models.py:1057-1089).  St2Config fields:
+                               dim_in = channels (2 * style_dim = 256), style_dim = context_features (256: StyleTransformer1d,
+                               multispeaker; 0: Transformer1d with plain LayerNorm), dim_out = context_embedding_features
+                               (PL-BERT hidden size, 768), n_resblock_kernels = num_layers, resblock_kernel_sizes[0..3] =
+                               num_heads, head_features, multiplier, embedding_max_length; the rest is ignored.  Uses create /
+                               load / num_keys / key / destroy of the decoder API and st2_sampler_* below. */
+
 /* arithmetic of the dense contractions */
 #define ST2_PREC_FP32 0 /* fp32 FFMA kernels, fp32 activations: the parity path        */
 #define ST2_PREC_BF16 1 /* tcgen05 bf16 x bf16 -> fp32 (TMEM), bf16 activations in HBM */
@@ -134,6 +143,37 @@ int st2_decoder_forward(St2Decoder* h, const float* asr, const float* f0, const 
 int64_t st2_f0n_workspace_bytes(const St2Decoder* h, int B, int T, int precision);
 int st2_f0n_forward(St2Decoder* h, const float* x, const float* s, float* f0_out, float* n_out,
                     void* workspace, int64_t workspace_bytes, int B, int T, int precision, void* stream);
+
+/* Style sampler (next row N2) on a handle created with kind ST2_KIND_SAMPLER.
+ *   s_pred = sampler(noise, embedding=bert_dur, embedding_scale=..., features=ref_s, num_steps=...)
+ *   (Demo/Inference_LibriTTS.ipynb cells 14, 16; DiffusionSampler.forward sampler.py:573-585). */
+typedef struct St2SamplerOpts {
+  int precision;          /* ST2_PREC_* of the token-level contractions (to_q, to_kv, to_out, feed_forward) */
+  int num_steps;          /* diffusion_steps: num_steps - 1 ADPM2 steps = 2 * (num_steps - 1) denoiser calls */
+  float sigma_min, sigma_max, rho; /* KarrasSchedule(sigma_min=1e-4, sigma_max=3.0, rho=9.0) */
+  float sampler_rho;      /* ADPM2Sampler(rho=1.0) */
+  float sigma_data;       /* KDiffusion.sigma_data (0.2) */
+  float embedding_scale;  /* classifier-free guidance scale; != 1 runs the denoiser a second time on the
+                             fixed embedding (modules.py:178-184), batched with the first run */
+  int clamp;              /* DiffusionSampler(clamp=...): clamp the result to [-1, 1] */
+  const float* step_noise;/* optional DEVICE [num_steps - 1, B, channels]: the randn_like draw of every
+                             ADPM2 step (sampler.py:510); NULL -> in-kernel Philox(seed, item, channel, step) */
+  uint64_t seed;
+  int64_t item_offset;    /* global index of row 0 (shards draw the noise the full batch would) */
+} St2SamplerOpts;
+
+/* guided != 0 when embedding_scale != 1 (twice the token rows). */
+int64_t st2_sampler_workspace_bytes(const St2Decoder* h, int B, int n_tokens, int precision, int guided);
+/* noise [B, channels], embedding [B, n_tokens, emb_features], features [B, context_features] (NULL for the
+ * Transformer1d variant) -> out [B, channels]; all device fp32, contiguous. */
+int st2_sampler_sample(St2Decoder* h, const float* noise, const float* embedding, const float* features, float* out,
+                       void* workspace, int64_t workspace_bytes, int B, int n_tokens, const St2SamplerOpts* opts,
+                       void* stream);
+/* One denoiser evaluation, KDiffusion.denoise_fn(x_noisy, sigma=sigma, ...) (sampler.py:193-208):
+ * x_noisy [B, channels] -> out [B, channels].  Uses precision, sigma_data and embedding_scale of opts. */
+int st2_sampler_denoise(St2Decoder* h, const float* x_noisy, float sigma, const float* embedding, const float* features,
+                        float* out, void* workspace, int64_t workspace_bytes, int B, int n_tokens,
+                        const St2SamplerOpts* opts, void* stream);
 
 /* Duration-based alignment (next row N3; Demo/Inference_LJSpeech.ipynb cell 17, Inference_LibriTTS.ipynb cell 16).
  *   dur [B, Ltext] int32 durations (frames per token, device) -> idx [B, frames] int32: the token shown by each

@@ -9,9 +9,10 @@ importing this package without the built library raises.
 from . import _cabi  # noqa: F401  (raises ImportError when libst2dec.so is missing)
 from .decoder import IstftnetDecoder, HifiganDecoder  # noqa: F401
 from .predictor import F0NPredictor  # noqa: F401  (ProsodyPredictor.F0Ntrain)
+from .sampler import StyleSampler  # noqa: F401  (ADPM2 style sampler over StyleTransformer1d)
 from . import ops  # noqa: F401  (registers torch.ops.styletts2_b200.decoder_forward)
 
-__all__ = ["IstftnetDecoder", "HifiganDecoder", "F0NPredictor", "build_decoder"]
+__all__ = ["IstftnetDecoder", "HifiganDecoder", "F0NPredictor", "StyleSampler", "build_decoder"]
 
 
 def build_decoder(decoder_args, hidden_dim=512, style_dim=128, n_mels=80):

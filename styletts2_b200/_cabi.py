@@ -12,7 +12,7 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "_lib", "libst2dec.so")
 
 ST2_OK = 0
-KIND_ISTFTNET, KIND_HIFIGAN, KIND_F0N = 0, 1, 2
+KIND_ISTFTNET, KIND_HIFIGAN, KIND_F0N, KIND_SAMPLER = 0, 1, 2, 3
 PREC_FP32, PREC_BF16 = 0, 1
 DT_F32, DT_BF16 = 0, 1
 ACT_NONE, ACT_LRELU, ACT_SNAKE = 0, 1, 2
@@ -41,6 +41,15 @@ class St2ForwardOpts(C.Structure):
         ("tap_decode", C.c_void_p), ("tap_stage", C.c_void_p * MAX_UPS),
         ("item_offset", C.c_int64), ("seed_dev", C.c_void_p),
         ("align_idx", C.c_void_p), ("align_len", C.c_int),
+    ]
+
+
+class St2SamplerOpts(C.Structure):
+    _fields_ = [
+        ("precision", C.c_int), ("num_steps", C.c_int),
+        ("sigma_min", C.c_float), ("sigma_max", C.c_float), ("rho", C.c_float),
+        ("sampler_rho", C.c_float), ("sigma_data", C.c_float), ("embedding_scale", C.c_float),
+        ("clamp", C.c_int), ("step_noise", C.c_void_p), ("seed", C.c_uint64), ("item_offset", C.c_int64),
     ]
 
 
@@ -76,6 +85,11 @@ SYMBOLS = {
     "st2_f0n_workspace_bytes": (C.c_int64, [C.c_void_p, C.c_int, C.c_int, C.c_int]),
     "st2_f0n_forward": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p,
                                   C.c_int64, C.c_int, C.c_int, C.c_int, C.c_void_p]),
+    "st2_sampler_workspace_bytes": (C.c_int64, [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int]),
+    "st2_sampler_sample": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64,
+                                     C.c_int, C.c_int, C.POINTER(St2SamplerOpts), C.c_void_p]),
+    "st2_sampler_denoise": (C.c_int, [C.c_void_p, C.c_void_p, C.c_float, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p,
+                                      C.c_int64, C.c_int, C.c_int, C.POINTER(St2SamplerOpts), C.c_void_p]),
     "st2_wave_to_pcm16": (C.c_int, [C.c_void_p, C.c_int, C.c_int64, C.c_int64, C.c_void_p, C.c_void_p]),
     "st2_alignment_indices": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p]),
     "st2_expand_alignment": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_void_p]),

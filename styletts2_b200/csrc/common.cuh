@@ -114,6 +114,34 @@ __device__ __forceinline__ float warp_sum(float v) {
   return v;
 }
 
+// ---- Philox4x32-10 + Box-Muller normal (source.cu: SineGen noise; sampler.cu: ADPM2 step noise) ----
+#ifdef __CUDACC__
+__device__ __forceinline__ void philox4x32(uint32_t c0, uint32_t c1, uint32_t c2, uint32_t c3,
+                                           uint32_t k0, uint32_t k1, uint32_t out[4]) {
+#pragma unroll
+  for (int r = 0; r < 10; ++r) {
+    const uint32_t hi0 = __umulhi(0xD2511F53u, c0), lo0 = 0xD2511F53u * c0;
+    const uint32_t hi1 = __umulhi(0xCD9E8D57u, c2), lo1 = 0xCD9E8D57u * c2;
+    c0 = hi1 ^ c1 ^ k0;
+    c1 = lo1;
+    c2 = hi0 ^ c3 ^ k1;
+    c3 = lo0;
+    k0 += 0x9E3779B9u;
+    k1 += 0xBB67AE85u;
+  }
+  out[0] = c0; out[1] = c1; out[2] = c2; out[3] = c3;
+}
+__device__ __forceinline__ void box_muller(uint32_t a, uint32_t b, float& z0, float& z1) {
+  const float u1 = ((float)a + 1.f) * 2.3283064365386963e-10f;  // (0,1]
+  const float u2 = (float)b * 2.3283064365386963e-10f;
+  const float r = sqrtf(-2.f * __logf(u1));
+  float s, c;
+  __sincosf(2.f * 3.14159265358979323846f * u2, &s, &c);
+  z0 = r * c;
+  z1 = r * s;
+}
+#endif
+
 // ---- kernel launchers implemented across the .cu files --------------------------------
 int launch_conv_simt(const St2ConvParams& p, cudaStream_t st);
 int launch_conv_umma(const St2ConvParams& p, cudaStream_t st);
@@ -173,5 +201,28 @@ int launch_ncl_to_hilo(const float* ncl, int C, int L, int rows_pad, __nv_bfloat
 int launch_hilo_to_ncl(const __nv_bfloat16* har, int rows_pad, int C, int L, float* ncl, int B, cudaStream_t st);
 int launch_istft(const float* x_cl, int ld, int B, int frames, float* wav, cudaStream_t st);
 int launch_tanh_inplace(float* x, int64_t n, cudaStream_t st);
+
+// sampler.cu: style sampler (StyleTransformer1d / Transformer1d denoiser + ADPM2 steps)
+int launch_small_linear(const float* x, int ldx, const float* xb, const float* W, const float* bias, float* y, int ldy,
+                        int R, int I, int O, int gelu, cudaStream_t st);
+int launch_time_fourier(float t, const float* w, int half, float* out, cudaStream_t st);
+int launch_build_rows(const float* x, float c_in, const float* emb, const float* fixed, float* X, int B, int Bx, int n,
+                      int C, int E, cudaStream_t st);
+template <typename AT>
+int launch_adaln2(float* X, const AT* delta, const float* mapping, int64_t map_bstride, const float* gb, int64_t gb_bstride,
+                  AT* nq, AT* nk, int64_t rows, int n, int B, int F, cudaStream_t st);
+template <typename AT>
+int launch_add_cast(float* X, const AT* delta, AT* Xc, int64_t n, cudaStream_t st);
+template <typename AT>
+int launch_gelu(AT* x, int64_t n, cudaStream_t st);
+template <typename AT>
+int launch_attention(const AT* Q, int ldq, const AT* KV, int ldkv, AT* O, int ldo, int Bx, int n, int heads, int head_dim,
+                     cudaStream_t st);
+template <typename AT>
+int launch_token_mean(const float* X, const AT* delta, float* out, int Bx, int n, int F, cudaStream_t st);
+int launch_sampler_step(const float* pred, const float* x_eval, const float* x_base, const float* noise, uint64_t seed,
+                        uint32_t step, int64_t item0, float* x_new, float* den_out, int B, int C, int cfg, float cfg_scale,
+                        float c_skip, float c_out, float sigma_eval, float dt, float sigma_up, int clamp, cudaStream_t st);
+int launch_scale(const float* x, float a, float* y, int n, cudaStream_t st);
 
 }  // namespace st2

@@ -101,6 +101,15 @@ struct St2Decoder {
   st2::ConvW f0n_proj[2];
   st2::ConvW conv_post_p;     // row-pair form of a 32-channel conv_post (hifigan)
   int64_t alpha_post_p = -1;  // alphas[n_ups] repeated twice
+  // ST2_KIND_SAMPLER: StyleTransformer1d / Transformer1d denoiser (Modules/diffusion/modules.py:40-426)
+  struct SamplerBlk {
+    st2::ConvW to_q, to_kv, to_out, ff1, ff2;
+  };
+  std::vector<SamplerBlk> sblk;
+  int64_t s_fcW = -1, s_fcB = -1;  // AdaLayerNorm fc of every block, rows (l, norm|norm_context, gamma|beta, F)
+  int64_t s_ln = -1;               // Transformer1d: [layers][4F] (w - 1, b, w_ctx - 1, b_ctx)
+  int64_t s_four = -1, s_timeW = -1, s_timeB = -1, s_featW = -1, s_featB = -1;
+  int64_t s_mapW[2] = {-1, -1}, s_mapB[2] = {-1, -1}, s_outW = -1, s_outB = -1, s_fixed = -1;
   int64_t last_launches = 0;
 };
 
@@ -150,6 +159,45 @@ static int prod_from(const int* r, int from, int n) {
 static void build_keys(St2Decoder* h) {
   const St2Config& c = h->cfg;
   const int style = c.style_dim;
+  if (c.kind == ST2_KIND_SAMPLER) {  // state_dict of StyleTransformer1d / Transformer1d (modules.py:40-119, 280-355)
+    const int C = c.dim_in, S = c.style_dim, E = c.dim_out, F = C + E;
+    const int mid = c.resblock_kernel_sizes[0] * c.resblock_kernel_sizes[1], mult = c.resblock_kernel_sizes[2];
+    for (int i = 0; i < c.n_resblock_kernels; ++i) {
+      const std::string p = "blocks." + std::to_string(i);
+      for (const char* nm : {".attention.norm", ".attention.norm_context"}) {
+        if (S) {
+          add_key(h, p + nm + ".fc.weight", {2 * F, S});
+          add_key(h, p + nm + ".fc.bias", {2 * F});
+        } else {
+          add_key(h, p + nm + ".weight", {F});
+          add_key(h, p + nm + ".bias", {F});
+        }
+      }
+      add_key(h, p + ".attention.to_q.weight", {mid, F});
+      add_key(h, p + ".attention.to_kv.weight", {2 * mid, F});
+      add_key(h, p + ".attention.attention.to_out.weight", {F, mid});
+      add_key(h, p + ".attention.attention.to_out.bias", {F});
+      add_key(h, p + ".feed_forward.0.weight", {F * mult, F});
+      add_key(h, p + ".feed_forward.0.bias", {F * mult});
+      add_key(h, p + ".feed_forward.2.weight", {F, F * mult});
+      add_key(h, p + ".feed_forward.2.bias", {F});
+    }
+    add_key(h, "to_out.1.weight", {C, F, 1});
+    add_key(h, "to_out.1.bias", {C});
+    for (int j : {0, 2}) {
+      add_key(h, "to_mapping." + std::to_string(j) + ".weight", {F, F});
+      add_key(h, "to_mapping." + std::to_string(j) + ".bias", {F});
+    }
+    add_key(h, "to_time.0.0.weights", {C / 2});
+    add_key(h, "to_time.0.1.weight", {F, C + 1});
+    add_key(h, "to_time.0.1.bias", {F});
+    if (S) {
+      add_key(h, "to_features.0.weight", {F, S});
+      add_key(h, "to_features.0.bias", {F});
+    }
+    add_key(h, "fixed_embedding.embedding.weight", {c.resblock_kernel_sizes[3], E});
+    return;
+  }
   if (c.kind == ST2_KIND_F0N) {  // models.py:562-590
     const int d = c.dim_in, hid = d / 2;
     for (int r = 0; r < 2; ++r) {
@@ -421,6 +469,23 @@ struct Loader {
                           reinterpret_cast<uint16_t*>(blob.data.data() + c.w16));
     return true;
   }
+  // nn.Linear weight [out][in] as a 1x1 conv (GEMM columns = out)
+  bool linear(ConvW& c, const std::string& p, bool has_bias) {
+    const St2Tensor* t = get(p + ".weight");
+    const St2Tensor* bt = has_bias ? get(p + ".bias") : nullptr;
+    if (!t || (has_bias && !bt)) return false;
+    const int64_t out = t->shape[0], in = t->shape[1];
+    c.k = 1; c.dil = 1; c.pad = 0; c.stride = 1;
+    c.cin = (int)in; c.n = (int)out; c.cstat = (int)out;
+    c.flops_per_row = 2.0 * (double)in * (double)out;
+    std::vector<float> kcn((size_t)in * out);
+    for (int64_t o = 0; o < out; ++o)
+      for (int64_t i = 0; i < in; ++i) kcn[(size_t)i * out + o] = t->data[(size_t)o * in + i];
+    std::vector<float> b;
+    if (has_bias) b.assign(bt->data, bt->data + out);
+    finish_conv(c, kcn, has_bias ? &b : nullptr, true);
+    return true;
+  }
   bool norm(NormW& n, const std::string& p, int C) {
     const St2Tensor* w = get(p + ".fc.weight");
     const St2Tensor* b = get(p + ".fc.bias");
@@ -517,6 +582,50 @@ static int do_load(St2Decoder* h, const St2Tensor* tensors, int n) {
   ST2_REQUIRE(L.by_name.size() == h->key_names.size(), "unexpected keys in state dict");
 
   bool ok = true;
+  if (c.kind == ST2_KIND_SAMPLER) {
+    const int C = c.dim_in, S = c.style_dim, E = c.dim_out, F = C + E, layers = c.n_resblock_kernels;
+    std::vector<float> fcW, fcB, ln;
+    h->sblk.assign(layers, St2Decoder::SamplerBlk());
+    for (int i = 0; i < layers && ok; ++i) {
+      const std::string p = "blocks." + std::to_string(i);
+      for (const char* nm : {".attention.norm", ".attention.norm_context"}) {
+        if (S) {
+          const St2Tensor* w = L.get(p + nm + ".fc.weight");
+          const St2Tensor* b = L.get(p + nm + ".fc.bias");
+          ok = ok && w && b;
+          if (!ok) break;
+          fcW.insert(fcW.end(), w->data, w->data + (int64_t)2 * F * S);
+          fcB.insert(fcB.end(), b->data, b->data + 2 * F);
+        } else {
+          const St2Tensor* w = L.get(p + nm + ".weight");
+          const St2Tensor* b = L.get(p + nm + ".bias");
+          ok = ok && w && b;
+          if (!ok) break;
+          for (int j = 0; j < F; ++j) ln.push_back(w->data[j] - 1.f);  // adaln2 applies (1 + g) * xhat + b
+          ln.insert(ln.end(), b->data, b->data + F);
+        }
+      }
+      St2Decoder::SamplerBlk& k = h->sblk[i];
+      ok = ok && L.linear(k.to_q, p + ".attention.to_q", false) && L.linear(k.to_kv, p + ".attention.to_kv", false) &&
+           L.linear(k.to_out, p + ".attention.attention.to_out", true) && L.linear(k.ff1, p + ".feed_forward.0", true) &&
+           L.linear(k.ff2, p + ".feed_forward.2", true);
+    }
+    if (ok && S) {
+      h->s_fcW = L.blob.add(fcW.data(), (int64_t)fcW.size() * 4);
+      h->s_fcB = L.blob.add(fcB.data(), (int64_t)fcB.size() * 4);
+      ok = L.vec(h->s_featW, "to_features.0.weight", (int64_t)F * S) && L.vec(h->s_featB, "to_features.0.bias", F);
+    } else if (ok) {
+      h->s_ln = L.blob.add(ln.data(), (int64_t)ln.size() * 4);
+    }
+    ok = ok && L.vec(h->s_four, "to_time.0.0.weights", C / 2) && L.vec(h->s_timeW, "to_time.0.1.weight", (int64_t)F * (C + 1)) &&
+         L.vec(h->s_timeB, "to_time.0.1.bias", F) && L.vec(h->s_mapW[0], "to_mapping.0.weight", (int64_t)F * F) &&
+         L.vec(h->s_mapB[0], "to_mapping.0.bias", F) && L.vec(h->s_mapW[1], "to_mapping.2.weight", (int64_t)F * F) &&
+         L.vec(h->s_mapB[1], "to_mapping.2.bias", F) && L.vec(h->s_outW, "to_out.1.weight", (int64_t)C * F) &&
+         L.vec(h->s_outB, "to_out.1.bias", C) &&
+         L.vec(h->s_fixed, "fixed_embedding.embedding.weight", (int64_t)c.resblock_kernel_sizes[3] * E);
+    ST2_REQUIRE(ok, L.err);
+    return finish_load(h, L);
+  }
   if (c.kind == ST2_KIND_F0N) {
     const int d = c.dim_in, hid = d / 2, in = d + c.style_dim, g4 = 4 * hid;
     // both directions' input projections as one GEMM: column dir * 4H + gate * H + unit
@@ -1195,6 +1304,16 @@ int Fwd<AT>::run(const float* asr, const float* f0, const float* nn, const float
 using namespace st2;
 
 static int validate_cfg(const St2Config& c) {
+  if (c.kind == ST2_KIND_SAMPLER) {
+    ST2_REQUIRE(c.dim_in >= 2 && c.dim_in % 2 == 0 && c.dim_out >= 1, "channels / context_embedding_features");
+    ST2_REQUIRE((c.dim_in + c.dim_out) % 64 == 0, "channels + context_embedding_features must be a multiple of 64");
+    ST2_REQUIRE(c.style_dim >= 0, "context_features");
+    ST2_REQUIRE(c.n_resblock_kernels >= 1 && c.n_resblock_kernels <= 64, "num_layers");
+    ST2_REQUIRE(c.resblock_kernel_sizes[0] >= 1 && c.resblock_kernel_sizes[1] == 64,
+                "num_heads >= 1, head_features must be 64 (attention kernel)");
+    ST2_REQUIRE(c.resblock_kernel_sizes[2] >= 1 && c.resblock_kernel_sizes[3] >= 1, "multiplier / embedding_max_length");
+    return ST2_OK;
+  }
   if (c.kind == ST2_KIND_F0N) {
     ST2_REQUIRE(c.dim_in == 512, "d_hid must be 512 (the LSTM kernel keeps 256 hidden units per direction)");
     ST2_REQUIRE(c.style_dim > 0 && c.style_dim <= 192 && (c.dim_in + c.style_dim) % 64 == 0, "style_dim");
@@ -1421,6 +1540,228 @@ extern "C" int st2_f0n_forward(St2Decoder* h, const float* x, const float* s, fl
            : f0n_t<float>(h, x, s, f0_out, n_out, workspace, workspace_bytes, B, T, st, false, nullptr);
   h->last_launches = launch_counter() - before;
   return rc;
+}
+
+// ---------------------------------------------------------------------------------------------
+// Style sampler.  DiffusionSampler.forward (Modules/diffusion/sampler.py:573-585) =
+// KarrasSchedule (:318-336) + ADPM2Sampler.forward / .step (:496-519) around KDiffusion.denoise_fn
+// (:193-208) around StyleTransformer1d.forward / .run (modules.py:146-186; Transformer1d :382-426).
+// Token rows of all items (and of the guidance run on the fixed embedding) are flattened into one
+// [Bx * n][F] matrix, so every nn.Linear over tokens is one 1x1 conv (tcgen05 GEMM on the bf16 path).
+// ---------------------------------------------------------------------------------------------
+struct SamplerSigmas {
+  std::vector<float> sig;
+};
+// KarrasSchedule.forward in fp32 like the reference's tensor arithmetic
+static void karras_sigmas(int num_steps, float smin, float smax, float rho, std::vector<float>& out) {
+  const double rho_inv = 1.0 / (double)rho;
+  const float a = (float)pow((double)smax, rho_inv), d = (float)(pow((double)smin, rho_inv) - pow((double)smax, rho_inv));
+  out.resize(num_steps + 1);
+  for (int i = 0; i < num_steps; ++i) {
+    const float t = (float)i / (float)(num_steps - 1);
+    out[i] = powf(a + t * d, rho);
+  }
+  out[num_steps] = 0.f;
+}
+
+template <typename AT>
+static int sampler_t(St2Decoder* h, const float* x_in, const float* emb, const float* feat, float* out, void* ws,
+                     int64_t ws_bytes, int B, int n, const St2SamplerOpts& o, bool single, float single_sigma,
+                     cudaStream_t st, bool dry, int64_t* peak) {
+  Fwd<AT> f;
+  f.h = h; f.st = st; f.B = 1; f.T = n; f.dry = dry;
+  f.ar.base = reinterpret_cast<uint8_t*>(ws); f.ar.cap = ws_bytes; f.ar.dry = dry;
+  Arena& ar = f.ar;
+  const St2Config& c = h->cfg;
+  const int C = c.dim_in, S = c.style_dim, E = c.dim_out, F = C + E, layers = c.n_resblock_kernels;
+  const int H = c.resblock_kernel_sizes[0], D = c.resblock_kernel_sizes[1], mid = H * D, mult = c.resblock_kernel_sizes[2];
+  const bool guided = o.embedding_scale != 1.f;
+  const int Bx = guided ? 2 * B : B;
+  const int64_t rows = (int64_t)Bx * n;
+  auto Wf = [&](int64_t off) { return f.template W<float>(off); };
+
+  float* hall = S ? ar.alloc<float>((int64_t)B * layers * 4 * F) : nullptr;
+  float* feat_act = S ? ar.alloc<float>((int64_t)B * F) : nullptr;
+  float* four = ar.alloc<float>(C + 1);
+  float* t_act = ar.alloc<float>(F);
+  float* m1 = ar.alloc<float>((int64_t)B * F);
+  float* mapping = ar.alloc<float>((int64_t)B * F);
+  float* X = ar.alloc<float>(rows * F);
+  AT* nq = ar.alloc<AT>(rows * F);
+  AT* nk = ar.alloc<AT>(rows * F);
+  AT* q = ar.alloc<AT>(rows * mid);
+  AT* kv = ar.alloc<AT>(rows * 2 * mid);
+  AT* att = ar.alloc<AT>(rows * mid);
+  AT* delta = ar.alloc<AT>(rows * F);
+  AT* xc = ar.alloc<AT>(rows * F);
+  AT* hf = ar.alloc<AT>(rows * F * mult);
+  float* xm = ar.alloc<float>((int64_t)Bx * F);
+  float* pred = ar.alloc<float>((int64_t)Bx * C);
+  float* x = ar.alloc<float>((int64_t)B * C);
+  float* x_mid = ar.alloc<float>((int64_t)B * C);
+  if (peak) *peak = ar.peak;
+  if (dry) return ST2_OK;
+#define SRUN(x)          \
+  do {                   \
+    int _rc = (x);       \
+    if (_rc) return _rc; \
+  } while (0)
+
+  auto gemm = [&](const ConvW& w, const AT* src, int ldx, AT* dst, int ldy) -> int {
+    typename Fwd<AT>::ConvIO io;
+    io.x = src; io.x_dtype = DT<AT>::id; io.x_bstride = 0; io.ldx = ldx; io.Lin = (int)rows;
+    io.y = dst; io.y_dtype = DT<AT>::id; io.y_bstride = 0; io.ldy = ldy; io.Lout = (int)rows;
+    return f.conv(w, io);
+  };
+  // features are constant over the sampling run: AdaLayerNorm fc of all blocks and to_features once
+  if (S) {
+    SRUN(launch_small_linear(feat, S, nullptr, Wf(h->s_fcW), Wf(h->s_fcB), hall, layers * 4 * F, B, S, layers * 4 * F, 0, st));
+    SRUN(launch_small_linear(feat, S, nullptr, Wf(h->s_featW), Wf(h->s_featB), feat_act, F, B, S, F, 1, st));
+  }
+  const float sd = o.sigma_data;
+  float c_skip = 0.f, c_out = 0.f;
+  // net(c_in * xin, c_noise, ...) -> pred [Bx][C]; sets c_skip / c_out of this sigma (sampler.py:184-191)
+  auto eval = [&](const float* xin, float sigma) -> int {
+    const float s2 = sigma * sigma + sd * sd;
+    const float c_in = powf(s2, -0.5f), c_noise = logf(sigma) * 0.25f;
+    c_skip = (sd * sd) / s2;
+    c_out = sigma * sd * powf(s2, -0.5f);
+    // mapping = to_mapping(to_time(c_noise) + to_features(features))  (modules.py:121-144)
+    SRUN(launch_time_fourier(c_noise, Wf(h->s_four), C / 2, four, st));
+    SRUN(launch_small_linear(four, C + 1, nullptr, Wf(h->s_timeW), Wf(h->s_timeB), t_act, F, 1, C + 1, F, 1, st));
+    const int Rm = S ? B : 1;
+    if (S) SRUN(launch_small_linear(feat_act, F, t_act, Wf(h->s_mapW[0]), Wf(h->s_mapB[0]), m1, F, B, F, F, 1, st));
+    else SRUN(launch_small_linear(t_act, F, nullptr, Wf(h->s_mapW[0]), Wf(h->s_mapB[0]), m1, F, 1, F, F, 1, st));
+    SRUN(launch_small_linear(m1, F, nullptr, Wf(h->s_mapW[1]), Wf(h->s_mapB[1]), mapping, F, Rm, F, F, 1, st));
+    SRUN(launch_build_rows(xin, c_in, emb, Wf(h->s_fixed), X, B, Bx, n, C, E, st));
+    for (int l = 0; l < layers; ++l) {
+      const St2Decoder::SamplerBlk& k = h->sblk[l];
+      const float* gb = S ? hall + (int64_t)l * 4 * F : Wf(h->s_ln) + (int64_t)l * 4 * F;
+      SRUN(launch_adaln2<AT>(X, l ? delta : nullptr, mapping, S ? F : 0, gb, S ? (int64_t)layers * 4 * F : 0, nq, nk, rows,
+                             n, B, F, st));
+      SRUN(gemm(k.to_q, nq, F, q, mid));
+      SRUN(gemm(k.to_kv, nk, F, kv, 2 * mid));
+      SRUN(launch_attention<AT>(q, mid, kv, 2 * mid, att, mid, Bx, n, H, D, st));
+      SRUN(gemm(k.to_out, att, mid, delta, F));
+      SRUN(launch_add_cast<AT>(X, delta, xc, rows * F, st));
+      SRUN(gemm(k.ff1, xc, F, hf, F * mult));
+      SRUN(launch_gelu<AT>(hf, rows * F * mult, st));
+      SRUN(gemm(k.ff2, hf, F * mult, delta, F));
+    }
+    SRUN(launch_token_mean<AT>(X, delta, xm, Bx, n, F, st));
+    SRUN(launch_small_linear(xm, F, nullptr, Wf(h->s_outW), Wf(h->s_outB), pred, C, Bx, F, C, 0, st));
+    return ST2_OK;
+  };
+  if (single) {
+    SRUN(eval(x_in, single_sigma));
+    return launch_sampler_step(pred, x_in, nullptr, nullptr, 0, 0, 0, nullptr, out, B, C, guided, o.embedding_scale, c_skip,
+                               c_out, single_sigma, 0.f, 0.f, 0, st);
+  }
+  std::vector<float> sig;
+  karras_sigmas(o.num_steps, o.sigma_min, o.sigma_max, o.rho, sig);
+  SRUN(launch_scale(x_in, sig[0], x, B * C, st));  // x = sigmas[0] * noise (sampler.py:499)
+  const int nst = o.num_steps - 1;
+  for (int i = 0; i < nst; ++i) {
+    // ADPM2Sampler.get_sigmas (sampler.py:489-494): fp32 tensor arithmetic, math.sqrt in double
+    const float s0 = sig[i], s1 = sig[i + 1];
+    const double up = sqrt((double)(s1 * s1 * (s0 * s0 - s1 * s1) / (s0 * s0)));
+    const double down = sqrt((double)(float)((double)(s1 * s1) - up * up));
+    const float r = o.sampler_rho;
+    const float smid = r == 1.f ? (s0 + (float)down) / 2.f : powf((powf(s0, 1.f / r) + (float)pow(down, 1.0 / r)) / 2.f, r);
+    const bool last = i == nst - 1;
+    SRUN(eval(x, s0));
+    SRUN(launch_sampler_step(pred, x, x, nullptr, 0, 0, 0, x_mid, nullptr, B, C, guided, o.embedding_scale, c_skip, c_out, s0,
+                             smid - s0, 0.f, 0, st));
+    SRUN(eval(x_mid, smid));
+    SRUN(launch_sampler_step(pred, x_mid, x, o.step_noise ? o.step_noise + (int64_t)i * B * C : nullptr, o.seed, (uint32_t)i,
+                             o.item_offset, last ? out : x, nullptr, B, C, guided, o.embedding_scale, c_skip, c_out, smid,
+                             (float)down - s0, (float)up, last && o.clamp, st));
+  }
+#undef SRUN
+  return ST2_OK;
+}
+
+static int sampler_check(St2Decoder* h, int B, int n, int precision, const char* who) {
+  if (!h) {
+    set_error(std::string(who) + ": null handle");
+    return ST2_EINVAL;
+  }
+  ST2_REQUIRE(h->cfg.kind == ST2_KIND_SAMPLER, std::string(who) + ": handle was not created with ST2_KIND_SAMPLER");
+  if (!h->loaded) {
+    set_error(std::string(who) + ": weights not loaded");
+    return ST2_ESTATE;
+  }
+  ST2_REQUIRE(B >= 1 && B <= 32767, "batch");
+  ST2_REQUIRE(n >= 1 && n <= h->cfg.resblock_kernel_sizes[3],
+              "n_tokens must be in [1, embedding_max_length] (FixedEmbedding, modules.py:654-690)");
+  ST2_REQUIRE((int64_t)2 * B * n < (int64_t)1 << 30, "too many token rows");
+  ST2_REQUIRE(precision == ST2_PREC_FP32 || precision == ST2_PREC_BF16, "precision");
+  return ST2_OK;
+}
+static int sampler_plan(St2Decoder* h, int B, int n, int precision, bool guided, int64_t* bytes) {
+  St2SamplerOpts o;
+  memset(&o, 0, sizeof(o));
+  o.embedding_scale = guided ? 2.f : 1.f;
+  int64_t peak = 0;
+  int rc = precision == ST2_PREC_BF16
+               ? sampler_t<__nv_bfloat16>(h, nullptr, nullptr, nullptr, nullptr, nullptr, 0, B, n, o, true, 1.f, 0, true, &peak)
+               : sampler_t<float>(h, nullptr, nullptr, nullptr, nullptr, nullptr, 0, B, n, o, true, 1.f, 0, true, &peak);
+  *bytes = round_up(peak, 256) + 256;
+  return rc;
+}
+extern "C" int64_t st2_sampler_workspace_bytes(const St2Decoder* hc, int B, int n_tokens, int precision, int guided) {
+  St2Decoder* h = const_cast<St2Decoder*>(hc);
+  int rc = sampler_check(h, B, n_tokens, precision, "st2_sampler_workspace_bytes");
+  if (rc) return rc;
+  int64_t bytes = 0;
+  rc = sampler_plan(h, B, n_tokens, precision, guided != 0, &bytes);
+  return rc ? rc : bytes;
+}
+static int sampler_call(St2Decoder* h, const float* x_in, const float* emb, const float* feat, float* out, void* ws,
+                        int64_t ws_bytes, int B, int n, const St2SamplerOpts* opts, bool single, float sigma, void* stream,
+                        const char* who) {
+  if (!opts || !x_in || !emb || !out || !ws) {
+    set_error(std::string(who) + ": null argument");
+    return ST2_EINVAL;
+  }
+  int rc = sampler_check(h, B, n, opts->precision, who);
+  if (rc) return rc;
+  ST2_REQUIRE((h->cfg.style_dim > 0) == (feat != nullptr),
+              "features are required by StyleTransformer1d and not accepted by Transformer1d");
+  ST2_REQUIRE(opts->sigma_data > 0.f, "sigma_data");
+  if (single) ST2_REQUIRE(sigma > 0.f, "sigma");
+  else ST2_REQUIRE(opts->num_steps >= 2 && opts->sigma_min > 0.f && opts->sigma_max > opts->sigma_min && opts->rho > 0.f &&
+                   opts->sampler_rho > 0.f, "num_steps >= 2, 0 < sigma_min < sigma_max, rho > 0");
+  ST2_REQUIRE(((uintptr_t)ws & 255) == 0, "workspace must be 256-byte aligned");
+  int dev = -1;
+  ST2_CUDA_OK(cudaGetDevice(&dev));
+  ST2_REQUIRE(dev == h->device, "handle belongs to another device");
+  int64_t need = 0;
+  rc = sampler_plan(h, B, n, opts->precision, opts->embedding_scale != 1.f, &need);
+  if (rc) return rc;
+  if (need > ws_bytes) {
+    set_error(std::string(who) + ": workspace too small (" + std::to_string(ws_bytes) + " < " + std::to_string(need) + ")");
+    return ST2_ENOMEM;
+  }
+  const int64_t before = launch_counter();
+  cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+  rc = opts->precision == ST2_PREC_BF16
+           ? sampler_t<__nv_bfloat16>(h, x_in, emb, feat, out, ws, ws_bytes, B, n, *opts, single, sigma, st, false, nullptr)
+           : sampler_t<float>(h, x_in, emb, feat, out, ws, ws_bytes, B, n, *opts, single, sigma, st, false, nullptr);
+  h->last_launches = launch_counter() - before;
+  return rc;
+}
+extern "C" int st2_sampler_sample(St2Decoder* h, const float* noise, const float* embedding, const float* features,
+                                  float* out, void* workspace, int64_t workspace_bytes, int B, int n_tokens,
+                                  const St2SamplerOpts* opts, void* stream) {
+  return sampler_call(h, noise, embedding, features, out, workspace, workspace_bytes, B, n_tokens, opts, false, 0.f, stream,
+                      "st2_sampler_sample");
+}
+extern "C" int st2_sampler_denoise(St2Decoder* h, const float* x_noisy, float sigma, const float* embedding,
+                                   const float* features, float* out, void* workspace, int64_t workspace_bytes, int B,
+                                   int n_tokens, const St2SamplerOpts* opts, void* stream) {
+  return sampler_call(h, x_noisy, embedding, features, out, workspace, workspace_bytes, B, n_tokens, opts, true, sigma, stream,
+                      "st2_sampler_denoise");
 }
 
 extern "C" int st2_wave_to_pcm16(const float* wav, int B, int64_t L, int64_t trim_tail, int16_t* out, void* stream) {

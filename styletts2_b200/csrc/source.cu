@@ -101,32 +101,6 @@ int launch_phase_scan(const float* f0, int B, int T, int spf, float* phase, cuda
   return ST2_OK;
 }
 
-// ---------------------------------------------------------------- Philox4x32-10 + normal
-__device__ __forceinline__ void philox4x32(uint32_t c0, uint32_t c1, uint32_t c2, uint32_t c3,
-                                           uint32_t k0, uint32_t k1, uint32_t out[4]) {
-#pragma unroll
-  for (int r = 0; r < 10; ++r) {
-    const uint32_t hi0 = __umulhi(0xD2511F53u, c0), lo0 = 0xD2511F53u * c0;
-    const uint32_t hi1 = __umulhi(0xCD9E8D57u, c2), lo1 = 0xCD9E8D57u * c2;
-    c0 = hi1 ^ c1 ^ k0;
-    c1 = lo1;
-    c2 = hi0 ^ c3 ^ k1;
-    c3 = lo0;
-    k0 += 0x9E3779B9u;
-    k1 += 0xBB67AE85u;
-  }
-  out[0] = c0; out[1] = c1; out[2] = c2; out[3] = c3;
-}
-__device__ __forceinline__ void box_muller(uint32_t a, uint32_t b, float& z0, float& z1) {
-  const float u1 = ((float)a + 1.f) * 2.3283064365386963e-10f;  // (0,1]
-  const float u2 = (float)b * 2.3283064365386963e-10f;
-  const float r = sqrtf(-2.f * __logf(u1));
-  float s, c;
-  __sincosf(2.f * F_PI * u2, &s, &c);
-  z0 = r * c;
-  z1 = r * s;
-}
-
 // ----------------------------------------------------------------------- har source
 __global__ void __launch_bounds__(256)
 har_source_kernel(const float* __restrict__ f0, const float* __restrict__ phase,

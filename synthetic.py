@@ -270,3 +270,80 @@ def synth_f0n_inputs(cfg, B: int, T: int, seed: int = 77):
     g = torch.Generator().manual_seed(seed)
     return {"x": torch.randn(B, cfg["d_hid"] + cfg["style_dim"], T, generator=g),
             "s": torch.randn(B, cfg["style_dim"], generator=g)}
+
+
+# ---------------------------------------------------------------------------------------------
+# Style sampler: StyleTransformer1d / Transformer1d denoiser of the ADPM2 sampler
+# ---------------------------------------------------------------------------------------------
+# models.py:1057-1069 with Configs/config_libritts.yml:68-75 (style_dim 128 -> channels 256, PL-BERT
+# hidden size 768): multispeaker = StyleTransformer1d(context_features=256), else Transformer1d.
+SAMPLER_CFG = {"channels": 256, "context_features": 256, "context_embedding_features": 768, "num_layers": 3,
+               "num_heads": 8, "head_features": 64, "multiplier": 2, "embedding_max_length": 512}
+SAMPLER_CFG_LJ = dict(SAMPLER_CFG, context_features=0)  # Transformer1d (Configs/config.yml, multispeaker: false)
+
+
+def sampler_param_spec(cfg) -> Spec:
+    """Names/shapes of ``StyleTransformer1d.state_dict()`` (context_features > 0) or
+    ``Transformer1d.state_dict()`` (Modules/diffusion/modules.py:40-119, 280-355)."""
+    spec: Spec = []
+    C, S, E = cfg["channels"], cfg["context_features"], cfg["context_embedding_features"]
+    F_, mid = C + E, cfg["num_heads"] * cfg["head_features"]
+    for i in range(cfg["num_layers"]):
+        p = f"blocks.{i}"
+        for nm in ("norm", "norm_context"):
+            if S:
+                spec.append((f"{p}.attention.{nm}.fc.weight", (2 * F_, S), "w", S))
+                spec.append((f"{p}.attention.{nm}.fc.bias", (2 * F_,), "bias", S))
+            else:
+                spec.append((f"{p}.attention.{nm}.weight", (F_,), "ln_w", 1))
+                spec.append((f"{p}.attention.{nm}.bias", (F_,), "ln_b", 1))
+        spec.append((f"{p}.attention.to_q.weight", (mid, F_), "w", F_))
+        spec.append((f"{p}.attention.to_kv.weight", (2 * mid, F_), "w", F_))
+        spec.append((f"{p}.attention.attention.to_out.weight", (F_, mid), "w", mid))
+        spec.append((f"{p}.attention.attention.to_out.bias", (F_,), "bias", mid))
+        spec.append((f"{p}.feed_forward.0.weight", (F_ * cfg["multiplier"], F_), "w", F_))
+        spec.append((f"{p}.feed_forward.0.bias", (F_ * cfg["multiplier"],), "bias", F_))
+        spec.append((f"{p}.feed_forward.2.weight", (F_, F_ * cfg["multiplier"]), "w", F_ * cfg["multiplier"]))
+        spec.append((f"{p}.feed_forward.2.bias", (F_,), "bias", F_ * cfg["multiplier"]))
+    spec.append(("to_out.1.weight", (C, F_, 1), "w", F_))
+    spec.append(("to_out.1.bias", (C,), "bias", F_))
+    for j in (0, 2):
+        spec.append((f"to_mapping.{j}.weight", (F_, F_), "w", F_))
+        spec.append((f"to_mapping.{j}.bias", (F_,), "bias", F_))
+    spec.append(("to_time.0.0.weights", (C // 2,), "randn", 1))
+    spec.append(("to_time.0.1.weight", (F_, C + 1), "w", C + 1))
+    spec.append(("to_time.0.1.bias", (F_,), "bias", C + 1))
+    if S:
+        spec.append(("to_features.0.weight", (F_, S), "w", S))
+        spec.append(("to_features.0.bias", (F_,), "bias", S))
+    spec.append(("fixed_embedding.embedding.weight", (cfg["embedding_max_length"], E), "randn", 1))
+    return spec
+
+
+def synth_sampler_state_dict(cfg, seed: int = 0) -> Dict[str, torch.Tensor]:
+    """torch-default-like init (U(+-1/sqrt(fan_in)) for linears, N(0,1) for the Fourier weights and the
+    embedding table, LayerNorm weights around 1), each tensor from its own seeded generator"""
+    sd: Dict[str, torch.Tensor] = {}
+    for name, shape, kind, fan_in in sampler_param_spec(cfg):
+        g = _gen_for("sampler." + name, seed)
+        if kind == "randn":
+            sd[name] = torch.randn(shape, generator=g).float()
+        elif kind == "ln_w":
+            sd[name] = (1.0 + 0.2 * torch.randn(shape, generator=g)).float()
+        elif kind == "ln_b":
+            sd[name] = (0.2 * torch.randn(shape, generator=g)).float()
+        else:
+            bound = 1.0 / math.sqrt(max(fan_in, 1))
+            sd[name] = ((torch.rand(shape, generator=g) * 2 - 1) * bound).float().contiguous()
+    return sd
+
+
+def synth_sampler_inputs(cfg, B: int, n_tokens: int, num_steps: int = 5, seed: int = 5):
+    """noise [B, 1, channels], embedding (PL-BERT output stand-in) [B, n, E], features (ref_s) [B, S],
+    step_noise [num_steps - 1, B, 1, channels]: the randn_like draws of ADPM2Sampler.step (sampler.py:510)"""
+    g = torch.Generator().manual_seed(seed)
+    C, S, E = cfg["channels"], cfg["context_features"], cfg["context_embedding_features"]
+    out = {"noise": torch.randn(B, 1, C, generator=g), "embedding": torch.randn(B, n_tokens, E, generator=g),
+           "step_noise": torch.randn(max(num_steps - 1, 1), B, 1, C, generator=g)}
+    out["features"] = torch.randn(B, S, generator=g) if S else None
+    return out

@@ -45,6 +45,22 @@ def test_key_list_matches_reference(kind):
     assert dec.samples_per_frame == 300
 
 
+@pytest.mark.parametrize("variant", ["style", "lj"])
+def test_sampler_key_list_matches_reference(variant):
+    import styletts2_b200 as st2
+    import synthetic as synth
+    cfg = synth.SAMPLER_CFG if variant == "style" else synth.SAMPLER_CFG_LJ
+    m = st2.StyleSampler(**cfg)
+    ref = json.load(open(os.path.join(ROOT, "tests", "golden", f"keys_sampler_{variant}.json")))
+    assert {k: list(v.shape) for k, v in m.state_dict().items()} == ref
+    with pytest.raises(_cabi.St2Error, match="head_features"):
+        st2.StyleSampler(head_features=32)
+    with pytest.raises(RuntimeError, match="CUDA"):  # no CPU path, fails loudly
+        m(torch.zeros(1, 1, 256), num_steps=3, embedding=torch.zeros(1, 4, 768),
+          features=torch.zeros(1, 256) if variant == "style" else None)
+    assert C.sizeof(_cabi.St2SamplerOpts) == 64
+
+
 def test_config_validation_and_errors():
     import styletts2_b200 as st2
     with pytest.raises(_cabi.St2Error, match="n_fft"):

@@ -133,3 +133,40 @@ def test_f0n_oracle_vs_reference(T):
     assert F0.shape == g["F0"].shape == (g["x"].shape[0], 2 * T)
     assert (F0 - g["F0"]).abs().max().item() < 5e-6
     assert (N - g["N"]).abs().max().item() < 5e-6
+
+
+# ------------------------------------------------------------- style sampler
+@pytest.mark.parametrize("variant", ["style", "lj"])
+def test_sampler_spec_matches_reference_keys(variant):
+    cfg = synth.SAMPLER_CFG if variant == "style" else synth.SAMPLER_CFG_LJ
+    ref = json.load(open(os.path.join(GOLD, f"keys_sampler_{variant}.json")))
+    mine = {n: list(s) for n, s, *_ in synth.sampler_param_spec(cfg)}
+    assert mine == ref and len(ref) == (48 if variant == "style" else 46)
+
+
+@pytest.mark.parametrize("name", ["style", "style_cfg", "lj"])
+def test_sampler_oracle_vs_reference(name):
+    """oracle/sampler_oracle.py against DiffusionSampler(ADPM2Sampler, KarrasSchedule) and KDiffusion.denoise_fn of
+    the real reference (oracle/make_golden_sampler.py), with and without classifier-free guidance, both networks"""
+    from oracle import sampler_oracle as sorc
+    cfg = synth.SAMPLER_CFG_LJ if name == "lj" else synth.SAMPLER_CFG
+    g = np.load(os.path.join(GOLD, f"sampler_{name}.npz"))
+    g = {k: torch.from_numpy(np.asarray(g[k])) for k in g.files}
+    sd = synth.synth_sampler_state_dict(cfg, seed=0)
+    feat, scale, steps = g.get("features"), float(g["embedding_scale"]), int(g["num_steps"])
+    out = sorc.sample(sd, cfg, g["noise"], g["embedding"], feat, steps, scale, g["step_noise"])
+    assert out.shape == g["out"].shape and (out - g["out"]).abs().max().item() < 5e-6
+    den = sorc.denoise(sorc.Net(sd, cfg), g["noise"] * 0.7, 0.45, 0.2, embedding=g["embedding"], features=feat,
+                       embedding_scale=scale)
+    assert (den - g["denoised"]).abs().max().item() < 5e-6
+
+
+def test_sampler_schedule_known_values():
+    """KarrasSchedule(1e-4, 3.0, rho=9) at 5 steps: endpoints exact, monotone, trailing 0; ADPM2 sigmas satisfy
+    sigma_up^2 + sigma_down^2 = sigma_next^2 and sigma_down <= sigma_mid <= sigma"""
+    from oracle import sampler_oracle as sorc
+    s = sorc.karras_sigmas(5, 1e-4, 3.0, 9.0)
+    assert s.shape == (6,) and abs(s[0].item() - 3.0) < 1e-5 and abs(s[4].item() - 1e-4) < 1e-8 and s[5].item() == 0.0
+    assert (s[:-1][1:] < s[:-1][:-1]).all()
+    up, down, mid = sorc.adpm2_sigmas(s[1], s[2])
+    assert abs(up ** 2 + down ** 2 - float(s[2]) ** 2) < 1e-6 and down <= float(mid) <= float(s[1])
