@@ -290,9 +290,166 @@ def run_f0n(args):
     return 0
 
 
+SAMPLER_SHAPE = dict(B=64, n=128, steps=5)  # BASELINE config 2: "style s from ADPM2 diffusion sampler, 5 steps", batch 64
+
+
+def sampler_flops(cfg, B, n, steps, guided=False):
+    """algorithmic 2*MAC of one sampling run: per denoiser call and token the five linears of every block
+    (to_q, to_kv, to_out, feed_forward.0/.2) + attention (QK^T and PV over n keys); per call and item the
+    mapping MLP / to_time / to_out; once per item the AdaLayerNorm fc and to_features (modules.py:40-278)."""
+    C, S, E = cfg["channels"], cfg["context_features"], cfg["context_embedding_features"]
+    F, mid, L, m = C + E, cfg["num_heads"] * cfg["head_features"], cfg["num_layers"], cfg["multiplier"]
+    per_tok = L * (2 * F * mid + 2 * F * 2 * mid + 2 * mid * F + 2 * 2 * F * F * m + 2 * 2 * n * mid)
+    per_item_call = 2 * 2 * F * F + 2 * F * C
+    runs = 2 if guided else 1
+    calls = 2 * (steps - 1)
+    once = (2 * S * L * 4 * F + 2 * S * F) if S else 0
+    return B * (calls * (runs * (n * per_tok + 2 * F * C) + per_item_call) + once) + calls * 2 * (C + 1) * F
+
+
+def run_sampler(args):
+    """next-row workload: the ADPM2 style sampler at BASELINE config 2's shape (B=64 items, 128 text
+    tokens each, 5 diffusion steps = 8 denoiser calls, embedding_scale 1 like Inference_LibriTTS.ipynb cell 20)."""
+    import torch
+    import torch.distributed as dist
+    import styletts2_b200 as st2
+    import synthetic as synth
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a CUDA device: styletts2_b200 has no CPU fallback")
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+    B, n, steps = SAMPLER_SHAPE["B"], SAMPLER_SHAPE["n"], SAMPLER_SHAPE["steps"]
+    cfg = synth.SAMPLER_CFG
+    m = st2.StyleSampler(**cfg)
+    sd = synth.synth_sampler_state_dict(cfg, seed=0)
+    m.load_state_dict(sd, strict=True)
+    m = m.to(dev).eval()
+    m.precision = args.precision
+    inp = synth.synth_sampler_inputs(cfg, B, n, steps, seed=4321 + rank)
+    del inp["step_noise"]  # throughput runs draw the step noise in-kernel (Philox)
+    host = {k: v.pin_memory() for k, v in inp.items()}
+    d = {k: v.to(dev) for k, v in inp.items()}
+    audio_s = B * 10.0  # every item conditions one 800-frame (10 s) utterance of config 2
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def max_over_ranks(ms):
+        if world == 1:
+            return ms
+        t = torch.tensor([ms], device=dev, dtype=torch.float64)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+
+    call = lambda a, i: m(a["noise"], num_steps=steps, embedding=a["embedding"], features=a["features"], seed=i,
+                          item_offset=rank * B)
+    for i in range(max(3, args.warmup)):
+        out = call(d, i)
+    barrier()
+    launches = m.last_launches
+    sampler = ClockSampler(local)
+    if sampler.ok:
+        sampler.start()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    barrier()
+    e0.record()
+    for i in range(args.steps):
+        out = call(d, 100 + i)
+    e1.record()
+    barrier()
+    clocks = sampler.stop()
+    ms_step = max_over_ranks(e0.elapsed_time(e1)) / args.steps
+    assert torch.isfinite(out).all()
+    out_host = torch.empty(B, 1, cfg["channels"]).pin_memory()
+
+    def e2e_step(i):
+        a = {k: host[k].to(dev, non_blocking=True) for k in host}
+        out_host.copy_(call(a, 200 + i), non_blocking=True)
+
+    for i in range(2):
+        e2e_step(i)
+    barrier()
+    e0.record()
+    for i in range(args.steps):
+        e2e_step(i)
+    e1.record()
+    barrier()
+    ms_e2e = max_over_ranks(e0.elapsed_time(e1)) / args.steps
+    if rank != 0:
+        if world > 1:
+            dist.destroy_process_group()
+        return 0
+    cpu = None
+    if world == 1 and not args.no_cpu_baseline:
+        v, tm, cores = _oracle_cpu_sampler(1, n, steps, 2, 1)
+        cpu = {"value": round(v, 3), "unit": UNIT, "cores": cores, "kind": "port",
+               "sample": f"1 item x {n} tokens x {steps} steps, fp32, torch CPU (oracle port of DiffusionSampler/ADPM2), {tm:.0f} ms"}
+    fl = sampler_flops(cfg, B, n, steps)
+    tf = fl / (ms_step * 1e-3) / 1e12
+    line = {
+        "metric": "audio-sec/sec of style vectors sampled (ADPM2 sampler over StyleTransformer1d, bf16)",
+        "value": round(world * audio_s / (ms_step * 1e-3), 2), "unit": UNIT, "n_gpus": world, "steps": args.steps,
+        "warmup": max(3, args.warmup), "ms_per_step": round(ms_step, 3), "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None, "dtype": args.precision, "data": "synthetic",
+        "config": {"workload": f"next row N2: style sampler, B={B} items x {n} text tokens, {steps} diffusion steps "
+                               f"({2 * (steps - 1)} denoiser calls), embedding_scale 1; one item = the style of one 10 s utterance",
+                   "batch_per_gpu": B, "tokens": n, "diffusion_steps": steps, "items_per_sec": round(world * B / (ms_step * 1e-3), 1),
+                   "weights": "random-init (synthetic.py, seed 0)", "noise": "in-kernel Philox",
+                   "l2": "activations of one denoiser call: 0.2 GB (> 126 MB L2); the 36 MB of bf16 weights stay L2-resident by design",
+                   "parallelism": f"dp{world} (independent batches, no collective)"},
+        "e2e": {"value": round(world * audio_s / (ms_e2e * 1e-3), 2), "unit": UNIT, "ms_per_step": round(ms_e2e, 3),
+                "h2d_bytes_per_step": sum(host[k].numel() * 4 for k in host), "d2h_bytes_per_step": out_host.numel() * 4},
+        "gpu_launches": int(launches * args.steps),
+        "roofline": {"bound": "tensor", "achieved": round(tf, 2), "peak": _peaks()["tf_sustained"], "unit": "TFLOP/s",
+                     "frac": round(tf / _peaks()["tf_sustained"], 4), "traffic": None,
+                     "note": "whole sampling run (8 dependent denoiser calls of 3 transformer blocks)"},
+        "cpu_baseline": cpu, "clocks": clocks,
+    }
+    print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+    return 0
+
+
+def _oracle_cpu_sampler(B, n, steps, reps, warm):
+    import torch
+    import synthetic as synth
+    from oracle import sampler_oracle as sorc
+    torch.set_num_threads(os.cpu_count() or 1)
+    cfg = synth.SAMPLER_CFG
+    sd = synth.synth_sampler_state_dict(cfg, seed=0)
+    one = synth.synth_sampler_inputs(cfg, B, n, steps, seed=1)
+    ts = []
+    for i in range(warm + reps):
+        t0 = time.perf_counter()
+        with torch.no_grad():
+            sorc.sample(sd, cfg, one["noise"], one["embedding"], one["features"], steps, 1.0, one["step_noise"])
+        ts.append(time.perf_counter() - t0)
+    tm = statistics.median(ts[warm:])
+    return B * 10.0 / tm, tm * 1e3, torch.get_num_threads()
+
+
 def run_reference(args):
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
+        return 0
+    if args.workload == "sampler":
+        n, steps = SAMPLER_SHAPE["n"], SAMPLER_SHAPE["steps"]
+        v, tm, cores = _oracle_cpu_sampler(1, n, steps, args.steps, max(1, args.warmup))
+        print(json.dumps({"impl": "reference", "metric": "audio-sec/sec of style vectors sampled (ADPM2 sampler over StyleTransformer1d, bf16)",
+                          "value": round(v, 3), "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps, "warmup": max(1, args.warmup),
+                          "ms_per_step": round(tm, 3), "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
+                          "data": "synthetic", "config": {"workload": "next row N2: style sampler", "sample": f"1 item x {n} tokens x {steps} steps per step on the CPU"},
+                          "cpu_baseline": {"value": round(v, 3), "unit": UNIT, "cores": cores, "kind": "port",
+                                           "sample": f"1 item x {n} tokens x {steps} steps, fp32, torch CPU (oracle port of Modules/diffusion)"},
+                          "e2e": {"value": round(v, 3), "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}), flush=True)
         return 0
     if args.workload == "f0n":
         import torch
@@ -507,7 +664,7 @@ def main():
     ap.add_argument("--steps", type=int, default=10)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--workload", default="c2", choices=sorted(WORKLOADS) + ["f0n"])
+    ap.add_argument("--workload", default="c2", choices=sorted(WORKLOADS) + ["f0n", "sampler"])
     ap.add_argument("--precision", default="bf16", choices=["bf16", "fp32"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-graphs", action="store_true", help="launch every kernel eagerly instead of replaying a CUDA graph")
@@ -521,6 +678,8 @@ def main():
         cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={args.gpus}",
                "--master-addr", "127.0.0.1", "--master-port", "29541", os.path.abspath(__file__)] + sys.argv[1:]
         return subprocess.call(cmd)
+    if args.workload == "sampler":
+        return run_sampler(args)
     return run_f0n(args) if args.workload == "f0n" else run_ours(args)
 
 

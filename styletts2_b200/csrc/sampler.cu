@@ -15,9 +15,34 @@ namespace st2 {
 
 __device__ __forceinline__ float gelu_erf(float v) { return 0.5f * v * (1.f + erff(v * 0.70710678118654752f)); }
 
+// four consecutive elements (16-byte fp32 / 8-byte bf16 accesses; the address must be aligned accordingly)
+template <typename T>
+__device__ __forceinline__ float4 ld4_f(const T* p);
+template <>
+__device__ __forceinline__ float4 ld4_f<float>(const float* p) { return *reinterpret_cast<const float4*>(p); }
+template <>
+__device__ __forceinline__ float4 ld4_f<__nv_bfloat16>(const __nv_bfloat16* p) {
+  const uint2 r = *reinterpret_cast<const uint2*>(p);
+  return make_float4(__uint_as_float(r.x << 16), __uint_as_float(r.x & 0xFFFF0000u), __uint_as_float(r.y << 16),
+                     __uint_as_float(r.y & 0xFFFF0000u));
+}
+template <typename T>
+__device__ __forceinline__ void st4_f(T* p, float4 v);
+template <>
+__device__ __forceinline__ void st4_f<float>(float* p, float4 v) { *reinterpret_cast<float4*>(p) = v; }
+template <>
+__device__ __forceinline__ void st4_f<__nv_bfloat16>(__nv_bfloat16* p, float4 v) {
+  __nv_bfloat162 a = __floats2bfloat162_rn(v.x, v.y), b = __floats2bfloat162_rn(v.z, v.w);
+  uint2 r;
+  r.x = *reinterpret_cast<uint32_t*>(&a);
+  r.y = *reinterpret_cast<uint32_t*>(&b);
+  *reinterpret_cast<uint2*>(p) = r;
+}
+
 // ------------------------------------------------------------------ small dense layers (fp32)
-// y[r][o] = act(bias[o] + sum_i W[o][i] * (x[r][i] + xb[i])), one warp per output feature and 8 rows
-template <int ROWS>
+// y[r][o] = act(bias[o] + sum_i W[o][i] * (x[r][i] + xb[i])), one warp per output feature and ROWS rows;
+// VEC: 16-byte loads (I, ldx multiples of 4, 16-byte aligned bases)
+template <int ROWS, bool VEC>
 __global__ void __launch_bounds__(256)
 small_linear_kernel(const float* __restrict__ x, int ldx, const float* __restrict__ xb, const float* __restrict__ W,
                     const float* __restrict__ bias, float* __restrict__ y, int ldy, int R, int I, int O, int act) {
@@ -28,13 +53,30 @@ small_linear_kernel(const float* __restrict__ x, int ldx, const float* __restric
 #pragma unroll
   for (int j = 0; j < ROWS; ++j) acc[j] = 0.f;
   const float* wr = W + (int64_t)o * I;
-  for (int i = lane; i < I; i += 32) {
-    const float w = __ldg(wr + i);
-    const float add = xb ? __ldg(xb + i) : 0.f;
+  if (VEC) {
+    for (int i = lane * 4; i < I; i += 128) {
+      const float4 w = __ldg(reinterpret_cast<const float4*>(wr + i));
+      float4 add = make_float4(0.f, 0.f, 0.f, 0.f);
+      if (xb) add = __ldg(reinterpret_cast<const float4*>(xb + i));
 #pragma unroll
-    for (int j = 0; j < ROWS; ++j) {
-      const int r = min(r0 + j, R - 1);
-      acc[j] = fmaf(w, __ldg(x + (int64_t)r * ldx + i) + add, acc[j]);
+      for (int j = 0; j < ROWS; ++j) {
+        const int r = min(r0 + j, R - 1);
+        const float4 v = __ldg(reinterpret_cast<const float4*>(x + (int64_t)r * ldx + i));
+        acc[j] = fmaf(w.x, v.x + add.x, acc[j]);
+        acc[j] = fmaf(w.y, v.y + add.y, acc[j]);
+        acc[j] = fmaf(w.z, v.z + add.z, acc[j]);
+        acc[j] = fmaf(w.w, v.w + add.w, acc[j]);
+      }
+    }
+  } else {
+    for (int i = lane; i < I; i += 32) {
+      const float w = __ldg(wr + i);
+      const float add = xb ? __ldg(xb + i) : 0.f;
+#pragma unroll
+      for (int j = 0; j < ROWS; ++j) {
+        const int r = min(r0 + j, R - 1);
+        acc[j] = fmaf(w, __ldg(x + (int64_t)r * ldx + i) + add, acc[j]);
+      }
     }
   }
 #pragma unroll
@@ -51,8 +93,16 @@ small_linear_kernel(const float* __restrict__ x, int ldx, const float* __restric
 }
 int launch_small_linear(const float* x, int ldx, const float* xb, const float* W, const float* bias, float* y, int ldy,
                         int R, int I, int O, int gelu, cudaStream_t st) {
-  dim3 grid(ceil_div(O, 8), ceil_div(R, 8));
-  small_linear_kernel<8><<<grid, 256, 0, st>>>(x, ldx, xb, W, bias, y, ldy, R, I, O, gelu);
+  const bool vec = I % 4 == 0 && ldx % 4 == 0 && (((uintptr_t)x | (uintptr_t)W | (uintptr_t)xb) & 15) == 0;
+  if (R == 1) {
+    dim3 grid(ceil_div(O, 8), 1);
+    if (vec) small_linear_kernel<1, true><<<grid, 256, 0, st>>>(x, ldx, xb, W, bias, y, ldy, R, I, O, gelu);
+    else small_linear_kernel<1, false><<<grid, 256, 0, st>>>(x, ldx, xb, W, bias, y, ldy, R, I, O, gelu);
+  } else {
+    dim3 grid(ceil_div(O, 8), ceil_div(R, 8));
+    if (vec) small_linear_kernel<8, true><<<grid, 256, 0, st>>>(x, ldx, xb, W, bias, y, ldy, R, I, O, gelu);
+    else small_linear_kernel<8, false><<<grid, 256, 0, st>>>(x, ldx, xb, W, bias, y, ldy, R, I, O, gelu);
+  }
   ST2_LAUNCH_OK("small_linear");
   return ST2_OK;
 }
@@ -96,11 +146,12 @@ int launch_build_rows(const float* x, float c_in, const float* emb, const float*
 // x = x + delta + mapping[b]  (written back, fp32), then the two (adaptive) layer norms of StyleAttention
 // (modules.py:268-275): nq = (1 + g1) * LN(x) + b1, nk = (1 + g2) * LN(x) + b2, LN biased variance, eps 1e-5.
 // One warp per row.  gb = [B or 1][gb_stride]: this block's (g1, b1, g2, b2), F values each.
-template <typename AT>
+template <typename AT, int NV>
 __global__ void __launch_bounds__(256)
 adaln2_kernel(float* __restrict__ X, const AT* __restrict__ delta, const float* __restrict__ mapping, int64_t map_bstride,
               const float* __restrict__ gb, int64_t gb_bstride, AT* __restrict__ nq, AT* __restrict__ nk, int64_t rows,
               int n, int B, int F) {
+  // lane owns the 4-channel groups c = 4 * (lane + 32 j), j < NV (F <= 128 NV): the row lives in registers
   const int64_t row = (int64_t)blockIdx.x * 8 + (threadIdx.x >> 5);
   const int lane = threadIdx.x & 31;
   if (row >= rows) return;
@@ -108,33 +159,59 @@ adaln2_kernel(float* __restrict__ X, const AT* __restrict__ delta, const float* 
   float* xr = X + row * F;
   const AT* dr = delta ? delta + row * F : nullptr;
   const float* mp = mapping + (int64_t)b * map_bstride;
+  float4 v[NV];
   float s = 0.f;
-  for (int c = lane; c < F; c += 32) {
-    float v = xr[c] + mp[c];
-    if (dr) v += ld_f(dr + c);
-    xr[c] = v;
-    s += v;
+#pragma unroll
+  for (int j = 0; j < NV; ++j) {
+    const int c = 4 * (lane + 32 * j);
+    v[j] = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (c < F) {
+      const float4 a = *reinterpret_cast<const float4*>(xr + c), m = __ldg(reinterpret_cast<const float4*>(mp + c));
+      v[j] = make_float4(a.x + m.x, a.y + m.y, a.z + m.z, a.w + m.w);
+      if (dr) {
+        const float4 d = ld4_f(dr + c);
+        v[j].x += d.x; v[j].y += d.y; v[j].z += d.z; v[j].w += d.w;
+      }
+      *reinterpret_cast<float4*>(xr + c) = v[j];
+      s += (v[j].x + v[j].y) + (v[j].z + v[j].w);
+    }
   }
   const float mean = warp_sum(s) / (float)F;
   float q = 0.f;
-  for (int c = lane; c < F; c += 32) {
-    const float d = xr[c] - mean;
-    q = fmaf(d, d, q);
+#pragma unroll
+  for (int j = 0; j < NV; ++j) {
+    if (4 * (lane + 32 * j) < F) {
+      const float d0 = v[j].x - mean, d1 = v[j].y - mean, d2 = v[j].z - mean, d3 = v[j].w - mean;
+      q += (d0 * d0 + d1 * d1) + (d2 * d2 + d3 * d3);
+    }
   }
   const float rstd = rsqrtf(warp_sum(q) / (float)F + 1e-5f);
   const float* g = gb + (int64_t)b * gb_bstride;
   AT* q_o = nq + row * F;
   AT* k_o = nk + row * F;
-  for (int c = lane; c < F; c += 32) {
-    const float xh = (xr[c] - mean) * rstd;
-    st_f(q_o + c, fmaf(1.f + g[c], xh, g[F + c]));
-    st_f(k_o + c, fmaf(1.f + g[2 * F + c], xh, g[3 * F + c]));
+#pragma unroll
+  for (int j = 0; j < NV; ++j) {
+    const int c = 4 * (lane + 32 * j);
+    if (c < F) {
+      const float xh[4] = {(v[j].x - mean) * rstd, (v[j].y - mean) * rstd, (v[j].z - mean) * rstd, (v[j].w - mean) * rstd};
+      const float4 g1 = __ldg(reinterpret_cast<const float4*>(g + c)), b1 = __ldg(reinterpret_cast<const float4*>(g + F + c));
+      const float4 g2 = __ldg(reinterpret_cast<const float4*>(g + 2 * F + c)), b2 = __ldg(reinterpret_cast<const float4*>(g + 3 * F + c));
+      const float ga[4] = {g1.x, g1.y, g1.z, g1.w}, ba[4] = {b1.x, b1.y, b1.z, b1.w};
+      const float gc[4] = {g2.x, g2.y, g2.z, g2.w}, bc[4] = {b2.x, b2.y, b2.z, b2.w};
+      st4_f(q_o + c, make_float4(fmaf(1.f + ga[0], xh[0], ba[0]), fmaf(1.f + ga[1], xh[1], ba[1]),
+                                 fmaf(1.f + ga[2], xh[2], ba[2]), fmaf(1.f + ga[3], xh[3], ba[3])));
+      st4_f(k_o + c, make_float4(fmaf(1.f + gc[0], xh[0], bc[0]), fmaf(1.f + gc[1], xh[1], bc[1]),
+                                 fmaf(1.f + gc[2], xh[2], bc[2]), fmaf(1.f + gc[3], xh[3], bc[3])));
+    }
   }
 }
 template <typename AT>
 int launch_adaln2(float* X, const AT* delta, const float* mapping, int64_t map_bstride, const float* gb, int64_t gb_bstride,
                   AT* nq, AT* nk, int64_t rows, int n, int B, int F, cudaStream_t st) {
-  adaln2_kernel<AT><<<(unsigned)((rows + 7) / 8), 256, 0, st>>>(X, delta, mapping, map_bstride, gb, gb_bstride, nq, nk, rows, n, B, F);
+  ST2_REQUIRE(F % 4 == 0 && F <= 2048, "adaln2: features must be a multiple of 4, at most 2048");
+  const unsigned grid = (unsigned)((rows + 7) / 8);
+  if (F <= 1024) adaln2_kernel<AT, 8><<<grid, 256, 0, st>>>(X, delta, mapping, map_bstride, gb, gb_bstride, nq, nk, rows, n, B, F);
+  else adaln2_kernel<AT, 16><<<grid, 256, 0, st>>>(X, delta, mapping, map_bstride, gb, gb_bstride, nq, nk, rows, n, B, F);
   ST2_LAUNCH_OK("adaln2");
   return ST2_OK;
 }
@@ -150,9 +227,10 @@ add_cast_kernel(float* __restrict__ X, const AT* __restrict__ delta, AT* __restr
   const int64_t i = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) * 4;
   if (i >= n) return;
   float4 v = *reinterpret_cast<float4*>(X + i);
-  v.x += ld_f(delta + i); v.y += ld_f(delta + i + 1); v.z += ld_f(delta + i + 2); v.w += ld_f(delta + i + 3);
+  const float4 d = ld4_f(delta + i);
+  v.x += d.x; v.y += d.y; v.z += d.z; v.w += d.w;
   *reinterpret_cast<float4*>(X + i) = v;
-  st_f(Xc + i, v.x); st_f(Xc + i + 1, v.y); st_f(Xc + i + 2, v.z); st_f(Xc + i + 3, v.w);
+  st4_f(Xc + i, v);
 }
 template <typename AT>
 int launch_add_cast(float* X, const AT* delta, AT* Xc, int64_t n, cudaStream_t st) {
@@ -197,7 +275,7 @@ template int launch_gelu<float>(float*, int64_t, cudaStream_t);
 template int launch_gelu<__nv_bfloat16>(__nv_bfloat16*, int64_t, cudaStream_t);
 
 // ------------------------------------------------------------------ attention
-// softmax(q k^T / sqrt(D)) v per (item, head) (modules.py:512-526), D = 64.  One thread per query row with
+// softmax(q k^T / sqrt(D)) v per (item, head) (modules.py:512-526), D = 64.  fp32 parity path: one thread per query row with
 // q and the output accumulator in registers; keys / values of the head are staged through shared memory in
 // tiles of 64 rows (fp32) and read as warp broadcasts; online softmax in fp32.
 template <typename AT>
@@ -282,15 +360,177 @@ attention_kernel(const AT* __restrict__ Q, int ldq, const AT* __restrict__ KV, i
     for (int d = 0; d < D; ++d) st_f(op + d, o[d] * inv);
   }
 }
+// bf16 path: flash-attention form on the warp-level tensor-core MMA (mma.sync m16n8k16, bf16 x bf16 -> fp32).
+// The attention core is 3 % of the sampler's FLOPs (n = 128 keys of 64 features per head); it is latency- and
+// shared-memory-bound, so each warp keeps its 16 query rows, the 16 x 64 score tile and the 16 x 64 output
+// accumulator in registers (scores never reach shared memory) and K / V tiles of 64 keys are staged with
+// cp.async (rows padded to 144 bytes: conflict-free ldmatrix).  CTA = 4 warps = 64 queries of one (item, head).
+__device__ __forceinline__ void mma_bf16_16816(float (&c)[4], const uint32_t (&a)[4], uint32_t b0, uint32_t b1) {
+  asm volatile("mma.sync.aligned.m16n8k16.row.col.f32.bf16.bf16.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
+               : "+f"(c[0]), "+f"(c[1]), "+f"(c[2]), "+f"(c[3])
+               : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b0), "r"(b1));
+}
+__device__ __forceinline__ void ldsm_x4(uint32_t addr, uint32_t& r0, uint32_t& r1, uint32_t& r2, uint32_t& r3) {
+  asm volatile("ldmatrix.sync.aligned.m8n8.x4.shared.b16 {%0,%1,%2,%3}, [%4];" : "=r"(r0), "=r"(r1), "=r"(r2), "=r"(r3) : "r"(addr));
+}
+__device__ __forceinline__ void ldsm_x4_t(uint32_t addr, uint32_t& r0, uint32_t& r1, uint32_t& r2, uint32_t& r3) {
+  asm volatile("ldmatrix.sync.aligned.m8n8.x4.trans.shared.b16 {%0,%1,%2,%3}, [%4];"
+               : "=r"(r0), "=r"(r1), "=r"(r2), "=r"(r3) : "r"(addr));
+}
+__device__ __forceinline__ uint32_t pack2_bf16(float lo, float hi) {
+  __nv_bfloat162 v = __floats2bfloat162_rn(lo, hi);
+  return *reinterpret_cast<uint32_t*>(&v);
+}
+__global__ void __launch_bounds__(128)
+attention_mma_kernel(const __nv_bfloat16* __restrict__ Q, int ldq, const __nv_bfloat16* __restrict__ KV, int ldkv,
+                     __nv_bfloat16* __restrict__ O, int ldo, int n, int mid, float scale_log2e) {
+  constexpr int D = 64, KT = 64, LDS = 72;  // padded row: 144 bytes
+  __shared__ __align__(16) __nv_bfloat16 ks[KT * LDS];
+  __shared__ __align__(16) __nv_bfloat16 vs[KT * LDS];
+  const int h = blockIdx.y, bx = blockIdx.z, warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int g = lane >> 2, t = lane & 3;
+  const int64_t base = (int64_t)bx * n;
+  const int q0 = blockIdx.x * 64 + warp * 16;
+  // A fragments of this warp's 16 query rows (rows g and g + 8), 4 k-steps of 16 features
+  uint32_t qa[4][4];
+  {
+    const int r0 = min(q0 + g, n - 1), r1 = min(q0 + g + 8, n - 1);
+    const __nv_bfloat16* p0 = Q + (base + r0) * ldq + h * D + 2 * t;
+    const __nv_bfloat16* p1 = Q + (base + r1) * ldq + h * D + 2 * t;
+#pragma unroll
+    for (int kk = 0; kk < 4; ++kk) {
+      qa[kk][0] = *reinterpret_cast<const uint32_t*>(p0 + kk * 16);
+      qa[kk][1] = *reinterpret_cast<const uint32_t*>(p1 + kk * 16);
+      qa[kk][2] = *reinterpret_cast<const uint32_t*>(p0 + kk * 16 + 8);
+      qa[kk][3] = *reinterpret_cast<const uint32_t*>(p1 + kk * 16 + 8);
+    }
+  }
+  float o[8][4];
+#pragma unroll
+  for (int i = 0; i < 8; ++i)
+#pragma unroll
+    for (int j = 0; j < 4; ++j) o[i][j] = 0.f;
+  float m0 = -INFINITY, m1 = -INFINITY, l0 = 0.f, l1 = 0.f;
+  const uint32_t ks_u = (uint32_t)__cvta_generic_to_shared(ks), vs_u = (uint32_t)__cvta_generic_to_shared(vs);
+  for (int k0 = 0; k0 < n; k0 += KT) {
+    const int kn = min(KT, n - k0);
+    __syncthreads();
+    // stage K and V rows [k0, k0 + 64) of this head (16-byte chunks; rows past n are zero)
+    for (int e = threadIdx.x; e < KT * 8; e += 128) {
+      const int r = e >> 3, ch = e & 7;
+      const uint32_t off = (uint32_t)(r * LDS + ch * 8) * 2u;
+      if (r < kn) {
+        const __nv_bfloat16* src = KV + (base + k0 + r) * ldkv + h * D + ch * 8;
+        asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(ks_u + off), "l"(src));
+        asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(vs_u + off), "l"(src + mid));
+      } else {
+        *reinterpret_cast<uint4*>(reinterpret_cast<uint8_t*>(ks) + off) = make_uint4(0u, 0u, 0u, 0u);
+        *reinterpret_cast<uint4*>(reinterpret_cast<uint8_t*>(vs) + off) = make_uint4(0u, 0u, 0u, 0u);
+      }
+    }
+    asm volatile("cp.async.commit_group;" ::: "memory");
+    asm volatile("cp.async.wait_group 0;" ::: "memory");
+    __syncthreads();
+    // S = Q K^T: 8 blocks of 8 keys
+    float sc[8][4];
+#pragma unroll
+    for (int nb = 0; nb < 8; ++nb)
+#pragma unroll
+      for (int j = 0; j < 4; ++j) sc[nb][j] = 0.f;
+#pragma unroll
+    for (int nb2 = 0; nb2 < 4; ++nb2) {  // 16 keys per ldmatrix.x4 pair
+#pragma unroll
+      for (int kk2 = 0; kk2 < 2; ++kk2) {  // 32 features per iteration
+        // matrices: (keys nb2*16 + [0,8), d kk2*32 + [0,8)), (.., d +8), (.., d +16), (.., d +24)
+        uint32_t b[4], c2[4];
+        const int row = nb2 * 16 + (lane & 7), col = kk2 * 32 + (lane >> 3) * 8;
+        ldsm_x4(ks_u + (uint32_t)(row * LDS + col) * 2u, b[0], b[1], b[2], b[3]);
+        ldsm_x4(ks_u + (uint32_t)((row + 8) * LDS + col) * 2u, c2[0], c2[1], c2[2], c2[3]);
+        mma_bf16_16816(sc[nb2 * 2], qa[kk2 * 2], b[0], b[1]);
+        mma_bf16_16816(sc[nb2 * 2], qa[kk2 * 2 + 1], b[2], b[3]);
+        mma_bf16_16816(sc[nb2 * 2 + 1], qa[kk2 * 2], c2[0], c2[1]);
+        mma_bf16_16816(sc[nb2 * 2 + 1], qa[kk2 * 2 + 1], c2[2], c2[3]);
+      }
+    }
+    // online softmax on rows g (c0, c1) and g + 8 (c2, c3); keys past n are masked
+    float mx0 = m0, mx1 = m1;
+#pragma unroll
+    for (int nb = 0; nb < 8; ++nb) {
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        const int key = nb * 8 + 2 * t + (j & 1);
+        const float v = key < kn ? sc[nb][j] * scale_log2e : -INFINITY;
+        sc[nb][j] = v;
+        if (j < 2) mx0 = fmaxf(mx0, v);
+        else mx1 = fmaxf(mx1, v);
+      }
+    }
+    mx0 = fmaxf(mx0, __shfl_xor_sync(0xffffffffu, mx0, 1));
+    mx0 = fmaxf(mx0, __shfl_xor_sync(0xffffffffu, mx0, 2));
+    mx1 = fmaxf(mx1, __shfl_xor_sync(0xffffffffu, mx1, 1));
+    mx1 = fmaxf(mx1, __shfl_xor_sync(0xffffffffu, mx1, 2));
+    const float cr0 = exp2f(m0 - mx0), cr1 = exp2f(m1 - mx1);
+    m0 = mx0; m1 = mx1;
+    l0 *= cr0; l1 *= cr1;
+#pragma unroll
+    for (int nb = 0; nb < 8; ++nb) {
+      o[nb][0] *= cr0; o[nb][1] *= cr0; o[nb][2] *= cr1; o[nb][3] *= cr1;
+    }
+    uint32_t pa[4][4];  // P as A fragments: k-step j covers keys [16 j, 16 j + 16) = score blocks 2j, 2j + 1
+#pragma unroll
+    for (int nb = 0; nb < 8; ++nb) {
+      const float p0 = exp2f(sc[nb][0] - mx0), p1 = exp2f(sc[nb][1] - mx0);
+      const float p2 = exp2f(sc[nb][2] - mx1), p3 = exp2f(sc[nb][3] - mx1);
+      l0 += p0 + p1;
+      l1 += p2 + p3;
+      pa[nb >> 1][(nb & 1) * 2] = pack2_bf16(p0, p1);
+      pa[nb >> 1][(nb & 1) * 2 + 1] = pack2_bf16(p2, p3);
+    }
+    // O += P V: B[k = key][n = d] from V[key][d] through ldmatrix.trans
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {      // 16 keys
+#pragma unroll
+      for (int db = 0; db < 4; ++db) {  // 16 features
+        // matrices: (keys 16j + [0,8), d 16db + [0,8)), (keys +8, d), (keys, d + 8), (keys + 8, d + 8)
+        uint32_t b0, b1, b2, b3;
+        const int row = j * 16 + (lane & 7) + ((lane >> 3) & 1) * 8, col = db * 16 + (lane >> 4) * 8;
+        ldsm_x4_t(vs_u + (uint32_t)(row * LDS + col) * 2u, b0, b1, b2, b3);
+        mma_bf16_16816(o[db * 2], pa[j], b0, b1);
+        mma_bf16_16816(o[db * 2 + 1], pa[j], b2, b3);
+      }
+    }
+  }
+  l0 += __shfl_xor_sync(0xffffffffu, l0, 1);
+  l0 += __shfl_xor_sync(0xffffffffu, l0, 2);
+  l1 += __shfl_xor_sync(0xffffffffu, l1, 1);
+  l1 += __shfl_xor_sync(0xffffffffu, l1, 2);
+  const float i0 = 1.f / l0, i1 = 1.f / l1;
+  const int r0 = q0 + g, r1 = q0 + g + 8;
+#pragma unroll
+  for (int nb = 0; nb < 8; ++nb) {
+    if (r0 < n) *reinterpret_cast<uint32_t*>(O + (base + r0) * ldo + h * D + nb * 8 + 2 * t) = pack2_bf16(o[nb][0] * i0, o[nb][1] * i0);
+    if (r1 < n) *reinterpret_cast<uint32_t*>(O + (base + r1) * ldo + h * D + nb * 8 + 2 * t) = pack2_bf16(o[nb][2] * i1, o[nb][3] * i1);
+  }
+}
+
 template <typename AT>
 int launch_attention(const AT* Q, int ldq, const AT* KV, int ldkv, AT* O, int ldo, int Bx, int n, int heads, int head_dim,
                      cudaStream_t st) {
   ST2_REQUIRE(head_dim == 64, "attention kernel is built for head_features = 64");
   ST2_REQUIRE(Bx <= 65535 && heads <= 65535, "attention grid");
-  dim3 grid(ceil_div(n, 128), heads, Bx);
-  attention_kernel<AT><<<grid, 128, 0, st>>>(Q, ldq, KV, ldkv, O, ldo, n, heads * head_dim, 1.f / sqrtf((float)head_dim));
-  ST2_LAUNCH_OK("attention");
-  return ST2_OK;
+  const float scale = 1.f / sqrtf((float)head_dim);
+  if constexpr (sizeof(AT) == 2) {
+    ST2_REQUIRE(ldq % 8 == 0 && ldkv % 8 == 0 && ldo % 2 == 0, "attention: 16-byte aligned rows");
+    dim3 grid(ceil_div(n, 64), heads, Bx);
+    attention_mma_kernel<<<grid, 128, 0, st>>>(Q, ldq, KV, ldkv, O, ldo, n, heads * head_dim, scale * 1.4426950408889634f);
+    ST2_LAUNCH_OK("attention_mma");
+    return ST2_OK;
+  } else {
+    dim3 grid(ceil_div(n, 128), heads, Bx);
+    attention_kernel<AT><<<grid, 128, 0, st>>>(Q, ldq, KV, ldkv, O, ldo, n, heads * head_dim, scale);
+    ST2_LAUNCH_OK("attention");
+    return ST2_OK;
+  }
 }
 template int launch_attention<float>(const float*, int, const float*, int, float*, int, int, int, int, int, cudaStream_t);
 template int launch_attention<__nv_bfloat16>(const __nv_bfloat16*, int, const __nv_bfloat16*, int, __nv_bfloat16*, int, int,
