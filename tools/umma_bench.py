@@ -11,7 +11,7 @@ from styletts2_b200 import _cabi
 from styletts2_b200._cabi import lib, check
 
 
-def make(B, L, cin, n, k, dil, act, with_res, with_stats, accumulate=False, f32out=False):
+def make(B, L, cin, n, k, dil, act, with_res, with_stats, accumulate=False, f32out=False, ident=False):
     dev = "cuda"
     g = torch.Generator().manual_seed(1)
     x = torch.randn(B, L, cin, generator=g).to(torch.bfloat16).to(dev)
@@ -31,7 +31,7 @@ def make(B, L, cin, n, k, dil, act, with_res, with_stats, accumulate=False, f32o
     p = _cabi.St2ConvParams()
     p.B = B
     p.x = x.data_ptr(); p.x_dtype = _cabi.DT_BF16; p.x_bstride = L * cin; p.ldx = cin; p.Lin = L; p.cin = cin
-    p.ss = ss.data_ptr(); p.ss_stride = cin; p.act = act; p.slope = 0.1; p.alpha = alpha.data_ptr()
+    p.ss = None if ident else ss.data_ptr(); p.ss_stride = cin; p.act = act; p.slope = 0.1; p.alpha = alpha.data_ptr()
     p.k, p.dil, p.pad, p.stride = k, dil, dil * (k - 1) // 2, 1
     p.w = wd.data_ptr(); p.bias = bias.data_ptr(); p.n_cols = n
     p.y = y.data_ptr(); p.y_dtype = _cabi.DT_F32 if f32out else _cabi.DT_BF16; p.y_bstride = L * n; p.ldy = n; p.Lout = L
@@ -80,8 +80,26 @@ def main():
         cases.append(("s1 k7 c2", 8000, 256, 256, 7, 1, _cabi.ACT_SNAKE, True, True, False, False))
         cases.append(("s1 k11 c2", 8000, 256, 256, 11, 1, _cabi.ACT_SNAKE, True, True, False, False))
         cases.append(("conv_post k7 n32 f32", 48001, 128, 32, 7, 1, _cabi.ACT_LRELU, False, False, False, True))
+    if "--case" in sys.argv:  # L,cin,n,k,dil,act(0 none,1 lrelu,2 snake),res,stats
+        L_, ci, n_, k, d, a, r, st_ = (int(v) for v in sys.argv[sys.argv.index("--case") + 1].split(","))
+        cases = [(f"case L{L_} c{ci} n{n_} k{k} d{d} act{a} res{r} stats{st_}", L_, ci, n_, k, d, a if a else -1, bool(r), bool(st_), False, False)]
+    if "--hifi" in sys.argv:
+        cases = []
+        for k in (2, 5, 7):  # pair-form tap counts of the 32-channel stage (k = 3, 7, 11 -> 3, 5, 7 taps of 64 x 64)
+            cases.append((f"s4 pair k{k} c1(stats)", 120000, 64, 64, k, 1, _cabi.ACT_SNAKE, False, True, False, False))
+            cases.append((f"s4 pair k{k} c2(res,stats)", 120000, 64, 64, k, 1, _cabi.ACT_SNAKE, True, True, False, False))
+        for k in (3, 7, 11):
+            cases.append((f"s3 c64 k{k} c1(stats)", 120000, 64, 64, k, 1, _cabi.ACT_SNAKE, False, True, False, False))
+        cases.append(("s3 c64 k1 ident", 120000, 64, 64, 1, 1, _cabi.ACT_NONE, False, False, False, False))
+        cases.append(("s3 c64 k7 ident", 120000, 64, 64, 7, 1, _cabi.ACT_NONE, False, False, False, False))
+        cases.append(("s3 c64 k7 ident stats", 120000, 64, 64, 7, 1, _cabi.ACT_NONE, False, True, False, False))
+        cases.append(("s3 c64 k7 snake nostats", 120000, 64, 64, 7, 1, _cabi.ACT_SNAKE, False, False, False, False))
+    if "--ident" in sys.argv:
+        cases = [(f"s2 k{k} ident", 48001, 128, 128, k, 1, _cabi.ACT_NONE, False, False, False, False) for k in (1, 3, 7, 11)]
+        cases += [(f"s2 k{k} ident stats", 48001, 128, 128, k, 1, _cabi.ACT_NONE, False, True, False, False) for k in (3,)]
+        cases += [(f"s2 k{k} ss-only", 48001, 128, 128, k, 1, -1, False, False, False, False) for k in (3,)]
     for name, L, cin, n, k, dil, act, r, s, acc, f32 in cases:
-        p, keep = make(B, L, cin, n, k, dil, act, r, s, acc, f32)
+        p, keep = make(B, L, cin, n, k, dil, max(act, 0), r, s, acc, f32, ident=(act == _cabi.ACT_NONE))
         us = time_it(p, iters)
         tf = p.algo_flops / us / 1e6
         gb = (B * L * cin * 2 + B * L * n * (4 if f32 else 2) * (1 + (1 if r else 0) + (1 if acc else 0))) / 1e9
