@@ -199,7 +199,7 @@ int launch_stft(const float* hs, int B, int Lw, float* har_cl, int ld, cudaStrea
 int launch_stft_hilo(const float* hs, int B, int Lw, int rows_pad, __nv_bfloat16* har, cudaStream_t st);
 int launch_ncl_to_hilo(const float* ncl, int C, int L, int rows_pad, __nv_bfloat16* har, int B, cudaStream_t st);
 int launch_hilo_to_ncl(const __nv_bfloat16* har, int rows_pad, int C, int L, float* ncl, int B, cudaStream_t st);
-int launch_istft(const float* x_cl, int ld, int B, int frames, float* wav, cudaStream_t st);
+int launch_istft(const float* x_cl, int ld, int B, int frames, float* wav, cudaStream_t st, bool fast = false);
 int launch_tanh_inplace(float* x, int64_t n, cudaStream_t st);
 
 // sampler.cu: style sampler (StyleTransformer1d / Transformer1d denoiser + ADPM2 steps)

@@ -1273,7 +1273,7 @@ int Fwd<AT>::run(const float* asr, const float* f0, const float* nn, const float
     io.y = cp; io.y_dtype = ST2_DT_F32; io.y_bstride = (int64_t)L2 * ldh; io.ldy = ldh; io.Lout = L2;
     int rc = conv(h->conv_post, io);
     if (rc) return rc;
-    RUN(launch_istft(cp, ldh, B, L2, wav, st));
+    RUN(launch_istft(cp, ldh, B, L2, wav, st, DT<AT>::id == ST2_DT_BF16));  // bf16 path: SFU exp / sin heads
   } else if (DT<AT>::id == ST2_DT_BF16 && h->conv_post_p.w16 >= 0 && x.ld == 32 && x.L % 2 == 0) {
     // row-pair form on the tensor cores: fp32 rows of 32 columns, columns 0/1 = samples 2q / 2q+1
     const int Lp = x.L / 2, ldp = h->conv_post_p.n16;

@@ -12,33 +12,48 @@
 namespace st2 {
 
 // ------------------------------------------------------------------------- style fc
-// one warp per output row j; the style vectors of up to 64 batch items sit in smem.
+// lane = output row j (a warp owns 32 consecutive rows and streams its 32 weight rows with 16-byte loads: every
+// 128-byte line is used completely over 8 iterations), the accumulators of up to SFC_NB batch items live in
+// registers and their style vectors are read from shared memory as warp-wide broadcasts: 1 LDG + SFC_NB LDS
+// per 4 * SFC_NB FMAs, and every weight is read from HBM exactly once per group of SFC_NB items.
+constexpr int SFC_NB = 32;
 __global__ void __launch_bounds__(256)
 style_fc_kernel(const float* __restrict__ s, const float* __restrict__ W,
                 const float* __restrict__ bvec, float* __restrict__ h, int B, int style, int rows) {
-  extern __shared__ float ssm[];  // [nb][style]
-  const int b0 = blockIdx.y * 64;
-  const int nb = min(64, B - b0);
-  for (int i = threadIdx.x; i < nb * style; i += blockDim.x) ssm[i] = s[(int64_t)b0 * style + i];
+  extern __shared__ __align__(16) float ssm[];  // [SFC_NB][style]
+  const int b0 = blockIdx.y * SFC_NB;
+  const int nb = min(SFC_NB, B - b0);
+  for (int i = threadIdx.x; i < SFC_NB * style; i += blockDim.x)
+    ssm[i] = i < nb * style ? s[(int64_t)b0 * style + i] : 0.f;
   __syncthreads();
-  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int j = blockIdx.x * 8 + warp;
+  const int j = blockIdx.x * 256 + threadIdx.x;
   if (j >= rows) return;
-  const float* wr = W + (int64_t)j * style;
-  const float bj = bvec[j];
-  for (int b = 0; b < nb; ++b) {
-    float a = 0.f;
-    for (int i = lane; i < style; i += 32) a = fmaf(wr[i], ssm[b * style + i], a);
-    a = warp_sum(a);
-    if (lane == 0) h[(int64_t)(b0 + b) * rows + j] = a + bj;
+  const float4* wr = reinterpret_cast<const float4*>(W + (int64_t)j * style);
+  float acc[SFC_NB];
+#pragma unroll
+  for (int b = 0; b < SFC_NB; ++b) acc[b] = 0.f;
+  for (int i4 = 0; i4 < style / 4; ++i4) {
+    const float4 w = __ldg(wr + i4);
+#pragma unroll
+    for (int b = 0; b < SFC_NB; ++b) {
+      const float4 v = *reinterpret_cast<const float4*>(ssm + b * style + 4 * i4);
+      acc[b] = fmaf(w.x, v.x, acc[b]);
+      acc[b] = fmaf(w.y, v.y, acc[b]);
+      acc[b] = fmaf(w.z, v.z, acc[b]);
+      acc[b] = fmaf(w.w, v.w, acc[b]);
+    }
   }
+  const float bj = bvec[j];
+#pragma unroll
+  for (int b = 0; b < SFC_NB; ++b)
+    if (b < nb) h[(int64_t)(b0 + b) * rows + j] = acc[b] + bj;
 }
 
 int launch_style_fc(const float* s, const float* W, const float* bvec, float* h, int B, int style,
                     int rows, cudaStream_t st) {
-  dim3 grid(ceil_div(rows, 8), ceil_div(B, 64));
-  size_t smem = (size_t)64 * style * sizeof(float);
-  ST2_REQUIRE(smem <= 48 * 1024, "style_dim too large");
+  dim3 grid(ceil_div(rows, 256), ceil_div(B, SFC_NB));
+  size_t smem = (size_t)SFC_NB * style * sizeof(float);
+  ST2_REQUIRE(smem <= 48 * 1024 && style % 4 == 0, "style_dim must be a multiple of 4, at most 384");
   style_fc_kernel<<<grid, 256, smem, st>>>(s, W, bvec, h, B, style, rows);
   ST2_LAUNCH_OK("style_fc");
   return ST2_OK;
@@ -50,7 +65,7 @@ int launch_style_fc(const float* s, const float* W, const float* bvec, float* h,
 // combined in a fixed order.  Partials are [B][n_tiles][n_cols][2]; channel c owns columns c, c+C,
 // ... (n_cols = phases*C for a polyphase transposed conv).  Sums run in fp64 in a fixed order, so
 // the result is deterministic and independent of how the producing grid was scheduled.
-constexpr int SF_WARPS = 8;
+constexpr int SF_WARPS = 32;
 __global__ void __launch_bounds__(SF_WARPS * 32)
 stats_finalize_kernel(const float* __restrict__ partials, int n_tiles, int n_cols, int C,
                       double inv_count, const float* __restrict__ hg, int h_stride, int Cn,
@@ -65,6 +80,16 @@ stats_finalize_kernel(const float* __restrict__ partials, int n_tiles, int n_col
   if (c < C) {
     for (int col = c; col < n_cols; col += C) {
       int t = warp;
+      for (; t + 7 * SF_WARPS < n_tiles; t += 8 * SF_WARPS) {  // 8 independent loads in flight
+        float2 v[8];
+#pragma unroll
+        for (int u = 0; u < 8; ++u) v[u] = pp[(int64_t)(t + u * SF_WARPS) * n_cols + col];
+#pragma unroll
+        for (int u = 0; u < 8; ++u) {
+          s += (double)v[u].x;
+          q += (double)v[u].y;
+        }
+      }
       for (; t + 3 * SF_WARPS < n_tiles; t += 4 * SF_WARPS) {  // 4 independent loads in flight
         const float2 v0 = pp[(int64_t)t * n_cols + col];
         const float2 v1 = pp[(int64_t)(t + SF_WARPS) * n_cols + col];

@@ -184,6 +184,8 @@ stft_kernel(const float* __restrict__ hs, int Lw, int frames, float* __restrict_
     xw[n] = x[idx] * c_hann20[n];
   }
   float* o = har + ((int64_t)b * frames + f) * ld;
+  float val[24];
+  val[22] = val[23] = 0.f;
 #pragma unroll
   for (int k = 0; k <= 10; ++k) {
     float re = 0.f, im = 0.f;
@@ -194,10 +196,19 @@ stft_kernel(const float* __restrict__ hs, int Lw, int frames, float* __restrict_
       im = fmaf(xw[n], -c_sin20[m], im);
     }
     if (k == 0 || k == 10) im = 0.f;  // r2c: DC / Nyquist have Im == +0 -> angle in {0, +pi}
-    o[k] = sqrtf(re * re + im * im);
-    o[11 + k] = atan2f(im, re);
+    val[k] = sqrtf(re * re + im * im);
+    val[11 + k] = atan2f(im, re);
   }
-  for (int c = 22; c < ld; ++c) o[c] = 0.f;
+  if ((ld & 3) == 0 && ld >= 24 && (((uintptr_t)har) & 15) == 0) {  // 16-byte stores (the decoder's rows: ld 32)
+    float4* o4 = reinterpret_cast<float4*>(o);
+#pragma unroll
+    for (int i = 0; i < 6; ++i) o4[i] = make_float4(val[4 * i], val[4 * i + 1], val[4 * i + 2], val[4 * i + 3]);
+    for (int c = 6; c < ld / 4; ++c) o4[c] = make_float4(0.f, 0.f, 0.f, 0.f);
+  } else {
+#pragma unroll
+    for (int c = 0; c < 22; ++c) o[c] = val[c];
+    for (int c = 22; c < ld; ++c) o[c] = 0.f;
+  }
 }
 
 // Same transform written as bf16 (hi, lo) pairs for the tcgen05 noise convs: row = 64 bf16 =
@@ -283,34 +294,59 @@ int launch_stft(const float* hs, int B, int Lw, float* har_cl, int ld, cudaStrea
 constexpr int IS_NS = 1024;            // output samples per block
 constexpr int IS_MAXF = IS_NS / 5 + 8; // frames touching them
 
+// Block = IS_NS output samples of one item.  Phase 1, one thread per frame touching them: exp / sin heads
+// (istftnet.py:377-378), then the inverse 20-point DFT of the frame entirely in registers -- the twiddles are
+// compile-time indices into constant memory (FFMA constant operands, no table loads), and the symmetry
+// x[20 - n] = A_n + B_n, x[n] = A_n - B_n halves the arithmetic -- and the 20 windowed samples go to shared
+// memory (row stride 33: conflict-free; the frame's inputs were staged in the same row by coalesced loads).  Phase 2, one thread per output sample: overlap-add of the 4 frames
+// that cover it, division by the window envelope, trimmed to [10, 10 + Lw).  FAST = SFU exp / sin (bf16 path).
+template <bool FAST>
 __global__ void __launch_bounds__(256)
 istft_kernel(const float* __restrict__ x, int ld, int frames, float* __restrict__ wav) {
-  __shared__ float Re[IS_MAXF][11];
-  __shared__ float Im[IS_MAXF][11];
+  __shared__ float fo[IS_MAXF][33];  // row fr: first the frame's 22 head inputs, then (same thread) its 20 samples
+  __shared__ float s_w2[20];
   const int b = blockIdx.y;
   const int Lw = 5 * (frames - 1);
   const int i0 = blockIdx.x * IS_NS;
   const int i1 = min(Lw, i0 + IS_NS);
-  __shared__ float s_cos[20], s_sin[20], s_win[20];
-  if (threadIdx.x < 20) {
-    s_cos[threadIdx.x] = c_cos20[threadIdx.x];
-    s_sin[threadIdx.x] = c_sin20[threadIdx.x];
-    s_win[threadIdx.x] = c_hann20[threadIdx.x];
-  }
+  if (threadIdx.x < 20) s_w2[threadIdx.x] = c_hann20[threadIdx.x] * c_hann20[threadIdx.x];
   // frames f with 0 <= (i+10) - 5f <= 19 for some i in [i0, i1): f in [(i+10)/5 - 3, (i+10)/5]
   const int fmin = max(0, (i0 + 10) / 5 - 3);
   const int fmax = min(frames - 1, (i1 - 1 + 10) / 5);
   const int nf = fmax - fmin + 1;
-  for (int idx = threadIdx.x; idx < nf * 11; idx += blockDim.x) {
-    const int fr = idx / 11, k = idx - fr * 11;
-    const float* row = x + ((int64_t)b * frames + fmin + fr) * ld;
-    const float spec = expf(row[k]);        // istftnet.py:377
-    const float ph = sinf(row[11 + k]);     // istftnet.py:378
-    float s, c;
-    sincosf(ph, &s, &c);
-    const float ck = (k == 0 || k == 10) ? 0.05f : 0.1f;  // c_k / n_fft
-    Re[fr][k] = spec * c * ck;
-    Im[fr][k] = spec * s * ck;
+  {  // one coalesced load per row (lane = column; a thread per row would touch 32 lines per instruction)
+    const float* base = x + ((int64_t)b * frames + fmin) * ld;
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    if (lane < 22)
+      for (int r = warp; r < nf; r += 8) fo[r][lane] = __ldg(base + (int64_t)r * ld + lane);
+  }
+  __syncthreads();
+  for (int fr = threadIdx.x; fr < nf; fr += blockDim.x) {
+    float re[11], im[11];
+#pragma unroll
+    for (int k = 0; k <= 10; ++k) {
+      const float lx = fo[fr][k], px = fo[fr][11 + k];
+      const float spec = FAST ? __expf(lx) : expf(lx);   // istftnet.py:377
+      const float ph = FAST ? __sinf(px) : sinf(px);     // istftnet.py:378
+      float sn, cs;
+      if (FAST) __sincosf(ph, &sn, &cs);
+      else sincosf(ph, &sn, &cs);
+      const float ck = (k == 0 || k == 10) ? 0.05f : 0.1f;  // c_k / n_fft
+      re[k] = spec * cs * ck;
+      im[k] = spec * sn * ck;
+    }
+#pragma unroll
+    for (int n = 0; n <= 10; ++n) {
+      float A = 0.f, Bn = 0.f;
+#pragma unroll
+      for (int k = 0; k <= 10; ++k) {
+        const int mm = (k * n) % 20;
+        A = fmaf(re[k], c_cos20[mm], A);
+        Bn = fmaf(im[k], c_sin20[mm], Bn);
+      }
+      fo[fr][n] = (A - Bn) * c_hann20[n];
+      if (n >= 1 && n <= 9) fo[fr][20 - n] = (A + Bn) * c_hann20[20 - n];
+    }
   }
   __syncthreads();
   for (int i = i0 + threadIdx.x; i < i1; i += blockDim.x) {
@@ -321,29 +357,21 @@ istft_kernel(const float* __restrict__ x, int ld, int frames, float* __restrict_
     for (int j = 0; j < 4; ++j) {
       const int f = fq - j, n = r + 5 * j;
       if (f < 0 || f >= frames) continue;
-      const int fr = f - fmin;
-      float a = 0.f;
-#pragma unroll
-      for (int k = 0; k <= 10; ++k) {
-        const int mm = (k * n) % 20;
-        a = fmaf(Re[fr][k], s_cos[mm], a);
-        a = fmaf(-Im[fr][k], s_sin[mm], a);
-      }
-      const float w = s_win[n];
-      val = fmaf(a, w, val);
-      env = fmaf(w, w, env);
+      val += fo[f - fmin][n];
+      env += s_w2[n];
     }
     wav[(int64_t)b * Lw + i] = val / env;
   }
 }
 
-int launch_istft(const float* x_cl, int ld, int B, int frames, float* wav, cudaStream_t st) {
+int launch_istft(const float* x_cl, int ld, int B, int frames, float* wav, cudaStream_t st, bool fast) {
   int rc = ensure_tables();
   if (rc) return rc;
   ST2_REQUIRE(frames >= 5 && ld >= 22, "istft: shape");
   const int Lw = 5 * (frames - 1);
   dim3 grid(ceil_div(Lw, IS_NS), B);
-  istft_kernel<<<grid, 256, 0, st>>>(x_cl, ld, frames, wav);
+  if (fast) istft_kernel<true><<<grid, 256, 0, st>>>(x_cl, ld, frames, wav);
+  else istft_kernel<false><<<grid, 256, 0, st>>>(x_cl, ld, frames, wav);
   ST2_LAUNCH_OK("istft");
   return ST2_OK;
 }
