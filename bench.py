@@ -665,6 +665,10 @@ def run_ours(args):
         cpu = {"value": round(v, 4), "unit": UNIT, "cores": threads, "kind": "port",
                "sample": f"1 utterance x {T} frames of the workload, fp32, torch CPU, median of 2 "
                          f"({ms_cpu:.0f} ms per forward)"}
+        if T <= 800:  # SURVEY 8d also asks for the single-thread figure (one more forward, a few seconds)
+            v1, ms1, _ = _oracle_cpu_decoder(kind, 1, T, steps=1, warmup=0, threads=1)
+            cpu["value_1_thread"] = round(v1, 4)
+            cpu["sample"] += f"; 1 thread: {ms1:.0f} ms"
     ws_bytes = int(_cabi.lib.st2_decoder_workspace_bytes(dec._native[local], B, T,
                                                          _cabi.PREC_BF16 if prec == "bf16" else _cabi.PREC_FP32))
     line = {

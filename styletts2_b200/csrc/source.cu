@@ -109,8 +109,8 @@ har_source_kernel(const float* __restrict__ f0, const float* __restrict__ phase,
                   const uint64_t* __restrict__ seed_dev) {
   if (seed_dev) seed = *seed_dev;
   const int b = blockIdx.y;
-  const int64_t Lw = (int64_t)T * spf;
-  const int64_t n = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  const int Lw = T * spf;  // < 2^31 (checked at launch): 32-bit index arithmetic, no 64-bit division
+  const int n = blockIdx.x * blockDim.x + threadIdx.x;
   if (n >= Lw) return;
   float src = fmaf(ratio, (float)n + 0.5f, -0.5f);
   src = src < 0.f ? 0.f : src;
@@ -119,7 +119,7 @@ har_source_kernel(const float* __restrict__ f0, const float* __restrict__ phase,
   const int i1 = min(i0 + 1, T - 1);
   const float l1 = __fsub_rn(src, (float)i0);
   const float l0 = __fsub_rn(1.f, l1);
-  const float fv = f0[(int64_t)b * T + (int)(n / spf)];
+  const float fv = f0[(int64_t)b * T + n / spf];
   const float uv = fv > 10.f ? 1.f : 0.f;                         // voiced_threshold 10 (istftnet.py:312)
   const float namp = uv > 0.f ? 0.003f : __fdiv_rn(0.1f, 3.f);   // istftnet.py:240
   float z[12];
@@ -145,10 +145,14 @@ har_source_kernel(const float* __restrict__ f0, const float* __restrict__ phase,
   for (int h = 0; h < NH; ++h) {
     const float p0 = pb[(int64_t)h * T + i0], p1 = pb[(int64_t)h * T + i1];
     const float ph = fmaf(l0, p0, __fmul_rn(l1, p1));
-    // sin of an fp32 phase that reaches 1e5 rad: reduce mod 2*pi in fp64 (exact to 1e-11), then MUFU.SIN on
-    // [-pi, pi] (abs error < 4e-7); libdevice sinf takes its slow Payne-Hanek path above 1e5 rad
-    const double rev = (double)ph * 0.15915494309189535;
-    const float red = (float)((rev - rint(rev)) * 6.283185307179586);
+    // sin of an fp32 phase that reaches 1e5 .. 1e6 rad (libdevice sinf would take its slow Payne-Hanek path):
+    // three-term Cody-Waite reduction, 2*pi = 6.28125 + 1.9350051879882812e-3 + 3.019916e-7.  The first fma is
+    // exact (ph and k * 6.28125 are multiples of 2^-5 or coarser and the difference is < 8), the other two round
+    // at 4e-7; then MUFU.SIN on [-pi, pi] (abs error < 4e-7).
+    const float kq = rintf(ph * 0.15915494309189535f);
+    float red = fmaf(-kq, 6.28125f, ph);
+    red = fmaf(-kq, 1.9350051879882812e-3f, red);
+    red = fmaf(-kq, 3.019916050561733e-7f, red);
     const float sv = __fmul_rn(__sinf(red), 0.1f);  // sine_amp
     const float sw = __fadd_rn(__fmul_rn(sv, uv), __fmul_rn(namp, z[h]));
     acc = fmaf(lin_w[h], sw, acc);
@@ -160,6 +164,7 @@ int launch_har_source(const float* f0, const float* phase, const float* noise, u
                       const float* lin_w9, float lin_b, int B, int T, int spf, float* out,
                       cudaStream_t st, int64_t item0, const uint64_t* seed_dev) {
   const int64_t Lw = (int64_t)T * spf;
+  ST2_REQUIRE(Lw < (1ll << 31) - 256, "har_source: T * samples_per_frame must fit 31 bits");
   dim3 grid((unsigned)((Lw + 255) / 256), B);
   const float ratio = (float)(1.0 / (double)spf);
   har_source_kernel<<<grid, 256, 0, st>>>(f0, phase, noise, seed, lin_w9, lin_b, T, spf, ratio, out, item0, seed_dev);
