@@ -619,8 +619,8 @@ def run_ours(args):
     # the package's host-to-host loop: uploads / downloads of neighbouring steps overlap the forward
     from styletts2_b200.pipeline import HostPipeline
     pipe = HostPipeline(dec, dev, depth=2)
-    for _ in range(2):
-        pipe.submit(host, wav_host)
+    for _ in range(max(3, args.warmup) + 1):  # warm-up: the caching allocator needs a few rounds until the waveform
+        pipe.submit(host, wav_host)           # blocks handed to the download stream are recycled without cudaMalloc
     pipe.wait()
     barrier()
     e0.record()
