@@ -40,55 +40,76 @@ __device__ __forceinline__ void st4_f<__nv_bfloat16>(__nv_bfloat16* p, float4 v)
 }
 
 // ------------------------------------------------------------------ small dense layers (fp32)
-// y[r][o] = act(bias[o] + sum_i W[o][i] * (x[r][i] + xb[i])), one warp per output feature and ROWS rows;
+// y[r][o] = act(bias[o] + sum_i W[o][i] * (x[r][i] + xb[i])).  A warp owns OUTS output features x ROWS rows
+// (register block: OUTS + ROWS 16-byte loads per 4 * OUTS * ROWS FMAs), lanes split the reduction.
 // VEC: 16-byte loads (I, ldx multiples of 4, 16-byte aligned bases)
-template <int ROWS, bool VEC>
+template <int ROWS, int OUTS, bool VEC>
 __global__ void __launch_bounds__(256)
 small_linear_kernel(const float* __restrict__ x, int ldx, const float* __restrict__ xb, const float* __restrict__ W,
                     const float* __restrict__ bias, float* __restrict__ y, int ldy, int R, int I, int O, int act) {
-  const int o = blockIdx.x * 8 + (threadIdx.x >> 5), lane = threadIdx.x & 31;
+  const int o0 = (blockIdx.x * 8 + (threadIdx.x >> 5)) * OUTS, lane = threadIdx.x & 31;
   const int r0 = blockIdx.y * ROWS;
-  if (o >= O) return;
-  float acc[ROWS];
+  if (o0 >= O) return;
+  float acc[OUTS][ROWS];
 #pragma unroll
-  for (int j = 0; j < ROWS; ++j) acc[j] = 0.f;
-  const float* wr = W + (int64_t)o * I;
+  for (int u = 0; u < OUTS; ++u)
+#pragma unroll
+    for (int j = 0; j < ROWS; ++j) acc[u][j] = 0.f;
+  const float* wr[OUTS];
+#pragma unroll
+  for (int u = 0; u < OUTS; ++u) wr[u] = W + (int64_t)min(o0 + u, O - 1) * I;
   if (VEC) {
     for (int i = lane * 4; i < I; i += 128) {
-      const float4 w = __ldg(reinterpret_cast<const float4*>(wr + i));
       float4 add = make_float4(0.f, 0.f, 0.f, 0.f);
       if (xb) add = __ldg(reinterpret_cast<const float4*>(xb + i));
+      float4 w[OUTS];
+#pragma unroll
+      for (int u = 0; u < OUTS; ++u) w[u] = __ldg(reinterpret_cast<const float4*>(wr[u] + i));
 #pragma unroll
       for (int j = 0; j < ROWS; ++j) {
         const int r = min(r0 + j, R - 1);
-        const float4 v = __ldg(reinterpret_cast<const float4*>(x + (int64_t)r * ldx + i));
-        acc[j] = fmaf(w.x, v.x + add.x, acc[j]);
-        acc[j] = fmaf(w.y, v.y + add.y, acc[j]);
-        acc[j] = fmaf(w.z, v.z + add.z, acc[j]);
-        acc[j] = fmaf(w.w, v.w + add.w, acc[j]);
+        float4 v = __ldg(reinterpret_cast<const float4*>(x + (int64_t)r * ldx + i));
+        v.x += add.x; v.y += add.y; v.z += add.z; v.w += add.w;
+#pragma unroll
+        for (int u = 0; u < OUTS; ++u) {
+          acc[u][j] = fmaf(w[u].x, v.x, acc[u][j]);
+          acc[u][j] = fmaf(w[u].y, v.y, acc[u][j]);
+          acc[u][j] = fmaf(w[u].z, v.z, acc[u][j]);
+          acc[u][j] = fmaf(w[u].w, v.w, acc[u][j]);
+        }
       }
     }
   } else {
     for (int i = lane; i < I; i += 32) {
-      const float w = __ldg(wr + i);
       const float add = xb ? __ldg(xb + i) : 0.f;
+      float w[OUTS];
+#pragma unroll
+      for (int u = 0; u < OUTS; ++u) w[u] = __ldg(wr[u] + i);
 #pragma unroll
       for (int j = 0; j < ROWS; ++j) {
         const int r = min(r0 + j, R - 1);
-        acc[j] = fmaf(w, __ldg(x + (int64_t)r * ldx + i) + add, acc[j]);
+        const float v = __ldg(x + (int64_t)r * ldx + i) + add;
+#pragma unroll
+        for (int u = 0; u < OUTS; ++u) acc[u][j] = fmaf(w[u], v, acc[u][j]);
       }
     }
   }
 #pragma unroll
-  for (int j = 0; j < ROWS; ++j) acc[j] = warp_sum(acc[j]);
-  if (lane == 0) {
-    const float b = bias ? bias[o] : 0.f;
+  for (int u = 0; u < OUTS; ++u)
 #pragma unroll
-    for (int j = 0; j < ROWS; ++j)
-      if (r0 + j < R) {
-        const float v = acc[j] + b;
-        y[(int64_t)(r0 + j) * ldy + o] = act ? gelu_erf(v) : v;
-      }
+    for (int j = 0; j < ROWS; ++j) acc[u][j] = warp_sum(acc[u][j]);
+  if (lane == 0) {
+#pragma unroll
+    for (int u = 0; u < OUTS; ++u) {
+      if (o0 + u >= O) continue;
+      const float b = bias ? bias[o0 + u] : 0.f;
+#pragma unroll
+      for (int j = 0; j < ROWS; ++j)
+        if (r0 + j < R) {
+          const float v = acc[u][j] + b;
+          y[(int64_t)(r0 + j) * ldy + o0 + u] = act ? gelu_erf(v) : v;
+        }
+    }
   }
 }
 int launch_small_linear(const float* x, int ldx, const float* xb, const float* W, const float* bias, float* y, int ldy,
@@ -96,12 +117,12 @@ int launch_small_linear(const float* x, int ldx, const float* xb, const float* W
   const bool vec = I % 4 == 0 && ldx % 4 == 0 && (((uintptr_t)x | (uintptr_t)W | (uintptr_t)xb) & 15) == 0;
   if (R == 1) {
     dim3 grid(ceil_div(O, 8), 1);
-    if (vec) small_linear_kernel<1, true><<<grid, 256, 0, st>>>(x, ldx, xb, W, bias, y, ldy, R, I, O, gelu);
-    else small_linear_kernel<1, false><<<grid, 256, 0, st>>>(x, ldx, xb, W, bias, y, ldy, R, I, O, gelu);
+    if (vec) small_linear_kernel<1, 1, true><<<grid, 256, 0, st>>>(x, ldx, xb, W, bias, y, ldy, R, I, O, gelu);
+    else small_linear_kernel<1, 1, false><<<grid, 256, 0, st>>>(x, ldx, xb, W, bias, y, ldy, R, I, O, gelu);
   } else {
-    dim3 grid(ceil_div(O, 8), ceil_div(R, 8));
-    if (vec) small_linear_kernel<8, true><<<grid, 256, 0, st>>>(x, ldx, xb, W, bias, y, ldy, R, I, O, gelu);
-    else small_linear_kernel<8, false><<<grid, 256, 0, st>>>(x, ldx, xb, W, bias, y, ldy, R, I, O, gelu);
+    dim3 grid(ceil_div(O, 8 * 4), ceil_div(R, 8));
+    if (vec) small_linear_kernel<8, 4, true><<<grid, 256, 0, st>>>(x, ldx, xb, W, bias, y, ldy, R, I, O, gelu);
+    else small_linear_kernel<8, 4, false><<<grid, 256, 0, st>>>(x, ldx, xb, W, bias, y, ldy, R, I, O, gelu);
   }
   ST2_LAUNCH_OK("small_linear");
   return ST2_OK;
