@@ -451,6 +451,122 @@ def run_sampler(args):
     return 0
 
 
+def run_chain(args):
+    """BASELINE config 2 taken literally: "multispeaker decoder (style s from ADPM2 diffusion sampler, 5 steps) batch
+    64 x 800 frames".  One step = sampler(noise, embedding, features) -> s_pred; F0Ntrain(en, s_pred[:, 128:]) ->
+    F0, N; Decoder(asr, F0, N, s_pred[:, :128]) -> waveform (Demo/Inference_LibriTTS.ipynb cell 16 from the
+    sampler call on), all three on this package's kernels, B=64 items, 128 text tokens, 400 prosody frames."""
+    import torch
+    import torch.distributed as dist
+    import styletts2_b200 as st2
+    import synthetic as synth
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a CUDA device: styletts2_b200 has no CPU fallback")
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+    B, T, n, steps = 64, 800, SAMPLER_SHAPE["n"], SAMPLER_SHAPE["steps"]
+    smp = st2.StyleSampler(**synth.SAMPLER_CFG)
+    smp.load_state_dict(synth.synth_sampler_state_dict(synth.SAMPLER_CFG, seed=0), strict=True)
+    f0n = st2.F0NPredictor(**synth.F0N_CFG)
+    f0n.load_state_dict(synth.synth_f0n_state_dict(synth.F0N_CFG, seed=0), strict=True)
+    dcfg = synth.ISTFTNET_CFG
+    dec = st2.IstftnetDecoder(**{k: v for k, v in dcfg.items() if k != "kind"})
+    dec.load_state_dict(synth.synth_state_dict(dcfg, seed=0), strict=True)
+    smp, f0n, dec = smp.to(dev).eval(), f0n.to(dev).eval(), dec.to(dev).eval()
+    for m in (smp, f0n, dec):
+        m.precision = args.precision
+    dec.cuda_graphs = not args.no_graphs
+    si = synth.synth_sampler_inputs(synth.SAMPLER_CFG, B, n, steps, seed=4321 + rank)
+    di = synth.synth_inputs(dcfg, B, T, seed=1234 + rank, with_noise=False)
+    fi = synth.synth_f0n_inputs(synth.F0N_CFG, B, T // 2, seed=99 + rank)
+    host = {"noise": si["noise"], "embedding": si["embedding"], "features": si["features"], "en": fi["x"], "asr": di["asr"]}
+    host = {k: v.contiguous().pin_memory() for k, v in host.items()}
+    d = {k: v.to(dev) for k, v in host.items()}
+    audio_s = B * T * 300 / 24000.0
+
+    def step(a, i):
+        s_pred = smp(a["noise"], num_steps=steps, embedding=a["embedding"], features=a["features"], seed=i,
+                     item_offset=rank * B).squeeze(1)
+        F0, N = f0n.F0Ntrain(a["en"], s_pred[:, 128:].contiguous())
+        return dec(a["asr"], F0, N, s_pred[:, :128].contiguous())
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def max_over_ranks(ms):
+        if world == 1:
+            return ms
+        t = torch.tensor([ms], device=dev, dtype=torch.float64)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+
+    for i in range(max(3, args.warmup)):
+        wav = step(d, i)
+    barrier()
+    launches = smp.last_launches + f0n.last_launches + dec.last_launches
+    sampler = ClockSampler(local)
+    if sampler.ok:
+        sampler.start()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    barrier()
+    e0.record()
+    for i in range(args.steps):
+        wav = step(d, 100 + i)
+    e1.record()
+    barrier()
+    clocks = sampler.stop()
+    ms_step = max_over_ranks(e0.elapsed_time(e1)) / args.steps
+    assert wav.shape == (B, 1, 300 * T) and torch.isfinite(wav).all()
+    wav_host = torch.empty(B, 1, 300 * T).pin_memory()
+
+    def e2e_step(i):
+        a = {k: host[k].to(dev, non_blocking=True) for k in host}
+        wav_host.copy_(step(a, 200 + i), non_blocking=True)
+
+    for i in range(3):
+        e2e_step(i)
+    barrier()
+    e0.record()
+    for i in range(args.steps):
+        e2e_step(i)
+    e1.record()
+    barrier()
+    ms_e2e = max_over_ranks(e0.elapsed_time(e1)) / args.steps
+    if rank == 0:
+        fl = MFLOP_PER_FRAME["istftnet"] * 1e6 * B * T + sampler_flops(synth.SAMPLER_CFG, B, n, steps)
+        tf = fl / (ms_step * 1e-3) / 1e12
+        line = {
+            "metric": METRIC, "value": round(world * audio_s / (ms_step * 1e-3), 2), "unit": UNIT, "n_gpus": world,
+            "steps": args.steps, "warmup": max(3, args.warmup), "ms_per_step": round(ms_step, 3), "higher_is_better": True,
+            "scaling": "weak", "vs_baseline": None, "dtype": args.precision, "data": "synthetic",
+            "config": {"workload": "BASELINE config 2, literal: ADPM2 style sampler (5 steps, 128 tokens) -> F0Ntrain -> iSTFTNet "
+                                   "decoder, B=64 x 800 frames, chained on the device",
+                       "batch_per_gpu": B, "mel_frames": T, "tokens": n, "diffusion_steps": steps,
+                       "weights": "random-init (synthetic.py, seed 0)", "noise": "in-kernel Philox",
+                       "l2": "every step streams > 6 GB through HBM (>> 126 MB L2)", "cuda_graph": bool(dec.cuda_graphs),
+                       "parallelism": f"dp{world} (independent batches, no collective)"},
+            "e2e": {"value": round(world * audio_s / (ms_e2e * 1e-3), 2), "unit": UNIT, "ms_per_step": round(ms_e2e, 3),
+                    "h2d_bytes_per_step": sum(v.numel() * 4 for v in host.values()), "d2h_bytes_per_step": wav_host.numel() * 4,
+                    "api": "StyleSampler.forward -> F0NPredictor.F0Ntrain -> IstftnetDecoder.forward, pinned host in/out"},
+            "gpu_launches": int(launches * args.steps),
+            "roofline": {"bound": "tensor", "achieved": round(tf, 2), "peak": _peaks()["tf_sustained"], "unit": "TFLOP/s",
+                         "frac": round(tf / _peaks()["tf_sustained"], 4), "traffic": None,
+                         "note": "whole chain (decoder + sampler algorithmic FLOPs; F0Ntrain not counted)"},
+            "cpu_baseline": None, "clocks": clocks,
+        }
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+    return 0
+
+
 def _oracle_cpu_sampler(B, n, steps, reps, warm):
     import torch
     import synthetic as synth
@@ -702,7 +818,7 @@ def main():
     ap.add_argument("--steps", type=int, default=10)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--workload", default="c2", choices=sorted(WORKLOADS) + ["f0n", "sampler"])
+    ap.add_argument("--workload", default="c2", choices=sorted(WORKLOADS) + ["f0n", "sampler", "chain"])
     ap.add_argument("--precision", default="bf16", choices=["bf16", "fp32"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-graphs", action="store_true", help="launch every kernel eagerly instead of replaying a CUDA graph")
@@ -718,6 +834,8 @@ def main():
         return subprocess.call(cmd)
     if args.workload == "sampler":
         return run_sampler(args)
+    if args.workload == "chain":
+        return run_chain(args)
     return run_f0n(args) if args.workload == "f0n" else run_ours(args)
 
 
