@@ -48,7 +48,8 @@ constexpr int UM_TM = 256;      // output rows per tile
 constexpr int UM_NACC = 2;      // 128-row accumulators per tile
 constexpr int UM_CK = 64;       // channels per A stage
 constexpr int UM_MAX_A = 4;     // A ring stages (3 when the halo is wide)
-constexpr int UM_W_STAGES = 3;
+constexpr int UM_W_STAGES = 3;  // default depth of the weight ring (UmLayout::nw)
+constexpr int UM_MAX_W = 8;
 constexpr int UM_MAX_HALO = 50; // (k-1)*dil of the widest resblock conv (k 11, d 5)
 constexpr int UM_THREADS = 448;
 constexpr int UM_PROD_WARP0 = 6, UM_PROD_THREADS = 256;
@@ -60,8 +61,11 @@ struct UmLayout {
   int n_tile;         // GEMM columns per tile (128 / 64 / 32)
   int a_bytes;        // bytes per A stage (rows x 128 B, multiple of 1024)
   int na;             // A stages in use
+  int nw;             // weight stages in use
   int dist;           // prefetch distance of the producers, in chunks (na - 2)
-  int dbg;            // ST2_UMMA_DBG experiments (bit 0: reuse the weight stages without reloading; wrong results)
+  int dbg;            // ST2_UMMA_DBG timing experiments, all with wrong results: 1 reuse the weight stages without
+                      // reloading, 2 producers skip the prologue arithmetic, 4 epilogue skips the statistics pass,
+                      // 8 epilogue skips TMEM read / staging / store, 16 no conv MMAs are issued (barriers only)
   int w_bytes;        // bytes per weight stage (= 8 * n_tile * 16)
   int out_row;        // bytes per output row segment (n_tile * element size), multiple of 128
   int n_res, n_acc;   // extra 64-channel chunks per tile: residual rows, y_old rows
@@ -78,7 +82,7 @@ struct UmLayout {
 struct UmMisc {
   uint64_t a_full[UM_MAX_A], a_empty[UM_MAX_A];
   uint64_t raw_full[UM_MAX_A];  // raw activation tile of the stage has landed (TMA transaction bytes)
-  uint64_t w_full[UM_W_STAGES], w_empty[UM_W_STAGES];
+  uint64_t w_full[UM_MAX_W], w_empty[UM_MAX_W];
   uint64_t t_full[2], t_empty[2];
   uint32_t tmem_base, pad_;
   // bias through the tensor core: one K=16 step with A = ones_a (every row (1, 1, 0, ...)) and
@@ -518,6 +522,10 @@ __device__ __forceinline__ void um_produce(const St2ConvParams& p, const UmLayou
       }
       mbar_wait(&misc->raw_full[q.stage], q.ph, 6);
     }
+    if (lay.dbg & 2) {
+      mbar_arrive(&misc->a_full[q.stage]);
+      return;
+    }
     const int row0 = q.t0 - p.pad + rbase;
     const int lo = -row0, hi = min(r_tot - rbase, p.Lin - row0), tot = r_tot - rbase;
     float sc[8], sh[8], wsc[8], wsh[8], hia[8];
@@ -730,6 +738,12 @@ __device__ __forceinline__ void um_epilogue(const St2ConvParams& p, const UmLayo
     // this tile's bias MMA has completed: its operand slot can take the next bias; the t_empty arrive
     // below (after the fence) hands it to the MMA warp together with the TMEM buffer
     if (et < n_tile) misc->bias_b[tb][et] = um_bias_split(bias2);
+    if (lay.dbg & 8) {
+      fence_proxy_async_smem();
+      tc_fence_before();
+      mbar_arrive(&misc->t_empty[tb]);
+      continue;
+    }
 #pragma unroll 1
     for (int acc = 0; acc < UM_NACC; ++acc) {
       // the staging tile is free once the previous TMA store has read it (issued by thread 0) and
@@ -770,7 +784,7 @@ __device__ __forceinline__ void um_epilogue(const St2ConvParams& p, const UmLayo
           tma_store_3d(ymap, stg + (uint32_t)sgi * 16384u, tl.nt * n_tile + sgi * seg_cols, row0, tl.b);
         bulk_commit();
       }
-      if (!OUT_F32 && p.stats) {
+      if (!OUT_F32 && p.stats && !(lay.dbg & 4)) {
         const int r1 = p.Lout - row0 - grp * ncp;  // valid rows of this thread's row group
         if (r1 >= ncp) {
           // rows grp*ncp + 8 m + i sit 1024 m bytes after col_addr[i] (the swizzle repeats every 8 rows)
@@ -842,7 +856,7 @@ __global__ void __launch_bounds__(UM_THREADS, 1) conv_umma_kernel(const St2ConvP
       mbar_init(&misc->a_empty[i], 1);
       mbar_init(&misc->raw_full[i], 1);
     }
-    for (int i = 0; i < UM_W_STAGES; ++i) {
+    for (int i = 0; i < lay.nw; ++i) {
       mbar_init(&misc->w_full[i], 1);
       mbar_init(&misc->w_empty[i], 1);
     }
@@ -894,6 +908,7 @@ __global__ void __launch_bounds__(UM_THREADS, 1) conv_umma_kernel(const St2ConvP
     const uint32_t a_kstep = 2u, w_kstep = 2u * (uint32_t)lay.n_tile;  // in 16-byte units
     const int nct = nchunks + lay.n_res + lay.n_acc;
     const uint32_t leader = elect_one() ? 1u : 0u;
+    const uint32_t mma_on = (lay.dbg & 16) ? 0u : leader;
     int as = 0, ws = 0;
     uint32_t aph = 0, wph = 0, t_it = 0;
     // The tensor-core queue is shallow, so everything between two groups of MMAs is on the critical
@@ -923,7 +938,7 @@ __global__ void __launch_bounds__(UM_THREADS, 1) conv_umma_kernel(const St2ConvP
           tc_fence_after();
           int wn = ws + 1;
           uint32_t wnph = wph;
-          if (wn == UM_W_STAGES) { wn = 0; wnph ^= 1u; }
+          if (wn == lay.nw) { wn = 0; wnph ^= 1u; }
           w_ready = mbar_try(&misc->w_full[wn], wnph);  // consumed after the MMAs below
           const uint32_t shift = (uint32_t)j * dil;  // rows
           // the swizzle is a function of the absolute smem address: a start that is not a multiple of
@@ -944,7 +959,7 @@ __global__ void __launch_bounds__(UM_THREADS, 1) conv_umma_kernel(const St2ConvP
 #pragma unroll
             for (int ks = 0; ks < UM_CK / 16; ++ks)
               umma_bf16_if(d0 + (uint32_t)(acc * lay.n_tile) + dcol, ad + (uint64_t)(acc * 1024 + ks * a_kstep),
-                           bd + (uint64_t)(ks * w_kstep), idesc, 1u, leader);
+                           bd + (uint64_t)(ks * w_kstep), idesc, 1u, mma_on);
           }
           umma_commit_if(&misc->w_empty[ws], leader);
           ws = wn;
@@ -974,13 +989,13 @@ __global__ void __launch_bounds__(UM_THREADS, 1) conv_umma_kernel(const St2ConvP
                                  : lay.ident_acc + (int64_t)(e - lay.n_res) * lay.w_bytes;
           }
           mbar_wait(&misc->w_empty[ws], wph ^ 1u, 4);
-          if ((lay.dbg & 1) && (tile != (int)blockIdx.x || s >= UM_W_STAGES)) {
+          if ((lay.dbg & 1) && (tile != (int)blockIdx.x || s >= lay.nw)) {
             mbar_arrive(&misc->w_full[ws]);  // timing experiment only
           } else {
             mbar_arrive_expect_tx(&misc->w_full[ws], (uint32_t)lay.w_bytes);
             bulk_g2s(wsm + (size_t)ws * lay.w_bytes, blob, (uint32_t)lay.w_bytes, &misc->w_full[ws]);
           }
-          if (++ws == UM_W_STAGES) { ws = 0; wph ^= 1u; }
+          if (++ws == lay.nw) { ws = 0; wph ^= 1u; }
         }
       }
     }
@@ -1078,7 +1093,13 @@ static int um_layout(const St2ConvParams& p, int dev, UmLayout& lay) {
   ST2_REQUIRE(lay.out_row % 128 == 0, "conv_umma: an output row segment must be a multiple of 128 bytes");
   const int stg_bytes = (lay.out_row / 128) * 16384;
   const int misc_bytes = (int)round_up((int64_t)sizeof(UmMisc), 128);
-  const int fixed = UM_W_STAGES * lay.w_bytes + stg_bytes + misc_bytes;
+  lay.nw = UM_W_STAGES;
+  if (const char* e = getenv("ST2_UMMA_WST")) {  // A/B switch
+    lay.nw = atoi(e);
+    if (lay.nw < 2) lay.nw = 2;
+    if (lay.nw > UM_MAX_W) lay.nw = UM_MAX_W;
+  }
+  const int fixed = lay.nw * lay.w_bytes + stg_bytes + misc_bytes;
   int na = (UM_SMEM_LIMIT - fixed) / lay.a_bytes;
   if (na > UM_MAX_A) na = UM_MAX_A;
   ST2_REQUIRE(na >= 3, "conv_umma: tile does not fit shared memory");
@@ -1095,7 +1116,7 @@ static int um_layout(const St2ConvParams& p, int dev, UmLayout& lay) {
   if (const char* e = getenv("ST2_UMMA_DBG")) lay.dbg = atoi(e);
   lay.off_a = (uint32_t)stg_bytes;
   lay.off_w = lay.off_a + (uint32_t)(na * lay.a_bytes);
-  lay.off_misc = lay.off_w + (uint32_t)(UM_W_STAGES * lay.w_bytes);
+  lay.off_misc = lay.off_w + (uint32_t)(lay.nw * lay.w_bytes);
   lay.total = lay.off_misc + (uint32_t)misc_bytes;
   lay.idesc = um_idesc(lay.n_tile);
   lay.idesc64 = um_idesc(64);
