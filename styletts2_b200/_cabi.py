@@ -121,7 +121,7 @@ class St2Error(RuntimeError):
 def _load():
     if not os.path.exists(LIB_PATH):
         raise ImportError(
-            f"{LIB_PATH} is missing: build it with `python -m styletts2_b200.build` "
+            f"{LIB_PATH} is missing: build it with `python styletts2_b200/build.py` "
             "(nvcc, sm_100a).  styletts2_b200 has no CPU or PyTorch fallback.")
     lib = C.CDLL(LIB_PATH)
     for name, (res, args) in SYMBOLS.items():

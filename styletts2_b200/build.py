@@ -1,4 +1,4 @@
-"""Build libst2dec.so in-tree: ``python -m styletts2_b200.build`` (nvcc, sm_100a, -lineinfo)."""
+"""Build libst2dec.so in-tree: ``python styletts2_b200/build.py`` (nvcc, sm_100a, -lineinfo)."""
 from __future__ import annotations
 
 import os
