@@ -62,6 +62,12 @@ struct UmLayout {
   int a_bytes;        // bytes per A stage (rows x 128 B, multiple of 1024)
   int na;             // A stages in use
   int nw;             // weight stages in use
+  int pair;           // 1 = two CTAs of a cluster run one M = 256 cta_group::2 MMA per step: each CTA feeds its own
+                      // 256-row tile (two 128-row accumulators) and HALF of the weight columns, so the weight stream
+                      // per SM and the B-operand reads of shared memory halve.  Same N tile in both, any (item, t0).
+  int n_bt;           // pair mode: B * n_ttiles
+  int total_ptiles;   // pair mode: n_ntiles * ceil(n_bt / 2)
+  uint32_t idesc_pair;  // M = 256
   int dist;           // prefetch distance of the producers, in chunks (na - 2)
   int dbg;            // ST2_UMMA_DBG timing experiments, all with wrong results: 1 reuse the weight stages without
                       // reloading, 2 producers skip the prologue arithmetic, 4 epilogue skips the statistics pass,
@@ -84,6 +90,7 @@ struct UmMisc {
   uint64_t raw_full[UM_MAX_A];  // raw activation tile of the stage has landed (TMA transaction bytes)
   uint64_t w_full[UM_MAX_W], w_empty[UM_MAX_W];
   uint64_t t_full[2], t_empty[2];
+  uint64_t peer_a_full[UM_MAX_A], peer_w_full[UM_MAX_W];  // pair mode, leader CTA: the peer's stage is ready
   uint32_t tmem_base, pad_;
   // bias through the tensor core: one K=16 step with A = ones_a (every row (1, 1, 0, ...)) and
   // B = bias_b[tb] (per column (hi, lo, 0, ...) bf16 split of the fp32 bias), issued first for each tile
@@ -231,6 +238,36 @@ __device__ __forceinline__ void umma_bf16_if(uint32_t tmem_d, uint64_t adesc, ui
       "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate), "r"(on)
       : "memory");
 }
+// ---- CTA-pair variants (cta_group::2): issued by the leader CTA of a 2-CTA cluster; the commit arrives on the
+// barrier at the same shared-memory offset in both CTAs
+__device__ __forceinline__ void umma2_commit_if(uint64_t* bar, uint32_t on) {
+  asm volatile(
+      "{ .reg .pred q; .reg .b16 m; setp.ne.b32 q, %1, 0; mov.b16 m, 3;\n"
+      "@q tcgen05.commit.cta_group::2.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], m; }" ::"r"(
+          smem_u32(bar)),
+      "r"(on)
+      : "memory");
+}
+__device__ __forceinline__ void umma2_bf16_if(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc, uint32_t idesc,
+                                              uint32_t accumulate, uint32_t on) {
+  asm volatile(
+      "{ .reg .pred p, q; setp.ne.b32 p, %4, 0; setp.ne.b32 q, %5, 0;\n"
+      "@q tcgen05.mma.cta_group::2.kind::f16 [%0], %1, %2, %3, p; }" ::"r"(tmem_d),
+      "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate), "r"(on)
+      : "memory");
+}
+__device__ __forceinline__ void cluster_sync_all() {
+  asm volatile("barrier.cluster.arrive.release.aligned;\n\tbarrier.cluster.wait.acquire.aligned;" ::: "memory");
+}
+// shared::cluster address of `addr` (a shared::cta address of this CTA) in CTA `cta` of the cluster
+__device__ __forceinline__ uint32_t mapa_cta(uint32_t addr, uint32_t cta) {
+  uint32_t r;
+  asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(r) : "r"(addr), "r"(cta));
+  return r;
+}
+__device__ __forceinline__ void mbar_arrive_cluster(uint32_t cluster_addr) {
+  asm volatile("mbarrier.arrive.release.cluster.shared::cluster.b64 _, [%0];" ::"r"(cluster_addr) : "memory");
+}
 // one non-blocking probe of an mbarrier phase
 __device__ __forceinline__ uint32_t mbar_try(uint64_t* bar, uint32_t parity) {
   uint32_t done;
@@ -255,8 +292,8 @@ __device__ __forceinline__ uint64_t umma_desc(uint32_t saddr, uint32_t lbo_bytes
   return d;
 }
 // instruction descriptor (cute::UMMA::InstrDescriptor): D fp32, A/B bf16, both K-major, M 128, N n_tile
-static inline uint32_t um_idesc(int n_tile) {
-  return (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(n_tile >> 3) << 17) | ((uint32_t)(128 >> 4) << 24);
+static inline uint32_t um_idesc(int n_tile, int m = 128) {
+  return (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(n_tile >> 3) << 17) | ((uint32_t)(m >> 4) << 24);
 }
 
 __device__ __forceinline__ void tmem_ld_wait() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
@@ -350,26 +387,47 @@ __device__ __forceinline__ UmTile um_tile_(int tile, int n_ttiles, int n_ntiles,
   return t;
 }
 
+// the it-th tile of this CTA (total_tiles = none left).  Pair mode: the cluster takes pair-tile q = (nt, btp) and its
+// CTA of rank r the (item, time) tile 2 btp + r, clamped to the last one (an odd count makes both CTAs compute the
+// same tile: identical bytes stored twice).
+#define um_tile_at(it, total_tiles, n_ntiles) um_tile_at_<PAIR>(it, total_tiles, n_ntiles, lay)
+template <bool PAIR>
+__device__ __forceinline__ int um_tile_at_(int it, int total_tiles, int n_ntiles, const UmLayout& lay) {
+  if (!PAIR) {
+    const int64_t t = (int64_t)blockIdx.x + (int64_t)it * gridDim.x;
+    return t < total_tiles ? (int)t : total_tiles;
+  }
+  const int64_t q = (int64_t)(blockIdx.x >> 1) + (int64_t)it * (gridDim.x >> 1);
+  if (q >= lay.total_ptiles) return total_tiles;
+  const uint32_t btp = um_div((uint32_t)q, lay.nt_m, lay.nt_l);
+  const int nt = (int)q - (int)btp * n_ntiles;
+  int bt = 2 * (int)btp + (int)(blockIdx.x & 1u);
+  if (bt >= lay.n_bt) bt = lay.n_bt - 1;
+  return bt * n_ntiles + nt;
+}
+
 // one producer cursor: which (tile, chunk) an operation is at, the tile's coordinates, and the A
 // stage / phase the chunk maps to
 struct UmCur {
   int tile, c, stage;
   uint32_t ph;
   int b, t0, nt;
+  int it;
 };
 #define um_cur_tile(q, total_tiles, n_ttiles, n_ntiles) um_cur_tile_(q, total_tiles, n_ttiles, n_ntiles, lay)
-#define um_advance(q, nchunks, na, total_tiles, n_ttiles, n_ntiles) um_advance_(q, nchunks, na, total_tiles, n_ttiles, n_ntiles, lay)
+#define um_advance(q, nchunks, na, total_tiles, n_ttiles, n_ntiles) um_advance_<PAIR>(q, nchunks, na, total_tiles, n_ttiles, n_ntiles, lay)
 __device__ __forceinline__ void um_cur_tile_(UmCur& q, int total_tiles, int n_ttiles, int n_ntiles, const UmLayout& lay) {
   if (q.tile < total_tiles) {
     const UmTile t = um_tile(q.tile, n_ttiles, n_ntiles);
     q.b = t.b; q.t0 = t.t0; q.nt = t.nt;
   }
 }
+template <bool PAIR>
 __device__ __forceinline__ void um_advance_(UmCur& q, int nchunks, int na, int total_tiles, int n_ttiles,
                                             int n_ntiles, const UmLayout& lay) {
   if (++q.c == nchunks) {
     q.c = 0;
-    q.tile += gridDim.x;
+    q.tile = um_tile_at(++q.it, total_tiles, n_ntiles);
     um_cur_tile(q, total_tiles, n_ttiles, n_ntiles);
   }
   if (++q.stage == na) {
@@ -392,7 +450,7 @@ __device__ __forceinline__ float um_act(float v, float sc, float sh, float wsc, 
   return u;
 }
 
-template <int ACT, bool HAS_SS>
+template <int ACT, bool HAS_SS, bool PAIR>
 __device__ __forceinline__ void um_produce(const St2ConvParams& p, const UmLayout& lay, const CUtensorMap* ymap,
                                            const CUtensorMap* rmap, const CUtensorMap* xmap,
                                            const CUtensorMap* xmap8, uint8_t* smem,
@@ -596,7 +654,7 @@ __device__ __forceinline__ void um_produce(const St2ConvParams& p, const UmLayou
   // a_empty barrier of the next slot and starts that chunk's loads as soon as the MMAs have released
   // it, up to na-1 chunks ahead.  (Residual / y_old chunks cost no arithmetic, so a fixed distance
   // counted in chunks would leave the following activation chunk no time to arrive.)
-  UmCur lc{(int)blockIdx.x, 0, 0, 0u, 0, 0, 0};
+  UmCur lc{um_tile_at(0, total_tiles, n_ntiles), 0, 0, 0u, 0, 0, 0, 0};
   um_cur_tile(lc, total_tiles, n_ttiles, n_ntiles);
   UmCur tc = lc;
   int n_l = 0, n_t = 0;  // chunks whose loads are issued / that are transformed
@@ -697,7 +755,7 @@ __device__ __forceinline__ void um_stage32(const uint32_t (&chunk_addr)[8], int 
   }
 }
 
-template <bool OUT_F32>
+template <bool OUT_F32, bool PAIR>
 __device__ __forceinline__ void um_epilogue(const St2ConvParams& p, const UmLayout& lay, const CUtensorMap* ymap,
                                             uint8_t* smem, UmMisc* misc, uint32_t tmem_base, int warp, int lane,
                                             int total_tiles, int n_ttiles, int n_ntiles) {
@@ -719,16 +777,26 @@ __device__ __forceinline__ void um_epilogue(const St2ConvParams& p, const UmLayo
     chunk_addr[j] = um_stg_addr(stg, rl, j * 16);
     col_addr[j] = um_stg_addr(stg, grp * ncp + j, cp * 4);
   }
+  // pair mode: this CTA owns half of the bias operand's columns, and the TMEM buffer goes back to the leader CTA
+  const int nb_cols = PAIR ? n_tile >> 1 : n_tile;
+  const int b_col0 = PAIR ? (int)(blockIdx.x & 1u) * nb_cols : 0;
+  const uint32_t t_empty0 = PAIR ? mapa_cta(smem_u32(&misc->t_empty[0]), 0u) : smem_u32(&misc->t_empty[0]);
+  auto release_tmem = [&](uint32_t tb) {
+    if (PAIR) mbar_arrive_cluster(t_empty0 + tb * 8u);
+    else mbar_arrive(&misc->t_empty[tb]);
+  };
   uint32_t t_it = 0;
-  for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, ++t_it) {
+  for (int it = 0;; ++it, ++t_it) {
+    const int tile = um_tile_at(it, total_tiles, n_ntiles);
+    if (tile >= total_tiles) break;
     const UmTile tl = um_tile(tile, n_ttiles, n_ntiles);
     const uint32_t tb = t_it & 1, tph = (t_it >> 1) & 1;
     // bias of the tile that will use this TMEM buffer next (two tiles ahead), loaded early
-    const int tile2 = tile + 2 * (int)gridDim.x;
+    const int tile2 = um_tile_at(it + 2, total_tiles, n_ntiles);
     float bias2 = 0.f;
-    if (et < n_tile && tile2 < total_tiles && p.bias) {
+    if (et < nb_cols && tile2 < total_tiles && p.bias) {
       const UmTile t2 = um_tile(tile2, n_ttiles, n_ntiles);
-      bias2 = __ldg(p.bias + (int64_t)t2.b * p.bias_bstride + t2.nt * n_tile + et);
+      bias2 = __ldg(p.bias + (int64_t)t2.b * p.bias_bstride + t2.nt * n_tile + b_col0 + et);
     }
     // two independent accumulator sets (even / odd rows) halve the dependent FADD/FFMA chains
     // (sum, sum of squares) of this thread's two columns as packed fp32x2
@@ -737,11 +805,11 @@ __device__ __forceinline__ void um_epilogue(const St2ConvParams& p, const UmLayo
     tc_fence_after();
     // this tile's bias MMA has completed: its operand slot can take the next bias; the t_empty arrive
     // below (after the fence) hands it to the MMA warp together with the TMEM buffer
-    if (et < n_tile) misc->bias_b[tb][et] = um_bias_split(bias2);
+    if (et < nb_cols) misc->bias_b[tb][et] = um_bias_split(bias2);
     if (lay.dbg & 8) {
       fence_proxy_async_smem();
       tc_fence_before();
-      mbar_arrive(&misc->t_empty[tb]);
+      release_tmem(tb);
       continue;
     }
 #pragma unroll 1
@@ -775,7 +843,7 @@ __device__ __forceinline__ void um_epilogue(const St2ConvParams& p, const UmLayo
       if (acc == UM_NACC - 1) {
         // all TMEM reads of this buffer are complete (tcgen05.wait::ld above)
         tc_fence_before();
-        mbar_arrive(&misc->t_empty[tb]);
+        release_tmem(tb);
       }
       named_bar_sync(1, UM_EPI_THREADS);
       const int row0 = tl.t0 + acc * 128;
@@ -835,6 +903,7 @@ __device__ __forceinline__ void um_epilogue(const St2ConvParams& p, const UmLayo
   if (et == 0) bulk_wait_all0();
 }
 
+template <bool PAIR>
 __global__ void __launch_bounds__(UM_THREADS, 1) conv_umma_kernel(const St2ConvParams p, const UmLayout lay,
                                                                    const __grid_constant__ CUtensorMap ymap,
                                                                    const __grid_constant__ CUtensorMap rmap,
@@ -862,7 +931,11 @@ __global__ void __launch_bounds__(UM_THREADS, 1) conv_umma_kernel(const St2ConvP
     }
     for (int i = 0; i < 2; ++i) {
       mbar_init(&misc->t_full[i], 1);
-      mbar_init(&misc->t_empty[i], UM_EPI_THREADS);
+      mbar_init(&misc->t_empty[i], PAIR ? 2 * UM_EPI_THREADS : UM_EPI_THREADS);  // pair: both CTAs' epilogues
+    }
+    if (PAIR) {
+      for (int i = 0; i < UM_MAX_A; ++i) mbar_init(&misc->peer_a_full[i], 1);
+      for (int i = 0; i < lay.nw; ++i) mbar_init(&misc->peer_w_full[i], 1);
     }
     fence_barrier_init();
   }
@@ -870,13 +943,15 @@ __global__ void __launch_bounds__(UM_THREADS, 1) conv_umma_kernel(const St2ConvP
     const int et0 = (int)threadIdx.x - UM_EPI_WARP0 * 32;
     if (et0 >= 0 && et0 < UM_EPI_THREADS) {
       if (et0 < 16) misc->ones_a[et0] = make_uint4(et0 < 8 ? 0x3F803F80u : 0u, 0u, 0u, 0u);
-      if (et0 < lay.n_tile) {
+      const int nb_cols = PAIR ? lay.n_tile >> 1 : lay.n_tile;
+      const int b_col0 = PAIR ? (int)(blockIdx.x & 1u) * nb_cols : 0;
+      if (et0 < nb_cols) {
         for (int i = 0; i < 2; ++i) {
-          const int tile = (int)blockIdx.x + i * (int)gridDim.x;
+          const int tile = um_tile_at(i, total_tiles, n_ntiles);
           float b = 0.f;
           if (tile < total_tiles && p.bias) {
             const UmTile t = um_tile(tile, n_ttiles, n_ntiles);
-            b = __ldg(p.bias + (int64_t)t.b * p.bias_bstride + t.nt * lay.n_tile + et0);
+            b = __ldg(p.bias + (int64_t)t.b * p.bias_bstride + t.nt * lay.n_tile + b_col0 + et0);
           }
           misc->bias_b[i][et0] = um_bias_split(b);
         }
@@ -885,27 +960,69 @@ __global__ void __launch_bounds__(UM_THREADS, 1) conv_umma_kernel(const St2ConvP
     }
   }
   if (warp == 0) {  // TMEM: all 512 columns (this CTA owns the SM: > 114 KB smem, 1 block/SM)
-    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(
-                     smem_u32(&misc->tmem_base)),
-                 "r"(512)
-                 : "memory");
-    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+    if (PAIR) {  // one warp of each CTA of the pair
+      asm volatile("tcgen05.alloc.cta_group::2.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(
+                       smem_u32(&misc->tmem_base)),
+                   "r"(512)
+                   : "memory");
+      asm volatile("tcgen05.relinquish_alloc_permit.cta_group::2.sync.aligned;" ::: "memory");
+    } else {
+      asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(
+                       smem_u32(&misc->tmem_base)),
+                   "r"(512)
+                   : "memory");
+      asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+    }
   }
   tc_fence_before();
-  __syncthreads();
+  if (PAIR) cluster_sync_all();  // the peer's barriers are initialised before any remote arrive / multicast commit
+  else __syncthreads();
   tc_fence_after();
+  const uint32_t rank = PAIR ? (blockIdx.x & 1u) : 0u;  // %cluster_ctarank of a (2, 1, 1) cluster
   const uint32_t tmem_base = misc->tmem_base;
 
-  if (warp == 0) {
+  if (warp == 0 && rank != 0) {
+    // ============================================================ pair mode, peer CTA: relay
+    // The leader's MMA warp cannot wait on this CTA's barriers; this warp does, and forwards every completed
+    // a_full / w_full phase to the leader's peer_a_full / peer_w_full (same ring positions in both CTAs).
+    const int nct = nchunks + lay.n_res + lay.n_acc;
+    const uint32_t pa = mapa_cta(smem_u32(&misc->peer_a_full[0]), 0u), pw = mapa_cta(smem_u32(&misc->peer_w_full[0]), 0u);
+    int as = 0, ws = 0;
+    uint32_t aph = 0, wph = 0;
+    for (int it = 0; um_tile_at(it, total_tiles, n_ntiles) < total_tiles; ++it) {
+      for (int c = 0; c < nct; ++c) {
+        mbar_wait(&misc->a_full[as], aph, 2);
+        fence_proxy_async_smem();
+        if (lane == 0) mbar_arrive_cluster(pa + (uint32_t)as * 8u);
+        const int taps = c < nchunks ? p.k : 1;
+        for (int j = 0; j < taps; ++j) {
+          mbar_wait(&misc->w_full[ws], wph, 3);
+          if (lane == 0) mbar_arrive_cluster(pw + (uint32_t)ws * 8u);
+          if (++ws == lay.nw) { ws = 0; wph ^= 1u; }
+        }
+        if (++as == lay.na) { as = 0; aph ^= 1u; }
+      }
+    }
+  } else if (warp == 0) {
     // ===================================================================== MMA issuer
     // The whole warp runs the (warp-uniform) loop and waits on the barriers; one elected lane issues
     // the MMAs and commits.  Descriptors are built once; per MMA only the 14-bit start-address field
     // moves (16-byte units): A (SWIZZLE_128B rows of 128 B) + 2 per 16-channel K step, + 8 per row
     // (128 rows per accumulator, dil rows per tap); W (core matrices) + 2*n_tile per K step.
     const uint32_t a_base = smem_u32(smem_raw + lay.off_a), w_base = smem_u32(smem_raw + lay.off_w);
-    const uint32_t w_lbo = (uint32_t)lay.n_tile * 16u;
+    // pair mode: this CTA's weight stage holds 64 of the 128 columns
+    const uint32_t w_lbo = PAIR ? 1024u : (uint32_t)lay.n_tile * 16u;
     const uint64_t a_desc0 = umma_desc(0, 16, 1024, 2), w_desc0 = umma_desc(0, w_lbo, 128);
-    const uint32_t a_kstep = 2u, w_kstep = 2u * (uint32_t)lay.n_tile;  // in 16-byte units
+    const uint32_t a_kstep = 2u, w_kstep = w_lbo >> 3;  // in 16-byte units (two K groups)
+    const uint32_t idesc_main = PAIR ? lay.idesc_pair : lay.idesc;
+    auto mma = [&](uint32_t d, uint64_t ad, uint64_t bd, uint32_t id, uint32_t accum, uint32_t on) {
+      if (PAIR) umma2_bf16_if(d, ad, bd, id, accum, on);
+      else umma_bf16_if(d, ad, bd, id, accum, on);
+    };
+    auto commit = [&](uint64_t* bar, uint32_t on) {
+      if (PAIR) umma2_commit_if(bar, on);
+      else umma_commit_if(bar, on);
+    };
     const int nct = nchunks + lay.n_res + lay.n_acc;
     const uint32_t leader = elect_one() ? 1u : 0u;
     const uint32_t mma_on = (lay.dbg & 16) ? 0u : leader;
@@ -915,7 +1032,7 @@ __global__ void __launch_bounds__(UM_THREADS, 1) conv_umma_kernel(const St2ConvP
     // path: the next weight stage's barrier is probed BEFORE the current group is issued (its
     // latency hides behind the issue), and issue / commit are predicated instead of branched.
     uint32_t w_ready = 0;
-    for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, ++t_it) {
+    for (int it = 0; um_tile_at(it, total_tiles, n_ntiles) < total_tiles; ++it, ++t_it) {
       const uint32_t tb = t_it & 1, tph = (t_it >> 1) & 1;
       mbar_wait(&misc->t_empty[tb], tph ^ 1, 1);
       const uint32_t d0 = tmem_base + (uint32_t)(tb * UM_NACC * lay.n_tile);
@@ -925,29 +1042,35 @@ __global__ void __launch_bounds__(UM_THREADS, 1) conv_umma_kernel(const St2ConvP
         const uint64_t bd = umma_desc(smem_u32(misc->bias_b[tb]), 0, 128);
 #pragma unroll
         for (int acc = 0; acc < UM_NACC; ++acc)
-          umma_bf16_if(d0 + (uint32_t)(acc * lay.n_tile), od, bd, lay.idesc, 0u, leader);
+          mma(d0 + (uint32_t)(acc * lay.n_tile), od, bd, idesc_main, 0u, leader);
       }
       for (int c = 0; c < nct; ++c) {
         mbar_wait(&misc->a_full[as], aph, 2);
+        if (PAIR) mbar_wait(&misc->peer_a_full[as], aph, 7);
         const uint32_t a_u = (a_base + (uint32_t)as * (uint32_t)lay.a_bytes) >> 4;
         // residual / y_old chunks: one identity "tap" at row offset 0
         const int taps = c < nchunks ? p.k : 1;
         const uint32_t dil = c < nchunks ? (uint32_t)p.dil : 0u;
         for (int j = 0; j < taps; ++j) {
-          if (!w_ready) mbar_wait(&misc->w_full[ws], wph, 3);
+          if (!w_ready) {
+            mbar_wait(&misc->w_full[ws], wph, 3);
+            if (PAIR) mbar_wait(&misc->peer_w_full[ws], wph, 8);
+          }
           tc_fence_after();
           int wn = ws + 1;
           uint32_t wnph = wph;
           if (wn == lay.nw) { wn = 0; wnph ^= 1u; }
           w_ready = mbar_try(&misc->w_full[wn], wnph);  // consumed after the MMAs below
+          if (PAIR && w_ready) w_ready = mbar_try(&misc->peer_w_full[wn], wnph);
           const uint32_t shift = (uint32_t)j * dil;  // rows
           // the swizzle is a function of the absolute smem address: a start that is not a multiple of
           // 8 rows needs no base offset (measured: base-offset variants fail the parity tests)
           const uint64_t ad = a_desc0 + (uint64_t)(a_u + shift * 8u);
           uint64_t bd = w_desc0 + (uint64_t)((w_base + (uint32_t)ws * (uint32_t)lay.w_bytes) >> 4);
           // identity chunk e of a 128-column tile only touches columns [64 e', 64 e' + 64): a 64-column MMA
-          uint32_t idesc = lay.idesc, dcol = 0;
-          if (c >= nchunks && lay.n_tile == 128) {
+          // (pair mode: the identity blob over all 128 columns, each CTA holding its half)
+          uint32_t idesc = idesc_main, dcol = 0;
+          if (c >= nchunks && lay.n_tile == 128 && !PAIR) {
             const int e = c - nchunks;
             const uint32_t hh = (uint32_t)(e < lay.n_res ? e : e - lay.n_res);
             idesc = lay.idesc64;
@@ -958,17 +1081,17 @@ __global__ void __launch_bounds__(UM_THREADS, 1) conv_umma_kernel(const St2ConvP
           for (int acc = 0; acc < UM_NACC; ++acc) {
 #pragma unroll
             for (int ks = 0; ks < UM_CK / 16; ++ks)
-              umma_bf16_if(d0 + (uint32_t)(acc * lay.n_tile) + dcol, ad + (uint64_t)(acc * 1024 + ks * a_kstep),
-                           bd + (uint64_t)(ks * w_kstep), idesc, 1u, mma_on);
+              mma(d0 + (uint32_t)(acc * lay.n_tile) + dcol, ad + (uint64_t)(acc * 1024 + ks * a_kstep),
+                  bd + (uint64_t)(ks * w_kstep), idesc, 1u, mma_on);
           }
-          umma_commit_if(&misc->w_empty[ws], leader);
+          commit(&misc->w_empty[ws], leader);
           ws = wn;
           wph = wnph;
         }
-        umma_commit_if(&misc->a_empty[as], leader);
+        commit(&misc->a_empty[as], leader);
         if (++as == lay.na) { as = 0; aph ^= 1u; }
       }
-      umma_commit_if(&misc->t_full[tb], leader);
+      commit(&misc->t_full[tb], leader);
     }
   } else if (warp == 1) {
     // ================================================================ weight producer
@@ -978,7 +1101,9 @@ __global__ void __launch_bounds__(UM_THREADS, 1) conv_umma_kernel(const St2ConvP
       const int per_nt = nchunks * p.k;
       int ws = 0;
       uint32_t wph = 0;
-      for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
+      for (int it = 0;; ++it) {
+        const int tile = um_tile_at(it, total_tiles, n_ntiles);
+        if (tile >= total_tiles) break;
         const UmTile tl = um_tile(tile, n_ttiles, n_ntiles);
         const uint8_t* src = wg + (int64_t)tl.nt * per_nt * lay.w_bytes;
         for (int s = 0; s < per_nt + lay.n_res + lay.n_acc; ++s) {
@@ -989,8 +1114,13 @@ __global__ void __launch_bounds__(UM_THREADS, 1) conv_umma_kernel(const St2ConvP
                                  : lay.ident_acc + (int64_t)(e - lay.n_res) * lay.w_bytes;
           }
           mbar_wait(&misc->w_empty[ws], wph ^ 1u, 4);
-          if ((lay.dbg & 1) && (tile != (int)blockIdx.x || s >= lay.nw)) {
+          if ((lay.dbg & 1) && (it != 0 || s >= lay.nw)) {
             mbar_arrive(&misc->w_full[ws]);  // timing experiment only
+          } else if (PAIR) {
+            // this CTA's 64 columns of each of the 8 K groups: 1 KB pieces of the [K group][128 columns][16 B] blob
+            mbar_arrive_expect_tx(&misc->w_full[ws], 8192u);
+            for (int v = 0; v < 8; ++v)
+              bulk_g2s(wsm + (size_t)ws * lay.w_bytes + v * 1024, blob + v * 2048 + rank * 1024u, 1024u, &misc->w_full[ws]);
           } else {
             mbar_arrive_expect_tx(&misc->w_full[ws], (uint32_t)lay.w_bytes);
             bulk_g2s(wsm + (size_t)ws * lay.w_bytes, blob, (uint32_t)lay.w_bytes, &misc->w_full[ws]);
@@ -1001,27 +1131,29 @@ __global__ void __launch_bounds__(UM_THREADS, 1) conv_umma_kernel(const St2ConvP
     }
   } else if (warp < UM_PROD_WARP0) {
     // ======================================================================= epilogue
-    if (p.y_dtype == ST2_DT_F32) um_epilogue<true>(p, lay, &ymap, smem_raw, misc, tmem_base, warp, lane, total_tiles, n_ttiles, n_ntiles);
-    else um_epilogue<false>(p, lay, &ymap, smem_raw, misc, tmem_base, warp, lane, total_tiles, n_ttiles, n_ntiles);
+    if (p.y_dtype == ST2_DT_F32) um_epilogue<true, PAIR>(p, lay, &ymap, smem_raw, misc, tmem_base, warp, lane, total_tiles, n_ttiles, n_ntiles);
+    else um_epilogue<false, PAIR>(p, lay, &ymap, smem_raw, misc, tmem_base, warp, lane, total_tiles, n_ttiles, n_ntiles);
   } else {
     // ============================================================ activation producers
     const int ptid = threadIdx.x - UM_PROD_WARP0 * 32;
     if (p.ss) {
-      if (p.act == ST2_ACT_SNAKE) um_produce<ST2_ACT_SNAKE, true>(p, lay, &ymap, &rmap, &xmap, &xmap8, smem_raw, misc, ptid, total_tiles, n_ttiles, n_ntiles, nchunks);
-      else if (p.act == ST2_ACT_LRELU) um_produce<ST2_ACT_LRELU, true>(p, lay, &ymap, &rmap, &xmap, &xmap8, smem_raw, misc, ptid, total_tiles, n_ttiles, n_ntiles, nchunks);
-      else um_produce<ST2_ACT_NONE, true>(p, lay, &ymap, &rmap, &xmap, &xmap8, smem_raw, misc, ptid, total_tiles, n_ttiles, n_ntiles, nchunks);
+      if (p.act == ST2_ACT_SNAKE) um_produce<ST2_ACT_SNAKE, true, PAIR>(p, lay, &ymap, &rmap, &xmap, &xmap8, smem_raw, misc, ptid, total_tiles, n_ttiles, n_ntiles, nchunks);
+      else if (p.act == ST2_ACT_LRELU) um_produce<ST2_ACT_LRELU, true, PAIR>(p, lay, &ymap, &rmap, &xmap, &xmap8, smem_raw, misc, ptid, total_tiles, n_ttiles, n_ntiles, nchunks);
+      else um_produce<ST2_ACT_NONE, true, PAIR>(p, lay, &ymap, &rmap, &xmap, &xmap8, smem_raw, misc, ptid, total_tiles, n_ttiles, n_ntiles, nchunks);
     } else {
-      if (p.act == ST2_ACT_SNAKE) um_produce<ST2_ACT_SNAKE, false>(p, lay, &ymap, &rmap, &xmap, &xmap8, smem_raw, misc, ptid, total_tiles, n_ttiles, n_ntiles, nchunks);
-      else if (p.act == ST2_ACT_LRELU) um_produce<ST2_ACT_LRELU, false>(p, lay, &ymap, &rmap, &xmap, &xmap8, smem_raw, misc, ptid, total_tiles, n_ttiles, n_ntiles, nchunks);
-      else um_produce<ST2_ACT_NONE, false>(p, lay, &ymap, &rmap, &xmap, &xmap8, smem_raw, misc, ptid, total_tiles, n_ttiles, n_ntiles, nchunks);
+      if (p.act == ST2_ACT_SNAKE) um_produce<ST2_ACT_SNAKE, false, PAIR>(p, lay, &ymap, &rmap, &xmap, &xmap8, smem_raw, misc, ptid, total_tiles, n_ttiles, n_ntiles, nchunks);
+      else if (p.act == ST2_ACT_LRELU) um_produce<ST2_ACT_LRELU, false, PAIR>(p, lay, &ymap, &rmap, &xmap, &xmap8, smem_raw, misc, ptid, total_tiles, n_ttiles, n_ntiles, nchunks);
+      else um_produce<ST2_ACT_NONE, false, PAIR>(p, lay, &ymap, &rmap, &xmap, &xmap8, smem_raw, misc, ptid, total_tiles, n_ttiles, n_ntiles, nchunks);
     }
   }
 
   tc_fence_before();
-  __syncthreads();
+  if (PAIR) cluster_sync_all();  // the leader's MMAs read this CTA's shared memory until its last commit
+  else __syncthreads();
   if (warp == 0) {
     tc_fence_after();
-    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(512) : "memory");
+    if (PAIR) asm volatile("tcgen05.dealloc.cta_group::2.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(512) : "memory");
+    else asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(512) : "memory");
   }
 }
 
@@ -1291,12 +1423,30 @@ int launch_conv_umma(const St2ConvParams& p, cudaStream_t st) {
   if (dev >= 64 || g_num_sms[dev] == 0) {
     int n = 0;
     ST2_CUDA_OK(cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev));
-    ST2_CUDA_OK(cudaFuncSetAttribute(conv_umma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+    ST2_CUDA_OK(cudaFuncSetAttribute(conv_umma_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                     UM_SMEM_LIMIT));
+    ST2_CUDA_OK(cudaFuncSetAttribute(conv_umma_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                      UM_SMEM_LIMIT));
     if (dev < 64) g_num_sms[dev] = n;
   }
   int sms = dev < 64 ? g_num_sms[dev] : 148;
-  const int grid = (int)(total < sms ? total : sms);
+  int grid = (int)(total < sms ? total : sms);
+  // CTA-pair mode (UmLayout::pair): 128-column bf16 tiles whose bias does not depend on the item.  Off unless
+  // ST2_UMMA_PAIR=1 (A/B switch).
+  lay.pair = 0;
+  {
+    const char* e = getenv("ST2_UMMA_PAIR");
+    const bool want = e && e[0] == '1';
+    if (want && lay.n_tile == 128 && p.y_dtype == ST2_DT_BF16 && (!p.bias || p.bias_bstride == 0) && sms >= 2 &&
+        !(lay.dbg & 1)) {
+      lay.pair = 1;
+      lay.n_bt = p.B * n_ttiles;
+      lay.total_ptiles = n_ntiles * ceil_div(lay.n_bt, 2);
+      lay.idesc_pair = um_idesc(128, 256);
+      const int64_t want_grid = 2 * (int64_t)lay.total_ptiles;
+      grid = (int)(want_grid < (sms & ~1) ? want_grid : (sms & ~1));
+    }
+  }
   cudaEvent_t e0 = nullptr, e1 = nullptr;
   if (g_prof.on) {
     if (g_prof.used + 2 > g_prof.ev.size()) {
@@ -1312,8 +1462,20 @@ int launch_conv_umma(const St2ConvParams& p, cudaStream_t st) {
     g_prof.flops += p.algo_flops;
     ST2_CUDA_OK(cudaEventRecord(e0, st));
   }
-  ST2_CUDA_OK(launch_pdl(conv_umma_kernel, dim3(grid), dim3(UM_THREADS), (size_t)lay.total, st, p, lay, ymap, rmap, xmap, xmap8, (int)total,
-                         n_ttiles, n_ntiles));
+  if (lay.pair) {
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3(grid); cfg.blockDim = dim3(UM_THREADS); cfg.dynamicSmemBytes = (size_t)lay.total; cfg.stream = st;
+    cudaLaunchAttribute attr[2];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = pdl_enabled() ? 1 : 0;
+    attr[1].id = cudaLaunchAttributeClusterDimension;
+    attr[1].val.clusterDim.x = 2; attr[1].val.clusterDim.y = 1; attr[1].val.clusterDim.z = 1;
+    cfg.attrs = attr; cfg.numAttrs = 2;
+    ST2_CUDA_OK(cudaLaunchKernelEx(&cfg, conv_umma_kernel<true>, p, lay, ymap, rmap, xmap, xmap8, (int)total, n_ttiles, n_ntiles));
+  } else {
+    ST2_CUDA_OK(launch_pdl(conv_umma_kernel<false>, dim3(grid), dim3(UM_THREADS), (size_t)lay.total, st, p, lay, ymap, rmap, xmap, xmap8, (int)total,
+                           n_ttiles, n_ntiles));
+  }
   ST2_LAUNCH_OK("conv_umma");
   if (e1) ST2_CUDA_OK(cudaEventRecord(e1, st));
   return ST2_OK;
