@@ -69,10 +69,14 @@ struct UmLayout {
   int total_ptiles;   // pair mode: n_ntiles * ceil(n_bt / 2)
   uint32_t idesc_pair;  // M = 256
   int dist;           // prefetch distance of the producers, in chunks (na - 2)
+  uint32_t spin;      // ST2_UMMA_SPIN: barrier classes that are polled instead of waited on with a suspend hint:
+                      // 1 t_empty (MMA warp), 2 a_full (MMA warp / relay), 4 w_full (MMA warp), 8 w_empty (weight
+                      // producer), 16 t_full (epilogue); 32 = the MMA warp's loop runs on its elected lane only
   int dbg;            // ST2_UMMA_DBG timing experiments, all with wrong results: 1 reuse the weight stages without
                       // reloading, 2 producers skip the prologue arithmetic, 4 epilogue skips the statistics pass,
                       // 8 epilogue skips TMEM read / staging / store, 16 no conv MMAs are issued (barriers only)
-  int w_bytes;        // bytes per weight stage (= 8 * n_tile * 16)
+  int w_bytes;        // bytes per weight blob (= 8 * n_tile * 16)
+  int w_slot;         // bytes per weight stage in shared memory (= w_bytes; half of it in pair mode)
   int out_row;        // bytes per output row segment (n_tile * element size), multiple of 128
   int n_res, n_acc;   // extra 64-channel chunks per tile: residual rows, y_old rows
   int res_tma, acc_tma;  // those rows come by TMA tensor loads (one thread) instead of 256 threads' cp.async
@@ -90,7 +94,7 @@ struct UmMisc {
   uint64_t raw_full[UM_MAX_A];  // raw activation tile of the stage has landed (TMA transaction bytes)
   uint64_t w_full[UM_MAX_W], w_empty[UM_MAX_W];
   uint64_t t_full[2], t_empty[2];
-  uint64_t peer_a_full[UM_MAX_A], peer_w_full[UM_MAX_W];  // pair mode, leader CTA: the peer's stage is ready
+  uint64_t peer_a_full[UM_MAX_A];  // pair mode, leader CTA: the peer's A stage is ready
   uint32_t tmem_base, pad_;
   // bias through the tensor core: one K=16 step with A = ones_a (every row (1, 1, 0, ...)) and
   // B = bias_b[tb] (per column (hi, lo, 0, ...) bf16 split of the fp32 bias), issued first for each tile
@@ -126,19 +130,26 @@ __device__ __forceinline__ uint64_t global_timer_ns() {
   return t;
 }
 // try_wait carries a suspend-time hint, so a waiting thread sleeps in hardware instead of spinning
-// through issue slots the working warps need; the 4 s deadline is checked every 64 wake-ups
-__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity, int which) {
+// through issue slots the working warps need; the 4 s deadline is checked every 64 wake-ups.  poll != 0 polls
+// test_wait instead: no suspension, so no wake-up latency (UmLayout::spin selects it per barrier class).
+__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity, int which, uint32_t poll = 0u) {
   const uint32_t addr = smem_u32(bar);
   uint32_t done = 0, spin = 0;
   uint64_t t0 = 0;
   while (true) {
-    asm volatile(
-        "{ .reg .pred p; mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2, %3; selp.u32 %0, 1, 0, p; }"
-        : "=r"(done)
-        : "r"(addr), "r"(parity), "r"(0x989680u)
-        : "memory");
+    if (poll)
+      asm volatile("{ .reg .pred p; mbarrier.test_wait.parity.shared::cta.b64 p, [%1], %2; selp.u32 %0, 1, 0, p; }"
+                   : "=r"(done)
+                   : "r"(addr), "r"(parity)
+                   : "memory");
+    else
+      asm volatile(
+          "{ .reg .pred p; mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2, %3; selp.u32 %0, 1, 0, p; }"
+          : "=r"(done)
+          : "r"(addr), "r"(parity), "r"(0x989680u)
+          : "memory");
     if (done) break;
-    if ((++spin & 63u) == 0u) {
+    if ((++spin & (poll ? 0xFFFFu : 63u)) == 0u) {
       const uint64_t now = global_timer_ns();
       if (t0 == 0) t0 = now;
       else if (now - t0 > 4000000000ull) mbar_timeout(which, parity);
@@ -178,6 +189,15 @@ __device__ __forceinline__ void tma_load_3d(const CUtensorMap* map, uint32_t sme
       "cp.async.bulk.tensor.3d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5}], [%2];" ::"r"(
           smem_dst),
       "l"(map), "r"(smem_u32(bar)), "r"(c0), "r"(c1), "r"(c2)
+      : "memory");
+}
+// the same from a CTA of a pair: the bytes are counted on a barrier of either CTA (shared::cluster address)
+__device__ __forceinline__ void tma_load_3d_pair(const CUtensorMap* map, uint32_t smem_dst, int c0, int c1, int c2,
+                                                 uint32_t bar_cluster_addr) {
+  asm volatile(
+      "cp.async.bulk.tensor.3d.cta_group::2.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5}], [%2];" ::"r"(
+          smem_dst),
+      "l"(map), "r"(bar_cluster_addr), "r"(c0), "r"(c1), "r"(c2)
       : "memory");
 }
 __device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
@@ -237,6 +257,36 @@ __device__ __forceinline__ void umma_bf16_if(uint32_t tmem_d, uint64_t adesc, ui
       "@q tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p; }" ::"r"(tmem_d),
       "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate), "r"(on)
       : "memory");
+}
+// One tap of a 64-channel chunk in a single asm block: 2 accumulators x 4 K steps.  Issued one by one, every MMA
+// costs the issuing thread a fresh transfer of all its operands into uniform registers (ELECT + 7 R2UR + vote loop in
+// the SASS), which is longer than the 64 cycles the MMA itself runs; inside one block the descriptors advance with
+// plain adds on values that are already there.
+#define ST2_UMMA_TAP8(GROUP)                                                                                 \
+  asm volatile(                                                                                              \
+      "{ .reg .pred q, t; .reg .b64 a, b, a1; .reg .b32 d1;\n"                                               \
+      "setp.ne.b32 q, %5, 0; setp.eq.b32 t, 0, 0;\n"                                                         \
+      "add.u32 d1, %0, %6; add.u64 a1, %1, 1024;\n"                                                          \
+      "@q tcgen05.mma.cta_group::" GROUP ".kind::f16 [%0], %1, %2, %3, t;\n"                                 \
+      "@q tcgen05.mma.cta_group::" GROUP ".kind::f16 [d1], a1, %2, %3, t;\n"                                 \
+      "add.u64 a, %1, 2; add.u64 a1, a1, 2; add.u64 b, %2, %4;\n"                                            \
+      "@q tcgen05.mma.cta_group::" GROUP ".kind::f16 [%0], a, b, %3, t;\n"                                   \
+      "@q tcgen05.mma.cta_group::" GROUP ".kind::f16 [d1], a1, b, %3, t;\n"                                  \
+      "add.u64 a, a, 2; add.u64 a1, a1, 2; add.u64 b, b, %4;\n"                                              \
+      "@q tcgen05.mma.cta_group::" GROUP ".kind::f16 [%0], a, b, %3, t;\n"                                   \
+      "@q tcgen05.mma.cta_group::" GROUP ".kind::f16 [d1], a1, b, %3, t;\n"                                  \
+      "add.u64 a, a, 2; add.u64 a1, a1, 2; add.u64 b, b, %4;\n"                                              \
+      "@q tcgen05.mma.cta_group::" GROUP ".kind::f16 [%0], a, b, %3, t;\n"                                   \
+      "@q tcgen05.mma.cta_group::" GROUP ".kind::f16 [d1], a1, b, %3, t; }" ::"r"(d),                         \
+      "l"(ad), "l"(bd), "r"(idesc), "l"((uint64_t)w_kstep), "r"(on), "r"(acc_cols)                           \
+      : "memory")
+__device__ __forceinline__ void umma_tap8_if(uint32_t d, uint32_t acc_cols, uint64_t ad, uint64_t bd, uint32_t w_kstep,
+                                             uint32_t idesc, uint32_t on) {
+  ST2_UMMA_TAP8("1");
+}
+__device__ __forceinline__ void umma2_tap8_if(uint32_t d, uint32_t acc_cols, uint64_t ad, uint64_t bd, uint32_t w_kstep,
+                                              uint32_t idesc, uint32_t on) {
+  ST2_UMMA_TAP8("2");
 }
 // ---- CTA-pair variants (cta_group::2): issued by the leader CTA of a 2-CTA cluster; the commit arrives on the
 // barrier at the same shared-memory offset in both CTAs
@@ -801,7 +851,7 @@ __device__ __forceinline__ void um_epilogue(const St2ConvParams& p, const UmLayo
     // two independent accumulator sets (even / odd rows) halve the dependent FADD/FFMA chains
     // (sum, sum of squares) of this thread's two columns as packed fp32x2
     uint64_t sa = 0ull, qa = 0ull, sb = 0ull, qb = 0ull;
-    mbar_wait(&misc->t_full[tb], tph, 5);
+    mbar_wait(&misc->t_full[tb], tph, 5, lay.spin & 16u);
     tc_fence_after();
     // this tile's bias MMA has completed: its operand slot can take the next bias; the t_empty arrive
     // below (after the fence) hands it to the MMA warp together with the TMEM buffer
@@ -909,6 +959,9 @@ __global__ void __launch_bounds__(UM_THREADS, 1) conv_umma_kernel(const St2ConvP
                                                                    const __grid_constant__ CUtensorMap rmap,
                                                                    const __grid_constant__ CUtensorMap xmap,
                                                                    const __grid_constant__ CUtensorMap xmap8,
+                                                                   const __grid_constant__ CUtensorMap wmap,
+                                                                   const __grid_constant__ CUtensorMap wmap_res,
+                                                                   const __grid_constant__ CUtensorMap wmap_acc,
                                                                    int total_tiles, int n_ttiles, int n_ntiles) {
   extern __shared__ __align__(1024) uint8_t smem_raw[];
   // launched with the programmatic-serialization attribute (common.cuh).  Waiting after the CTA-local setup
@@ -935,7 +988,6 @@ __global__ void __launch_bounds__(UM_THREADS, 1) conv_umma_kernel(const St2ConvP
     }
     if (PAIR) {
       for (int i = 0; i < UM_MAX_A; ++i) mbar_init(&misc->peer_a_full[i], 1);
-      for (int i = 0; i < lay.nw; ++i) mbar_init(&misc->peer_w_full[i], 1);
     }
     fence_barrier_init();
   }
@@ -984,22 +1036,18 @@ __global__ void __launch_bounds__(UM_THREADS, 1) conv_umma_kernel(const St2ConvP
   if (warp == 0 && rank != 0) {
     // ============================================================ pair mode, peer CTA: relay
     // The leader's MMA warp cannot wait on this CTA's barriers; this warp does, and forwards every completed
-    // a_full / w_full phase to the leader's peer_a_full / peer_w_full (same ring positions in both CTAs).
+    // a_full phase to the leader's peer_a_full (same ring positions in both CTAs).  Weight stages need no relay: the
+    // peer's TMA loads are counted on the leader's w_full directly.
     const int nct = nchunks + lay.n_res + lay.n_acc;
-    const uint32_t pa = mapa_cta(smem_u32(&misc->peer_a_full[0]), 0u), pw = mapa_cta(smem_u32(&misc->peer_w_full[0]), 0u);
-    int as = 0, ws = 0;
-    uint32_t aph = 0, wph = 0;
+    const uint32_t pa = mapa_cta(smem_u32(&misc->peer_a_full[0]), 0u);
+    int as = 0;
+    uint32_t aph = 0;
+    if (!(lay.spin & 32u) || lane == 0)
     for (int it = 0; um_tile_at(it, total_tiles, n_ntiles) < total_tiles; ++it) {
       for (int c = 0; c < nct; ++c) {
-        mbar_wait(&misc->a_full[as], aph, 2);
+        mbar_wait(&misc->a_full[as], aph, 2, lay.spin & 2u);
         fence_proxy_async_smem();
         if (lane == 0) mbar_arrive_cluster(pa + (uint32_t)as * 8u);
-        const int taps = c < nchunks ? p.k : 1;
-        for (int j = 0; j < taps; ++j) {
-          mbar_wait(&misc->w_full[ws], wph, 3);
-          if (lane == 0) mbar_arrive_cluster(pw + (uint32_t)ws * 8u);
-          if (++ws == lay.nw) { ws = 0; wph ^= 1u; }
-        }
         if (++as == lay.na) { as = 0; aph ^= 1u; }
       }
     }
@@ -1020,21 +1068,30 @@ __global__ void __launch_bounds__(UM_THREADS, 1) conv_umma_kernel(const St2ConvP
       else umma_bf16_if(d, ad, bd, id, accum, on);
     };
     auto commit = [&](uint64_t* bar, uint32_t on) {
+      if (!PAIR && (lay.dbg & 32)) {  // timing experiment (with bit 16): a plain arrive instead of tcgen05.commit
+        if (on) mbar_arrive(bar);
+        return;
+      }
       if (PAIR) umma2_commit_if(bar, on);
       else umma_commit_if(bar, on);
     };
     const int nct = nchunks + lay.n_res + lay.n_acc;
-    const uint32_t leader = elect_one() ? 1u : 0u;
-    const uint32_t mma_on = (lay.dbg & 16) ? 0u : leader;
+    // the loop runs on ONE elected lane: the other lanes wait at the end of the kernel.  (With all lanes in the
+    // loop every tcgen05.mma becomes a vote / ELECT / R2UR loop over the active lanes in the SASS.)
+    const uint32_t leader = 1u;
+    const uint32_t mma_on = (lay.dbg & 16) ? 0u : 1u;
     int as = 0, ws = 0;
     uint32_t aph = 0, wph = 0, t_it = 0;
     // The tensor-core queue is shallow, so everything between two groups of MMAs is on the critical
     // path: the next weight stage's barrier is probed BEFORE the current group is issued (its
     // latency hides behind the issue), and issue / commit are predicated instead of branched.
     uint32_t w_ready = 0;
+    // ST2_UMMA_SPIN bit 32: only the elected lane runs the loop (an mbarrier probe by 32 lanes costs the warp
+    // hundreds of cycles per tap)
+    if (elect_one())
     for (int it = 0; um_tile_at(it, total_tiles, n_ntiles) < total_tiles; ++it, ++t_it) {
       const uint32_t tb = t_it & 1, tph = (t_it >> 1) & 1;
-      mbar_wait(&misc->t_empty[tb], tph ^ 1, 1);
+      mbar_wait(&misc->t_empty[tb], tph ^ 1, 1, lay.spin & 1u);
       const uint32_t d0 = tmem_base + (uint32_t)(tb * UM_NACC * lay.n_tile);
       tc_fence_after();
       {  // D = ones x bias: A rows all alias one core matrix (SBO 0), B's second K group aliases the first (LBO 0, x 0)
@@ -1045,28 +1102,26 @@ __global__ void __launch_bounds__(UM_THREADS, 1) conv_umma_kernel(const St2ConvP
           mma(d0 + (uint32_t)(acc * lay.n_tile), od, bd, idesc_main, 0u, leader);
       }
       for (int c = 0; c < nct; ++c) {
-        mbar_wait(&misc->a_full[as], aph, 2);
-        if (PAIR) mbar_wait(&misc->peer_a_full[as], aph, 7);
+        mbar_wait(&misc->a_full[as], aph, 2, lay.spin & 2u);
+        if (PAIR) mbar_wait(&misc->peer_a_full[as], aph, 7, lay.spin & 2u);
         const uint32_t a_u = (a_base + (uint32_t)as * (uint32_t)lay.a_bytes) >> 4;
         // residual / y_old chunks: one identity "tap" at row offset 0
         const int taps = c < nchunks ? p.k : 1;
         const uint32_t dil = c < nchunks ? (uint32_t)p.dil : 0u;
         for (int j = 0; j < taps; ++j) {
           if (!w_ready) {
-            mbar_wait(&misc->w_full[ws], wph, 3);
-            if (PAIR) mbar_wait(&misc->peer_w_full[ws], wph, 8);
+            mbar_wait(&misc->w_full[ws], wph, 3, lay.spin & 4u);
           }
-          tc_fence_after();
+          if (!(lay.spin & 64u)) tc_fence_after();
           int wn = ws + 1;
           uint32_t wnph = wph;
           if (wn == lay.nw) { wn = 0; wnph ^= 1u; }
           w_ready = mbar_try(&misc->w_full[wn], wnph);  // consumed after the MMAs below
-          if (PAIR && w_ready) w_ready = mbar_try(&misc->peer_w_full[wn], wnph);
           const uint32_t shift = (uint32_t)j * dil;  // rows
           // the swizzle is a function of the absolute smem address: a start that is not a multiple of
           // 8 rows needs no base offset (measured: base-offset variants fail the parity tests)
           const uint64_t ad = a_desc0 + (uint64_t)(a_u + shift * 8u);
-          uint64_t bd = w_desc0 + (uint64_t)((w_base + (uint32_t)ws * (uint32_t)lay.w_bytes) >> 4);
+          uint64_t bd = w_desc0 + (uint64_t)((w_base + (uint32_t)ws * (uint32_t)lay.w_slot) >> 4);
           // identity chunk e of a 128-column tile only touches columns [64 e', 64 e' + 64): a 64-column MMA
           // (pair mode: the identity blob over all 128 columns, each CTA holding its half)
           uint32_t idesc = idesc_main, dcol = 0;
@@ -1077,13 +1132,9 @@ __global__ void __launch_bounds__(UM_THREADS, 1) conv_umma_kernel(const St2ConvP
             dcol = hh * 64u;
             bd += (uint64_t)(hh * 64u);  // 64 columns x 16 bytes, in 16-byte units
           }
-#pragma unroll
-          for (int acc = 0; acc < UM_NACC; ++acc) {
-#pragma unroll
-            for (int ks = 0; ks < UM_CK / 16; ++ks)
-              mma(d0 + (uint32_t)(acc * lay.n_tile) + dcol, ad + (uint64_t)(acc * 1024 + ks * a_kstep),
-                  bd + (uint64_t)(ks * w_kstep), idesc, 1u, mma_on);
-          }
+          static_assert(UM_NACC == 2 && UM_CK == 64, "umma_tap8_if issues 2 accumulators x 4 K steps");
+          if (PAIR) umma2_tap8_if(d0 + dcol, (uint32_t)lay.n_tile, ad, bd, w_kstep, idesc, mma_on);
+          else umma_tap8_if(d0 + dcol, (uint32_t)lay.n_tile, ad, bd, w_kstep, idesc, mma_on);
           commit(&misc->w_empty[ws], leader);
           ws = wn;
           wph = wnph;
@@ -1098,6 +1149,7 @@ __global__ void __launch_bounds__(UM_THREADS, 1) conv_umma_kernel(const St2ConvP
     if (lane == 0) {
       const uint8_t* wg = reinterpret_cast<const uint8_t*>(p.w);
       uint8_t* wsm = smem_raw + lay.off_w;
+      const uint32_t wf0 = PAIR ? mapa_cta(smem_u32(&misc->w_full[0]), 0u) : 0u;
       const int per_nt = nchunks * p.k;
       int ws = 0;
       uint32_t wph = 0;
@@ -1113,17 +1165,24 @@ __global__ void __launch_bounds__(UM_THREADS, 1) conv_umma_kernel(const St2ConvP
             blob = e < lay.n_res ? lay.ident_res + (int64_t)e * lay.w_bytes
                                  : lay.ident_acc + (int64_t)(e - lay.n_res) * lay.w_bytes;
           }
-          mbar_wait(&misc->w_empty[ws], wph ^ 1u, 4);
+          mbar_wait(&misc->w_empty[ws], wph ^ 1u, 4, lay.spin & 8u);
           if ((lay.dbg & 1) && (it != 0 || s >= lay.nw)) {
             mbar_arrive(&misc->w_full[ws]);  // timing experiment only
           } else if (PAIR) {
-            // this CTA's 64 columns of each of the 8 K groups: 1 KB pieces of the [K group][128 columns][16 B] blob
-            mbar_arrive_expect_tx(&misc->w_full[ws], 8192u);
-            for (int v = 0; v < 8; ++v)
-              bulk_g2s(wsm + (size_t)ws * lay.w_bytes + v * 1024, blob + v * 2048 + rank * 1024u, 1024u, &misc->w_full[ws]);
+            // this CTA's 64 columns of each of the 8 K groups of the [K group][128 columns][16 B] blob: one TMA box,
+            // counted on the LEADER's barrier next to the leader's own half (no hand-over through this CTA)
+            const CUtensorMap* mp = &wmap;
+            int row = (tl.nt * per_nt + s) * 8;
+            if (s >= per_nt) {
+              const int e = s - per_nt;
+              mp = e < lay.n_res ? &wmap_res : &wmap_acc;
+              row = (e < lay.n_res ? e : e - lay.n_res) * 8;
+            }
+            if (rank == 0) mbar_arrive_expect_tx(&misc->w_full[ws], (uint32_t)lay.w_bytes);
+            tma_load_3d_pair(mp, smem_u32(wsm + (size_t)ws * lay.w_slot), 0, 64 * (int)rank, row, wf0 + (uint32_t)ws * 8u);
           } else {
             mbar_arrive_expect_tx(&misc->w_full[ws], (uint32_t)lay.w_bytes);
-            bulk_g2s(wsm + (size_t)ws * lay.w_bytes, blob, (uint32_t)lay.w_bytes, &misc->w_full[ws]);
+            bulk_g2s(wsm + (size_t)ws * lay.w_slot, blob, (uint32_t)lay.w_bytes, &misc->w_full[ws]);
           }
           if (++ws == lay.nw) { ws = 0; wph ^= 1u; }
         }
@@ -1225,13 +1284,28 @@ static int um_layout(const St2ConvParams& p, int dev, UmLayout& lay) {
   ST2_REQUIRE(lay.out_row % 128 == 0, "conv_umma: an output row segment must be a multiple of 128 bytes");
   const int stg_bytes = (lay.out_row / 128) * 16384;
   const int misc_bytes = (int)round_up((int64_t)sizeof(UmMisc), 128);
-  lay.nw = UM_W_STAGES;
+  // CTA-pair mode (UmLayout::pair): 128-column bf16 tiles whose bias does not depend on the item.  Off unless
+  // ST2_UMMA_PAIR=1 (A/B switch).  A stage then holds half a blob, and the ring is twice as deep in the same bytes:
+  // a stage's round trip includes the relay through the peer CTA.
+  lay.dbg = 0;
+  if (const char* e = getenv("ST2_UMMA_DBG")) lay.dbg = atoi(e);
+  lay.spin = 0;
+  if (const char* e = getenv("ST2_UMMA_SPIN")) lay.spin = (uint32_t)atoi(e);
+  lay.pair = 0;
+  {
+    const char* e = getenv("ST2_UMMA_PAIR");
+    if (e && e[0] == '1' && lay.n_tile == 128 && p.y_dtype == ST2_DT_BF16 && (!p.bias || p.bias_bstride == 0) &&
+        !(lay.dbg & 1))
+      lay.pair = 1;
+  }
+  lay.w_slot = lay.pair ? lay.w_bytes / 2 : lay.w_bytes;
+  lay.nw = lay.pair ? 2 * UM_W_STAGES : UM_W_STAGES;
   if (const char* e = getenv("ST2_UMMA_WST")) {  // A/B switch
     lay.nw = atoi(e);
     if (lay.nw < 2) lay.nw = 2;
     if (lay.nw > UM_MAX_W) lay.nw = UM_MAX_W;
   }
-  const int fixed = lay.nw * lay.w_bytes + stg_bytes + misc_bytes;
+  const int fixed = lay.nw * lay.w_slot + stg_bytes + misc_bytes;
   int na = (UM_SMEM_LIMIT - fixed) / lay.a_bytes;
   if (na > UM_MAX_A) na = UM_MAX_A;
   ST2_REQUIRE(na >= 3, "conv_umma: tile does not fit shared memory");
@@ -1244,11 +1318,9 @@ static int um_layout(const St2ConvParams& p, int dev, UmLayout& lay) {
     if (lay.dist > na - 1) lay.dist = na - 1;
     if (lay.dist < 0) lay.dist = 0;
   }
-  lay.dbg = 0;
-  if (const char* e = getenv("ST2_UMMA_DBG")) lay.dbg = atoi(e);
   lay.off_a = (uint32_t)stg_bytes;
   lay.off_w = lay.off_a + (uint32_t)(na * lay.a_bytes);
-  lay.off_misc = lay.off_w + (uint32_t)(lay.nw * lay.w_bytes);
+  lay.off_misc = lay.off_w + (uint32_t)(lay.nw * lay.w_slot);
   lay.total = lay.off_misc + (uint32_t)misc_bytes;
   lay.idesc = um_idesc(lay.n_tile);
   lay.idesc64 = um_idesc(64);
@@ -1337,6 +1409,25 @@ static int um_xmap(const St2ConvParams& p, int rows, CUtensorMap* map) {
                               CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
   if (r != CUDA_SUCCESS) {
     set_error("conv_umma: cuTensorMapEncodeTiled (input) failed with code " + std::to_string((int)r));
+    return ST2_ECUDA;
+  }
+  return ST2_OK;
+}
+
+// weight blobs [blob][K group (8)][column (128)][8 channels] as a 3-D tensor: a box of 8 K groups x 64 columns is one
+// CTA's half of a blob in pair mode
+static int um_wmap(const void* ptr, int n_blobs, CUtensorMap* map) {
+  int rc = um_encode_fn();
+  if (rc) return rc;
+  const cuuint64_t gdim[3] = {8u, 128u, (cuuint64_t)n_blobs * 8u};
+  const cuuint64_t gstr[2] = {16u, 2048u};
+  const cuuint32_t box[3] = {8u, 64u, 8u};
+  const cuuint32_t estr[3] = {1u, 1u, 1u};
+  const CUresult r = g_encode(map, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 3, const_cast<void*>(ptr), gdim, gstr, box, estr,
+                              CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE,
+                              CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) {
+    set_error("conv_umma: cuTensorMapEncodeTiled (weights) failed with code " + std::to_string((int)r));
     return ST2_ECUDA;
   }
   return ST2_OK;
@@ -1431,21 +1522,19 @@ int launch_conv_umma(const St2ConvParams& p, cudaStream_t st) {
   }
   int sms = dev < 64 ? g_num_sms[dev] : 148;
   int grid = (int)(total < sms ? total : sms);
-  // CTA-pair mode (UmLayout::pair): 128-column bf16 tiles whose bias does not depend on the item.  Off unless
-  // ST2_UMMA_PAIR=1 (A/B switch).
-  lay.pair = 0;
-  {
-    const char* e = getenv("ST2_UMMA_PAIR");
-    const bool want = e && e[0] == '1';
-    if (want && lay.n_tile == 128 && p.y_dtype == ST2_DT_BF16 && (!p.bias || p.bias_bstride == 0) && sms >= 2 &&
-        !(lay.dbg & 1)) {
-      lay.pair = 1;
-      lay.n_bt = p.B * n_ttiles;
-      lay.total_ptiles = n_ntiles * ceil_div(lay.n_bt, 2);
-      lay.idesc_pair = um_idesc(128, 256);
-      const int64_t want_grid = 2 * (int64_t)lay.total_ptiles;
-      grid = (int)(want_grid < (sms & ~1) ? want_grid : (sms & ~1));
-    }
+  CUtensorMap wmap = ymap, wmap_res = ymap, wmap_acc = ymap;
+  if (lay.pair) {  // decided in um_layout
+    rc = um_wmap(p.w, n_ntiles * (p.cin / UM_CK) * p.k, &wmap);
+    if (rc) return rc;
+    if (lay.n_res) rc = um_wmap(lay.ident_res, lay.n_res, &wmap_res);
+    if (rc) return rc;
+    if (lay.n_acc) rc = um_wmap(lay.ident_acc, lay.n_acc, &wmap_acc);
+    if (rc) return rc;
+    lay.n_bt = p.B * n_ttiles;
+    lay.total_ptiles = n_ntiles * ceil_div(lay.n_bt, 2);
+    lay.idesc_pair = um_idesc(128, 256);
+    const int64_t want_grid = 2 * (int64_t)lay.total_ptiles;
+    grid = (int)(want_grid < (sms & ~1) ? want_grid : (sms & ~1));
   }
   cudaEvent_t e0 = nullptr, e1 = nullptr;
   if (g_prof.on) {
@@ -1471,9 +1560,9 @@ int launch_conv_umma(const St2ConvParams& p, cudaStream_t st) {
     attr[1].id = cudaLaunchAttributeClusterDimension;
     attr[1].val.clusterDim.x = 2; attr[1].val.clusterDim.y = 1; attr[1].val.clusterDim.z = 1;
     cfg.attrs = attr; cfg.numAttrs = 2;
-    ST2_CUDA_OK(cudaLaunchKernelEx(&cfg, conv_umma_kernel<true>, p, lay, ymap, rmap, xmap, xmap8, (int)total, n_ttiles, n_ntiles));
+    ST2_CUDA_OK(cudaLaunchKernelEx(&cfg, conv_umma_kernel<true>, p, lay, ymap, rmap, xmap, xmap8, wmap, wmap_res, wmap_acc, (int)total, n_ttiles, n_ntiles));
   } else {
-    ST2_CUDA_OK(launch_pdl(conv_umma_kernel<false>, dim3(grid), dim3(UM_THREADS), (size_t)lay.total, st, p, lay, ymap, rmap, xmap, xmap8, (int)total,
+    ST2_CUDA_OK(launch_pdl(conv_umma_kernel<false>, dim3(grid), dim3(UM_THREADS), (size_t)lay.total, st, p, lay, ymap, rmap, xmap, xmap8, wmap, wmap_res, wmap_acc, (int)total,
                            n_ttiles, n_ntiles));
   }
   ST2_LAUNCH_OK("conv_umma");
