@@ -1146,7 +1146,7 @@ __global__ void __launch_bounds__(UM_THREADS, 1) conv_umma_kernel(const St2ConvP
     }
   } else if (warp == 1) {
     // ================================================================ weight producer
-    if (lane == 0) {
+    if (elect_one()) {
       const uint8_t* wg = reinterpret_cast<const uint8_t*>(p.w);
       uint8_t* wsm = smem_raw + lay.off_w;
       const uint32_t wf0 = PAIR ? mapa_cta(smem_u32(&misc->w_full[0]), 0u) : 0u;

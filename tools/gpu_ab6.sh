@@ -1,0 +1,10 @@
+#!/bin/bash
+# same-box A/B of gpurun_ab/libst2dec_{old,new}.so: C2 and C4 steps, sampler run
+for v in old new old new; do
+  cp gpurun_ab/libst2dec_$v.so styletts2_b200/_lib/libst2dec.so
+  for w in c2 c4; do
+    timeout 600 python bench.py --workload $w --steps 10 --warmup 3 --no-cpu-baseline 2>/dev/null | tail -n 1 | python -c 'import sys,json; d=json.loads(sys.stdin.read()); print("'$v' '$w'", d["ms_per_step"], d["e2e"]["ms_per_step"], d["roofline"]["kernel_ms_per_step"], d["roofline"]["frac"], d["clocks"]["sm_mhz"])'
+  done
+  timeout 600 python bench.py --workload sampler --no-cpu-baseline 2>/dev/null | tail -n 1 | python -c 'import sys,json; d=json.loads(sys.stdin.read()); print("'$v' sampler", d["ms_per_step"])'
+done
+cp gpurun_ab/libst2dec_new.so styletts2_b200/_lib/libst2dec.so
