@@ -764,7 +764,7 @@ def run_ours(args):
             traffic = round(json.load(open(tp))["dram_bytes_per_launch"])
         roof = {"bound": "tensor", "achieved": round(ach, 2), "peak": peaks["tf_sustained"], "unit": "TFLOP/s",
                 "frac": round(ach / peaks["tf_sustained"], 4), "traffic": traffic,
-                "traffic_unit": "bytes per launch (dram read+write, ncu, profiles/r1_v6_ncu_conv_umma_step_c2.csv)",
+                "traffic_unit": "bytes per launch (dram read+write, ncu, profiles/r1_v7_ncu_conv_umma_step_c2.csv)",
                 "kernel": "conv_umma_kernel (tcgen05 implicit-GEMM conv)",
                 "launches_per_step": umma_n.value // args.steps,
                 "kernel_ms_per_step": round(umma_ms.value / args.steps, 3),
