@@ -14,7 +14,12 @@
 // (N tile, channel chunk, tap), streamed with cp.async.bulk (mbarrier complete_tx).
 //
 // Persistent, warp-specialised CTA (1 per SM, 448 threads):
-//   warp 0      MMA issuer (one lane) + TMEM allocation (512 columns: 2 tiles x 2 accumulators)
+//   warp 0      MMA issuer + TMEM allocation (512 columns: 2 tiles x 2 accumulators).  The issue loop runs on ONE
+//               elected lane and issues the 8 MMAs of a tap as one block: with all lanes in the loop every
+//               tcgen05.mma costs a vote / ELECT / R2UR loop (~90 cycles) around a 64-cycle MMA.
+//               Pair mode (template PAIR, ST2_UMMA_PAIR=1): the kernel runs as 2-CTA clusters, the leader issues
+//               cta_group::2 MMAs (M = 256: 128 rows of each CTA) and each CTA stages half of the weight columns;
+//               the peer's warp 0 relays its A stages to the leader.
 //   warp 1      weight producer (one lane, bulk copies through a 3-deep ring)
 //   warps 2-5   epilogue: tcgen05.ld -> * scale + bias -> 128B-swizzled staging tile in smem -> one TMA
 //               tensor store per 128-byte column segment (coalesced, asynchronous, clipped at Lout by

@@ -248,3 +248,33 @@ def test_istft_head_matches_oracle(frames):
     check(lib.st2_istft_head(xcl.cuda().contiguous().data_ptr(), 2, frames, wav.data_ptr(), None))
     torch.cuda.synchronize()
     assert (wav.cpu() - ref[:, 0]).abs().max().item() < 5e-6 * max(1.0, ref.abs().max().item())
+
+
+@pytest.mark.parametrize("case", [
+    # B, Lin, cin, n, k, dil, act, residual, accumulate
+    (3, 1000, 128, 128, 7, 3, _cabi.ACT_SNAKE, True, False),    # odd tile count: the last pair computes one tile twice
+    (2, 2000, 256, 256, 11, 5, _cabi.ACT_SNAKE, True, False),   # two N tiles, widest halo
+    (5, 777, 128, 128, 3, 1, _cabi.ACT_LRELU, False, False),
+    (2, 1500, 128, 128, 7, 1, _cabi.ACT_SNAKE, True, True),     # running mean through the identity blocks
+    (1, 300, 64, 128, 1, 1, _cabi.ACT_NONE, False, False),      # prologue-free path (TMA bytes straight to the MMAs)
+])
+def test_conv_umma_cta_pair_mode_is_bit_identical(case, monkeypatch):
+    """ST2_UMMA_PAIR=1 runs the same conv with cta_group::2 MMAs over 2-CTA clusters (conv_umma.cu, UmLayout::pair):
+    every stored byte and every statistic must equal the single-CTA kernel's."""
+    B, Lin, cin, n, k, dil, act, with_res, acc = case
+    x, w, bias, ss, alpha = _mk_case(B, Lin, cin, n, k, seed=sum(case[:6]), act=act, with_ss=act != _cabi.ACT_NONE)
+    g = torch.Generator().manual_seed(5)
+    res = torch.randn(B, Lin, n, generator=g).to(torch.bfloat16) if with_res else None
+    y_old = torch.randn(B, Lin, n, generator=g).to(torch.bfloat16) if acc else None
+    outs = []
+    for mode in ("0", "1"):
+        monkeypatch.setenv("ST2_UMMA_PAIR", mode)
+        y, st = run_conv("umma", x.to(torch.bfloat16).cuda(), w, bias, k=k, dil=dil, pad=dil * (k - 1) // 2, ss=ss,
+                         act=act, slope=0.1, alpha=alpha, res=res, out_scale=0.5 if acc else 1.0, y_old=y_old,
+                         want_stats=not acc)
+        torch.cuda.synchronize()
+        outs.append((y.float().cpu(), None if st is None else st.cpu()))
+    assert torch.isfinite(outs[0][0]).all()
+    assert torch.equal(outs[0][0], outs[1][0])
+    if outs[0][1] is not None:
+        assert torch.equal(outs[0][1], outs[1][1])
