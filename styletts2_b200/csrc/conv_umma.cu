@@ -1305,6 +1305,14 @@ static int um_layout(const St2ConvParams& p, int dev, UmLayout& lay) {
   }
   lay.w_slot = lay.pair ? lay.w_bytes / 2 : lay.w_bytes;
   lay.nw = lay.pair ? 2 * UM_W_STAGES : UM_W_STAGES;
+  // With 5 or more taps per chunk the weight stream, not the activation ring, is what the MMAs wait for: up to 5
+  // stages as long as 3 A stages still fit (measured after the issue-loop change: k = 11 460 -> 424 us, k = 7
+  // 332 -> 310 us at 5 stages; k = 3 loses 3 % when its A ring shrinks from 4 to 3, so it keeps 3 weight stages).
+  if (!lay.pair && p.k >= 5) {
+    int nw = 5;
+    while (nw > UM_W_STAGES && (UM_SMEM_LIMIT - (nw * lay.w_slot + stg_bytes + misc_bytes)) / lay.a_bytes < 3) --nw;
+    lay.nw = nw;
+  }
   if (const char* e = getenv("ST2_UMMA_WST")) {  // A/B switch
     lay.nw = atoi(e);
     if (lay.nw < 2) lay.nw = 2;
