@@ -17,6 +17,12 @@ oracle port of the reference's CPU decoder on this box's host cores, bounded sam
 --impl reference times the reference's own CPU implementation of the path: the reference is pure
 Python/PyTorch and /root/reference does not exist on the GPU box, so this arm runs the oracle port
 (oracle/decoder_oracle.py: the same ATen CPU convolutions, same op order) with all host threads.
+
+--impl reference-gpu times the LIBRARY baseline on the same B200:
+the reference's op sequence (oracle port in library mode: F.conv1d / F.conv_transpose1d / F.instance_norm /
+torch.stft / torch.istft on cuDNN, cuFFT and ATen) at the full workload, (i) eager fp32 with TF32 off
+(train_second.py:183-186) and (ii) under torch.autocast('cuda', bfloat16).  The default line of the c2 / c4
+workloads carries the same two figures in `library_baseline` (fewer steps).
 """
 from __future__ import annotations
 
@@ -41,7 +47,38 @@ WORKLOADS = {
     "c5": ("istftnet", 512, 2400, "BASELINE config 4 on one GPU: B=512 x 2400 frames, decoded in micro-batches"),
     "c5shard": ("istftnet", 64, 2400, "BASELINE config 4 per-GPU shard at 8 GPUs: B=64 x 2400 frames (30 s each)"),
 }
+DEFAULT_STEPS = {"c1": 500, "c2": 100, "c3": 50, "c4": 50, "c5": 2, "c5shard": 10, "f0n": 200, "sampler": 100, "chain": 40}
 MFLOP_PER_FRAME = {"istftnet": 649.05, "hifigan": 873.90}  # SURVEY.md section 8d (2*MAC, convs + linears)
+
+
+def _rows_of_rank(workload, B, world, rank):
+    """(rows this rank decodes, global index of its first row, scaling).  Every workload is weak-scaled (each rank
+    decodes its own batch of B rows) except c5: BASELINE.json config 4 is ONE batch of 512 x 2400 frames "sharded at
+    1/2/4/8 B200", so its 512 rows are split over the ranks (strong scaling, styletts2_b200.shard.shard_range)."""
+    if workload != "c5":
+        return B, rank * B, "weak"
+    from styletts2_b200.shard import shard_range
+    lo, hi = shard_range(B, world, rank)
+    return hi - lo, lo, "strong"
+
+
+def _config(workload, world, graphs=True):
+    """the `config` object of the JSON line; identical in the `ours` and `reference` arms (the reference arm's
+    bounded sample is described in its cpu_baseline.sample)."""
+    kind, B, T, desc = WORKLOADS[workload]
+    act = B * (60 * T + 1) * 128 * 2 if kind == "istftnet" else B * 120 * T * 64 * 2
+    per_rank = B if workload != "c5" else -(-B // world)
+    big = act * (per_rank / B) > 126e6
+    return {"workload": desc, "batch_per_gpu": per_rank, "mel_frames": T, "decoder": kind,
+            "weights": "random-init, the reference constructor's distributions (synthetic.py init=\"reference\", seed 0)",
+            "noise": "in-kernel Philox",
+            "l2": (f"no explicit flush: one layer's activation is {act * (per_rank / B) / 1e9:.2f} GB per GPU (>> 126 MB L2) and "
+                   "every step streams ~70 of them through HBM") if big else
+                  (f"no explicit flush, and the working set is L2-sized (one layer's activation: {act * (per_rank / B) / 1e6:.1f} MB "
+                   "against 126 MB of L2): a latency workload, replays run L2-warm as a real single-utterance loop would"),
+            "cuda_graph": bool(graphs),
+            "parallelism": (f"dp{world} (independent batches, no collective)" if workload != "c5" else
+                            f"dp{world}: the 512 rows split into {per_rank} per GPU, no collective (strong scaling)")}
 METRIC = "audio-sec/sec decoded (iSTFTNet, bf16)"
 UNIT = "audio-sec/sec"
 
@@ -129,33 +166,93 @@ def _oracle_cpu_decoder(kind, B, T, steps, warmup, threads=None):
     return audio_s / statistics.median(times), statistics.median(times) * 1e3, torch.get_num_threads()
 
 
-def _quality(kind, dev):
-    """parity of the measured build on a small case (B=2 x 40 frames, excitation injected) against the oracle port
-    of the reference: fp32-path max-abs (north star: <= 1e-3), bf16-path waveform SNR (>= 30 dB) and log-mel L1
-    with the reference's mel definition (meldataset.py:35-43)."""
+def _quality(kind, dev, dec, T, seed):
+    """parity of the MEASURED build and module on ONE FULL-SIZE item of the measured workload (T mel frames, the
+    reference constructor's init regime) against the oracle port of the reference, noise injected so both sides see
+    the same excitation: the product chain in bf16 (phase scan -> har_source -> stft_hilo -> tcgen05 convs -> iSTFT):
+    har_source error, torch.angle branch flips of `har`, waveform SNR (north star: >= 30 dB) and log-mel L1 with the
+    reference's mel definition (meldataset.py:35-43); fp32 path max-abs (<= 1e-3).  The waveform comparisons feed the
+    oracle with the har this run produced (iSTFTNet), which keeps the branch flips out of them."""
     import torch
-    import styletts2_b200 as st2
     import synthetic as synth
     from oracle import decoder_oracle as orc
     cfg = synth.ISTFTNET_CFG if kind == "istftnet" else synth.HIFIGAN_CFG
     sd = synth.synth_state_dict(cfg, seed=0)
-    dec = (st2.IstftnetDecoder if kind == "istftnet" else st2.HifiganDecoder)(**{k: v for k, v in cfg.items() if k != "kind"})
-    dec.load_state_dict(sd, strict=True)
-    dec = dec.to(dev).eval()
-    inp = synth.synth_inputs(cfg, 2, 40, seed=2024)
-    hs = orc.source_module(inp["F0_curve"], inp["noise"], orc.Params(sd), 300)
-    kw = {"har_source": hs}
-    if kind == "istftnet":
-        mag, ph = orc.stft_transform(hs, 20, 5)
-        kw = {"har": torch.cat([mag, ph], dim=1)}
-    ref = orc.decoder_forward(sd, cfg, inp["asr"], inp["F0_curve"], inp["N"], inp["s"], **kw)
-    args = [inp[k].to(dev) for k in ("asr", "F0_curve", "N", "s")]
-    dkw = {k: v.to(dev) for k, v in kw.items()}
-    w32 = dec(*args, precision="fp32", **dkw).cpu()
-    w16 = dec(*args, precision="bf16", **dkw).cpu()
-    out = {"case": "B=2 x 40 frames, excitation injected, vs the oracle port of the reference",
-           "fp32_max_abs": float((w32 - ref).abs().max()), "bf16_snr_db": round(float(orc.snr_db(ref, w16)), 2)}
-    out["bf16_log_mel_l1"] = round(orc.log_mel_l1(ref, w16), 5)
+    inp = synth.synth_inputs(cfg, 1, T, seed=seed)
+    graphs, dec.cuda_graphs = dec.cuda_graphs, False
+    try:
+        args = [inp[k].to(dev) for k in ("asr", "F0_curve", "N", "s")]
+        w16, exc = dec(*args, noise=inp["noise"].to(dev), precision="bf16", return_excitation=True)
+        hs = orc.source_module(inp["F0_curve"], inp["noise"], orc.Params(sd), 300)
+        out = {"case": f"1 item x {T} frames of the workload (seed {seed}), noise injected, vs the oracle port of the reference",
+               "har_source_max_abs": float((exc["har_source"].cpu() - hs).abs().max())}
+        if kind == "istftnet":
+            mag, ph = orc.stft_transform(hs, 20, 5)
+            har = exc["har"].cpu()
+            out["har_angle_branch_flips"] = int(((har[:, 11:] - ph).abs() > 3.0).sum())
+            out["har_mag_max_abs"] = float((har[:, :11] - mag).abs().max())
+            kw = {"har": har}
+        else:
+            kw = {"har_source": exc["har_source"].cpu()}
+        ref = orc.decoder_forward(sd, cfg, inp["asr"], inp["F0_curve"], inp["N"], inp["s"], **kw)
+        w32 = dec(*args, precision="fp32", **{k: v.to(dev) for k, v in kw.items()}).cpu()
+        out.update({"fp32_max_abs": float((w32 - ref).abs().max()),
+                    "bf16_snr_db": round(float(orc.snr_db(ref, w16.cpu())), 2),
+                    "bf16_log_mel_l1": round(orc.log_mel_l1(ref, w16.cpu()), 5),
+                    "ref_rms": round(float(ref.pow(2).mean().sqrt()), 4)})
+    finally:
+        dec.cuda_graphs = graphs
+    return out
+
+
+def _library_gpu(kind, B, T, steps, warmup, dev):
+    """the library baseline on this GPU (SURVEY 8d / BASELINE.md section 4): the reference's op sequence on ATen
+    (oracle port in library mode, oracle/decoder_oracle.py) at the full workload shape, the randn draw of SineGen
+    inside the step like the reference; (i) eager fp32, TF32 off (train_second.py:183-186); (ii) bf16 autocast.
+    Device-timed with CUDA events.  Falls back to micro-batches of 8 items when the eager graph does not fit."""
+    import contextlib
+    import torch
+    import synthetic as synth
+    from oracle import decoder_oracle as orc
+    cfg = synth.ISTFTNET_CFG if kind == "istftnet" else synth.HIFIGAN_CFG
+    sd = {k: v.to(dev) for k, v in synth.synth_state_dict(cfg, seed=0).items()}
+    inp = {k: v.to(dev) for k, v in synth.synth_inputs(cfg, B, T, seed=1234, with_noise=False).items()}
+    torch.backends.cudnn.allow_tf32 = False
+    torch.backends.cuda.matmul.allow_tf32 = False
+    audio_s = B * T * 300 / 24000.0
+    out = {"what": "the reference's op sequence on cuDNN / cuFFT / ATen (oracle port, library mode) on this GPU, same "
+                   f"workload (B={B} x {T} frames), randn noise drawn per step, eager launches",
+           "unit": UNIT, "steps": steps, "warmup": warmup}
+    mb = B
+    for name, ctx in (("fp32_eager_tf32_off", contextlib.nullcontext),
+                      ("bf16_autocast", lambda: torch.autocast("cuda", dtype=torch.bfloat16))):
+        def step():
+            for lo in range(0, B, mb):
+                sl = slice(lo, min(B, lo + mb))
+                noise = torch.randn(sl.stop - sl.start, T * 300, 9, device=dev)
+                with ctx():
+                    w = orc.decoder_forward(sd, cfg, inp["asr"][sl], inp["F0_curve"][sl], inp["N"][sl], inp["s"][sl],
+                                            noise=noise, library=True)
+            return w
+        try:
+            for _ in range(warmup):
+                step()
+        except torch.OutOfMemoryError:
+            torch.cuda.empty_cache()
+            mb = 8
+            for _ in range(warmup):
+                step()
+        torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(steps):
+            w = step()
+        e1.record()
+        torch.cuda.synchronize()
+        ms = e0.elapsed_time(e1) / steps
+        assert torch.isfinite(w.float()).all()
+        out[name] = {"value": round(audio_s / (ms * 1e-3), 2), "ms_per_step": round(ms, 2), "micro_batch": mb,
+                     "peak_mem_gb": round(torch.cuda.max_memory_allocated(dev) / 1e9, 1)}
     return out
 
 
@@ -170,7 +267,8 @@ def _hbm_kernels(B, T, dev, peaks):
     lw = torch.randn(9, generator=g).to(dev)
     ph = torch.empty(B * 9 * T, device=dev)
     hs = torch.empty(B, Lw, device=dev)
-    har = torch.empty(B, L2, 32, device=dev)
+    rows_pad = (L2 + 5) // 6 * 6 + 12
+    har16 = torch.empty(B, rows_pad, 64, device=dev, dtype=torch.bfloat16)
     x = (torch.randn(B, L2, 32, generator=g) * 0.3).to(dev)
     wav = torch.empty(B, Lw, device=dev)
     flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
@@ -179,8 +277,9 @@ def _hbm_kernels(B, T, dev, peaks):
         ("phase_scan + har_source (SineGen + SourceModuleHnNSF, Philox noise)", B * Lw * 4 + B * T * 4,
          lambda: check(lib.st2_source_har(f0.data_ptr(), None, 7, lw.data_ptr(), 0.0, B, T, 300, ph.data_ptr(),
                                           hs.data_ptr(), st))),
-        ("stft_kernel (20-point DFT, |X| and angle)", B * Lw * 4 + B * L2 * 128,
-         lambda: check(lib.st2_stft_har(hs.data_ptr(), B, Lw, har.data_ptr(), st))),
+        ("stft_hilo_kernel (20-point DFT, |X| and angle as bf16 hi/lo rows: the STFT of the bf16 path)",
+         B * Lw * 4 + B * rows_pad * 128,
+         lambda: check(lib.st2_stft_har16(hs.data_ptr(), B, Lw, rows_pad, har16.data_ptr(), st))),
         ("istft_kernel (exp/sin heads, inverse DFT, overlap-add)", B * L2 * 88 + B * Lw * 4,
          lambda: check(lib.st2_istft_head(x.data_ptr(), B, L2, wav.data_ptr(), st))),
     ]
@@ -630,14 +729,45 @@ def run_reference(args):
     line = {
         "impl": "reference", "metric": METRIC, "value": round(v, 4), "unit": UNIT, "n_gpus": args.gpus,
         "steps": args.steps, "warmup": max(1, args.warmup), "ms_per_step": round(ms, 2),
-        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-        "config": {"workload": desc, "sample": f"B={sb} x {st} frames per step on the CPU"},
+        "higher_is_better": True, "scaling": "strong" if args.workload == "c5" else "weak", "vs_baseline": None,
+        "dtype": "f32", "data": "synthetic",
+        "config": _config(args.workload, max(1, args.gpus), graphs=not args.no_graphs),
         "cpu_baseline": {"value": round(v, 4), "unit": UNIT, "cores": threads, "kind": "port",
-                         "sample": f"{sb} utterance x {st} frames, fp32, torch CPU (oracle port of "
-                                   f"Modules/{kind}.py Decoder.forward)"},
+                         "sample": f"each step = {sb} utterance x {st} frames of the workload (its rows are independent, "
+                                   f"so audio-sec/sec does not depend on the batch), fp32, torch CPU on all host threads "
+                                   f"(oracle port of Modules/{kind}.py Decoder.forward; /root/reference is absent on the GPU box)"},
         "e2e": {"value": round(v, 4), "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
+    print(json.dumps(line), flush=True)
+    return 0
+
+
+def run_reference_gpu(args):
+    """--impl reference-gpu: the library baseline (cuDNN / cuFFT / ATen) on the B200, full workload, N=1."""
+    import torch
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return 0
+    if not torch.cuda.is_available():
+        print(json.dumps({"impl": "reference-gpu", "unavailable": "no CUDA device"}), flush=True)
+        return 0
+    kind, B, T, desc = WORKLOADS[args.workload]
+    if args.workload == "c5":
+        B = 64  # one 8-GPU shard; 512 x 2400 eager fp32 does not fit
+    dev = torch.device("cuda", 0)
+    torch.cuda.set_device(dev)
+    sampler = ClockSampler(0)
+    if sampler.ok:
+        sampler.start()
+    lib_ = _library_gpu(kind, B, T, args.steps, max(3, args.warmup), dev)
+    clocks = sampler.stop()
+    best = lib_["bf16_autocast"]
+    line = {"impl": "reference-gpu", "metric": METRIC, "value": best["value"], "unit": UNIT, "n_gpus": 1, "steps": args.steps,
+            "warmup": max(3, args.warmup), "ms_per_step": best["ms_per_step"], "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "dtype": "bf16 (autocast); fp32 figure in library_baseline", "data": "synthetic",
+            "config": _config(args.workload, 1, graphs=False), "library_baseline": lib_, "clocks": clocks,
+            "gpu_launches": 0}
     print(json.dumps(line), flush=True)
     return 0
 
@@ -659,7 +789,8 @@ def run_ours(args):
     dev = torch.device("cuda", local)
     if world > 1:
         dist.init_process_group("nccl", device_id=dev)
-    kind, B, T, desc = WORKLOADS[args.workload]
+    kind, B_job, T, desc = WORKLOADS[args.workload]
+    B, row0, scaling = _rows_of_rank(args.workload, B_job, world, rank)
     cfg = synth.ISTFTNET_CFG if kind == "istftnet" else synth.HIFIGAN_CFG
     prec = args.precision
 
@@ -672,7 +803,9 @@ def run_ours(args):
     inp = synth.synth_inputs(cfg, B, T, seed=1234 + rank, with_noise=False)  # per-rank shard, Philox noise
     host = {k: v.pin_memory() for k, v in inp.items()}
     d = {k: v.to(dev) for k, v in inp.items()}
-    audio_s = B * T * 300 / 24000.0
+    audio_s = B * T * 300 / 24000.0          # this rank's audio per step
+    job_audio_s = (B_job if scaling == "strong" else world * B) * T * 300 / 24000.0
+    fwd = lambda a: dec(a["asr"], a["F0_curve"], a["N"], a["s"], item_offset=row0)
 
     def barrier():
         if world > 1:
@@ -688,7 +821,7 @@ def run_ours(args):
 
     # ---- device-resident arm
     for _ in range(max(3, args.warmup)):
-        out = dec(d["asr"], d["F0_curve"], d["N"], d["s"])
+        out = fwd(d)
     barrier()
     launches_per_step = dec.last_launches
     sampler = ClockSampler(local)
@@ -698,30 +831,38 @@ def run_ours(args):
     barrier()
     e0.record()
     for _ in range(args.steps):
-        out = dec(d["asr"], d["F0_curve"], d["N"], d["s"])
+        out = fwd(d)
     e1.record()
     barrier()
     clocks = sampler.stop()
+    ms_rank = e0.elapsed_time(e1) / args.steps
     ms_total = max_over_ranks(e0.elapsed_time(e1))
     ms_step = ms_total / args.steps
-    value = world * audio_s / (ms_step * 1e-3)
+    value = job_audio_s / (ms_step * 1e-3)
     assert torch.isfinite(out).all()
+    per_rank_ms = [round(ms_rank, 3)]
+    if world > 1:  # off the timed path: the spread behind the max-over-ranks figure
+        t = torch.zeros(world, device=dev, dtype=torch.float64)
+        t[rank] = ms_rank
+        dist.all_reduce(t)
+        per_rank_ms = [round(float(x), 3) for x in t.tolist()]
 
     # ---- roofline leg: the same K steps launched eagerly with a CUDA-event pair around every tcgen05
     # conv launch on the launch stream (a graph replay cannot carry the per-launch events)
     graphs_on = dec.cuda_graphs
     dec.cuda_graphs = False
+    roof_steps = max(1, min(args.steps, 20))
     for _ in range(2):
-        dec(d["asr"], d["F0_curve"], d["N"], d["s"])
+        fwd(d)
     barrier()
     _cabi.lib.st2_prof_enable(1)
     _cabi.lib.st2_prof_read(None, None, None, 1)
     e0.record()
-    for _ in range(args.steps):
-        dec(d["asr"], d["F0_curve"], d["N"], d["s"])
+    for _ in range(roof_steps):
+        fwd(d)
     e1.record()
     barrier()
-    ms_step_eager = e0.elapsed_time(e1) / args.steps
+    ms_step_eager = e0.elapsed_time(e1) / roof_steps
     umma_ms, umma_n, umma_fl = C.c_double(), C.c_int64(), C.c_double()
     _cabi.lib.st2_prof_read(C.byref(umma_ms), C.byref(umma_n), C.byref(umma_fl), 1)
     _cabi.lib.st2_prof_enable(0)
@@ -734,7 +875,7 @@ def run_ours(args):
 
     # the package's host-to-host loop: uploads / downloads of neighbouring steps overlap the forward
     from styletts2_b200.pipeline import HostPipeline
-    pipe = HostPipeline(dec, dev, depth=2)
+    pipe = HostPipeline(dec, dev, depth=2, item_offset=row0)
     for _ in range(max(3, args.warmup) + 1):  # warm-up: the caching allocator needs a few rounds until the waveform
         pipe.submit(host, wav_host)           # blocks handed to the download stream are recycled without cudaMalloc
     pipe.wait()
@@ -746,7 +887,7 @@ def run_ours(args):
     pipe.wait()
     barrier()
     ms_e2e = max_over_ranks(e0.elapsed_time(e1)) / args.steps
-    e2e_value = world * audio_s / (ms_e2e * 1e-3)
+    e2e_value = job_audio_s / (ms_e2e * 1e-3)
 
     if rank != 0:
         if world > 1:
@@ -766,12 +907,12 @@ def run_ours(args):
                 "frac": round(ach / peaks["tf_sustained"], 4), "traffic": traffic,
                 "traffic_unit": "bytes per launch (dram read+write, ncu, profiles/r1_v7_ncu_conv_umma_step_c2.csv)",
                 "kernel": "conv_umma_kernel (tcgen05 implicit-GEMM conv)",
-                "launches_per_step": umma_n.value // args.steps,
-                "kernel_ms_per_step": round(umma_ms.value / args.steps, 3),
-                "kernel_share_of_step": round(umma_ms.value / args.steps / ms_step_eager, 4),
-                "measured_in": f"a second pass of the same {args.steps} steps launched eagerly "
+                "launches_per_step": umma_n.value // roof_steps,
+                "kernel_ms_per_step": round(umma_ms.value / roof_steps, 3),
+                "kernel_share_of_step": round(umma_ms.value / roof_steps / ms_step_eager, 4),
+                "measured_in": f"a second pass of {roof_steps} of the same steps launched eagerly "
                                f"({ms_step_eager:.3f} ms per step) with CUDA events around each launch",
-                "algo_tflop_per_step_in_kernel": round(umma_fl.value / args.steps / 1e12, 4),
+                "algo_tflop_per_step_in_kernel": round(umma_fl.value / roof_steps / 1e12, 4),
                 "peak_source": peaks["source"] + " bf16_tflops_sustained (kernel timed inside a long step); "
                                f"burst peak {peaks['tf_burst']}",
                 "whole_step_tflops": round(algo_tflop_step / (ms_step * 1e-3), 2)}
@@ -790,21 +931,19 @@ def run_ours(args):
     line = {
         "metric": METRIC, "value": round(value, 2), "unit": UNIT, "n_gpus": world, "steps": args.steps,
         "warmup": max(3, args.warmup), "ms_per_step": round(ms_step, 3), "higher_is_better": True,
-        "scaling": "weak", "vs_baseline": None, "dtype": prec, "data": "synthetic",
-        "config": {"workload": desc, "batch_per_gpu": B, "mel_frames": T, "decoder": kind,
-                   "weights": "random-init (synthetic.py, seed 0)", "noise": "in-kernel Philox",
-                   "l2": f"no explicit flush: every step streams a {ws_bytes / 1e9:.2f} GB working set "
-                         "through HBM (>> 126 MB L2)",
-                   "cuda_graph": bool(dec.cuda_graphs),
-                   "parallelism": f"dp{world} (independent batches, no collective)"},
+        "scaling": scaling, "vs_baseline": None, "dtype": prec, "data": "synthetic",
+        "config": _config(args.workload, world, graphs=dec.cuda_graphs),
+        "workspace_gb": round(ws_bytes / 1e9, 2), "per_rank_ms_per_step": per_rank_ms,
         "e2e": {"value": round(e2e_value, 2), "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
                 "api": "styletts2_b200.pipeline.HostPipeline.submit (pinned host in -> pinned host out, copies of "
                        "neighbouring steps overlap the forward)",
                 "ms_per_step": round(ms_e2e, 3)},
         "gpu_launches": int(launches_per_step * args.steps),
         "roofline": roof, "cpu_baseline": cpu, "clocks": clocks,
-        "hbm_kernels": _hbm_kernels(B, T, dev, peaks) if (world == 1 and kind == "istftnet") else None,
-        "quality": _quality(kind, dev) if world == 1 else None,
+        "hbm_kernels": _hbm_kernels(min(B, 64), T, dev, peaks) if (world == 1 and kind == "istftnet") else None,
+        "quality": _quality(kind, dev, dec, T, 1234) if world == 1 and not args.no_quality else None,
+        "library_baseline": (_library_gpu(kind, B, T, 3, 2, dev)
+                             if world == 1 and args.workload in ("c2", "c4") and not args.no_library_baseline else None),
     }
     print(json.dumps(line), flush=True)
     if world > 1:
@@ -815,16 +954,22 @@ def run_ours(args):
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=10)
-    ap.add_argument("--warmup", type=int, default=3)
-    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--steps", type=int, default=None, help="timed steps (default per workload: a >= 2 s timed region)")
+    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference", "reference-gpu"])
     ap.add_argument("--workload", default="c2", choices=sorted(WORKLOADS) + ["f0n", "sampler", "chain"])
     ap.add_argument("--precision", default="bf16", choices=["bf16", "fp32"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-library-baseline", action="store_true", help="skip the cuDNN/ATen-on-this-GPU block (c2, c4)")
+    ap.add_argument("--no-quality", action="store_true", help="skip the full-size parity item against the oracle")
     ap.add_argument("--no-graphs", action="store_true", help="launch every kernel eagerly instead of replaying a CUDA graph")
     args = ap.parse_args()
+    if args.steps is None:
+        args.steps = 20 if args.impl != "ours" else DEFAULT_STEPS[args.workload]
     if args.impl == "reference":
         return run_reference(args)
+    if args.impl == "reference-gpu":
+        return run_reference_gpu(args)
     world = int(os.environ.get("WORLD_SIZE", "1"))
     if args.gpus > 1 and world == 1:
         # convenience: relaunch under torchrun (the driver launches torchrun itself)

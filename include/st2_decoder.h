@@ -227,6 +227,9 @@ int st2_source_har(const float* f0, const float* noise, uint64_t seed, const flo
                    float lin_b, int B, int T, int spf, float* phase_scratch, float* har_source,
                    void* stream);
 int st2_stft_har(const float* har_source, int B, int Lw, float* har_cl32, void* stream);
+/* the STFT of the bf16 path (what the benchmarked forward launches): every frame is one row of 64 bf16 =
+ * [hi(22) | 0(10) | lo(22) | 0(10)], hi = bf16(v), lo = bf16(v - hi); rows [Lw/5+1, rows_pad) are zero. */
+int st2_stft_har16(const float* har_source, int B, int Lw, int rows_pad, uint16_t* har_hilo, void* stream);
 int st2_istft_head(const float* x_cl32, int B, int frames, float* wav, void* stream);
 
 #ifdef __cplusplus

@@ -30,6 +30,15 @@ file against those vectors.
 
 Every function takes a ``dtype`` (float32 mirrors the reference, float64 gives a
 numerically cleaner yardstick) and works on NCL tensors like the reference.
+
+Library mode (``decoder_forward(..., library=True)``): the three places where this file writes the
+arithmetic out (instance norm, STFT, inverse STFT) call the SAME torch entry points the reference calls
+instead (``F.instance_norm`` = nn.InstanceNorm1d, ``torch.stft`` / ``torch.istft`` as in
+istftnet.py:91-104), and every tensor follows the device of the inputs.  That is the reference's own op
+sequence on ATen; ``bench.py --impl reference-gpu`` / the ``library_baseline`` block run it on the B200
+(cuDNN / cuFFT, eager fp32 with TF32 off as train_second.py:183-186, and under bf16 autocast) as the
+library baseline the kernels have to beat.  ``tests/test_oracle_golden.py`` checks library mode against
+the same goldens of the real reference.
 """
 from __future__ import annotations
 
@@ -58,9 +67,10 @@ def fold_weight_norm(g: torch.Tensor, v: torch.Tensor) -> torch.Tensor:
 class Params:
     """state dict view with weight-norm folded on access, in a working dtype."""
 
-    def __init__(self, sd: Dict[str, torch.Tensor], dtype=torch.float32):
+    def __init__(self, sd: Dict[str, torch.Tensor], dtype=torch.float32, library: bool = False):
         self.sd = {(k[7:] if k.startswith("module.") else k): v for k, v in sd.items()}
         self.dtype = dtype
+        self.library = library   # see the module doc: torch's own instance_norm / stft / istft
         self._cache: Dict[str, torch.Tensor] = {}
 
     def get(self, name: str) -> torch.Tensor:
@@ -94,7 +104,8 @@ def adain(x, s, P: Params, prefix: str):
     """AdaIN1d.forward, istftnet.py:21-25."""
     h = F.linear(s, P.get(prefix + ".fc.weight"), P.get(prefix + ".fc.bias"))
     gamma, beta = torch.chunk(h[:, :, None], 2, dim=1)
-    return (1 + gamma) * instance_norm(x) + beta
+    xn = F.instance_norm(x, eps=1e-5) if P.library else instance_norm(x)
+    return (1 + gamma) * xn + beta
 
 
 def snake(x, alpha):
@@ -179,7 +190,7 @@ def sine_gen(f0_frames: torch.Tensor, noise: torch.Tensor, spf: int, dtype=torch
     """
     B, T = f0_frames.shape
     f0f = f0_frames.to(torch.float32)
-    harm = torch.arange(1, N_HARM + 1, dtype=torch.float32)
+    harm = torch.arange(1, N_HARM + 1, dtype=torch.float32, device=f0f.device)
     fn = f0f[:, :, None] * harm  # :227, per frame (nearest upsample keeps frame values)
     rad = (fn / SAMPLING_RATE) % 1  # :152
     # :174 linear interpolation by 1/spf: 0.5*rad[..149] + 0.5*rad[..150] == rad (frame value)
@@ -216,15 +227,18 @@ def hann_periodic(n: int, dtype) -> torch.Tensor:
     return (0.5 - 0.5 * torch.cos(2 * math.pi * k / n)).to(torch.float32).to(dtype)
 
 
-def stft_transform(x: torch.Tensor, n_fft: int, hop: int):
+def stft_transform(x: torch.Tensor, n_fft: int, hop: int, library: bool = False):
     """TorchSTFT.transform, istftnet.py:91-97: torch.stft(center=True, reflect pad,
     onesided) then abs / angle.  x: [B, L] -> mag, phase [B, n_fft/2+1, L/hop+1]."""
     dtype = x.dtype
-    w = hann_periodic(n_fft, dtype)
+    w = hann_periodic(n_fft, dtype).to(x.device)
+    if library:  # the reference's own call, istftnet.py:92-97
+        X = torch.stft(x, n_fft, hop, n_fft, window=w, return_complex=True)
+        return torch.abs(X), torch.angle(X)
     xp = F.pad(x[:, None, :], (n_fft // 2, n_fft // 2), mode="reflect")[:, 0]
     frames = xp.unfold(1, n_fft, hop)  # [B, F, n_fft]
-    n = torch.arange(n_fft, dtype=torch.float64)
-    k = torch.arange(n_fft // 2 + 1, dtype=torch.float64)
+    n = torch.arange(n_fft, dtype=torch.float64, device=x.device)
+    k = torch.arange(n_fft // 2 + 1, dtype=torch.float64, device=x.device)
     ang = 2 * math.pi * k[:, None] * n[None, :] / n_fft
     cosb, sinb = torch.cos(ang).to(dtype), torch.sin(ang).to(dtype)
     fw = frames * w
@@ -237,18 +251,22 @@ def stft_transform(x: torch.Tensor, n_fft: int, hop: int):
     return torch.sqrt(re * re + im * im), torch.atan2(im, re)
 
 
-def istft_inverse(mag: torch.Tensor, phase: torch.Tensor, n_fft: int, hop: int):
+def istft_inverse(mag: torch.Tensor, phase: torch.Tensor, n_fft: int, hop: int, library: bool = False):
     """TorchSTFT.inverse, istftnet.py:99-104: torch.istft(mag*exp(i*phase)), center=True.
     Per frame irfft (imag of DC/Nyquist ignored), window, overlap-add, divide by the
     summed squared window, trim n_fft/2 both sides -> [B, 1, hop*(F-1)]."""
     dtype = mag.dtype
+    dev = mag.device
     B, K, Fr = mag.shape
-    w = hann_periodic(n_fft, dtype)
+    w = hann_periodic(n_fft, dtype).to(dev)
+    if library:  # the reference's own call, istftnet.py:100-104
+        y = torch.istft(mag.float() * torch.exp(phase.float() * 1j), n_fft, hop, n_fft, window=w.float())
+        return y.unsqueeze(-2).to(dtype)
     re, im = mag * torch.cos(phase), mag * torch.sin(phase)
-    n = torch.arange(n_fft, dtype=torch.float64)
-    k = torch.arange(K, dtype=torch.float64)
+    n = torch.arange(n_fft, dtype=torch.float64, device=dev)
+    k = torch.arange(K, dtype=torch.float64, device=dev)
     ang = 2 * math.pi * k[:, None] * n[None, :] / n_fft
-    c = torch.full((K,), 2.0, dtype=torch.float64)
+    c = torch.full((K,), 2.0, dtype=torch.float64, device=dev)
     c[0] = 1.0
     c[-1] = 1.0
     cosb = (c[:, None] * torch.cos(ang) / n_fft).to(dtype)
@@ -256,8 +274,8 @@ def istft_inverse(mag: torch.Tensor, phase: torch.Tensor, n_fft: int, hop: int):
     fr = torch.einsum("bkf,kn->bfn", re, cosb) - torch.einsum("bkf,kn->bfn", im, sinb)
     fr = fr * w
     total = hop * (Fr - 1) + n_fft
-    y = torch.zeros(B, total, dtype=dtype)
-    env = torch.zeros(total, dtype=dtype)
+    y = torch.zeros(B, total, dtype=dtype, device=dev)
+    env = torch.zeros(total, dtype=dtype, device=dev)
     for f in range(Fr):  # overlap-add (small Fr in tests; vectorised below for long ones)
         if Fr > 4096:
             break
@@ -283,7 +301,7 @@ def generator_istftnet(x, s, f0_frames, P: Params, cfg, noise=None, har_source=N
     if har is None:
         if har_source is None:
             har_source = source_module(f0_frames, noise, P, spf)
-        mag, ph = stft_transform(har_source.to(P.dtype), n_fft, hop)
+        mag, ph = stft_transform(har_source.to(P.dtype), n_fft, hop, P.library)
         har = torch.cat([mag, ph], dim=1)  # :356
     har = har.to(P.dtype)
     if taps is not None:
@@ -318,7 +336,7 @@ def generator_istftnet(x, s, f0_frames, P: Params, cfg, noise=None, har_source=N
         taps["conv_post"] = x
     nb = n_fft // 2 + 1
     spec, phase = torch.exp(x[:, :nb]), torch.sin(x[:, nb:])  # :377-378
-    return istft_inverse(spec, phase, n_fft, hop)
+    return istft_inverse(spec, phase, n_fft, hop, P.library)
 
 
 def generator_hifigan(x, s, f0_frames, P: Params, cfg, noise=None, har_source=None,
@@ -364,13 +382,13 @@ def generator_hifigan(x, s, f0_frames, P: Params, cfg, noise=None, har_source=No
 @torch.no_grad()
 def decoder_forward(sd: Dict[str, torch.Tensor], cfg, asr, F0_curve, N, s, noise=None,
                     har_source=None, har=None, dtype=torch.float32,
-                    taps: Optional[dict] = None) -> torch.Tensor:
+                    taps: Optional[dict] = None, library: bool = False) -> torch.Tensor:
     """Decoder.forward in eval mode, istftnet.py:509-527 / hifigan.py:456-474.
 
     asr [B,512,T/2], F0_curve [B,T], N [B,T], s [B,style].  Exactly one of ``noise``
     ([B, T*spf, 9] standard normal), ``har_source`` ([B, T*spf]) or ``har``
     ([B,22,60T+1], istftnet only) supplies the excitation.  Returns [B,1,T*spf]."""
-    P = Params(sd, dtype)
+    P = Params(sd, dtype, library)
     asr, F0_curve, N, s = (t.to(dtype) for t in (asr, F0_curve, N, s))
     F0 = F.conv1d(F0_curve[:, None], P.weight("F0_conv"), P.bias("F0_conv"), stride=2, padding=1)
     Nn = F.conv1d(N[:, None], P.weight("N_conv"), P.bias("N_conv"), stride=2, padding=1)

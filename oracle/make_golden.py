@@ -6,7 +6,13 @@ unmodified, loads the synthetic state dict of ``synthetic.py`` into the referenc
 ``generator.m_source`` (no edits to reference files), and writes
 
   tests/golden/keys_<kind>.json        state-dict names + shapes of the reference
-  tests/golden/<kind>_T<T>.npz         inputs, injected excitation, wav, a few taps
+  tests/golden/init_stats_<kind>.json  per-tensor [std, abs-max, mean] of the reference's OWN
+                                       ``torch.manual_seed(0); Decoder(...)`` state dict (pins the
+                                       distributions of synthetic.synth_state_dict(init="reference"))
+  tests/golden/<kind>_T<T>.npz         inputs, injected excitation, wav, a few taps; weights =
+                                       synth_state_dict(init="reference") (the reference's real init regime)
+  tests/golden/<kind>_legacy_T<T>.npz  the same with init="legacy" (round-1 regime: N(0, 0.01) resblock
+                                       weights, perturbed weight_g and Snake alpha)
 
 ``/root/reference`` does not exist on the GPU box, which is why the vectors are
 committed.  Usage:  python oracle/make_golden.py
@@ -106,34 +112,48 @@ def main():
                                      [k for k in ref_keys if k in my_keys and ref_keys[k] != my_keys[k]])
         with open(os.path.join(gold, f"keys_{kind}.json"), "w") as f:
             json.dump(ref_keys, f, indent=0, sort_keys=True)
-        sd = synth.synth_state_dict(cfg, seed=0)
-        dec.load_state_dict(sd, strict=True)
-        for T, full in ((8, True), (40, False)):
-            inp = synth.synth_inputs(cfg, B=2, T=T, seed=1234 + T)
-            wav, taps = run_reference(dec, inp, cfg)
-            out = {k: v.numpy() for k, v in inp.items()}
-            out["wav"] = wav.numpy()
-            out["har_source"] = taps["har_source"].numpy()
-            if full:
-                for k, v in taps.items():
-                    out["tap_" + k] = v.numpy()
-            elif "har" in taps:
-                out["tap_har"] = taps["har"].numpy()
-            np.savez_compressed(os.path.join(gold, f"{kind}_T{T}.npz"), **out)
-            # oracle vs reference, three excitation entry points
-            o_noise = orc.decoder_forward(sd, cfg, inp["asr"], inp["F0_curve"], inp["N"], inp["s"],
-                                          noise=inp["noise"])
-            o_hs = orc.decoder_forward(sd, cfg, inp["asr"], inp["F0_curve"], inp["N"], inp["s"],
-                                       har_source=taps["har_source"])
-            rep = dict(noise=float((o_noise - wav).abs().max()),
-                       har_source=float((o_hs - wav).abs().max()),
-                       wav_absmax=float(wav.abs().max()), wav_rms=float(wav.pow(2).mean().sqrt()))
-            if "har" in taps:
-                o_har = orc.decoder_forward(sd, cfg, inp["asr"], inp["F0_curve"], inp["N"], inp["s"],
-                                            har=taps["har"])
-                rep["har"] = float((o_har - wav).abs().max())
-            report[f"{kind}_T{T}"] = rep
-            print(kind, T, rep, flush=True)
+        stats = {k: [float(f"{x:.6g}") for x in v] for k, v in synth.init_stats(ref_sd).items()}
+        with open(os.path.join(gold, f"init_stats_{kind}.json"), "w") as f:
+            json.dump(stats, f, indent=0, sort_keys=True)
+        # the oracle on the reference's own seed-0 weights (not committed: 53 M parameters)
+        inp = synth.synth_inputs(cfg, B=1, T=40, seed=999)
+        own_sd = {k: v.clone() for k, v in ref_sd.items()}
+        wav, taps = run_reference(dec, inp, cfg)
+        kw = {"har": taps["har"]} if "har" in taps else {"har_source": taps["har_source"]}
+        o = orc.decoder_forward(own_sd, cfg, inp["asr"], inp["F0_curve"], inp["N"], inp["s"], **kw)
+        report[f"{kind}_own_seed0_init_T40"] = dict(err=float((o - wav).abs().max()), wav_absmax=float(wav.abs().max()),
+                                                     wav_rms=float(wav.pow(2).mean().sqrt()))
+        print(kind, "own init", report[f"{kind}_own_seed0_init_T40"], flush=True)
+        for init in ("reference", "legacy"):
+            sd = synth.synth_state_dict(cfg, seed=0, init=init)
+            dec.load_state_dict(sd, strict=True)
+            tag = kind if init == "reference" else kind + "_legacy"
+            for T, full in ((8, True), (40, False)):
+                inp = synth.synth_inputs(cfg, B=2, T=T, seed=1234 + T)
+                wav, taps = run_reference(dec, inp, cfg)
+                out = {k: v.numpy() for k, v in inp.items()}
+                out["wav"] = wav.numpy()
+                out["har_source"] = taps["har_source"].numpy()
+                if full:
+                    for k, v in taps.items():
+                        out["tap_" + k] = v.numpy()
+                elif "har" in taps:
+                    out["tap_har"] = taps["har"].numpy()
+                np.savez_compressed(os.path.join(gold, f"{tag}_T{T}.npz"), **out)
+                # oracle vs reference, three excitation entry points
+                o_noise = orc.decoder_forward(sd, cfg, inp["asr"], inp["F0_curve"], inp["N"], inp["s"],
+                                              noise=inp["noise"])
+                o_hs = orc.decoder_forward(sd, cfg, inp["asr"], inp["F0_curve"], inp["N"], inp["s"],
+                                           har_source=taps["har_source"])
+                rep = dict(noise=float((o_noise - wav).abs().max()),
+                           har_source=float((o_hs - wav).abs().max()),
+                           wav_absmax=float(wav.abs().max()), wav_rms=float(wav.pow(2).mean().sqrt()))
+                if "har" in taps:
+                    o_har = orc.decoder_forward(sd, cfg, inp["asr"], inp["F0_curve"], inp["N"], inp["s"],
+                                                har=taps["har"])
+                    rep["har"] = float((o_har - wav).abs().max())
+                report[f"{tag}_T{T}"] = rep
+                print(tag, T, rep, flush=True)
     with open(os.path.join(gold, "oracle_vs_reference.json"), "w") as f:
         json.dump(report, f, indent=1, sort_keys=True)
 

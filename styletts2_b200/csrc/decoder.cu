@@ -1423,9 +1423,9 @@ static int plan_bytes(St2Decoder* h, int B, int T, const St2ForwardOpts& o, int6
 
 extern "C" int64_t st2_decoder_workspace_bytes(const St2Decoder* hc, int B, int T, int precision) {
   St2Decoder* h = const_cast<St2Decoder*>(hc);
-  if (!h || !h->loaded || h->cfg.kind == ST2_KIND_F0N || B < 1 || T < 2 || (T & 1) ||
-      (precision != ST2_PREC_FP32 && precision != ST2_PREC_BF16)) {
-    set_error("st2_decoder_workspace_bytes: bad argument or weights not loaded");
+  if (!h || !h->loaded || (h->cfg.kind != ST2_KIND_ISTFTNET && h->cfg.kind != ST2_KIND_HIFIGAN) || B < 1 || T < 2 ||
+      (T & 1) || (precision != ST2_PREC_FP32 && precision != ST2_PREC_BF16)) {
+    set_error("st2_decoder_workspace_bytes: bad argument, weights not loaded, or not a decoder handle");
     return ST2_EINVAL;
   }
   St2ForwardOpts o;
@@ -1447,7 +1447,8 @@ extern "C" int st2_decoder_forward(St2Decoder* h, const float* asr, const float*
     set_error("st2_decoder_forward: weights not loaded");
     return ST2_ESTATE;
   }
-  ST2_REQUIRE(h->cfg.kind != ST2_KIND_F0N, "st2_decoder_forward: this handle is an F0/N predictor (use st2_f0n_forward)");
+  ST2_REQUIRE(h->cfg.kind == ST2_KIND_ISTFTNET || h->cfg.kind == ST2_KIND_HIFIGAN,
+              "st2_decoder_forward: this handle is not a decoder (F0/N predictor: st2_f0n_forward, sampler: st2_sampler_sample)");
   ST2_REQUIRE(B >= 1 && T >= 2, "batch / length");
   ST2_REQUIRE((T & 1) == 0, "len(F0_curve) must equal 2 * asr.shape[-1] (istftnet.py:513)");
   ST2_REQUIRE(B <= 65535, "batch too large for one call");
@@ -1814,6 +1815,10 @@ extern "C" int st2_source_har(const float* f0, const float* noise, uint64_t seed
 }
 extern "C" int st2_stft_har(const float* har_source, int B, int Lw, float* har_cl32, void* stream) {
   return launch_stft(har_source, B, Lw, har_cl32, 32, reinterpret_cast<cudaStream_t>(stream));
+}
+extern "C" int st2_stft_har16(const float* har_source, int B, int Lw, int rows_pad, uint16_t* har_hilo, void* stream) {
+  return launch_stft_hilo(har_source, B, Lw, rows_pad, reinterpret_cast<__nv_bfloat16*>(har_hilo),
+                          reinterpret_cast<cudaStream_t>(stream));
 }
 extern "C" int st2_istft_head(const float* x_cl32, int B, int frames, float* wav, void* stream) {
   return launch_istft(x_cl32, 32, B, frames, wav, reinterpret_cast<cudaStream_t>(stream));

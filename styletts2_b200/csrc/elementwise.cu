@@ -210,7 +210,7 @@ prep_inputs_kernel(const float* __restrict__ asr, const float* __restrict__ f0,
       if (ch < dim_in) {
         if (align_idx) {  // asr = t_en @ one-hot alignment, fused: frame t reads token align_idx[b][t]
           const int tok = align_idx[(int64_t)b * T2 + t];
-          v = tok >= 0 ? asr[((int64_t)b * dim_in + ch) * align_len + tok] : 0.f;
+          v = (tok >= 0 && tok < align_len) ? asr[((int64_t)b * dim_in + ch) * align_len + tok] : 0.f;
         } else {
           v = asr[((int64_t)b * dim_in + ch) * T2 + t];
         }
@@ -317,7 +317,7 @@ __global__ void expand_alignment_kernel(const float* __restrict__ x, const int* 
   const int f = blockIdx.x * blockDim.x + threadIdx.x, c = blockIdx.y, b = blockIdx.z;
   if (f >= frames) return;
   const int tok = idx[(int64_t)b * frames + f];
-  out[((int64_t)b * C + c) * frames + f] = tok >= 0 ? x[((int64_t)b * C + c) * Ltext + tok] : 0.f;
+  out[((int64_t)b * C + c) * frames + f] = (tok >= 0 && tok < Ltext) ? x[((int64_t)b * C + c) * Ltext + tok] : 0.f;
 }
 int launch_expand_alignment(const float* x, const int* idx, int B, int C, int Ltext, int frames, float* out,
                             cudaStream_t st) {

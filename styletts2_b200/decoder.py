@@ -107,21 +107,19 @@ class _DecoderBase(nn.Module):
 
     @torch.no_grad()
     def _reset_parameters(self):
-        """Same distributions as the reference's constructors: torch default U(+-1/sqrt(fan_in))
-        everywhere, N(0, 0.01) where ``init_weights`` is applied (Modules/utils.py:1-4 via
-        istftnet.py:38,48,343-344), weight_g = ||v||, Snake alpha = 1."""
+        """Same distributions as the reference's constructors leave behind: torch's default
+        kaiming-uniform U(+-1/sqrt(fan_in)) for every weight and bias, ``weight_v`` of the weight-normed
+        layers included (``init_weights``, Modules/utils.py:1-4 via istftnet.py:38,48,343-344, writes the
+        derived ``.weight`` attribute of an old-style weight-normed module, which the next forward
+        recomputes from g and v, so its N(0, 0.01) never lands), weight_g = ||v||, Snake alpha = 1."""
         sd = dict(self.named_parameters())
         for key, p in sd.items():
             leaf = key.rsplit(".", 1)[-1]
             if leaf.startswith("alpha") or ".alphas." in key or ".alpha1." in key or ".alpha2." in key:
                 p.fill_(1.0)
             elif leaf == "weight_v":
-                init01 = any(t in key for t in (".ups.", ".conv_post", ".convs1.", ".convs2."))
                 fan_in = p.shape[1] * p.shape[2]
-                if init01:
-                    p.normal_(0.0, 0.01)
-                else:
-                    p.uniform_(-1 / math.sqrt(fan_in), 1 / math.sqrt(fan_in))
+                p.uniform_(-1 / math.sqrt(fan_in), 1 / math.sqrt(fan_in))
             elif leaf == "weight":
                 fan_in = p[0].numel()
                 p.uniform_(-1 / math.sqrt(fan_in), 1 / math.sqrt(fan_in))

@@ -17,10 +17,13 @@ _KEYS = ("asr", "F0_curve", "N", "s")
 
 
 class HostPipeline:
-    def __init__(self, decoder, device: torch.device, depth: int = 2):
+    def __init__(self, decoder, device: torch.device, depth: int = 2, item_offset: int = 0):
+        """``item_offset``: global index of row 0 of every submitted batch (a rank decoding rows [lo, hi) of a
+        sharded batch passes ``lo`` so that the in-kernel noise equals the unsharded batch's)."""
         if depth < 1:
             raise ValueError("depth must be >= 1")
         self.dec, self.dev, self.depth = decoder, torch.device(device), depth
+        self.item_offset = int(item_offset)
         self.h2d = torch.cuda.Stream(self.dev)
         self.d2h = torch.cuda.Stream(self.dev)
         self._slots: List[Dict[str, torch.Tensor]] = [dict() for _ in range(depth)]
@@ -53,6 +56,8 @@ class HostPipeline:
             self._in_ready[slot].record(self.h2d)
         self._used[slot] = True
         compute.wait_event(self._in_ready[slot])
+        if self.item_offset:
+            kw.setdefault("item_offset", self.item_offset)
         wav = self.dec(dev_in["asr"], dev_in["F0_curve"], dev_in["N"], dev_in["s"], **kw)
         self._in_free[slot].record(compute)
         done = torch.cuda.Event()

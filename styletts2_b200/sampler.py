@@ -149,6 +149,8 @@ class StyleSampler(_DecoderBase):
                 raise RuntimeError("step_noise needs num_steps - 1 draws")
         prec = precision or self.precision
         out = self._run(False, x, 0.0, emb, feat, self._opts(prec, num_steps, embedding_scale, sn, seed, item_offset), prec)
+        if sn is None and seed is None:
+            self.seed += 1   # fresh step noise on every call, like the reference's randn_like (sampler.py:510)
         return out.reshape(lead)
 
     def denoise_fn(self, x_noisy: torch.Tensor, sigma: float, embedding: Optional[torch.Tensor] = None,

@@ -45,6 +45,27 @@ def test_key_list_matches_reference(kind):
     assert dec.samples_per_frame == 300
 
 
+@pytest.mark.parametrize("kind", ["istftnet", "hifigan"])
+def test_module_default_init_matches_reference_constructor(kind):
+    """the drop-in module's own random init (what a user gets from ``Decoder(...)`` before loading a
+    checkpoint) has the per-layer statistics of the reference's constructor (tests/golden/init_stats_*.json):
+    kaiming-uniform ``weight_v`` everywhere, because ``init_weights`` never lands on weight-normed layers"""
+    import styletts2_b200 as st2
+    import synthetic as synth
+    torch.manual_seed(0)
+    dec = (st2.IstftnetDecoder if kind == "istftnet" else st2.HifiganDecoder)(style_dim=128)
+    ref = json.load(open(os.path.join(ROOT, "tests", "golden", f"init_stats_{kind}.json")))
+    sd = dec.state_dict()
+    mine = synth.init_stats(sd)
+    for k in ("generator.resblocks.3.convs1.0.weight_v", "generator.ups.0.weight_v", "generator.conv_post.weight_v",
+              "decode.0.conv1.weight_v", "generator.noise_convs.0.weight", "encode.norm1.fc.weight"):
+        assert abs(mine[k][0] / ref[k][0] - 1) < 0.05, (k, mine[k], ref[k])
+        assert abs(mine[k][1] / ref[k][1] - 1) < 0.05, (k, mine[k], ref[k])
+    for k, v in mine.items():
+        if k.endswith("weight_g"):
+            assert v[0] < 1e-6 and abs(v[2] - 1) < 1e-6, k
+
+
 @pytest.mark.parametrize("variant", ["style", "lj"])
 def test_sampler_key_list_matches_reference(variant):
     import styletts2_b200 as st2

@@ -17,13 +17,16 @@ pytestmark = pytest.mark.gpu
 GOLD = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
 
 
-def _setup(kind):
+INITS = ["reference", "legacy"]   # synthetic.py: the reference's real init regime / the round-1 regime
+
+
+def _setup(kind, init):
     import synthetic as synth
     import styletts2_b200 as st2
     cfg = synth.ISTFTNET_CFG if kind == "istftnet" else synth.HIFIGAN_CFG
     kw = {k: v for k, v in cfg.items() if k != "kind"}
     dec = (st2.IstftnetDecoder if kind == "istftnet" else st2.HifiganDecoder)(**kw)
-    sd = synth.synth_state_dict(cfg, seed=0)
+    sd = synth.synth_state_dict(cfg, seed=0, init=init)
     dec.load_state_dict(sd, strict=True)
     return dec.cuda().eval(), sd, cfg
 
@@ -31,14 +34,15 @@ def _setup(kind):
 _CACHE = {}
 
 
-def _get(kind):
-    if kind not in _CACHE:
-        _CACHE[kind] = _setup(kind)
-    return _CACHE[kind]
+def _get(kind, init="reference"):
+    if (kind, init) not in _CACHE:
+        _CACHE[(kind, init)] = _setup(kind, init)
+    return _CACHE[(kind, init)]
 
 
-def _gold(kind, T):
-    g = np.load(os.path.join(GOLD, f"{kind}_T{T}.npz"))
+def _gold(kind, T, init="reference"):
+    tag = kind if init == "reference" else kind + "_legacy"
+    g = np.load(os.path.join(GOLD, f"{tag}_T{T}.npz"))
     return {k: torch.from_numpy(g[k]) for k in g.files}
 
 
@@ -46,55 +50,97 @@ def _c(t):
     return t.cuda()
 
 
+@pytest.mark.parametrize("init", INITS)
 @pytest.mark.parametrize("T", [8, 40])
-def test_istftnet_fp32_vs_reference_golden_har_injected(T):
-    dec, sd, cfg = _get("istftnet")
-    g = _gold("istftnet", T)
+def test_istftnet_fp32_vs_reference_golden_har_injected(T, init):
+    dec, sd, cfg = _get("istftnet", init)
+    g = _gold("istftnet", T, init)
     wav = dec(_c(g["asr"]), _c(g["F0_curve"]), _c(g["N"]), _c(g["s"]), har=_c(g["tap_har"]), precision="fp32")
     err = (wav.cpu() - g["wav"]).abs().max().item()
     assert wav.shape == g["wav"].shape
+    print(f"istftnet {init} T={T}: fp32 path max-abs vs the reference {err:.2e}")
     assert err < 1e-3, err
-    assert err < 5e-5, err  # what fp32 FFMA actually reaches
+    assert err < 1e-4, err  # what fp32 FFMA actually reaches
 
 
+@pytest.mark.parametrize("init", INITS)
+@pytest.mark.parametrize("prec", ["fp32", "bf16"])
 @pytest.mark.parametrize("T", [8, 40])
-def test_istftnet_fp32_excitation_vs_reference_golden(T):
-    """noise injected: har_source must match tightly; har on the circle (angle branch cut)."""
+def test_istftnet_excitation_vs_reference_golden(T, prec, init):
+    """noise injected, the excitation chain the product runs: phase scan -> har_source -> STFT.  ``prec="bf16"``
+    is the benchmarked chain (``stft_hilo_kernel``: har as bf16 (hi, lo) pairs, exported through
+    ``hilo_to_ncl``); ``fp32`` the parity path's ``stft_kernel``.  har_source must match tightly; har magnitude
+    <= 1e-3 relative, phase on the circle weighted by the magnitude (torch.angle's branch cut).  The waveform is
+    then checked against the ORACLE fed with the har this run produced (isolates everything downstream of the
+    STFT from the branch flips): fp32 <= 1e-3, bf16 >= 30 dB."""
     from tests.util import wrap_phase_err
-    dec, sd, cfg = _get("istftnet")
-    g = _gold("istftnet", T)
+    from oracle import decoder_oracle as orc
+    dec, sd, cfg = _get("istftnet", init)
+    g = _gold("istftnet", T, init)
     wav, exc = dec(_c(g["asr"]), _c(g["F0_curve"]), _c(g["N"]), _c(g["s"]), noise=_c(g["noise"]),
-                   precision="fp32", return_excitation=True)
+                   precision=prec, return_excitation=True)
     assert (exc["har_source"].cpu() - g["har_source"]).abs().max().item() < 2e-5
     har, ref = exc["har"].cpu(), g["tap_har"]
-    assert (har[:, :11] - ref[:, :11]).abs().max().item() < 1e-4
+    mag_tol = 1e-4 if prec == "fp32" else 1e-3 * max(1.0, ref[:, :11].abs().max().item())
+    assert (har[:, :11] - ref[:, :11]).abs().max().item() < mag_tol
     perr = wrap_phase_err(har[:, 11:], ref[:, 11:]) * ref[:, :11].double()
-    assert perr.max().item() < 1e-4
-    # the waveform itself is only comparable up to the branch flips; report, and bound loosely
+    assert perr.max().item() < (1e-4 if prec == "fp32" else 1e-3)
     d = (wav.cpu() - g["wav"]).abs()
     flips = ((har[:, 11:] - ref[:, 11:]).abs() > 3.0).sum().item()
-    print(f"T={T} branch flips={flips} wav max-abs={d.max().item():.3e} rms={d.pow(2).mean().sqrt().item():.3e}")
-    assert d.max().item() < 1.0
+    own = orc.decoder_forward(sd, cfg, g["asr"], g["F0_curve"], g["N"], g["s"], har=har)
+    e_own = (wav.cpu() - own).abs().max().item()
+    snr = orc.snr_db(own, wav.cpu())
+    print(f"{init} T={T} {prec}: branch flips={flips} wav vs golden max-abs={d.max().item():.3e}; vs oracle(har of "
+          f"this run) max-abs={e_own:.3e} SNR={snr:.1f} dB")
+    if prec == "fp32":
+        assert e_own < 1e-3
+        if flips == 0:
+            assert d.max().item() < 1e-3
+    else:
+        assert snr >= 30.0
+    assert d.max().item() < 2.0
 
 
+@pytest.mark.parametrize("init", INITS)
 @pytest.mark.parametrize("T", [8, 40])
-def test_hifigan_fp32_vs_reference_golden(T):
-    dec, sd, cfg = _get("hifigan")
-    g = _gold("hifigan", T)
+def test_hifigan_fp32_vs_reference_golden(T, init):
+    dec, sd, cfg = _get("hifigan", init)
+    g = _gold("hifigan", T, init)
     wav = dec(_c(g["asr"]), _c(g["F0_curve"]), _c(g["N"]), _c(g["s"]), noise=_c(g["noise"]), precision="fp32")
     err = (wav.cpu() - g["wav"]).abs().max().item()
-    assert err < 1e-3, err
     wav2 = dec(_c(g["asr"]), _c(g["F0_curve"]), _c(g["N"]), _c(g["s"]), har_source=_c(g["har_source"]),
                precision="fp32")
-    assert (wav2.cpu() - g["wav"]).abs().max().item() < 2e-4
+    err2 = (wav2.cpu() - g["wav"]).abs().max().item()
+    print(f"hifigan {init} T={T}: fp32 path max-abs vs the reference {err:.2e} (noise) {err2:.2e} (har_source)")
+    assert err < 1e-3, err
+    assert err2 < 1e-3, err2
 
 
+@pytest.mark.parametrize("init", INITS)
 @pytest.mark.parametrize("kind", ["istftnet", "hifigan"])
-def test_bf16_path_snr_vs_oracle(kind):
+@pytest.mark.parametrize("T", [8, 40])
+def test_bf16_path_vs_reference_golden(kind, T, init):
+    """the bf16 tensor-core path against the REAL reference's waveform (har / har_source injected):
+    SNR >= 30 dB at T=40 (T=8 gives InstanceNorm too few samples: reported, bounded at 25 dB), log-mel L1"""
+    from oracle import decoder_oracle as orc
+    dec, sd, cfg = _get(kind, init)
+    g = _gold(kind, T, init)
+    kw = {"har": _c(g["tap_har"])} if kind == "istftnet" else {"har_source": _c(g["har_source"])}
+    w16 = dec(_c(g["asr"]), _c(g["F0_curve"]), _c(g["N"]), _c(g["s"]), precision="bf16", **kw).cpu()
+    snr = orc.snr_db(g["wav"], w16)
+    mel = orc.log_mel_l1(g["wav"], w16)
+    print(f"{kind} {init} T={T}: bf16 SNR vs the reference {snr:.1f} dB, log-mel L1 {mel:.4f}")
+    assert snr >= (30.0 if T >= 40 else 25.0), snr
+    assert mel < 0.1
+
+
+@pytest.mark.parametrize("init", INITS)
+@pytest.mark.parametrize("kind", ["istftnet", "hifigan"])
+def test_bf16_path_snr_vs_oracle(kind, init):
     """bf16 tensor-core path at a mid size against the fp32 oracle: SNR >= 30 dB, log-mel L1 reported."""
     from oracle import decoder_oracle as orc
     import synthetic as synth
-    dec, sd, cfg = _get(kind)
+    dec, sd, cfg = _get(kind, init)
     B, T = 2, 120
     inp = synth.synth_inputs(cfg, B, T, seed=4321)
     hs = orc.source_module(inp["F0_curve"], inp["noise"], orc.Params(sd), 300)
@@ -112,7 +158,7 @@ def test_bf16_path_snr_vs_oracle(kind):
     w16 = dec(*args, precision="bf16", **ckw).cpu()
     snr = orc.snr_db(ref, w16)
     mel = orc.log_mel_l1(ref, w16)
-    print(f"{kind}: bf16 SNR {snr:.1f} dB, log-mel L1 {mel:.4f}, max-abs {(w16 - ref).abs().max().item():.3e}")
+    print(f"{kind} {init}: bf16 SNR {snr:.1f} dB, log-mel L1 {mel:.4f}, max-abs {(w16 - ref).abs().max().item():.3e}")
     assert snr >= 30.0, snr
     assert mel < 0.1
 
@@ -328,30 +374,85 @@ def test_pcm16_output_stage():
 
 
 @pytest.mark.parametrize("kind,B,T", [("istftnet", 32, 800), ("hifigan", 32, 800)])
-def test_full_size_config_properties(kind, B, T):
-    """BASELINE configs 1 and 3 at their full size (B=32 x 800 frames), where the oracle would take minutes:
-    size-independent properties instead.  (1) rows are independent and position-independent: items 0 and 17 get
-    identical inputs and the same injected excitation -> bitwise identical waveforms, and item 0 equals the same
-    item decoded alone (B=1); (2) a 40-frame prefix decoded alone by the ORACLE agrees with the full-size bf16 run
-    only up to the receptive field, so instead the whole first item is checked against the fp32 path of the same
-    library (SNR >= 30 dB, the north star's bf16 bar); (3) finite, plausible level (rms 0.05 .. 1.5)."""
+def test_full_size_config_vs_oracle(kind, B, T):
+    """BASELINE configs C2 (iSTFTNet) and C4 (HiFi-GAN) at their FULL size, B=32 x 800 frames, on the
+    reference's real init regime, noise injected, against the ORACLE (0.5-4 s per 800-frame item): items 0
+    and 17 of the batch.
+      * the product chain (bf16, what bench.py times): har_source <= 5e-5 of the oracle's SineGen; iSTFTNet
+        har magnitude / phase-on-the-circle vs the oracle's STFT; waveform SNR >= 30 dB and log-mel L1 against
+        the oracle fed with this run's own har (iSTFTNet: isolates the torch.angle branch flips, which are
+        counted and reported) or with the same noise (HiFi-GAN);
+      * fp32 path on the same two rows, same excitation injected: <= 1e-3 max-abs;
+      * items 0 and 17 decoded alone (B=1) equal their rows of the batch bit for bit."""
     import synthetic as synth
     from oracle import decoder_oracle as orc
+    from tests.util import wrap_phase_err
     dec, sd, cfg = _get(kind)
-    inp = synth.synth_inputs(cfg, B, T, seed=4242, with_noise=False)
-    for k in ("asr", "F0_curve", "N", "s"):
-        inp[k][17] = inp[k][0]
-    g = torch.Generator().manual_seed(5)
-    hs = (torch.randn(B, 300 * T, generator=g) * 0.05).tanh()
-    hs[17] = hs[0]
+    inp = synth.synth_inputs(cfg, B, T, seed=1234 + (2 if kind == "istftnet" else 4), with_noise=True)
     args = [inp[k].cuda() for k in ("asr", "F0_curve", "N", "s")]
-    wav = dec(*args, har_source=hs.cuda(), precision="bf16")
+    noise = inp["noise"].cuda()
+    wav, exc = dec(*args, noise=noise, precision="bf16", return_excitation=True)
     assert wav.shape == (B, 1, 300 * T) and torch.isfinite(wav).all()
-    assert torch.equal(wav[0], wav[17])
-    one = dec(*[a[:1] for a in args], har_source=hs[:1].cuda(), precision="bf16")
-    assert torch.equal(one[0], wav[0])
-    ref32 = dec(*[a[:2] for a in args], har_source=hs[:2].cuda(), precision="fp32")
-    snr = orc.snr_db(ref32.cpu(), wav[:2].cpu())
-    rms = wav.float().pow(2).mean().sqrt().item()
-    print(f"full size {kind}: bf16 vs fp32 path SNR {snr:.1f} dB, rms {rms:.3f}")
-    assert snr >= 30.0 and 0.05 < rms < 1.5
+    P = orc.Params(sd)
+    rows = [0, 17]
+    for i in rows:
+        sl = slice(i, i + 1)
+        hs = orc.source_module(inp["F0_curve"][sl], inp["noise"][sl], P, 300)
+        e_hs = (exc["har_source"][sl].cpu() - hs).abs().max().item()
+        assert e_hs < 5e-5, e_hs
+        a4 = [inp[k][sl] for k in ("asr", "F0_curve", "N", "s")]
+        if kind == "istftnet":
+            mag, ph = orc.stft_transform(hs, 20, 5)
+            har = exc["har"][sl].cpu()
+            assert (har[:, :11] - mag).abs().max().item() < 1e-3 * max(1.0, mag.abs().max().item())
+            assert (wrap_phase_err(har[:, 11:], ph) * mag.double()).max().item() < 1e-3
+            flips = ((har[:, 11:] - ph).abs() > 3.0).sum().item()
+            kw = {"har": har}
+        else:
+            flips = 0
+            kw = {"har_source": exc["har_source"][sl].cpu()}
+        ref = orc.decoder_forward(sd, cfg, *a4, **kw)
+        w16 = wav[sl].cpu()
+        snr, mel = orc.snr_db(ref, w16), orc.log_mel_l1(ref, w16)
+        ckw = {k: v.cuda() for k, v in kw.items()}
+        w32 = dec(*[a[sl] for a in args], precision="fp32", **ckw).cpu()
+        e32 = (w32 - ref).abs().max().item()
+        one = dec(*[a[sl] for a in args], noise=noise[sl], precision="bf16", item_offset=i)
+        print(f"full size {kind} item {i}: har_source err {e_hs:.1e}, angle flips {flips}, fp32 path max-abs {e32:.2e}, "
+              f"bf16 SNR {snr:.1f} dB, log-mel L1 {mel:.4f}, rms {ref.pow(2).mean().sqrt().item():.3f}")
+        assert e32 < 1e-3, e32
+        assert snr >= 30.0, snr
+        assert mel < 0.1, mel
+        assert torch.equal(one[0], wav[i])
+
+
+def test_long_form_item_vs_oracle():
+    """BASELINE config C5's length: one 2400-frame (30 s) iSTFTNet item, noise injected.  The unwrapped fp32
+    SineGen phase reaches ~5e5 rad there (ulp 0.03), so the CUDA scan must reproduce ATen's rounding points
+    (istftnet.py:146-186); har on the circle; waveform against the oracle fed with this run's har."""
+    import synthetic as synth
+    from oracle import decoder_oracle as orc
+    from tests.util import wrap_phase_err
+    dec, sd, cfg = _get("istftnet")
+    T = 2400
+    inp = synth.synth_inputs(cfg, 1, T, seed=1234 + 5, with_noise=True)
+    args = [inp[k].cuda() for k in ("asr", "F0_curve", "N", "s")]
+    P = orc.Params(sd)
+    hs = orc.source_module(inp["F0_curve"], inp["noise"], P, 300)
+    mag, ph = orc.stft_transform(hs, 20, 5)
+    for prec in ("bf16", "fp32"):
+        wav, exc = dec(*args, noise=inp["noise"].cuda(), precision=prec, return_excitation=True)
+        assert wav.shape == (1, 1, 300 * T)
+        e_hs = (exc["har_source"].cpu() - hs).abs().max().item()
+        har = exc["har"].cpu()
+        assert e_hs < 1e-4, e_hs
+        assert (har[:, :11] - mag).abs().max().item() < 1e-3 * max(1.0, mag.abs().max().item())
+        assert (wrap_phase_err(har[:, 11:], ph) * mag.double()).max().item() < 1e-3
+        ref = orc.decoder_forward(sd, cfg, inp["asr"], inp["F0_curve"], inp["N"], inp["s"], har=har)
+        err, snr = (wav.cpu() - ref).abs().max().item(), orc.snr_db(ref, wav.cpu())
+        print(f"2400 frames {prec}: har_source err {e_hs:.1e}, wav max-abs {err:.2e}, SNR {snr:.1f} dB, "
+              f"log-mel L1 {orc.log_mel_l1(ref, wav.cpu()):.4f}")
+        if prec == "fp32":
+            assert err < 1e-3, err
+        else:
+            assert snr >= 30.0, snr

@@ -178,7 +178,7 @@ def _oracle():
     return orc, synth
 
 
-@pytest.mark.parametrize("T", [8, 40, 400])
+@pytest.mark.parametrize("T", [8, 40, 400, 800, 2400])
 def test_har_source_matches_oracle(T):
     orc, synth = _oracle()
     cfg = synth.ISTFTNET_CFG
@@ -194,7 +194,8 @@ def test_har_source_matches_oracle(T):
                              out.data_ptr(), None))
     torch.cuda.synchronize()
     d = (out.cpu() - ref).abs()
-    # the phase reaches ~8e4 rad at T=400 (ulp 8e-3): identical fp32 rounding points are required
+    # the phase reaches ~8e4 rad at T=400 (ulp 8e-3) and ~5e5 rad at T=2400 (config C5; ulp 0.03, where the
+    # reference's own sine is 8.3e-2 away from an fp64 evaluation): identical fp32 rounding points are required
     assert d.max().item() < 2e-5, (d.max().item(), (d > 1e-5).float().mean().item())
 
 
@@ -234,6 +235,31 @@ def test_stft_matches_oracle(T):
     assert (o[:, :, 22:] == 0).all()
     # DC / Nyquist: Im == +0 -> angle in {0, +pi}, never -pi (probed reference behaviour)
     assert (o[:, :, 11] >= 0).all() and (o[:, :, 21] >= 0).all()
+
+
+@pytest.mark.parametrize("T", [8, 40, 800])
+def test_stft_hilo_matches_oracle(T):
+    """stft_hilo_kernel, the STFT the bf16 (benchmarked) path launches: bf16 (hi, lo) pairs whose sum carries
+    ~16 mantissa bits of |X| / angle; padding rows and columns are zero"""
+    orc, synth = _oracle()
+    g = torch.Generator().manual_seed(100 + T)
+    hs = torch.tanh(torch.randn(2, T * 300, generator=g) * 0.3)
+    mag, ph = orc.stft_transform(hs, 20, 5)
+    L2 = T * 60 + 1
+    rows_pad = (L2 + 5) // 6 * 6 + 12
+    out = torch.full((2, rows_pad, 64), float("nan"), device="cuda", dtype=torch.bfloat16)
+    check(lib.st2_stft_har16(hs.cuda().contiguous().data_ptr(), 2, T * 300, rows_pad, out.data_ptr(), None))
+    torch.cuda.synchronize()
+    o = out.float().cpu()
+    assert (o[:, L2:] == 0).all() and (o[:, :, 22:32] == 0).all() and (o[:, :, 54:] == 0).all()
+    v = o[:, :L2, :22] + o[:, :L2, 32:54]
+    hi = o[:, :L2, :22]
+    assert (hi.to(torch.bfloat16).float() == hi).all()
+    m = v[:, :, :11].transpose(1, 2)
+    assert ((m - mag).abs() / mag.abs().clamp_min(1e-2)).max().item() < 4e-5     # 2^-16 relative + fp32 DFT noise
+    perr = wrap_phase_err(v[:, :, 11:].transpose(1, 2), ph)
+    assert (perr * mag.double()).max().item() < 1e-4 * max(1.0, mag.max().item())
+    assert (v[:, :, 11] >= 0).all() and (v[:, :, 21] >= 0).all()
 
 
 @pytest.mark.parametrize("frames", [5, 481, 2401])

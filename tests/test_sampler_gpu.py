@@ -98,6 +98,25 @@ def test_sampler_rows_independent_and_philox_sharding():
     assert torch.equal(shard, full[4:])
 
 
+def test_sampler_default_calls_draw_fresh_step_noise():
+    """two calls without an explicit seed differ (the reference draws fresh randn_like noise in every
+    ADPM2Sampler.step, sampler.py:510); resetting ``.seed`` reproduces the first call"""
+    import synthetic as synth
+    m, sd, cfg = _get("style")
+    inp = synth.synth_sampler_inputs(cfg, 3, 20, 4, seed=2)
+    a = {k: (v.cuda() if v is not None else None) for k, v in inp.items()}
+    call = lambda: m(a["noise"], num_steps=4, embedding=a["embedding"], features=a["features"], precision="bf16")
+    m.seed = 41
+    o1, o2 = call(), call()
+    assert m.seed == 43 and not torch.equal(o1, o2)
+    m.seed = 41
+    assert torch.equal(call(), o1)
+    # injected step noise or an explicit seed leave the counter alone
+    m(a["noise"], num_steps=4, embedding=a["embedding"], features=a["features"], step_noise=a["step_noise"])
+    m(a["noise"], num_steps=4, embedding=a["embedding"], features=a["features"], seed=7)
+    assert m.seed == 42
+
+
 def test_sampler_errors_and_prefix_loading():
     import synthetic as synth
     import styletts2_b200 as st2
