@@ -219,6 +219,9 @@ int st2_debug_pack_conv(const St2Tensor* tensors, int n, const char* prefix, int
  * launches and their algorithmic FLOPs (St2ConvParams.algo_flops); reset != 0 clears the log. */
 int st2_prof_enable(int on);
 int st2_prof_read(double* umma_ms, int64_t* umma_launches, double* umma_flops, int reset);
+/* Debug: per-role barrier-wait accounting of conv_umma_kernel, filled while ST2_UMMA_DBG has bit 64 set (SM clock
+ * cycles summed over all CTAs since the last reset; index meaning in csrc/conv_umma.cu, g_um_wait).  Synchronises. */
+int st2_umma_wait_profile(uint64_t out[16], int reset);
 /* rows of the time tile and partial-statistics tiles each implementation uses. */
 int st2_conv_tile_rows(int use_umma);
 
