@@ -229,6 +229,16 @@ int st2_conv_tile_rows(int use_umma);
 int st2_source_har(const float* f0, const float* noise, uint64_t seed, const float* lin_w9,
                    float lin_b, int B, int T, int spf, float* phase_scratch, float* har_source,
                    void* stream);
+/* st2_source_har without the phase_scratch argument and without any allocation (no cudaMalloc / cudaFree, no
+ * allocating library call): the [B][9][T] phase table lives in a file-scope static __device__ array inside the
+ * library (4 MiB per GPU that loads it, held until exit).  No counterpart in the reference: added
+ * for callers that cannot allocate (CUDA-graph capture, tight serving loops, harnesses that
+ * forbid cudaMalloc).  Limit: B * 9 * T <= 1 048 576 floats (B * T <= 116 508 frames; config C2 needs 230 400),
+ * beyond that ST2_EINVAL with a message.  Every call on a device shares the one array: calls that overlap on the
+ * GPU (different streams) race; calls on one stream are ordered.  Nothing needs clearing between calls (the scan
+ * overwrites every element the second kernel reads).  Same results as st2_source_har, bit for bit. */
+int st2_source_har_static(const float* f0, const float* noise, uint64_t seed, const float* lin_w9,
+                          float lin_b, int B, int T, int spf, float* har_source, void* stream);
 int st2_stft_har(const float* har_source, int B, int Lw, float* har_cl32, void* stream);
 /* the STFT of the bf16 path (what the benchmarked forward launches): every frame is one row of 64 bf16 =
  * [hi(22) | 0(10) | lo(22) | 0(10)], hi = bf16(v), lo = bf16(v - hi); rows [Lw/5+1, rows_pad) are zero. */

@@ -110,6 +110,8 @@ SYMBOLS = {
     "st2_conv_tile_rows": (C.c_int, [C.c_int]),
     "st2_source_har": (C.c_int, [C.c_void_p, C.c_void_p, C.c_uint64, C.c_void_p, C.c_float, C.c_int,
                                  C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p]),
+    "st2_source_har_static": (C.c_int, [C.c_void_p, C.c_void_p, C.c_uint64, C.c_void_p, C.c_float, C.c_int,
+                                        C.c_int, C.c_int, C.c_void_p, C.c_void_p]),
     "st2_stft_har": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.c_void_p]),
     "st2_stft_har16": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_void_p]),
     "st2_istft_head": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.c_void_p]),

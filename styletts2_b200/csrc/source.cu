@@ -382,3 +382,51 @@ int launch_istft(const float* x_cl, int ld, int B, int frames, float* wav, cudaS
 }
 
 }  // namespace st2
+
+// ------------------------------------------------------------------------------------------------------------------
+// st2_source_har_static: st2_source_har without a caller-provided phase scratch and without any allocation.
+// No counterpart in the reference; added for callers that cannot call
+// cudaMalloc (CUDA-graph capture, tight serving loops, harnesses that forbid it).
+// The frame-rate phase table [B][9][T] of phase_scan lives in this file-scope device array (4 MiB per GPU that
+// loads the library, held until exit).  In host code the array's name is only a stand-in for the symbol: its device
+// address is looked up once per device with cudaGetSymbolAddress (that device current) and cached.  phase_scan
+// overwrites every element har_source reads, so nothing has to be cleared between calls; all calls share the one
+// array, so two calls that overlap on the GPU (different streams) race.
+#define ST2_STATIC_PHASE_FLOATS (1 << 20)
+static __device__ __align__(256) float g_static_phase[ST2_STATIC_PHASE_FLOATS];
+namespace st2 {
+static float* g_static_phase_ptr[64] = {};
+static int static_phase_ptr(float** out) {
+  int dev = 0;
+  ST2_CUDA_OK(cudaGetDevice(&dev));
+  ST2_REQUIRE(dev >= 0 && dev < 64, "st2_source_har_static: device index out of range");
+  if (!g_static_phase_ptr[dev]) {
+    float* p = nullptr;
+    ST2_CUDA_OK(cudaGetSymbolAddress((void**)&p, g_static_phase));
+    ST2_REQUIRE(p != nullptr, "st2_source_har_static: no device address for the scratch array");
+    g_static_phase_ptr[dev] = p;
+  }
+  *out = g_static_phase_ptr[dev];
+  return ST2_OK;
+}
+}  // namespace st2
+
+extern "C" int st2_source_har_static(const float* f0, const float* noise, uint64_t seed, const float* lin_w9,
+                                     float lin_b, int B, int T, int spf, float* har_source, void* stream) {
+  using namespace st2;
+  ST2_REQUIRE(f0 && lin_w9 && har_source, "st2_source_har_static: null pointer");
+  ST2_REQUIRE(B >= 1 && T >= 1 && spf >= 1, "st2_source_har_static: empty shape");
+  if ((int64_t)B * NH * T > (int64_t)ST2_STATIC_PHASE_FLOATS) {
+    set_error("st2_source_har_static: B * 9 * T = " + std::to_string((int64_t)B * NH * T) +
+              " floats exceeds the static scratch of " + std::to_string((int64_t)ST2_STATIC_PHASE_FLOATS) +
+              " floats (B * T <= 116508 frames); use st2_source_har with a caller-owned scratch");
+    return ST2_EINVAL;
+  }
+  float* phase = nullptr;
+  int rc = static_phase_ptr(&phase);
+  if (rc) return rc;
+  cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+  rc = launch_phase_scan(f0, B, T, spf, phase, st);
+  if (rc) return rc;
+  return launch_har_source(f0, phase, noise, seed, lin_w9, lin_b, B, T, spf, har_source, st, 0, nullptr);
+}
