@@ -391,11 +391,11 @@ def run_f0n(args):
         ts = []
         for i in range(3):
             t0 = time.perf_counter()
-            porc.f0n_forward(sd, one["x"], one["s"])
+            porc.f0n_forward(sd, one["x"], one["s"], aten_lstm=True)
             ts.append(time.perf_counter() - t0)
         tm = statistics.median(ts[1:])
         cpu = {"value": round(2 * T * 300 / 24000.0 / tm, 3), "unit": UNIT, "cores": torch.get_num_threads(), "kind": "port",
-               "sample": f"1 item x {T} prosody frames, fp32, torch CPU (oracle port of models.py F0Ntrain), {tm * 1e3:.0f} ms"}
+               "sample": f"1 item x {T} prosody frames, fp32, torch CPU (oracle port of models.py F0Ntrain, recurrence on ATen's nn.LSTM like the reference), {tm * 1e3:.0f} ms"}
     # algorithmic work: LSTM 2 dirs x (4H x (In + H)) + the six AdainResBlk1d convs + projections, 2*MAC per prosody frame
     H, In, dd = 256, 640, 512
     lstm = 2 * 2 * 4 * H * (In + H)
@@ -709,7 +709,7 @@ def run_reference(args):
         ts = []
         for i in range(max(1, args.warmup) + args.steps):
             t0 = time.perf_counter()
-            porc.f0n_forward(sd, one["x"], one["s"])
+            porc.f0n_forward(sd, one["x"], one["s"], aten_lstm=True)   # nn.LSTM, what models.py:562-564 runs
             ts.append(time.perf_counter() - t0)
         tm = statistics.median(ts[max(1, args.warmup):])
         v = 10.0 / tm

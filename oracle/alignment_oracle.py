@@ -2,8 +2,9 @@
 
 Follows Demo/Inference_LJSpeech.ipynb cell 17 and Demo/Inference_LibriTTS.ipynb cell 16 literally: a
 one-hot ``pred_aln_trg`` built in a Python loop, ``x @ pred_aln_trg``, and the HiFi-GAN one-frame right
-shift.  The reference holds no golden vectors for this step (parity unpinned by the reference
-itself; the restatement is the notebook's own six lines)."""
+shift.  The reference holds no golden vectors for this step; the restatement is pinned on the notebook's
+own statements, cut out of the notebook JSON and executed by oracle/make_golden_alignment.py
+(tests/golden/alignment_notebook.npz, tests/test_oracle_golden.py::test_alignment_oracle_vs_notebook_cell)."""
 import torch
 
 

@@ -33,8 +33,23 @@ def lstm_direction(x: torch.Tensor, w_ih, w_hh, b_ih, b_hh, reverse: bool) -> to
     return out
 
 
-def shared_lstm(x_ncl: torch.Tensor, P: Params) -> torch.Tensor:
+def shared_lstm_aten(x_ncl: torch.Tensor, P: Params) -> torch.Tensor:
+    """The same layer the way the reference runs it: ATen's fused ``nn.LSTM(d_hid + style, d_hid // 2, 1,
+    batch_first=True, bidirectional=True)`` (models.py:562-564, 639) with the state dict's weights.  Used by the timed
+    CPU baseline of ``bench.py --workload f0n`` (the Python time loop below understates the reference's CPU speed) and
+    checked against the explicit recurrence in tests/test_oracle_golden.py."""
+    w_ih = P.get("shared.weight_ih_l0")
+    lstm = torch.nn.LSTM(w_ih.shape[1], w_ih.shape[0] // 4, 1, batch_first=True, bidirectional=True).to(w_ih.dtype)
+    with torch.no_grad():
+        for name, prm in lstm.named_parameters():
+            prm.copy_(P.get("shared." + name))
+        return lstm(x_ncl.transpose(1, 2))[0]
+
+
+def shared_lstm(x_ncl: torch.Tensor, P: Params, aten: bool = False) -> torch.Tensor:
     """``x, _ = self.shared(x.transpose(-1, -2))`` (models.py:639): [B, In, T] -> [B, T, 2H]."""
+    if aten:
+        return shared_lstm_aten(x_ncl, P)
     x = x_ncl.transpose(1, 2)
     outs = []
     for sfx, rev in (("", False), ("_reverse", True)):
@@ -44,11 +59,12 @@ def shared_lstm(x_ncl: torch.Tensor, P: Params) -> torch.Tensor:
 
 
 def f0n_forward(sd: Dict[str, torch.Tensor], x: torch.Tensor, s: torch.Tensor,
-                dtype=torch.float32) -> Tuple[torch.Tensor, torch.Tensor]:
-    """``F0Ntrain(x, s)`` (models.py:638-654): x [B, d_hid + style, T], s [B, style] -> F0, N [B, 2T]."""
+                dtype=torch.float32, aten_lstm: bool = False) -> Tuple[torch.Tensor, torch.Tensor]:
+    """``F0Ntrain(x, s)`` (models.py:638-654): x [B, d_hid + style, T], s [B, style] -> F0, N [B, 2T].
+    ``aten_lstm``: run the recurrence through ``torch.nn.LSTM`` like the reference (timed baseline)."""
     P = Params(sd, dtype)
     x, s = x.to(dtype), s.to(dtype)
-    h = shared_lstm(x, P).transpose(1, 2)  # [B, 2H, T]
+    h = shared_lstm(x, P, aten_lstm).transpose(1, 2)  # [B, 2H, T]
     outs = []
     for br in ("F0", "N"):
         y = h

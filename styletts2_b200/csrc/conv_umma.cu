@@ -1458,7 +1458,39 @@ static int um_ident(int dev, int n_tile, float mult, const uint8_t** out) {
   return ST2_OK;
 }
 
-static int um_layout(const St2ConvParams& p, int dev, UmLayout& lay) {
+// A/B and debug switches (ST2_UMMA_*), read from the environment ONCE (first launch) and again only when a tool asks
+// for it with st2_umma_reload_env(): no getenv on the launch path.
+struct UmEnv {
+  int dbg = 0;
+  uint32_t spin = 0;
+  bool pair = false;
+  int wst = 0;    // 0 = default depth
+  int dist = -1;  // -1 = default
+  bool res_tma = true, x_tma = true, loader = true;
+};
+static std::mutex g_env_mu;
+static UmEnv g_env;
+static bool g_env_ready = false;
+static void um_env_read_locked() {
+  UmEnv e;
+  if (const char* v = getenv("ST2_UMMA_DBG")) e.dbg = atoi(v);
+  if (const char* v = getenv("ST2_UMMA_SPIN")) e.spin = (uint32_t)atoi(v);
+  if (const char* v = getenv("ST2_UMMA_PAIR")) e.pair = v[0] == '1';
+  if (const char* v = getenv("ST2_UMMA_WST")) e.wst = atoi(v);
+  if (const char* v = getenv("ST2_UMMA_DIST")) e.dist = atoi(v);
+  if (const char* v = getenv("ST2_UMMA_RES_TMA")) e.res_tma = v[0] != '0';
+  if (const char* v = getenv("ST2_UMMA_X_TMA")) e.x_tma = v[0] != '0';
+  if (const char* v = getenv("ST2_UMMA_LOADER")) e.loader = v[0] != '0';
+  g_env = e;
+  g_env_ready = true;
+}
+static UmEnv um_env() {
+  std::lock_guard<std::mutex> lk(g_env_mu);
+  if (!g_env_ready) um_env_read_locked();
+  return g_env;
+}
+
+static int um_layout(const St2ConvParams& p, int dev, const UmEnv& env, UmLayout& lay) {
   lay.n_tile = umma_n_tile(p.n_cols);
   ST2_REQUIRE(lay.n_tile != 0, "conv_umma: n_cols must be a multiple of 32");
   const int halo = (p.k - 1) * p.dil;
@@ -1472,17 +1504,11 @@ static int um_layout(const St2ConvParams& p, int dev, UmLayout& lay) {
   // CTA-pair mode (UmLayout::pair): 128-column bf16 tiles whose bias does not depend on the item.  Off unless
   // ST2_UMMA_PAIR=1 (A/B switch).  A stage then holds half a blob, and the ring is twice as deep in the same bytes:
   // a stage's round trip includes the relay through the peer CTA.
-  lay.dbg = 0;
-  if (const char* e = getenv("ST2_UMMA_DBG")) lay.dbg = atoi(e);
-  lay.spin = 0;
-  if (const char* e = getenv("ST2_UMMA_SPIN")) lay.spin = (uint32_t)atoi(e);
+  lay.dbg = env.dbg;
+  lay.spin = env.spin;
   lay.pair = 0;
-  {
-    const char* e = getenv("ST2_UMMA_PAIR");
-    if (e && e[0] == '1' && lay.n_tile == 128 && p.y_dtype == ST2_DT_BF16 && (!p.bias || p.bias_bstride == 0) &&
-        !(lay.dbg & 1))
-      lay.pair = 1;
-  }
+  if (env.pair && lay.n_tile == 128 && p.y_dtype == ST2_DT_BF16 && (!p.bias || p.bias_bstride == 0) && !(lay.dbg & 1))
+    lay.pair = 1;
   lay.w_slot = lay.pair ? lay.w_bytes / 2 : lay.w_bytes;
   lay.nw = lay.pair ? 2 * UM_W_STAGES : UM_W_STAGES;
   // With 5 or more taps per chunk the weight stream, not the activation ring, is what the MMAs wait for: up to 5
@@ -1493,8 +1519,8 @@ static int um_layout(const St2ConvParams& p, int dev, UmLayout& lay) {
     while (nw > UM_W_STAGES && (UM_SMEM_LIMIT - (nw * lay.w_slot + stg_bytes + misc_bytes)) / lay.a_bytes < 3) --nw;
     lay.nw = nw;
   }
-  if (const char* e = getenv("ST2_UMMA_WST")) {  // A/B switch
-    lay.nw = atoi(e);
+  if (env.wst > 0) {  // A/B switch
+    lay.nw = env.wst;
     if (lay.nw < 2) lay.nw = 2;
     if (lay.nw > UM_MAX_W) lay.nw = UM_MAX_W;
   }
@@ -1506,8 +1532,8 @@ static int um_layout(const St2ConvParams& p, int dev, UmLayout& lay) {
   // producers' prefetch policy: 0 = opportunistic (issue as soon as a slot is released), > 0 = fixed
   // distance in chunks.  ST2_UMMA_DIST overrides for A/B measurements.
   lay.dist = na - 2;  // measured: fixed distance beats opportunistic issue by 5-10 % on residual convs
-  if (const char* e = getenv("ST2_UMMA_DIST")) {
-    lay.dist = atoi(e);
+  if (env.dist >= 0) {
+    lay.dist = env.dist;
     if (lay.dist > na - 1) lay.dist = na - 1;
     if (lay.dist < 0) lay.dist = 0;
   }
@@ -1542,7 +1568,9 @@ typedef CUresult (*UmEncodeTiled)(CUtensorMap*, CUtensorMapDataType, cuuint32_t,
                                   const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
                                   CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
 static UmEncodeTiled g_encode = nullptr;
+static std::mutex g_init_mu;  // g_encode, g_num_sms
 static int um_encode_fn() {
+  std::lock_guard<std::mutex> lk(g_init_mu);
   if (g_encode) return ST2_OK;
   void* fn = nullptr;
   cudaDriverEntryPointQueryResult qres;
@@ -1634,6 +1662,48 @@ static void um_fastdiv(uint32_t d, uint32_t& m, uint32_t& l) {
 
 static int g_num_sms[64] = {};
 
+// SM count + the kernels' dynamic shared-memory limit, once per device
+static int um_device_setup(int dev, int* sms) {
+  std::lock_guard<std::mutex> lk(g_init_mu);
+  if (dev >= 64 || g_num_sms[dev] == 0) {
+    int n = 0;
+    ST2_CUDA_OK(cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev));
+    ST2_CUDA_OK(cudaFuncSetAttribute(conv_umma_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                     UM_SMEM_LIMIT));
+    ST2_CUDA_OK(cudaFuncSetAttribute(conv_umma_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                     UM_SMEM_LIMIT));
+    if (dev < 64) g_num_sms[dev] = n;
+    else { *sms = n; return ST2_OK; }
+  }
+  *sms = g_num_sms[dev];
+  return ST2_OK;
+}
+
+// Everything conv_umma would otherwise set up on its first launch on a device (driver entry point, shared-memory
+// attribute, the identity blobs of the residual / running-mean chunks: a cudaMalloc + synchronous copy), done at
+// st2_decoder_load time so that forward allocates nothing and never synchronises the host.  `acc_mult` = number of
+// resblock kernels (the running mean's 1/out_scale), 0 = none.
+int umma_prepare(int acc_mult) {
+  int dev = 0;
+  ST2_CUDA_OK(cudaGetDevice(&dev));
+  int rc = um_encode_fn();
+  if (rc) return rc;
+  int sms = 0;
+  rc = um_device_setup(dev, &sms);
+  if (rc) return rc;
+  um_env();
+  const uint8_t* blob = nullptr;
+  for (int n_tile : {64, 128}) {
+    rc = um_ident(dev, n_tile, 1.f, &blob);
+    if (rc) return rc;
+    for (int m = 2; m <= acc_mult; ++m) {
+      rc = um_ident(dev, n_tile, (float)m, &blob);
+      if (rc) return rc;
+    }
+  }
+  return ST2_OK;
+}
+
 // optional per-launch event timing (st2_prof_enable / st2_prof_read)
 struct UmProf {
   bool on = false;
@@ -1669,14 +1739,15 @@ int launch_conv_umma(const St2ConvParams& p, cudaStream_t st) {
   ST2_CUDA_OK(cudaGetDevice(&dev));
   UmLayout lay;
   memset(&lay, 0, sizeof(lay));
-  int rc = um_layout(p, dev, lay);
+  const UmEnv env = um_env();
+  int rc = um_layout(p, dev, env, lay);
   if (rc) return rc;
   CUtensorMap ymap;
   rc = um_ymap(p, &ymap);
   if (rc) return rc;
   // residual / y_old rows by TMA when the source is a plain [B][Lout][>= n_cols] bf16 view (not the x2-repeated
   // shortcut of the upsampling block); ST2_UMMA_RES_TMA=0 keeps the cp.async path (A/B switch)
-  static const bool tma_ok = [] { const char* e = getenv("ST2_UMMA_RES_TMA"); return !(e && e[0] == '0'); }();
+  const bool tma_ok = env.res_tma;
   CUtensorMap rmap = ymap;
   lay.res_tma = lay.acc_tma = 0;
   if (tma_ok && p.y_dtype == ST2_DT_BF16) {
@@ -1688,7 +1759,7 @@ int launch_conv_umma(const St2ConvParams& p, cudaStream_t st) {
       lay.res_tma = 1;
     }
   }
-  static const bool x_tma_ok = [] { const char* e = getenv("ST2_UMMA_X_TMA"); return !(e && e[0] == '0'); }();
+  const bool x_tma_ok = env.x_tma;
   CUtensorMap xmap = ymap, xmap8 = ymap;
   lay.x_tma = 0;
   if (x_tma_ok && (((uintptr_t)p.x) & 15) == 0 && (p.ldx % 8) == 0 && (p.x_bstride % 8) == 0) {
@@ -1698,7 +1769,7 @@ int launch_conv_umma(const St2ConvParams& p, cudaStream_t st) {
     if (rc) return rc;
     lay.x_tma = 1;
   }
-  static const bool loader_ok = [] { const char* e = getenv("ST2_UMMA_LOADER"); return !(e && e[0] == '0'); }();
+  const bool loader_ok = env.loader;
   lay.loader = loader_ok && lay.x_tma && (!lay.n_res || lay.res_tma) && (!lay.n_acc || lay.acc_tma);
   const int n_ttiles = ceil_div(p.Lout, UM_TM), n_ntiles = p.n_cols / lay.n_tile;
   ST2_REQUIRE(!p.stats || p.n_tiles >= n_ttiles, "conv_umma: n_tiles");
@@ -1706,16 +1777,9 @@ int launch_conv_umma(const St2ConvParams& p, cudaStream_t st) {
   um_fastdiv((uint32_t)n_ttiles, lay.tt_m, lay.tt_l);
   const int64_t total = (int64_t)p.B * n_ttiles * n_ntiles;
   ST2_REQUIRE(total < (1ll << 31), "conv_umma: too many tiles");
-  if (dev >= 64 || g_num_sms[dev] == 0) {
-    int n = 0;
-    ST2_CUDA_OK(cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev));
-    ST2_CUDA_OK(cudaFuncSetAttribute(conv_umma_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                     UM_SMEM_LIMIT));
-    ST2_CUDA_OK(cudaFuncSetAttribute(conv_umma_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                     UM_SMEM_LIMIT));
-    if (dev < 64) g_num_sms[dev] = n;
-  }
-  int sms = dev < 64 ? g_num_sms[dev] : 148;
+  int sms = 148;
+  rc = um_device_setup(dev, &sms);
+  if (rc) return rc;
   int grid = (int)(total < sms ? total : sms);
   CUtensorMap wmap = ymap, wmap_res = ymap, wmap_acc = ymap;
   if (lay.pair) {  // decided in um_layout
@@ -1767,6 +1831,11 @@ int launch_conv_umma(const St2ConvParams& p, cudaStream_t st) {
 
 }  // namespace st2
 
+extern "C" int st2_umma_reload_env(void) {
+  std::lock_guard<std::mutex> lk(st2::g_env_mu);
+  st2::um_env_read_locked();
+  return ST2_OK;
+}
 extern "C" int st2_umma_wait_profile(uint64_t out[16], int reset) {
   unsigned long long h[16];
   ST2_CUDA_OK(cudaDeviceSynchronize());

@@ -12,6 +12,8 @@
 //   istft        exp / sin heads, inverse 20-point DFT, windowed overlap-add, envelope division and
 //                trimming (istftnet.py:377-379, 99-104); writes the final waveform.
 // All four are memory-bound; bytes per unit are listed in DESIGN.md.
+#include <mutex>
+
 #include "common.cuh"
 
 namespace st2 {
@@ -23,10 +25,14 @@ __constant__ float c_cos20[20];
 __constant__ float c_sin20[20];
 __constant__ float c_hann20[20];
 static bool g_tables_ready[64] = {};
+static std::mutex g_tables_mu;
 
+// constant tables of the 20-point DFT, once per device (st2_decoder_load calls it through source_prepare, so a forward
+// never runs the synchronous cudaMemcpyToSymbol)
 static int ensure_tables() {
   int dev = 0;
   ST2_CUDA_OK(cudaGetDevice(&dev));
+  std::lock_guard<std::mutex> lk(g_tables_mu);
   if (dev < 64 && g_tables_ready[dev]) return ST2_OK;
   float c[20], s[20], w[20];
   const double pi = 3.14159265358979323846;
@@ -44,6 +50,8 @@ static int ensure_tables() {
   if (dev < 64) g_tables_ready[dev] = true;
   return ST2_OK;
 }
+
+int source_prepare() { return ensure_tables(); }
 
 // ----------------------------------------------------------------------- phase scan
 // grid B, block 256.  phase layout [B][9][T] (harmonic-major).

@@ -341,6 +341,22 @@ def test_alignment_expansion_matches_the_notebook(shift):
     assert torch.equal(got, ref)
 
 
+@pytest.mark.parametrize("typ", ["istftnet", "hifigan"])
+def test_alignment_kernels_vs_notebook_fixture(typ):
+    """row N3 against the notebook's own statements (tests/golden/alignment_notebook.npz, generated by
+    oracle/make_golden_alignment.py from Demo/Inference_LibriTTS.ipynb cell 16): indices + gather bit exact"""
+    import numpy as np
+    from styletts2_b200.alignment import alignment_indices, expand
+    g = np.load(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "alignment_notebook.npz"))
+    for name in "abcd":
+        dur = torch.from_numpy(g[f"{name}_dur"])
+        idx, totals = alignment_indices(dur.cuda(), shift=(typ == "hifigan"))
+        assert int(totals[0]) == int(dur.sum()) and idx.shape[1] == int(dur.sum())
+        for src, key in ((torch.from_numpy(g[f"{name}_d"]).transpose(-1, -2), "en"), (torch.from_numpy(g[f"{name}_t_en"]), "asr")):
+            got = expand(src.contiguous().cuda(), idx).cpu()
+            assert torch.equal(got, torch.from_numpy(g[f"{name}_{typ}_{key}"]))
+
+
 @pytest.mark.parametrize("kind", ["istftnet", "hifigan"])
 def test_decoder_with_fused_alignment_equals_materialised_asr(kind):
     import synthetic as synth

@@ -184,6 +184,8 @@ def test_f0n_oracle_vs_reference(T):
     sd = synth.synth_f0n_state_dict(synth.F0N_CFG, seed=0)
     lstm = porc.shared_lstm(g["x"], porc.Params(sd))
     assert (lstm - g["lstm"]).abs().max().item() < 2e-6
+    F0a, Na = porc.f0n_forward(sd, g["x"], g["s"], aten_lstm=True)   # the timed baseline's nn.LSTM route
+    assert (F0a - g["F0"]).abs().max().item() < 5e-6 and (Na - g["N"]).abs().max().item() < 5e-6
     F0, N = porc.f0n_forward(sd, g["x"], g["s"])
     assert F0.shape == g["F0"].shape == (g["x"].shape[0], 2 * T)
     assert (F0 - g["F0"]).abs().max().item() < 5e-6
@@ -225,3 +227,22 @@ def test_sampler_schedule_known_values():
     assert (s[:-1][1:] < s[:-1][:-1]).all()
     up, down, mid = sorc.adpm2_sigmas(s[1], s[2])
     assert abs(up ** 2 + down ** 2 - float(s[2]) ** 2) < 1e-6 and down <= float(mid) <= float(s[1])
+
+
+@pytest.mark.parametrize("typ", ["istftnet", "hifigan"])
+def test_alignment_oracle_vs_notebook_cell(typ):
+    """oracle/alignment_oracle.py against the statements of Demo/Inference_LibriTTS.ipynb cell 16 themselves
+    (oracle/make_golden_alignment.py cuts them out of the notebook JSON and exec()s them): bit exact, incl. a
+    one-token text and the ``pred_dur[-1] = 1`` branch.  This is what pins row N3."""
+    from oracle import alignment_oracle as aorc
+    g = np.load(os.path.join(GOLD, "alignment_notebook.npz"))
+    for name in "abcd":
+        dur = torch.from_numpy(g[f"{name}_dur"])
+        frames = int(dur.sum())
+        aln = aorc.one_hot_alignment(dur, frames)
+        assert torch.equal(aln, torch.from_numpy(g[f"{name}_{typ}_aln"]))
+        d, t_en = torch.from_numpy(g[f"{name}_d"]), torch.from_numpy(g[f"{name}_t_en"])
+        en = aorc.expand(d.transpose(-1, -2), dur[None], frames, typ == "hifigan")
+        asr = aorc.expand(t_en, dur[None], frames, typ == "hifigan")
+        assert torch.equal(en, torch.from_numpy(g[f"{name}_{typ}_en"]))
+        assert torch.equal(asr, torch.from_numpy(g[f"{name}_{typ}_asr"]))
