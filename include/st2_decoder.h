@@ -13,9 +13,13 @@
  * Conventions: plain C, no torch types.  Every function returns 0 on success or a
  * negative ST2_E* code and never throws; st2_last_error() gives a thread-local message.
  * All device pointers belong to the caller (torch allocates wav_out and the workspace).
- * A handle is bound to the CUDA device current at create time, is immutable after load,
- * and may be used concurrently from several streams as long as each call has its own
- * workspace.  No hidden host synchronisation inside forward.  sm_100a only; there is no
+ * A handle is bound to the CUDA device current at create time and is immutable after load.
+ * One forward at a time per handle: callers serialise the calls on ONE handle (the Python
+ * module holds a lock per module; the per-call launch count lives in the handle); different
+ * handles (one per device / per thread, e.g. the one-thread-per-device calling convention
+ * of train_finetune.py:96-101) run concurrently.  All one-time per-device setup (identity
+ * blobs, constant tables, kernel attributes) happens in st2_decoder_load: forward allocates
+ * nothing and never synchronises the host, so it can be stream-captured.  sm_100a only; there is no
  * CPU fallback: without a usable GPU every compute entry point fails with ST2_ECUDA.
  */
 #ifndef ST2_DECODER_H
@@ -189,6 +193,12 @@ int st2_expand_alignment(const float* x, const int32_t* idx, int B, int C, int L
  * clip(rint(x * 32767), -32768, 32767); trim_tail drops the last samples of every item (the LibriTTS
  * notebook cuts 50: "weird pulse at the end of the model"). */
 int st2_wave_to_pcm16(const float* wav, int B, int64_t L, int64_t trim_tail, int16_t* out, void* stream);
+/* The reference's log-mel front end (next row N4; /root/reference/meldataset.py:35-43: torchaudio MelSpectrogram(n_mels 80,
+ * n_fft 2048, win_length 1200, hop_length 300) with torchaudio's defaults (sample_rate 16000, centre, reflect padding,
+ * periodic Hann, power 2, HTK scale, no normalisation), then (log(1e-5 + mel) + 4) / 4).  wav [B, L] fp32 (L > 1024) ->
+ * mel_out [B, 80, L / 300 + 1] fp32.  One CTA per frame: 2048-point FFT in shared memory. */
+int st2_log_mel(const float* wav, int B, int64_t L, float* mel_out, void* stream);
+int st2_log_mel_frames(int64_t L);
 
 /* Number of kernel launches the last forward on this handle issued (bench bookkeeping). */
 int64_t st2_decoder_last_launches(const St2Decoder* h);
@@ -222,6 +232,9 @@ int st2_prof_read(double* umma_ms, int64_t* umma_launches, double* umma_flops, i
 /* Debug: per-role barrier-wait accounting of conv_umma_kernel, filled while ST2_UMMA_DBG has bit 64 set (SM clock
  * cycles summed over all CTAs since the last reset; index meaning in csrc/conv_umma.cu, g_um_wait).  Synchronises. */
 int st2_umma_wait_profile(uint64_t out[16], int reset);
+/* Debug: the ST2_UMMA_* A/B switches (csrc/conv_umma.cu) are read from the environment once, at the first launch;
+ * a tool that changes them afterwards calls this to have them read again.  No counterpart in the reference. */
+int st2_umma_reload_env(void);
 /* rows of the time tile and partial-statistics tiles each implementation uses. */
 int st2_conv_tile_rows(int use_umma);
 

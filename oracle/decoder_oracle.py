@@ -413,10 +413,13 @@ def snr_db(ref: torch.Tensor, test: torch.Tensor) -> float:
     return float(10 * torch.log10((ref ** 2).sum() / ((ref - test) ** 2).sum().clamp_min(1e-300)))
 
 
-def log_mel(wav: torch.Tensor, sr=24000, n_fft=2048, win=1200, hop=300, n_mels=80):
+def log_mel(wav: torch.Tensor, sr=16000, n_fft=2048, win=1200, hop=300, n_mels=80):
     """The reference's mel front end (meldataset.py:35-43: torchaudio MelSpectrogram
     n_mels 80 / n_fft 2048 / win 1200 / hop 300, log(1e-5+mel), (x+4)/4) restated with
-    torch.stft and an HTK mel filterbank (torchaudio's defaults: power 2, htk, norm None)."""
+    torch.stft and an HTK mel filterbank (torchaudio's defaults: power 2, htk, norm None, and
+    sample_rate 16000 -- the reference never passes its 24 kHz rate, so the filters span 0..8000 "Hz" over
+    the 1025 bins).  Pinned on the reference's own statements by oracle/make_golden_logmel.py ->
+    tests/golden/logmel.npz (round 1 used sr=24000 here: 2.0 off the reference's values)."""
     wav = wav.reshape(-1, wav.shape[-1]).double()
     w = torch.hann_window(win, periodic=True, dtype=torch.float64)
     X = torch.stft(wav, n_fft, hop, win, window=w, center=True, pad_mode="reflect",

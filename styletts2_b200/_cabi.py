@@ -107,6 +107,9 @@ SYMBOLS = {
     "st2_prof_enable": (C.c_int, [C.c_int]),
     "st2_prof_read": (C.c_int, [C.POINTER(C.c_double), C.POINTER(C.c_int64), C.POINTER(C.c_double), C.c_int]),
     "st2_umma_wait_profile": (C.c_int, [C.POINTER(C.c_uint64), C.c_int]),
+    "st2_umma_reload_env": (C.c_int, []),
+    "st2_log_mel": (C.c_int, [C.c_void_p, C.c_int, C.c_int64, C.c_void_p, C.c_void_p]),
+    "st2_log_mel_frames": (C.c_int, [C.c_int64]),
     "st2_conv_tile_rows": (C.c_int, [C.c_int]),
     "st2_source_har": (C.c_int, [C.c_void_p, C.c_void_p, C.c_uint64, C.c_void_p, C.c_float, C.c_int,
                                  C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p]),

@@ -147,6 +147,8 @@ int launch_conv_simt(const St2ConvParams& p, cudaStream_t st);
 int launch_conv_umma(const St2ConvParams& p, cudaStream_t st);
 int conv_tile_rows(bool umma);
 int umma_n_tile(int n_cols);  // GEMM columns per tcgen05 tile for a layer of n_cols (0: none)
+int umma_prepare(int acc_mult);  // conv_umma's one-time per-device setup (called by st2_decoder_load, never by forward)
+int source_prepare();            // the DFT constant tables of source.cu, likewise
 
 int launch_style_fc(const float* s, const float* W, const float* bvec, float* h, int B, int style,
                     int rows, cudaStream_t st);

@@ -54,6 +54,17 @@
 
 #include "common.cuh"
 
+// compile-time A/B switches (tools build variants with -D...)
+#ifndef UM_OPT_NOMASK
+#define UM_OPT_NOMASK 1     // producers: no row mask in the arithmetic, out-of-range rows zeroed afterwards (edge tiles)
+#endif
+#ifndef UM_OPT_SNAKE4
+#define UM_OPT_SNAKE4 1     // Snake with 4 parameters per channel: w = 2a (x + h) - 1 instead of its own scale / shift pair
+#endif
+#ifndef UM_OPT_STATS16
+#define UM_OPT_STATS16 0    // epilogue statistics pass: 16 instead of 8 shared-memory loads in flight
+#endif
+
 namespace st2 {
 
 constexpr int UM_TM = 256;      // output rows per tile
@@ -546,7 +557,11 @@ __device__ __forceinline__ float um_act(float v, float sc, float sh, float wsc, 
                                         float slope) {
   if (ACT == ST2_ACT_SNAKE) {
     const float u2 = fmaf(v, sc, sh);     // u + 1/(2a)
+#if UM_OPT_SNAKE4
+    const float w2 = fmaf(wsc, u2, -1.f); // wsc = 2a: 2a (u + 1/(2a)) - 1 = 2 a u
+#else
     const float w2 = fmaf(v, wsc, wsh);   // 2 a u
+#endif
     return fmaf(-hia, __cosf(w2), u2);
   }
   const float u = fmaf(v, sc, sh);
@@ -721,8 +736,12 @@ __device__ __forceinline__ void um_produce(const St2ConvParams& p, const UmLayou
       if (ACT == ST2_ACT_SNAKE) {
         const float a = alr[e];
         hia[e] = __fdividef(0.5f, a);
+#if UM_OPT_SNAKE4
+        wsc[e] = a + a;
+#else
         wsc[e] = 2.f * a * sc[e];
         wsh[e] = 2.f * a * sh[e];
+#endif
         sh[e] += hia[e];
       }
     }
@@ -752,11 +771,15 @@ __device__ __forceinline__ void um_produce(const St2ConvParams& p, const UmLayou
         const int i = i0 + ii;
         const bool in_tile = h < NB || 32 * i < tot;
         const uint32_t addr = dst + (uint32_t)i * 4096u;
+#if UM_OPT_NOMASK
+        if (IDENT) continue;  // rows outside [0, Lin) are zeroed below
+#else
         const uint32_t mask = (32 * i >= lo && 32 * i < hi) ? 0xFFFFFFFFu : 0u;
         if (IDENT) {
           if (in_tile && mask == 0u) sts128(addr, make_uint4(0u, 0u, 0u, 0u));
           continue;
         }
+#endif
         const uint32_t w[4] = {raw[ii].x, raw[ii].y, raw[ii].z, raw[ii].w};
         uint32_t o[4];
 #pragma unroll
@@ -765,11 +788,24 @@ __device__ __forceinline__ void um_produce(const St2ConvParams& p, const UmLayou
                                         hia[2 * e2], p.slope);
           const float hi_ = um_act<ACT>(bf16hi(w[e2]), sc[2 * e2 + 1], sh[2 * e2 + 1], wsc[2 * e2 + 1],
                                         wsh[2 * e2 + 1], hia[2 * e2 + 1], p.slope);
+#if UM_OPT_NOMASK
+          o[e2] = pack_bf16x2(lo_, hi_);
+#else
           o[e2] = pack_bf16x2(lo_, hi_) & mask;
+#endif
         }
         if (in_tile) sts128(addr, make_uint4(o[0], o[1], o[2], o[3]));
       }
     }
+#if UM_OPT_NOMASK
+    // the conv's zero padding applies after the activation: rows outside [0, Lin) become zeros (first / last tiles
+    // of an item only; a branch no thread of an interior tile takes).  Measured: -2..8 % on every conv shape.
+    if (lo > 0 || hi < tot) {
+#pragma unroll 1
+      for (int i = 0; 32 * i < tot; ++i)
+        if (32 * i < lo || 32 * i >= hi) sts128(dst + (uint32_t)i * 4096u, make_uint4(0u, 0u, 0u, 0u));
+    }
+#endif
     fence_proxy_async_smem();
     mbar_arrive(&misc->a_full[q.stage]);
     w_math += um_clk(prof) - c_ar;
@@ -1006,7 +1042,11 @@ __device__ __forceinline__ void um_epilogue(const St2ConvParams& p, const UmLayo
         const int r1 = p.Lout - row0 - grp * ncp;  // valid rows of this thread's row group
         if (r1 >= ncp) {
           // rows grp*ncp + 8 m + i sit 1024 m bytes after col_addr[i] (the swizzle repeats every 8 rows)
+#if UM_OPT_STATS16
+#pragma unroll 2
+#else
 #pragma unroll 1
+#endif
           for (int m = 0; m < ncp; m += 8) {
 #pragma unroll
             for (int i = 0; i < 8; i += 2) {

@@ -1395,6 +1395,18 @@ extern "C" int st2_decoder_load(St2Decoder* h, const St2Tensor* tensors, int n) 
               ", this library is built for sm_100a only");
     return ST2_ECUDA;
   }
+  // one-time per-device setup of the kernels (identity blobs, constant tables, shared-memory attributes, the
+  // tensor-map encoder) happens here, so that forward neither allocates nor synchronises the host
+  {
+    int cur = 0;
+    ST2_CUDA_OK(cudaGetDevice(&cur));
+    if (cur != h->device) ST2_CUDA_OK(cudaSetDevice(h->device));
+    const bool dec = h->cfg.kind == ST2_KIND_ISTFTNET || h->cfg.kind == ST2_KIND_HIFIGAN;
+    int rc = umma_prepare(dec ? h->cfg.n_resblock_kernels : 0);
+    if (!rc) rc = source_prepare();
+    if (cur != h->device) ST2_CUDA_OK(cudaSetDevice(cur));
+    if (rc) return rc;
+  }
   return do_load(h, tensors, n);
 }
 

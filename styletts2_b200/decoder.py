@@ -15,6 +15,7 @@ from __future__ import annotations
 
 import ctypes as C
 import math
+import threading
 from typing import Dict, List, Optional, Sequence
 
 import torch
@@ -93,6 +94,10 @@ class _DecoderBase(nn.Module):
         self.cuda_graphs = False
         self.max_graphs = 4
         self._graphs: Dict[tuple, dict] = {}
+        # one forward at a time per module (include/st2_decoder.h): the handle table, the graph cache, the seed and the
+        # handle's launch count are shared by the threads of a one-thread-per-device caller (train_finetune.py:96-101);
+        # launches are asynchronous, so devices still overlap
+        self._lock = threading.RLock()
         self.eval()
 
     # ------------------------------------------------------------------ parameters
@@ -210,6 +215,13 @@ class _DecoderBase(nn.Module):
             raise RuntimeError("styletts2_b200.Decoder is forward-only: call .eval() first")
         if not asr.is_cuda:
             raise RuntimeError("styletts2_b200.Decoder needs CUDA tensors (sm_100a); there is no CPU path")
+        with self._lock:
+            return self._forward_locked(asr, F0_curve, N, s, noise=noise, har_source=har_source, har=har,
+                                        precision=precision, return_excitation=return_excitation,
+                                        return_taps=return_taps, item_offset=item_offset, alignment=alignment)
+
+    def _forward_locked(self, asr, F0_curve, N, s, *, noise, har_source, har, precision, return_excitation,
+                        return_taps, item_offset, alignment):
         if asr.dim() != 3 or F0_curve.dim() != 2 or N.dim() != 2 or s.dim() != 2:
             raise RuntimeError("expected asr [B,C,T/2], F0_curve [B,T], N [B,T], s [B,style]")
         B, Cin, T2 = asr.shape

@@ -71,8 +71,8 @@ class F0NPredictor(_DecoderBase):
         dev = x.device
         x_ = x.to(dev, torch.float32).contiguous()
         s_ = s.to(dev, torch.float32).contiguous()
-        h = self._handle_for(dev)
-        with torch.cuda.device(dev):
+        with self._lock, torch.cuda.device(dev):
+            h = self._handle_for(dev)
             need = lib.st2_f0n_workspace_bytes(h, B, T, prec_id)
             if need < 0:
                 check(int(need), "st2_f0n_workspace_bytes")

@@ -114,8 +114,8 @@ class StyleSampler(_DecoderBase):
     def _run(self, single, x, sigma, embedding, features, opts, prec):
         B, n = x.shape[0], embedding.shape[1]
         dev = x.device
-        h = self._handle_for(dev)
-        with torch.cuda.device(dev):
+        with self._lock, torch.cuda.device(dev):
+            h = self._handle_for(dev)
             need = lib.st2_sampler_workspace_bytes(h, B, n, opts.precision, int(opts.embedding_scale != 1.0))
             if need < 0:
                 check(int(need), "st2_sampler_workspace_bytes")

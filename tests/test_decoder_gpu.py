@@ -475,3 +475,34 @@ def test_long_form_item_vs_oracle():
             assert err < 1e-3, err
         else:
             assert snr >= 30.0, snr
+
+
+def test_two_threads_share_one_module():
+    """one-thread-per-device callers (the reference's train_finetune.py:96-101 convention) may call ONE module from
+    several threads: the module serialises the calls on its handle / graph cache (decoder.py ``_lock``), each thread on
+    its own stream, and every result equals the single-threaded one bit for bit (explicit item_offset / noise)."""
+    import threading
+    import synthetic as synth
+    dec, sd, cfg = _get("istftnet")
+    inp = synth.synth_inputs(cfg, 2, 40, seed=77)
+    args = [inp[k].cuda() for k in ("asr", "F0_curve", "N", "s")]
+    noise = inp["noise"].cuda()
+    want = dec(*args, noise=noise, precision="bf16").clone()
+    torch.cuda.synchronize()
+    outs, errs = {}, []
+
+    def worker(i):
+        try:
+            st = torch.cuda.Stream()
+            with torch.cuda.stream(st):
+                for _ in range(6):
+                    outs[i] = dec(*args, noise=noise, precision="bf16")
+            st.synchronize()
+        except Exception as e:  # noqa: BLE001
+            errs.append(e)
+    ths = [threading.Thread(target=worker, args=(i,)) for i in range(2)]
+    [t.start() for t in ths]
+    [t.join() for t in ths]
+    assert not errs, errs
+    for i in range(2):
+        assert torch.equal(outs[i], want)

@@ -295,12 +295,36 @@ def test_conv_umma_cta_pair_mode_is_bit_identical(case, monkeypatch):
     outs = []
     for mode in ("0", "1"):
         monkeypatch.setenv("ST2_UMMA_PAIR", mode)
+        _cabi.check(_cabi.lib.st2_umma_reload_env())       # the switches are cached: read them again
         y, st = run_conv("umma", x.to(torch.bfloat16).cuda(), w, bias, k=k, dil=dil, pad=dil * (k - 1) // 2, ss=ss,
                          act=act, slope=0.1, alpha=alpha, res=res, out_scale=0.5 if acc else 1.0, y_old=y_old,
                          want_stats=not acc)
         torch.cuda.synchronize()
         outs.append((y.float().cpu(), None if st is None else st.cpu()))
+    monkeypatch.delenv("ST2_UMMA_PAIR")
+    _cabi.check(_cabi.lib.st2_umma_reload_env())
     assert torch.isfinite(outs[0][0]).all()
     assert torch.equal(outs[0][0], outs[1][0])
     if outs[0][1] is not None:
         assert torch.equal(outs[0][1], outs[1][1])
+
+
+def test_log_mel_kernel_vs_reference_front_end():
+    """next row N4: st2_log_mel (2048-point FFT per frame in shared memory + sparse HTK filterbank) against the
+    reference's own torchaudio front end (tests/golden/logmel.npz from meldataset.py:35-43) and the oracle; a batch
+    of items with ragged lengths goes through one call each"""
+    import os
+    from styletts2_b200.output import log_mel
+    from oracle import decoder_oracle as orc
+    g = np.load(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "logmel.npz"))
+    for n in "abc":
+        wave = torch.from_numpy(g[f"{n}_wave"])
+        got = log_mel(wave[None].cuda()).cpu()
+        ref = torch.from_numpy(g[f"{n}_mel"])
+        assert got.shape == ref.shape
+        assert (got - ref).abs().max().item() < 2e-4
+    w = 0.2 * torch.randn(3, 1, 12000, generator=torch.Generator().manual_seed(4))
+    got = log_mel(w.cuda()).cpu().double()
+    assert (got - orc.log_mel(w[:, 0])).abs().max().item() < 2e-4
+    with pytest.raises(ValueError):
+        log_mel(torch.zeros(1, 1000).cuda())

@@ -246,3 +246,13 @@ def test_alignment_oracle_vs_notebook_cell(typ):
         asr = aorc.expand(t_en, dur[None], frames, typ == "hifigan")
         assert torch.equal(en, torch.from_numpy(g[f"{name}_{typ}_en"]))
         assert torch.equal(asr, torch.from_numpy(g[f"{name}_{typ}_asr"]))
+
+
+def test_log_mel_oracle_vs_reference_front_end():
+    """oracle log_mel against meldataset.py:35-43 executed verbatim with torchaudio (oracle/make_golden_logmel.py);
+    the reference computes in fp32, the oracle in double"""
+    g = np.load(os.path.join(GOLD, "logmel.npz"))
+    for n in "abc":
+        m = orc.log_mel(torch.from_numpy(g[f"{n}_wave"]))
+        ref = torch.from_numpy(g[f"{n}_mel"]).double()
+        assert m.shape == ref.shape and (m - ref).abs().max().item() < 1e-4

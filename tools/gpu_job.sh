@@ -10,6 +10,7 @@
 #   step:<wl>        per-launch ncu metric list (time, DRAM bytes, tensor-active) of every conv_umma launch of one step
 #   launches:<wl>    ncu launch list (gpu__time_duration) of one bench run
 #   sanitize         compute-sanitizer memcheck + racecheck of the kernel unit tests (small shapes)
+#   scale:<wl>       bench.py --workload <wl> at N = 1 2 4 8 GPUs of one box (SCALE_NS / SCALE_ARGS override)
 #   ab:<wl>          same-box A/B of gpurun_ab/libst2dec_{old,new}.so on bench workload <wl> (old new old new)
 mkdir -p gpurun_out
 S=gpurun_out/summary.txt
@@ -34,8 +35,16 @@ for job in "$@"; do
       run ncu_launches_$wl 1200 ncu --metrics gpu__time_duration.sum --clock-control none -c 1500 --csv \
           --log-file gpurun_out/launches_$wl.csv python bench.py --workload $wl --steps 2 --warmup 3 --no-cpu-baseline --no-graphs ;;
     sanitize)
-      run san_mem 1500 compute-sanitizer --tool memcheck --error-exitcode 9 python -m pytest tests/test_kernels_gpu.py -q -m gpu -x -k "sanitize or umma or lstm"
-      run san_race 1500 compute-sanitizer --tool racecheck --error-exitcode 9 python -m pytest tests/test_kernels_gpu.py -q -m gpu -x -k "sanitize or umma or lstm" ;;
+      SEL='tests/test_kernels_gpu.py tests/test_predictor_gpu.py -k "umma or f0n_fp32 or f0n_ragged"'
+      run san_mem 900 bash -c "compute-sanitizer --tool memcheck --error-exitcode 9 python -m pytest $SEL -q -m gpu -x --tb=line -p no:cacheprovider"
+      run san_race 900 bash -c "compute-sanitizer --tool racecheck --error-exitcode 9 python -m pytest $SEL -q -m gpu -x --tb=line -p no:cacheprovider"
+      run san_sync 900 bash -c "compute-sanitizer --tool synccheck --error-exitcode 9 python -m pytest $SEL -q -m gpu -x --tb=line -p no:cacheprovider" ;;
+    scale:*) wl=${job#scale:}   # needs gpurun --gpus 8: one line per N in gpurun_out/scale_<wl>.jsonl
+      for n in ${SCALE_NS:-1 2 4 8}; do
+        if [ $n = 1 ]; then cmd="python bench.py"; else cmd="python -m torch.distributed.run --nnodes=1 --nproc-per-node $n --master-addr 127.0.0.1 --master-port $((29500 + n)) bench.py"; fi
+        timeout 900 $cmd --gpus $n --workload $wl --no-cpu-baseline --no-library-baseline ${SCALE_ARGS:-} 2> gpurun_out/scale_${wl}_$n.err | tail -n 1 >> gpurun_out/scale_$wl.jsonl
+        echo "scale_${wl}_$n rc=$?" >> $S
+      done ;;
     ab:*) wl=${job#ab:}
       for v in old new old new; do
         cp gpurun_ab/libst2dec_$v.so styletts2_b200/_lib/libst2dec.so

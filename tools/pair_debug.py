@@ -19,6 +19,7 @@ def case(B, L, cin, n, k, dil, act, res, stats, acc=False, f32=False, bias_on=Tr
     out = {}
     for mode in ("0", "1"):
         os.environ["ST2_UMMA_PAIR"] = mode
+        _cabi.check(_cabi.lib.st2_umma_reload_env())
         try:
             y, st = run_conv("umma", x, w, bias, k=k, dil=dil, pad=dil * (k - 1) // 2, ss=ss, act=act, slope=0.1, alpha=alpha,
                              res=r, out_scale=0.5 if acc else 1.0, y_old=yo, want_stats=stats,

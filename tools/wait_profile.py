@@ -40,8 +40,10 @@ if "--hifi" in sys.argv:
 for name, L, cin, n, k, dil, act, r, s, acc in cases:
     p, keep = make(B, L, cin, n, k, dil, act, r, s, acc)
     os.environ.pop("ST2_UMMA_DBG", None)
+    check(lib.st2_umma_reload_env())
     us = time_it(p, 5)
     os.environ["ST2_UMMA_DBG"] = "64"
+    check(lib.st2_umma_reload_env())
     out = (C.c_uint64 * 16)()
     check(lib.st2_conv_umma(C.byref(p), None))
     check(lib.st2_umma_wait_profile(out, 1))
@@ -58,5 +60,6 @@ for name, L, cin, n, k, dil, act, r, s, acc in cases:
           f"| EPI: t_full {pct(6, 5):4.1f}% stg_free {pct(7, 5):4.1f}% stats {pct(8, 5):4.1f}% "
           f"| PROD: a_empty {pct(10, 9):4.1f}% raw_full {pct(11, 9):4.1f}% math {pct(12, 9):4.1f}%", flush=True)
     os.environ.pop("ST2_UMMA_DBG", None)
+    check(lib.st2_umma_reload_env())
     del keep
     torch.cuda.empty_cache()
