@@ -80,6 +80,11 @@ def _config(workload, world, graphs=True):
             "parallelism": (f"dp{world} (independent batches, no collective)" if workload != "c5" else
                             f"dp{world}: the 512 rows split into {per_rank} per GPU, no collective (strong scaling)")}
 METRIC = "audio-sec/sec decoded (iSTFTNet, bf16)"
+
+
+def _metric(kind):
+    """BASELINE.json's metric for the iSTFTNet shapes; the HiFi-GAN shape (config 3) names its decoder"""
+    return METRIC if kind == "istftnet" else "audio-sec/sec decoded (HiFi-GAN, bf16)"
 UNIT = "audio-sec/sec"
 
 
@@ -727,7 +732,7 @@ def run_reference(args):
     sb, st = 1, T  # bounded sample: one utterance of the workload per step
     v, ms, threads = _oracle_cpu_decoder(kind, sb, st, args.steps, max(1, args.warmup))
     line = {
-        "impl": "reference", "metric": METRIC, "value": round(v, 4), "unit": UNIT, "n_gpus": args.gpus,
+        "impl": "reference", "metric": _metric(kind), "value": round(v, 4), "unit": UNIT, "n_gpus": args.gpus,
         "steps": args.steps, "warmup": max(1, args.warmup), "ms_per_step": round(ms, 2),
         "higher_is_better": True, "scaling": "strong" if args.workload == "c5" else "weak", "vs_baseline": None,
         "dtype": "f32", "data": "synthetic",
@@ -763,7 +768,7 @@ def run_reference_gpu(args):
     lib_ = _library_gpu(kind, B, T, args.steps, max(3, args.warmup), dev)
     clocks = sampler.stop()
     best = lib_["bf16_autocast"]
-    line = {"impl": "reference-gpu", "metric": METRIC, "value": best["value"], "unit": UNIT, "n_gpus": 1, "steps": args.steps,
+    line = {"impl": "reference-gpu", "metric": _metric(kind), "value": best["value"], "unit": UNIT, "n_gpus": 1, "steps": args.steps,
             "warmup": max(3, args.warmup), "ms_per_step": best["ms_per_step"], "higher_is_better": True, "scaling": "weak",
             "vs_baseline": None, "dtype": "bf16 (autocast); fp32 figure in library_baseline", "data": "synthetic",
             "config": _config(args.workload, 1, graphs=False), "library_baseline": lib_, "clocks": clocks,
@@ -899,13 +904,14 @@ def run_ours(args):
     roof = None
     if umma_n.value > 0 and umma_ms.value > 0:
         ach = umma_fl.value / (umma_ms.value * 1e-3) / 1e12
-        traffic = None  # DRAM bytes per launch of this kernel, from the committed ncu capture (profiles/)
+        traffic, traffic_src = None, None  # DRAM bytes per launch of this kernel, from the committed ncu capture (profiles/)
         tp = os.path.join(ROOT, "profiles", "conv_umma_traffic.json")
         if args.workload == "c2" and os.path.exists(tp):
-            traffic = round(json.load(open(tp))["dram_bytes_per_launch"])
+            tj = json.load(open(tp))
+            traffic, traffic_src = round(tj["dram_bytes_per_launch"]), tj.get("source")
         roof = {"bound": "tensor", "achieved": round(ach, 2), "peak": peaks["tf_sustained"], "unit": "TFLOP/s",
                 "frac": round(ach / peaks["tf_sustained"], 4), "traffic": traffic,
-                "traffic_unit": "bytes per launch (dram read+write, ncu, profiles/r1_v7_ncu_conv_umma_step_c2.csv)",
+                "traffic_unit": f"bytes per launch (dram read + write, ncu: {traffic_src})",
                 "kernel": "conv_umma_kernel (tcgen05 implicit-GEMM conv)",
                 "launches_per_step": umma_n.value // roof_steps,
                 "kernel_ms_per_step": round(umma_ms.value / roof_steps, 3),
@@ -929,7 +935,7 @@ def run_ours(args):
     ws_bytes = int(_cabi.lib.st2_decoder_workspace_bytes(dec._native[local], B, T,
                                                          _cabi.PREC_BF16 if prec == "bf16" else _cabi.PREC_FP32))
     line = {
-        "metric": METRIC, "value": round(value, 2), "unit": UNIT, "n_gpus": world, "steps": args.steps,
+        "metric": _metric(kind), "value": round(value, 2), "unit": UNIT, "n_gpus": world, "steps": args.steps,
         "warmup": max(3, args.warmup), "ms_per_step": round(ms_step, 3), "higher_is_better": True,
         "scaling": scaling, "vs_baseline": None, "dtype": prec, "data": "synthetic",
         "config": _config(args.workload, world, graphs=dec.cuda_graphs),

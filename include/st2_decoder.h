@@ -56,6 +56,9 @@ extern "C" {
 /* arithmetic of the dense contractions */
 #define ST2_PREC_FP32 0 /* fp32 FFMA kernels, fp32 activations: the parity path        */
 #define ST2_PREC_BF16 1 /* tcgen05 bf16 x bf16 -> fp32 (TMEM), bf16 activations in HBM */
+#define ST2_PREC_FP32_TC 2 /* the parity path on the tensor cores: fp32 activations, every dense conv as three bf16
+                              products x_hi w_hi + x_lo w_hi + x_hi w_lo with fp32 accumulation in TMEM (decoders only;
+                              needs st2_decoder_set_option(h, "fp32_tc", 1) before load: 3x the bf16 weight bytes) */
 
 #define ST2_MAX_UPS 4
 #define ST2_MAX_RESK 4
@@ -114,6 +117,11 @@ typedef struct St2ForwardOpts {
 
 /* Decoder(**kwargs): validates the config and builds the layer plan (no weights yet). */
 int st2_decoder_create(const St2Config* cfg, St2Decoder** out);
+
+/* Options that change what load builds; call between create and load.  "fp32_tc" = 1: also pack the (hi, hi, lo) bf16
+ * blobs ST2_PREC_FP32_TC needs.  No counterpart in the reference (its precision is torch's dtype / autocast context,
+ * train_second.py:183-186).  Unknown names -> ST2_EINVAL; after load -> ST2_ESTATE. */
+int st2_decoder_set_option(St2Decoder* h, const char* name, int value);
 
 /* load_state_dict: folds weight-norm (w = g*v/||v||, dim 0), repacks every conv into the
  * kernel layouts (fp32 tap-major and bf16 UMMA core-matrix blobs), expands ConvTranspose1d
@@ -215,9 +223,14 @@ const char* st2_version(void);
 struct St2ConvParams;
 int st2_conv_simt(const struct St2ConvParams* p, void* stream);
 int st2_conv_umma(const struct St2ConvParams* p, void* stream);
+/* Debug counter: st2_conv_simt launches of the calling thread with cin >= 64 at stride 1 (layers the tcgen05 kernel can
+ * take) since the last reset; ST2_PREC_FP32_TC must leave it at 0 for the decoders' dense convs. */
+int64_t st2_conv_simt_dense_launches(int reset);
 /* packs fp32 [k][Cin][N] host weights into the UMMA blob layout (host only, no GPU). */
 int64_t st2_umma_packed_elems(int k, int cin_pad, int n);
 int st2_umma_pack_weights(const float* w_kcn, int k, int cin, int cin_pad, int n, uint16_t* out_bf16);
+/* the same for an explicit tile width n_tile (32 / 64 / 128 dividing n; 0 = the default): St2ConvParams.n_tile */
+int st2_umma_pack_weights_nt(const float* w_kcn, int k, int cin, int cin_pad, int n, int n_tile, uint16_t* out_bf16);
 /* host-only test hook: folds weight-norm and repacks one Conv1d (transposed=0) or
  * ConvTranspose1d (transposed=1, polyphase form) exactly as st2_decoder_load does. */
 int st2_debug_pack_conv(const St2Tensor* tensors, int n, const char* prefix, int transposed, int K,

@@ -13,7 +13,7 @@ LIB_PATH = os.path.join(_HERE, "_lib", "libst2dec.so")
 
 ST2_OK = 0
 KIND_ISTFTNET, KIND_HIFIGAN, KIND_F0N, KIND_SAMPLER = 0, 1, 2, 3
-PREC_FP32, PREC_BF16 = 0, 1
+PREC_FP32, PREC_BF16, PREC_FP32_TC = 0, 1, 2
 DT_F32, DT_BF16 = 0, 1
 ACT_NONE, ACT_LRELU, ACT_SNAKE = 0, 1, 2
 MAX_UPS, MAX_RESK = 4, 4
@@ -67,12 +67,14 @@ class St2ConvParams(C.Structure):
         ("res", C.c_void_p), ("res_bstride", C.c_int64), ("ldres", C.c_int), ("res_shift", C.c_int),
         ("out_scale", C.c_float), ("accumulate", C.c_int),
         ("stats", C.c_void_p), ("n_tiles", C.c_int), ("algo_flops", C.c_double), ("bias_bstride", C.c_int64),
+        ("n_tile", C.c_int),
     ]
 
 
 # every symbol include/st2_decoder.h declares: (restype, argtypes)
 SYMBOLS = {
     "st2_decoder_create": (C.c_int, [C.POINTER(St2Config), C.POINTER(C.c_void_p)]),
+    "st2_decoder_set_option": (C.c_int, [C.c_void_p, C.c_char_p, C.c_int]),
     "st2_decoder_load": (C.c_int, [C.c_void_p, C.POINTER(St2Tensor), C.c_int]),
     "st2_decoder_num_keys": (C.c_int, [C.c_void_p]),
     "st2_decoder_key": (C.c_int, [C.c_void_p, C.c_int, C.POINTER(C.c_char_p), C.POINTER(C.c_int),
@@ -99,8 +101,10 @@ SYMBOLS = {
     "st2_version": (C.c_char_p, []),
     "st2_conv_simt": (C.c_int, [C.POINTER(St2ConvParams), C.c_void_p]),
     "st2_conv_umma": (C.c_int, [C.POINTER(St2ConvParams), C.c_void_p]),
+    "st2_conv_simt_dense_launches": (C.c_int64, [C.c_int]),
     "st2_umma_packed_elems": (C.c_int64, [C.c_int, C.c_int, C.c_int]),
     "st2_umma_pack_weights": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_void_p]),
+    "st2_umma_pack_weights_nt": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_void_p]),
     "st2_debug_pack_conv": (C.c_int, [C.POINTER(St2Tensor), C.c_int, C.c_char_p, C.c_int, C.c_int, C.c_int,
                                       C.c_int, C.c_void_p, C.c_int64, C.c_void_p, C.POINTER(C.c_int),
                                       C.POINTER(C.c_int), C.POINTER(C.c_int), C.POINTER(C.c_int)]),

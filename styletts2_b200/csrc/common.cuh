@@ -157,7 +157,13 @@ int launch_stats_finalize(const float* partials, int n_tiles, int n_cols, int C,
                           int c_off, int B, cudaStream_t st, int reps = 1);
 template <typename T>
 int launch_colstats(const T* x, int64_t bstride, int ld, int L, int c0, int ncols, float* partials,
-                    int B, cudaStream_t st);
+                    int B, cudaStream_t st, int n_tiles_total = 0);
+// fp32 parity path on the tensor cores (elementwise.cu): prologue + (hi, lo, hi) bf16 split, and the fp32 epilogue
+int launch_split3(const float* x, int64_t x_bstride, int ldx, int L, int cin, int cin_pad, const float* ss,
+                  int ss_stride, int act, float slope, const float* alpha, __nv_bfloat16* y, int B, cudaStream_t st);
+int launch_post32(const float* acc, int ldacc, int L, int n_cols, const float* res, int64_t res_bstride, int ldres,
+                  int res_shift, float out_scale, int accumulate, float* y, int64_t y_bstride, int ldy, int B,
+                  cudaStream_t st);
 int colstats_tiles(int L);
 template <typename T>
 int launch_prep_inputs(const float* asr, const float* f0, const float* n, const float* f0w,

@@ -62,6 +62,7 @@ typedef struct St2ConvParams {
   int n_tiles;        // ceil(Lout / tile_rows) of the implementation that is called
   double algo_flops;  // algorithmic FLOPs of this call (2*MAC, no padding), bookkeeping only
   int64_t bias_bstride;  // elements between the bias rows of two batch items (0: one shared bias)
+  int n_tile;            // UMMA only: GEMM columns per tile the blob was packed for (0 = the default for n_cols)
 } St2ConvParams;
 
 #endif

@@ -293,8 +293,18 @@ static int launch_thin(const St2ConvParams& p, cudaStream_t st) {
   }
 }
 
+// launches of this thread with a GEMM-sized contraction (cin >= 64 at stride 1: the layers the tcgen05 kernel can take);
+// tests use it to show that ST2_PREC_FP32_TC leaves no dense conv on the FFMA kernel
+static thread_local int64_t g_simt_dense = 0;
+int64_t conv_simt_dense_launches(bool reset) {
+  const int64_t v = g_simt_dense;
+  if (reset) g_simt_dense = 0;
+  return v;
+}
+
 int launch_conv_simt(const St2ConvParams& p, cudaStream_t st) {
   ST2_REQUIRE(p.B > 0 && p.Lout > 0 && p.cin > 0 && p.n_cols > 0 && p.k > 0, "conv_simt: empty shape");
+  if (p.cin >= 64 && p.stride == 1) ++g_simt_dense;
   ST2_REQUIRE(p.stride >= 1 && p.dil >= 1, "conv_simt: stride/dilation");
   ST2_REQUIRE(!(p.stats && p.accumulate), "conv_simt: stats with accumulate");
   ST2_REQUIRE(!p.stats || p.n_tiles >= ceil_div(p.Lout, SIMT_TT), "conv_simt: n_tiles");

@@ -1531,8 +1531,10 @@ static UmEnv um_env() {
 }
 
 static int um_layout(const St2ConvParams& p, int dev, const UmEnv& env, UmLayout& lay) {
-  lay.n_tile = umma_n_tile(p.n_cols);
+  lay.n_tile = p.n_tile ? p.n_tile : umma_n_tile(p.n_cols);
   ST2_REQUIRE(lay.n_tile != 0, "conv_umma: n_cols must be a multiple of 32");
+  ST2_REQUIRE((lay.n_tile == 32 || lay.n_tile == 64 || lay.n_tile == 128) && p.n_cols % lay.n_tile == 0,
+              "conv_umma: n_tile must be 32, 64 or 128 and divide n_cols");
   const int halo = (p.k - 1) * p.dil;
   lay.a_bytes = (int)round_up((int64_t)(UM_TM + halo) * 128, 1024);
   lay.w_bytes = 8 * lay.n_tile * 16;
@@ -1765,7 +1767,7 @@ int launch_conv_umma(const St2ConvParams& p, cudaStream_t st) {
   if (p.y_dtype == ST2_DT_F32) {
     ST2_REQUIRE(!p.res && !p.accumulate && !p.stats, "conv_umma: fp32 output takes no residual / accumulate / stats");
     ST2_REQUIRE(p.ldy % 4 == 0 && p.y_bstride % 4 == 0, "conv_umma: 16-byte alignment of fp32 output rows");
-    ST2_REQUIRE(umma_n_tile(p.n_cols) != 128, "conv_umma: fp32 output needs a 32- or 64-column tile");
+    ST2_REQUIRE((p.n_tile ? p.n_tile : umma_n_tile(p.n_cols)) != 128, "conv_umma: fp32 output needs a 32- or 64-column tile");
   } else {
     ST2_REQUIRE(p.y_dtype == ST2_DT_BF16, "conv_umma: output dtype");
     ST2_REQUIRE(p.ldy % 8 == 0 && p.y_bstride % 8 == 0, "conv_umma: 16-byte alignment of output rows");
@@ -1918,9 +1920,17 @@ extern "C" int64_t st2_umma_packed_elems(int k, int cin_pad, int n) {
 
 using st2::f32_to_bf16_rn;
 
+extern "C" int st2_umma_pack_weights_nt(const float* w_kcn, int k, int cin, int cin_pad, int n, int n_tile,
+                                        uint16_t* out);
 extern "C" int st2_umma_pack_weights(const float* w_kcn, int k, int cin, int cin_pad, int n,
                                      uint16_t* out) {
-  const int ntile = st2::umma_n_tile(n);
+  return st2_umma_pack_weights_nt(w_kcn, k, cin, cin_pad, n, 0, out);
+}
+// the same for an explicit tile width (0 = the default for n): the fp32-output convs of the 3 x bf16 path use 64
+extern "C" int st2_umma_pack_weights_nt(const float* w_kcn, int k, int cin, int cin_pad, int n, int n_tile,
+                                        uint16_t* out) {
+  const int ntile = n_tile ? ((n_tile == 32 || n_tile == 64 || n_tile == 128) && n % n_tile == 0 ? n_tile : 0)
+                           : st2::umma_n_tile(n);
   if (!w_kcn || !out || k < 1 || cin < 1 || cin_pad < cin || cin_pad % st2::UM_CK || ntile == 0) {
     st2::set_error("st2_umma_pack_weights: bad shape");
     return ST2_EINVAL;

@@ -8,9 +8,36 @@
 #include <string>
 #include <vector>
 
+#include <nvtx3/nvToolsExt.h>  // header-only: the ranges are no-ops unless a profiler injects the NVTX library
+
 #include "common.cuh"
 
 namespace st2 {
+
+// NVTX ranges around the stages of a forward (ST2_NVTX=1; read once).  Host-side markers: they bracket the LAUNCHES
+// of a stage on the calling thread, which is what a timeline view (nsys / ncu --nvtx) groups kernels by.
+static bool nvtx_enabled() {
+  static const bool on = [] {
+    const char* e = getenv("ST2_NVTX");
+    return e && e[0] == '1';
+  }();
+  return on;
+}
+struct NvtxRange {
+  bool on;
+  explicit NvtxRange(const char* name, bool enable = true) : on(enable && nvtx_enabled()) {
+    if (on) nvtxRangePushA(name);
+  }
+  ~NvtxRange() {
+    if (on) nvtxRangePop();
+  }
+  void next(const char* name) {  // close the current range, open the next one
+    if (on) {
+      nvtxRangePop();
+      nvtxRangePushA(name);
+    }
+  }
+};
 
 static thread_local std::string g_err;
 static thread_local int64_t g_launches = 0;
@@ -35,6 +62,10 @@ struct ConvW {
   int cstat = 0;    // real channels the columns fold onto for statistics
   double flops_per_row = 0.0;  // algorithmic 2*MAC per output row (per INPUT row for a transposed conv)
   int64_t w32 = -1, w16 = -1, bias = -1, bias16 = -1;  // byte offsets into the device weight arena
+  // fp32 parity path on the tensor cores (ST2_PREC_FP32_TC): bf16 blob over 3 * cin_pad input channels, weight rows
+  // [w_hi | w_hi | w_lo] against activations [x_hi | x_lo | x_hi]; packed for tiles of nt48 columns (fp32 output)
+  int64_t w48 = -1;
+  int nt48 = 0;
 };
 struct NormW {
   int C = 0;
@@ -71,6 +102,7 @@ struct St2Decoder {
   St2Config cfg;
   int device = 0;
   bool loaded = false;
+  bool opt_fp32_tc = false;  // st2_decoder_set_option("fp32_tc", 1) before load: pack the 3 x bf16 blobs
   int spf = 0;
   std::vector<std::string> key_names;
   std::vector<std::vector<int64_t>> key_shapes;
@@ -271,6 +303,7 @@ struct Loader {
   std::vector<float> fcW, fcB;  // concatenated AdaIN fc layers
   int style = 0;
   int ss_pairs = 0;
+  bool fp32_tc = false;  // also pack the 3 x bf16 blobs of the ST2_PREC_FP32_TC path
   std::string err;
 
   const St2Tensor* get(const std::string& n) {
@@ -323,6 +356,31 @@ struct Loader {
       c.w16 = blob.add(nullptr, elems * 2);
       st2_umma_pack_weights(wsrc->data(), c.k, c.cin, c.cin_pad, c.n16,
                             reinterpret_cast<uint16_t*>(blob.data.data() + c.w16));
+      if (fp32_tc) {
+        // [k][3 * cin_pad][n16] fp32 with rows [w_hi | w_hi | w_lo] (all exactly representable in bf16)
+        const int cp = c.cin_pad, n16 = c.n16;
+        std::vector<float> w3((size_t)c.k * 3 * cp * n16, 0.f);
+        for (int j = 0; j < c.k; ++j)
+          for (int ch = 0; ch < c.cin; ++ch)
+            for (int nn = 0; nn < n16; ++nn) {
+              const float w = (*wsrc)[((size_t)j * c.cin + ch) * n16 + nn];
+              uint32_t u;
+              memcpy(&u, &w, 4);
+              uint32_t r = u + 0x7fffu + ((u >> 16) & 1u);  // round to nearest even bf16 (finite weights)
+              r &= 0xffff0000u;
+              float hi;
+              memcpy(&hi, &r, 4);
+              const float lo = w - hi;
+              const size_t base = (size_t)j * 3 * cp;
+              w3[(base + ch) * n16 + nn] = hi;
+              w3[(base + cp + ch) * n16 + nn] = hi;
+              w3[(base + 2 * cp + ch) * n16 + nn] = lo;
+            }
+        c.nt48 = n16 % 64 == 0 ? 64 : 32;
+        c.w48 = blob.add(nullptr, st2_umma_packed_elems(c.k, 3 * cp, n16) * 2);
+        st2_umma_pack_weights_nt(w3.data(), c.k, 3 * cp, 3 * cp, n16, c.nt48,
+                                 reinterpret_cast<uint16_t*>(blob.data.data() + c.w48));
+      }
     }
   }
   // Conv1d: torch [Cout][Cin][k] -> [k][Cin][Cout]
@@ -563,6 +621,7 @@ static int do_load(St2Decoder* h, const St2Tensor* tensors, int n) {
   const St2Config& c = h->cfg;
   Loader L;
   L.style = c.style_dim;
+  L.fp32_tc = h->opt_fp32_tc && (c.kind == ST2_KIND_ISTFTNET || c.kind == ST2_KIND_HIFIGAN);
   std::vector<std::string> names(n);
   for (int i = 0; i < n; ++i) {
     ST2_REQUIRE(tensors[i].name && tensors[i].data, "tensor without name/data");
@@ -792,6 +851,7 @@ struct Fwd {
   cudaStream_t st;
   int B, T;
   bool dry;
+  bool tc32 = false;            // ST2_PREC_FP32_TC: fp32 activations, dense convs as 3 x bf16 on tcgen05
   const float* hall = nullptr;  // [B][fc_rows]
   float* ss = nullptr;          // [B][ss_pairs][2]
 
@@ -830,9 +890,58 @@ struct Fwd {
   float* last_partials = nullptr;
   int last_tiles = 0, last_cols = 0;
 
+  // ST2_PREC_FP32_TC: the same fused conv with fp32 activations on the tensor cores.  (1) split3: the layer's prologue
+  // in fp32 + (hi, lo, hi) bf16 split of every input value; (2) conv_umma without prologue over 3 * cin_pad channels
+  // against the [w_hi | w_hi | w_lo] blob, fp32 accumulation, fp32 output (bias included); (3) post32 when a residual,
+  // scale or running mean follows; (4) colstats for the next InstanceNorm.  Same St2ConvParams semantics as conv().
+  int conv_tc32(const ConvW& c, const ConvIO& io) {
+    float* stats = nullptr;
+    int n_tiles = 0;
+    if (io.want_stats) {
+      n_tiles = colstats_tiles(io.Lout) + io.extra_stat_tiles;
+      stats = ar.alloc<float>((int64_t)B * n_tiles * c.n * 2);
+      last_partials = stats; last_tiles = n_tiles; last_cols = c.n;
+      if (io.extra_stat_tiles) RUN((cudaMemsetAsync(stats, 0, (size_t)B * n_tiles * c.n * 8, st) == cudaSuccess) ? ST2_OK : ST2_ECUDA);
+    }
+    const int64_t m0 = ar.mark();
+    const int cp3 = 3 * c.cin_pad;
+    __nv_bfloat16* xs = ar.alloc<__nv_bfloat16>((int64_t)B * io.Lin * cp3);
+    RUN(launch_split3(reinterpret_cast<const float*>(io.x), io.x_bstride, io.ldx, io.Lin, c.cin, c.cin_pad,
+                      io.pre_norm ? ss_of(*io.pre_norm) : nullptr, h->ss_pairs, io.act, io.slope, io.alpha, xs, B, st));
+    const bool post = io.res || io.accumulate || io.out_scale != 1.f || c.n16 > io.ldy || (io.ldy & 3) ||
+                      (io.y_bstride & 3) || ((uintptr_t)io.y & 15);
+    float* acc = post ? ar.alloc<float>((int64_t)B * io.Lout * c.n16) : reinterpret_cast<float*>(io.y);
+    St2ConvParams p;
+    memset(&p, 0, sizeof(p));
+    p.B = B;
+    p.x = xs; p.x_dtype = ST2_DT_BF16; p.x_bstride = (int64_t)io.Lin * cp3; p.ldx = cp3; p.Lin = io.Lin; p.cin = cp3;
+    p.act = ST2_ACT_NONE;
+    p.k = c.k; p.dil = c.dil; p.pad = c.pad; p.stride = 1;
+    p.w = W<uint16_t>(c.w48); p.bias = W<float>(c.bias16); p.n_cols = c.n16; p.n_tile = c.nt48;
+    p.y = acc; p.y_dtype = ST2_DT_F32;
+    p.y_bstride = post ? (int64_t)io.Lout * c.n16 : io.y_bstride;
+    p.ldy = post ? c.n16 : io.ldy;
+    p.Lout = io.Lout;
+    p.out_scale = 1.f;
+    p.algo_flops = c.flops_per_row * (double)io.Lout * (double)B;
+    RUN(launch_conv_umma(p, st));
+    if (post)
+      RUN(launch_post32(acc, c.n16, io.Lout, c.n, reinterpret_cast<const float*>(io.res), io.res_bstride, io.ldres,
+                        io.res_shift, io.out_scale, io.accumulate, reinterpret_cast<float*>(io.y), io.y_bstride, io.ldy,
+                        B, st));
+    if (io.want_stats)
+      RUN(launch_colstats<float>(reinterpret_cast<const float*>(io.y), io.y_bstride, io.ldy, io.Lout, 0, c.n, stats, B, st,
+                                 n_tiles));
+    ar.release(m0);
+    return ST2_OK;
+  }
+
   // runs one fused conv; partial statistics (if requested) are left in arena scratch that the
   // caller must consume (finalize) before the next arena allocation that follows a release.
   int conv(const ConvW& c, const ConvIO& io) {
+    if (tc32 && DT<AT>::id == ST2_DT_F32 && c.w48 >= 0 && io.x_dtype == ST2_DT_F32 && io.y_dtype == ST2_DT_F32 &&
+        !io.bias_b)
+      return conv_tc32(c, io);
     // tcgen05 path: bf16 activations in; bf16 out, or fp32 out when the layer's padded width is the
     // row stride of the destination (conv_post -> [rows][32] fp32)
     const bool umma = DT<AT>::id == ST2_DT_BF16 && c.w16 >= 0 && io.x_dtype == ST2_DT_BF16 &&
@@ -1066,6 +1175,7 @@ int Fwd<AT>::run(const float* asr, const float* f0, const float* nn, const float
   const int spf = h->spf;
   const int64_t Lw = (int64_t)T * spf;
 
+  NvtxRange nvtx("st2.decoder.style_fc", !dry);
   // ---- all AdaIN fc layers at once; zeroed (scale, shift) arena (padding channels stay 0)
   float* hall_w = ar.alloc<float>((int64_t)B * h->fc_rows);
   hall = hall_w;
@@ -1073,6 +1183,7 @@ int Fwd<AT>::run(const float* asr, const float* f0, const float* nn, const float
   RUN(launch_style_fc(s, W<float>(h->fcW), W<float>(h->fcB), hall_w, B, c.style_dim, h->fc_rows, st));
   RUN(cudaMemsetAsync(ss, 0, (size_t)B * h->ss_pairs * 8, st) == cudaSuccess ? ST2_OK : ST2_ECUDA);
 
+  nvtx.next("st2.decoder.encode_decode");
   // ---- encode / decode (istftnet.py:510-524)
   const int din0 = c.dim_in + 2, ld0 = (int)round_up(din0, 64);
   const int ldc = h->decode[0].din_pad, c_f0 = 1024 + 64;  // [x(1024) | asr_res(64) | F0 | N | 0...]
@@ -1126,6 +1237,7 @@ int Fwd<AT>::run(const float* asr, const float* f0, const float* nn, const float
 
   if (o.tap_decode) RUN(launch_act_to_ncl<AT>(xg.p, xg.bstride, xg.ld, 512, T, o.tap_decode, B, st));
 
+  nvtx.next("st2.generator.excitation");
   // ---- excitation (istftnet.py:350-356 / hifigan.py:320-323)
   const int n_fft = c.gen_istft_n_fft, hop = c.gen_istft_hop_size;
   const int L2 = istft ? (int)(Lw / hop) + 1 : 0;
@@ -1176,6 +1288,7 @@ int Fwd<AT>::run(const float* asr, const float* f0, const float* nn, const float
     RUN(launch_row_mean(hs, Lw, hs_mean, B, st));
   }
 
+  nvtx.next("st2.generator.stages");
   // ---- generator stages (istftnet.py:358-374 / hifigan.py:327-341)
   Act<AT> x = xg;
   const int nk = c.n_resblock_kernels;
@@ -1264,6 +1377,7 @@ int Fwd<AT>::run(const float* asr, const float* f0, const float* nn, const float
     if (o.tap_stage[i]) RUN(launch_act_to_ncl<AT>(x.p, x.bstride, x.ld, C, Ls, o.tap_stage[i], B, st));
   }
 
+  nvtx.next("st2.generator.head");
   // ---- output head
   if (istft) {
     float* cp = ar.alloc<float>((int64_t)B * L2 * ldh);
@@ -1376,6 +1490,23 @@ extern "C" int st2_decoder_key(const St2Decoder* h, int i, const char** name, in
 
 extern "C" int st2_decoder_samples_per_frame(const St2Decoder* h) { return h ? h->spf : 0; }
 
+extern "C" int st2_decoder_set_option(St2Decoder* h, const char* name, int value) {
+  if (!h || !name) {
+    set_error("st2_decoder_set_option: null argument");
+    return ST2_EINVAL;
+  }
+  if (strcmp(name, "fp32_tc") == 0) {
+    if (h->loaded && (value != 0) != h->opt_fp32_tc) {
+      set_error("st2_decoder_set_option: fp32_tc must be set before st2_decoder_load (it adds weight blobs)");
+      return ST2_ESTATE;
+    }
+    h->opt_fp32_tc = value != 0;
+    return ST2_OK;
+  }
+  set_error(std::string("st2_decoder_set_option: unknown option ") + name);
+  return ST2_EINVAL;
+}
+
 extern "C" int st2_decoder_load(St2Decoder* h, const St2Tensor* tensors, int n) {
   if (!h || !tensors || n <= 0) {
     set_error("st2_decoder_load: null argument");
@@ -1416,6 +1547,7 @@ static int forward_t(St2Decoder* h, const float* asr, const float* f0, const flo
                      cudaStream_t st, bool dry, int64_t* peak) {
   Fwd<AT> f;
   f.h = h; f.st = st; f.B = B; f.T = T; f.dry = dry;
+  f.tc32 = o.precision == ST2_PREC_FP32_TC;
   f.ar.base = reinterpret_cast<uint8_t*>(ws); f.ar.cap = ws_bytes; f.ar.dry = dry;
   int rc = f.run(asr, f0, n, s, wav, o);
   if (peak) *peak = f.ar.peak;
@@ -1436,8 +1568,10 @@ static int plan_bytes(St2Decoder* h, int B, int T, const St2ForwardOpts& o, int6
 extern "C" int64_t st2_decoder_workspace_bytes(const St2Decoder* hc, int B, int T, int precision) {
   St2Decoder* h = const_cast<St2Decoder*>(hc);
   if (!h || !h->loaded || (h->cfg.kind != ST2_KIND_ISTFTNET && h->cfg.kind != ST2_KIND_HIFIGAN) || B < 1 || T < 2 ||
-      (T & 1) || (precision != ST2_PREC_FP32 && precision != ST2_PREC_BF16)) {
-    set_error("st2_decoder_workspace_bytes: bad argument, weights not loaded, or not a decoder handle");
+      (T & 1) || (precision != ST2_PREC_FP32 && precision != ST2_PREC_BF16 && precision != ST2_PREC_FP32_TC) ||
+      (precision == ST2_PREC_FP32_TC && !h->opt_fp32_tc)) {
+    set_error("st2_decoder_workspace_bytes: bad argument, weights not loaded, not a decoder handle, or ST2_PREC_FP32_TC "
+              "without st2_decoder_set_option(\"fp32_tc\", 1) before load");
     return ST2_EINVAL;
   }
   St2ForwardOpts o;
@@ -1467,7 +1601,9 @@ extern "C" int st2_decoder_forward(St2Decoder* h, const float* asr, const float*
   St2ForwardOpts o;
   memset(&o, 0, sizeof(o));
   if (opts) o = *opts;
-  ST2_REQUIRE(o.precision == ST2_PREC_FP32 || o.precision == ST2_PREC_BF16, "precision");
+  ST2_REQUIRE(o.precision == ST2_PREC_FP32 || o.precision == ST2_PREC_BF16 || o.precision == ST2_PREC_FP32_TC, "precision");
+  ST2_REQUIRE(o.precision != ST2_PREC_FP32_TC || h->opt_fp32_tc,
+              "ST2_PREC_FP32_TC needs st2_decoder_set_option(h, \"fp32_tc\", 1) before st2_decoder_load");
   ST2_REQUIRE(!(o.har && h->cfg.kind != ST2_KIND_ISTFTNET), "har injection is istftnet-only");
   ST2_REQUIRE(!o.align_idx || o.align_len >= 1, "align_len must be the token count of t_en");
   ST2_REQUIRE(((uintptr_t)workspace & 255) == 0, "workspace must be 256-byte aligned");
@@ -1811,6 +1947,8 @@ extern "C" int st2_conv_simt(const St2ConvParams* p, void* stream) {
   if (!p) return ST2_EINVAL;
   return launch_conv_simt(*p, reinterpret_cast<cudaStream_t>(stream));
 }
+namespace st2 { int64_t conv_simt_dense_launches(bool reset); }
+extern "C" int64_t st2_conv_simt_dense_launches(int reset) { return st2::conv_simt_dense_launches(reset != 0); }
 extern "C" int st2_conv_umma(const St2ConvParams* p, void* stream) {
   if (!p) return ST2_EINVAL;
   return launch_conv_umma(*p, reinterpret_cast<cudaStream_t>(stream));

@@ -178,16 +178,16 @@ colstats_kernel(const T* __restrict__ x, int64_t bstride, int ld, int L, int c0,
 
 template <typename T>
 int launch_colstats(const T* x, int64_t bstride, int ld, int L, int c0, int ncols, float* partials,
-                    int B, cudaStream_t st) {
-  const int nt = colstats_tiles(L);
+                    int B, cudaStream_t st, int n_tiles_total) {
+  const int nt = colstats_tiles(L);  // n_tiles_total > nt: the partial buffer has extra tiles other kernels fill
   dim3 grid(nt, ceil_div(ncols, 64), B);
-  colstats_kernel<T><<<grid, 256, 0, st>>>(x, bstride, ld, L, c0, ncols, partials, nt);
+  colstats_kernel<T><<<grid, 256, 0, st>>>(x, bstride, ld, L, c0, ncols, partials, n_tiles_total > nt ? n_tiles_total : nt);
   ST2_LAUNCH_OK("colstats");
   return ST2_OK;
 }
-template int launch_colstats<float>(const float*, int64_t, int, int, int, int, float*, int, cudaStream_t);
+template int launch_colstats<float>(const float*, int64_t, int, int, int, int, float*, int, cudaStream_t, int);
 template int launch_colstats<__nv_bfloat16>(const __nv_bfloat16*, int64_t, int, int, int, int, float*,
-                                            int, cudaStream_t);
+                                            int, cudaStream_t, int);
 
 // ---------------------------------------------------------------------- prep inputs
 // grid (ceil(T2/32), ceil(ld0/32), B), block (32, 8).  f0w / nw = {w0, w1, w2, bias} (folded).
@@ -646,6 +646,84 @@ __global__ void cols_tanh_kernel(const float* __restrict__ cp, int ld, int ncol,
 int launch_cols_tanh(const float* cp, int ld, int ncol, float* wav, int64_t n, cudaStream_t st) {
   cols_tanh_kernel<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(cp, ld, ncol, wav, n);
   ST2_LAUNCH_OK("cols_tanh");
+  return ST2_OK;
+}
+
+}  // namespace st2
+
+// ------------------------------------------------- fp32 parity path on the tensor cores (ST2_PREC_FP32_TC)
+// A bf16 x bf16 -> fp32 MMA reproduces an fp32 product to ~2^-17 when both operands are split into bf16 (hi, lo) pairs
+// and the three significant products are kept:  x w ~= x_hi w_hi + x_lo w_hi + x_hi w_lo.  As ONE conv on the existing
+// tcgen05 kernel: input channels [x_hi | x_lo | x_hi] (3 * cin_pad bf16 per row, written by split3_kernel below
+// together with the layer's fused prologue AdaIN scale / shift + LeakyReLU / Snake, in fp32, exactly as
+// conv_simt_kernel applies it) against weight rows [w_hi | w_hi | w_lo] (packed at load time), fp32 accumulation in
+// TMEM, fp32 output; residual / scale / running mean are applied by post32_kernel, statistics by colstats_kernel.
+namespace st2 {
+
+// grid (ceil(L / 8), B), block 256: a warp converts rows, lanes stride over channels (coalesced 4-byte reads,
+// 2-byte writes into each of the three blocks)
+__global__ void __launch_bounds__(256)
+split3_kernel(const float* __restrict__ x, int64_t x_bstride, int ldx, int L, int cin, int cin_pad,
+              const float* __restrict__ ss, int ss_stride, int act, float slope, const float* __restrict__ alpha,
+              __nv_bfloat16* __restrict__ y) {
+  pdl_wait_then_trigger();
+  const int b = blockIdx.y, lane = threadIdx.x & 31, wrp = threadIdx.x >> 5;
+  const int t = blockIdx.x * 8 + wrp;
+  if (t >= L) return;
+  const float* xr = x + (int64_t)b * x_bstride + (int64_t)t * ldx;
+  const float* ssb = ss ? ss + (int64_t)b * ss_stride * 2 : nullptr;
+  __nv_bfloat16* yr = y + ((int64_t)b * L + t) * (3 * (int64_t)cin_pad);
+  for (int c = lane; c < cin_pad; c += 32) {
+    float v = 0.f;
+    if (c < cin) {
+      v = xr[c];
+      if (ssb) v = fmaf(v, ssb[2 * c], ssb[2 * c + 1]);
+      float a = 1.f;
+      if (act == ST2_ACT_SNAKE) a = alpha[c];
+      v = apply_act<true>(v, act, slope, a, 1.f / a);
+    }
+    const __nv_bfloat16 hi = __float2bfloat16_rn(v);
+    const __nv_bfloat16 lo = __float2bfloat16_rn(v - __bfloat162float(hi));
+    yr[c] = hi;
+    yr[cin_pad + c] = lo;
+    yr[2 * cin_pad + c] = hi;
+  }
+}
+
+int launch_split3(const float* x, int64_t x_bstride, int ldx, int L, int cin, int cin_pad, const float* ss,
+                  int ss_stride, int act, float slope, const float* alpha, __nv_bfloat16* y, int B, cudaStream_t st) {
+  ST2_CUDA_OK(launch_pdl(split3_kernel, dim3(ceil_div(L, 8), B), dim3(256), 0, st, x, x_bstride, ldx, L, cin, cin_pad, ss,
+                         ss_stride, act, slope, alpha, y));
+  ST2_LAUNCH_OK("split3");
+  return ST2_OK;
+}
+
+// y[b,t,n] = (acc[b,t,n] + res[b, t >> res_shift, n]) * out_scale (+ y_old[b,t,n]); acc [B][L][ldacc] fp32 (the conv
+// with its bias), n < n_cols.  grid (ceil(L * n_cols / 256), B)
+__global__ void __launch_bounds__(256)
+post32_kernel(const float* __restrict__ acc, int ldacc, int L, int n_cols, const float* __restrict__ res,
+              int64_t res_bstride, int ldres, int res_shift, float out_scale, int accumulate, float* __restrict__ y,
+              int64_t y_bstride, int ldy) {
+  pdl_wait_then_trigger();
+  const int b = blockIdx.y;
+  const int64_t i = (int64_t)blockIdx.x * 256 + threadIdx.x;
+  if (i >= (int64_t)L * n_cols) return;
+  const int t = (int)(i / n_cols), n = (int)(i - (int64_t)t * n_cols);
+  float v = acc[((int64_t)b * L + t) * ldacc + n];
+  if (res) v += res[(int64_t)b * res_bstride + (int64_t)(t >> res_shift) * ldres + n];
+  v *= out_scale;
+  float* yp = y + (int64_t)b * y_bstride + (int64_t)t * ldy + n;
+  if (accumulate) v += *yp;
+  *yp = v;
+}
+
+int launch_post32(const float* acc, int ldacc, int L, int n_cols, const float* res, int64_t res_bstride, int ldres,
+                  int res_shift, float out_scale, int accumulate, float* y, int64_t y_bstride, int ldy, int B,
+                  cudaStream_t st) {
+  const int64_t n = (int64_t)L * n_cols;
+  ST2_CUDA_OK(launch_pdl(post32_kernel, dim3((unsigned)((n + 255) / 256), B), dim3(256), 0, st, acc, ldacc, L, n_cols, res,
+                         res_bstride, ldres, res_shift, out_scale, accumulate, y, y_bstride, ldy));
+  ST2_LAUNCH_OK("post32");
   return ST2_OK;
 }
 

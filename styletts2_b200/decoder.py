@@ -85,6 +85,10 @@ class _DecoderBase(nn.Module):
         self._id = _NEXT_ID[0]
         _NEXT_ID[0] += 1
         self.precision = "bf16"
+        # "fp32tc" (the fp32 parity path with its dense convs on the tensor cores as 3 x bf16 products) needs extra weight
+        # blobs: set fp32_tc = True BEFORE the first forward / after changing it the weights are re-packed
+        self.fp32_tc = False
+        self._native_tc: Dict[int, bool] = {}
         self.seed = 0
         # a batch whose workspace would exceed this is decoded in micro-batches (utterances are
         # independent, SURVEY 8d: config C5 is 512 x 2400 frames); 0 = never split
@@ -153,13 +157,22 @@ class _DecoderBase(nn.Module):
         idx = device.index if device.index is not None else torch.cuda.current_device()
         ver = self._weights_version()
         h = self._native.get(idx)
-        if h is not None and self._native_version.get(idx) == ver:
+        want_tc = bool(getattr(self, "fp32_tc", False))
+        if h is not None and self._native_version.get(idx) == ver and self._native_tc.get(idx, False) == want_tc:
             return h
         with torch.cuda.device(idx):
+            if h is not None and self._native_tc.get(idx, False) != want_tc:
+                lib.st2_decoder_destroy(h)      # the option changes what load packs: start from a fresh handle
+                h = None
+                for k in [k for k in self._graphs if k[0] == idx]:
+                    del self._graphs[k]
             if h is None:
                 h = C.c_void_p()
                 check(lib.st2_decoder_create(C.byref(self._cfg), C.byref(h)), "st2_decoder_create")
+                if want_tc:
+                    check(lib.st2_decoder_set_option(h, b"fp32_tc", 1), "st2_decoder_set_option")
                 self._native[idx] = h
+                self._native_tc[idx] = want_tc
             sd = {k: v.detach().to("cpu", torch.float32).contiguous() for k, v in self.state_dict().items()}
             arr = (_cabi.St2Tensor * len(sd))()
             keep = []
@@ -239,7 +252,9 @@ class _DecoderBase(nn.Module):
         if Cin != self._cfg.dim_in or s.shape[1] != self._cfg.style_dim:
             raise RuntimeError("channel / style dimension mismatch")
         prec = precision or self.precision
-        prec_id = {"fp32": _cabi.PREC_FP32, "bf16": _cabi.PREC_BF16}[prec]
+        prec_id = {"fp32": _cabi.PREC_FP32, "bf16": _cabi.PREC_BF16, "fp32tc": _cabi.PREC_FP32_TC}[prec]
+        if prec == "fp32tc" and not self.fp32_tc:
+            self.fp32_tc = True           # packs the extra blobs on this (first) use
         dev = asr.device
         f32 = lambda t: None if t is None else t.to(dev, torch.float32).contiguous()
         asr_, f0_, n_, s_ = f32(asr), f32(F0_curve), f32(N), f32(s)

@@ -506,3 +506,31 @@ def test_two_threads_share_one_module():
     assert not errs, errs
     for i in range(2):
         assert torch.equal(outs[i], want)
+
+
+@pytest.mark.parametrize("kind", ["istftnet", "hifigan"])
+def test_fp32_tensor_core_path_vs_reference_golden(kind):
+    """ST2_PREC_FP32_TC ("fp32tc"): fp32 activations with every dense conv on tcgen05 as three bf16 products (x_hi w_hi +
+    x_lo w_hi + x_hi w_lo, fp32 accumulation): <= 1e-3 max-abs against the reference goldens with the excitation
+    injected, like the FFMA parity path, and NO dense conv left on the FFMA kernel"""
+    from styletts2_b200 import _cabi
+    import styletts2_b200 as st2
+    import synthetic as synth
+    cfg = synth.ISTFTNET_CFG if kind == "istftnet" else synth.HIFIGAN_CFG
+    dec = (st2.IstftnetDecoder if kind == "istftnet" else st2.HifiganDecoder)(**{k: v for k, v in cfg.items() if k != "kind"})
+    dec.load_state_dict(synth.synth_state_dict(cfg, seed=0), strict=True)
+    dec = dec.cuda().eval()
+    dec.fp32_tc = True
+    for T in (8, 40):
+        g = _gold(kind, T)
+        kw = dict(har=_c(g["tap_har"])) if kind == "istftnet" else dict(har_source=_c(g["har_source"]))
+        args = (_c(g["asr"]), _c(g["F0_curve"]), _c(g["N"]), _c(g["s"]))
+        ref32 = dec(*args, precision="fp32", **kw).cpu()
+        _cabi.lib.st2_conv_simt_dense_launches(1)
+        wav = dec(*args, precision="fp32tc", **kw).cpu()
+        dense = int(_cabi.lib.st2_conv_simt_dense_launches(1))
+        err = (wav - g["wav"]).abs().max().item()
+        print(f"{kind} T={T}: fp32tc max-abs vs the reference {err:.2e} (FFMA path {(ref32 - g['wav']).abs().max().item():.2e}), "
+              f"dense convs left on conv_simt: {dense}, launches {dec.last_launches}")
+        assert torch.isfinite(wav).all() and err < 1e-3
+        assert dense == 0
