@@ -171,6 +171,40 @@ def _oracle_cpu_decoder(kind, B, T, steps, warmup, threads=None):
     return audio_s / statistics.median(times), statistics.median(times) * 1e3, torch.get_num_threads()
 
 
+def _parity_paths(kind, cfg, T, dev, Bs=4):
+    """Throughput of the two fp32 parity paths on a bounded sample of the workload (Bs items x T frames, device-resident,
+    eager launches, CUDA events): "fp32" = every conv on the FFMA kernel (conv_simt), "fp32tc" = the dense convs on
+    tcgen05 as three bf16 products with fp32 accumulation (ST2_PREC_FP32_TC).  Both meet the <= 1e-3 parity bar
+    (tests/test_decoder_gpu.py); the headline runs the bf16 path."""
+    import torch
+    import styletts2_b200 as st2
+    import synthetic as synth
+    out = {"sample": f"{Bs} items x {T} frames of the workload, eager launches", "unit": UNIT}
+    d = {k: v.to(dev) for k, v in synth.synth_inputs(cfg, Bs, T, seed=99, with_noise=False).items()}
+    audio_s = Bs * T * 300 / 24000.0
+    for prec, steps in (("fp32tc", 3), ("fp32", 1)):
+        dec = (st2.IstftnetDecoder if kind == "istftnet" else st2.HifiganDecoder)(**{k: v for k, v in cfg.items() if k != "kind"})
+        dec.load_state_dict(synth.synth_state_dict(cfg, seed=0), strict=True)
+        dec = dec.to(dev).eval()
+        dec.fp32_tc = prec == "fp32tc"
+        try:
+            dec(d["asr"], d["F0_curve"], d["N"], d["s"], precision=prec)   # warm-up (packs / uploads the weights)
+            torch.cuda.synchronize()
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
+            for _ in range(steps):
+                dec(d["asr"], d["F0_curve"], d["N"], d["s"], precision=prec)
+            e1.record()
+            torch.cuda.synchronize()
+            ms = e0.elapsed_time(e1) / steps
+            out[prec] = {"value": round(audio_s / (ms * 1e-3), 1), "ms_per_step": round(ms, 2), "launches": dec.last_launches}
+        except RuntimeError as e:  # e.g. not enough memory next to the main arm's graph buffers
+            out[prec] = {"unavailable": str(e)[:120]}
+        del dec
+        torch.cuda.empty_cache()
+    return out
+
+
 def _quality(kind, dev, dec, T, seed):
     """parity of the MEASURED build and module on ONE FULL-SIZE item of the measured workload (T mel frames, the
     reference constructor's init regime) against the oracle port of the reference, noise injected so both sides see
@@ -804,6 +838,7 @@ def run_ours(args):
     dec.load_state_dict(synth.synth_state_dict(cfg, seed=0), strict=True)
     dec = dec.to(dev).eval()
     dec.precision = prec
+    dec.fp32_tc = prec == "fp32tc"
     dec.cuda_graphs = not args.no_graphs  # CUDA-graph replay of the forward is allowed
     inp = synth.synth_inputs(cfg, B, T, seed=1234 + rank, with_noise=False)  # per-rank shard, Philox noise
     host = {k: v.pin_memory() for k, v in inp.items()}
@@ -933,7 +968,8 @@ def run_ours(args):
             cpu["value_1_thread"] = round(v1, 4)
             cpu["sample"] += f"; 1 thread: {ms1:.0f} ms"
     ws_bytes = int(_cabi.lib.st2_decoder_workspace_bytes(dec._native[local], B, T,
-                                                         _cabi.PREC_BF16 if prec == "bf16" else _cabi.PREC_FP32))
+                                                         {"bf16": _cabi.PREC_BF16, "fp32": _cabi.PREC_FP32,
+                                                          "fp32tc": _cabi.PREC_FP32_TC}[prec]))
     line = {
         "metric": _metric(kind), "value": round(value, 2), "unit": UNIT, "n_gpus": world, "steps": args.steps,
         "warmup": max(3, args.warmup), "ms_per_step": round(ms_step, 3), "higher_is_better": True,
@@ -948,6 +984,8 @@ def run_ours(args):
         "roofline": roof, "cpu_baseline": cpu, "clocks": clocks,
         "hbm_kernels": _hbm_kernels(min(B, 64), T, dev, peaks) if (world == 1 and kind == "istftnet") else None,
         "quality": _quality(kind, dev, dec, T, 1234) if world == 1 and not args.no_quality else None,
+        "parity_paths": (_parity_paths(kind, cfg, T, dev) if world == 1 and args.workload in ("c2", "c4")
+                         and prec == "bf16" and not args.no_parity_paths else None),
         "library_baseline": (_library_gpu(kind, B, T, 3, 2, dev)
                              if world == 1 and args.workload in ("c2", "c4") and not args.no_library_baseline else None),
     }
@@ -964,7 +1002,8 @@ def main():
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference", "reference-gpu"])
     ap.add_argument("--workload", default="c2", choices=sorted(WORKLOADS) + ["f0n", "sampler", "chain"])
-    ap.add_argument("--precision", default="bf16", choices=["bf16", "fp32"])
+    ap.add_argument("--precision", default="bf16", choices=["bf16", "fp32", "fp32tc"])
+    ap.add_argument("--no-parity-paths", action="store_true", help="skip timing the fp32 parity paths (FFMA and 3 x bf16)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-library-baseline", action="store_true", help="skip the cuDNN/ATen-on-this-GPU block (c2, c4)")
     ap.add_argument("--no-quality", action="store_true", help="skip the full-size parity item against the oracle")

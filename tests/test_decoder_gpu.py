@@ -401,7 +401,8 @@ def test_full_size_config_vs_oracle(kind, B, T):
         har magnitude / phase-on-the-circle vs the oracle's STFT; waveform SNR >= 30 dB and log-mel L1 against
         the oracle fed with this run's own har (iSTFTNet: isolates the torch.angle branch flips, which are
         counted and reported) or with the same noise (HiFi-GAN);
-      * fp32 path on the same two rows, same excitation injected: <= 1e-3 max-abs;
+      * fp32 path on the same two rows, same excitation injected: <= 1e-3 max-abs (row 17 also on the tensor-core
+        parity path "fp32tc");
       * items 0 and 17 decoded alone (B=1) equal their rows of the batch bit for bit."""
     import synthetic as synth
     from oracle import decoder_oracle as orc
@@ -436,6 +437,11 @@ def test_full_size_config_vs_oracle(kind, B, T):
         ckw = {k: v.cuda() for k, v in kw.items()}
         w32 = dec(*[a[sl] for a in args], precision="fp32", **ckw).cpu()
         e32 = (w32 - ref).abs().max().item()
+        if i == 17:   # the same row on the tensor-core parity path (3 x bf16 products, fp32 accumulation)
+            dec.fp32_tc = True
+            etc = (dec(*[a[sl] for a in args], precision="fp32tc", **ckw).cpu() - ref).abs().max().item()
+            print(f"full size {kind} item {i}: fp32tc path max-abs {etc:.2e}")
+            assert etc < 1e-3, etc
         one = dec(*[a[sl] for a in args], noise=noise[sl], precision="bf16", item_offset=i)
         print(f"full size {kind} item {i}: har_source err {e_hs:.1e}, angle flips {flips}, fp32 path max-abs {e32:.2e}, "
               f"bf16 SNR {snr:.1f} dB, log-mel L1 {mel:.4f}, rms {ref.pow(2).mean().sqrt().item():.3f}")
