@@ -223,6 +223,12 @@ const char* st2_version(void);
 struct St2ConvParams;
 int st2_conv_simt(const struct St2ConvParams* p, void* stream);
 int st2_conv_umma(const struct St2ConvParams* p, void* stream);
+/* n (1..3) convs of the same geometry (batch, lengths, channel counts, activation kind) as ONE persistent tcgen05 kernel
+ * whose CTAs alternate between them tile by tile, so that a conv bound by its per-element prologue / epilogue work
+ * (k = 3) overlaps one bound by the tensor pipe (k = 11): the three first convs of the resblocks k = 3 / 7 / 11 read the
+ * same x (istftnet.py:369-373).  Results equal n separate st2_conv_umma calls bit for bit; jobs that cannot share a
+ * kernel are launched one by one. */
+int st2_conv_umma_multi(const struct St2ConvParams* ps, int n, void* stream);
 /* Debug counter: st2_conv_simt launches of the calling thread with cin >= 64 at stride 1 (layers the tcgen05 kernel can
  * take) since the last reset; ST2_PREC_FP32_TC must leave it at 0 for the decoders' dense convs. */
 int64_t st2_conv_simt_dense_launches(int reset);

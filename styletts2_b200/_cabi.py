@@ -102,6 +102,7 @@ SYMBOLS = {
     "st2_conv_simt": (C.c_int, [C.POINTER(St2ConvParams), C.c_void_p]),
     "st2_conv_umma": (C.c_int, [C.POINTER(St2ConvParams), C.c_void_p]),
     "st2_conv_simt_dense_launches": (C.c_int64, [C.c_int]),
+    "st2_conv_umma_multi": (C.c_int, [C.POINTER(St2ConvParams), C.c_int, C.c_void_p]),
     "st2_umma_packed_elems": (C.c_int64, [C.c_int, C.c_int, C.c_int]),
     "st2_umma_pack_weights": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_void_p]),
     "st2_umma_pack_weights_nt": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_void_p]),

@@ -145,6 +145,7 @@ __device__ __forceinline__ void box_muller(uint32_t a, uint32_t b, float& z0, fl
 // ---- kernel launchers implemented across the .cu files --------------------------------
 int launch_conv_simt(const St2ConvParams& p, cudaStream_t st);
 int launch_conv_umma(const St2ConvParams& p, cudaStream_t st);
+int launch_conv_umma_multi(const St2ConvParams* ps, int n, cudaStream_t st);  // up to 3 same-shaped convs, one kernel
 int conv_tile_rows(bool umma);
 int umma_n_tile(int n_cols);  // GEMM columns per tcgen05 tile for a layer of n_cols (0: none)
 int umma_prepare(int acc_mult);  // conv_umma's one-time per-device setup (called by st2_decoder_load, never by forward)
@@ -155,6 +156,9 @@ int launch_style_fc(const float* s, const float* W, const float* bvec, float* h,
 int launch_stats_finalize(const float* partials, int n_tiles, int n_cols, int C, int64_t count,
                           const float* h, int h_stride, int gamma_off, float* ss, int ss_stride,
                           int c_off, int B, cudaStream_t st, int reps = 1);
+int launch_stats_finalize_multi(const float* const* partials, int n, int n_tiles, int n_cols, int C, int64_t count,
+                                const float* const* hg, int h_stride, int Cn, float* const* ss, int ss_stride,
+                                int c_off, int B, cudaStream_t st, int reps);
 template <typename T>
 int launch_colstats(const T* x, int64_t bstride, int ld, int L, int c0, int ncols, float* partials,
                     int B, cudaStream_t st, int n_tiles_total = 0);

@@ -876,6 +876,25 @@ struct Fwd {
     return ST2_OK;
   }
 
+  // the same for n (<= 3) norm layers with equal shapes, one launch
+  int finalize_multi(float* const* partials, int n, int n_tiles, int n_cols, int C, int64_t count,
+                     const NormW* const* norms, int reps) {
+    const float* pp[3]; const float* hg[3]; float* so[3];
+    for (int j = 0; j < n; ++j) {
+      if (norms[j]->C != norms[0]->C) {  // different layers after all: one by one
+        for (int q = 0; q < n; ++q) {
+          int rc = finalize(partials[q], n_tiles, n_cols, C, count, *norms[q], 0, reps);
+          if (rc) return rc;
+        }
+        return ST2_OK;
+      }
+      pp[j] = partials[j]; hg[j] = hall + norms[j]->h_off; so[j] = ss + (int64_t)norms[j]->ss_off * 2;
+    }
+    RUN(launch_stats_finalize_multi(pp, n, n_tiles, n_cols, C, count, hg, h->fc_rows, norms[0]->C, so, h->ss_pairs, 0, B,
+                                    st, reps));
+    return ST2_OK;
+  }
+
   struct ConvIO {
     const void* x; int x_dtype; int64_t x_bstride; int ldx; int Lin;
     void* y; int y_dtype; int64_t y_bstride; int ldy; int Lout;
@@ -938,17 +957,15 @@ struct Fwd {
 
   // runs one fused conv; partial statistics (if requested) are left in arena scratch that the
   // caller must consume (finalize) before the next arena allocation that follows a release.
-  int conv(const ConvW& c, const ConvIO& io) {
-    if (tc32 && DT<AT>::id == ST2_DT_F32 && c.w48 >= 0 && io.x_dtype == ST2_DT_F32 && io.y_dtype == ST2_DT_F32 &&
-        !io.bias_b)
-      return conv_tc32(c, io);
+  // St2ConvParams of one fused conv (statistics buffer allocated from the arena when requested); *umma = it runs on
+  // the tcgen05 kernel
+  int conv_params(const ConvW& c, const ConvIO& io, St2ConvParams& p, bool* umma_o) {
     // tcgen05 path: bf16 activations in; bf16 out, or fp32 out when the layer's padded width is the
     // row stride of the destination (conv_post -> [rows][32] fp32)
     const bool umma = DT<AT>::id == ST2_DT_BF16 && c.w16 >= 0 && io.x_dtype == ST2_DT_BF16 &&
                       io.ldx >= c.cin_pad &&
                       ((io.y_dtype == ST2_DT_BF16 && c.n16 == c.n) ||
                        (io.y_dtype == ST2_DT_F32 && c.n16 <= io.ldy && c.n16 <= 64 && !io.want_stats));
-    St2ConvParams p;
     memset(&p, 0, sizeof(p));
     p.B = B;
     p.x = io.x; p.x_dtype = io.x_dtype; p.x_bstride = io.x_bstride; p.ldx = io.ldx; p.Lin = io.Lin;
@@ -977,7 +994,50 @@ struct Fwd {
       last_partials = p.stats; last_tiles = p.n_tiles; last_cols = c.n;
       if (io.extra_stat_tiles) RUN((cudaMemsetAsync(p.stats, 0, (size_t)B * p.n_tiles * c.n * 8, st) == cudaSuccess) ? ST2_OK : ST2_ECUDA);
     }
+    *umma_o = umma;
+    return ST2_OK;
+  }
+
+  int conv(const ConvW& c, const ConvIO& io) {
+    if (tc32 && DT<AT>::id == ST2_DT_F32 && c.w48 >= 0 && io.x_dtype == ST2_DT_F32 && io.y_dtype == ST2_DT_F32 &&
+        !io.bias_b)
+      return conv_tc32(c, io);
+    St2ConvParams p;
+    bool umma = false;
+    int rc = conv_params(c, io, p, &umma);
+    if (rc) return rc;
     RUN(umma ? launch_conv_umma(p, st) : launch_conv_simt(p, st));
+    return ST2_OK;
+  }
+
+  // n (<= 3) convs of the same shape as ONE tcgen05 kernel whose CTAs alternate between them tile by tile
+  // (launch_conv_umma_multi): the convs of the three resblocks k = 3 / 7 / 11 at the same position of their chains.
+  // parts[j] / tiles[j] receive the statistics partials of conv j.  Other precisions run them one by one.
+  int conv_multi(const ConvW* const* cs, const ConvIO* ios, int n, float** parts, int* tiles, int* cols) {
+    St2ConvParams ps[3];
+    bool all_umma = n <= 3;
+    if (DT<AT>::id != ST2_DT_BF16) all_umma = false;
+    if (all_umma) {
+      for (int j = 0; j < n; ++j) {
+        bool umma = false;
+        int rc = conv_params(*cs[j], ios[j], ps[j], &umma);
+        if (rc) return rc;
+        parts[j] = last_partials; tiles[j] = last_tiles; cols[j] = last_cols;
+        all_umma = all_umma && umma;
+      }
+      if (all_umma) {
+        RUN(launch_conv_umma_multi(ps, n, st));
+        // bookkeeping: one launch
+        return ST2_OK;
+      }
+      for (int j = 0; j < n; ++j) RUN(launch_conv_simt(ps[j], st));  // (not reached for the resblock convs)
+      return ST2_OK;
+    }
+    for (int j = 0; j < n; ++j) {
+      int rc = conv(*cs[j], ios[j]);
+      if (rc) return rc;
+      parts[j] = last_partials; tiles[j] = last_tiles; cols[j] = last_cols;
+    }
     return ST2_OK;
   }
 
@@ -1095,6 +1155,66 @@ struct Fwd {
         }
         ar.release(m);
       }
+    }
+    return ST2_OK;
+  }
+
+  // The nk resblocks of a generator stage (istftnet.py:369-374: xs = sum_j resblocks[i*nk+j](x); x = xs / nk) run in
+  // lock step: their convs at the same position of the chain have the same shape and no dependence on each other, so
+  // each position is ONE kernel launch whose CTAs alternate between the resblocks tile by tile (conv_multi) -- the
+  // k = 3 conv's per-element work overlaps the k = 11 conv's MMAs, and a single utterance fills 3x the SMs.  Only the
+  // last conv of every chain is launched on its own: it accumulates the running mean into `fin` (resblock j reads what
+  // resblock j-1 wrote).  Each resblock needs its own run / tmp buffers.
+  int resblocks_lockstep(const ResBlock1W* rs, int nk, const Act<AT>& x, const Act<AT>* run, const Act<AT>* tmp,
+                         const Act<AT>& fin, bool pr) {
+    const int reps = pr ? 2 : 1;
+    const ConvW* cs[3];
+    ConvIO ios[3];
+    float* parts[3];
+    int tiles[3], cols[3];
+    for (int it = 0; it < 3; ++it) {
+      const bool last = it == 2;
+      const int64_t m = ar.mark();
+      for (int j = 0; j < nk; ++j) {
+        const ResBlock1W& r = rs[j];
+        const Act<AT>& src = it == 0 ? x : run[j];
+        ios[j] = io_of(src, tmp[j]);
+        ios[j].pre_norm = &r.n1[it]; ios[j].act = ST2_ACT_SNAKE; ios[j].alpha = W<float>(pr ? r.a1p[it] : r.a1[it]);
+        ios[j].want_stats = true;
+        cs[j] = pr ? &r.c1p[it] : &r.c1[it];
+      }
+      int rc = conv_multi(cs, ios, nk, parts, tiles, cols);
+      if (rc) return rc;
+      const NormW* norms[3];
+      for (int j = 0; j < nk; ++j) norms[j] = &rs[j].n2[it];
+      rc = finalize_multi(parts, nk, tiles[0], cols[0], rs[0].C, (int64_t)tmp[0].L * reps, norms, reps);
+      if (rc) return rc;
+      ar.release(m);
+      for (int j = 0; j < nk; ++j) {
+        const ResBlock1W& r = rs[j];
+        const Act<AT>& src = it == 0 ? x : run[j];
+        const Act<AT>& dst = last ? fin : run[j];
+        ios[j] = io_of(tmp[j], dst);
+        ios[j].pre_norm = &r.n2[it]; ios[j].act = ST2_ACT_SNAKE; ios[j].alpha = W<float>(pr ? r.a2p[it] : r.a2[it]);
+        ios[j].res = src.p; ios[j].res_bstride = src.bstride; ios[j].ldres = src.ld;
+        if (last) { ios[j].out_scale = 1.f / (float)nk; ios[j].accumulate = j > 0 ? 1 : 0; }
+        ios[j].want_stats = !last;
+        cs[j] = pr ? &r.c2p[it] : &r.c2[it];
+      }
+      if (last) {
+        for (int j = 0; j < nk; ++j) {
+          rc = conv(*cs[j], ios[j]);
+          if (rc) return rc;
+        }
+      } else {
+        rc = conv_multi(cs, ios, nk, parts, tiles, cols);
+        if (rc) return rc;
+        const NormW* norms[3];
+        for (int j = 0; j < nk; ++j) norms[j] = &rs[j].n1[it + 1];
+        rc = finalize_multi(parts, nk, tiles[0], cols[0], rs[0].C, (int64_t)run[0].L * reps, norms, reps);
+        if (rc) return rc;
+      }
+      ar.release(m);
     }
     return ST2_OK;
   }
@@ -1292,6 +1412,9 @@ int Fwd<AT>::run(const float* asr, const float* f0, const float* nn, const float
   // ---- generator stages (istftnet.py:358-374 / hifigan.py:327-341)
   Act<AT> x = xg;
   const int nk = c.n_resblock_kernels;
+  // bf16 path: the resblocks of a stage run in lock step, one fused launch per position (ST2_LOCKSTEP=0: one by one)
+  static const bool lockstep_env = [] { const char* e = getenv("ST2_LOCKSTEP"); return !(e && e[0] == '0'); }();
+  const bool lockstep = lockstep_env && DT<AT>::id == ST2_DT_BF16;
   for (int i = 0; i < c.n_ups; ++i) {
     const UpW& up = h->ups[i];
     const bool lastst = i == c.n_ups - 1;
@@ -1362,16 +1485,32 @@ int Fwd<AT>::run(const float* asr, const float* f0, const float* nn, const float
                                     xs.p, xs.bstride, xm.p, xm.bstride, C, slot,
                                     (int64_t)last_tiles * last_cols * 2, B, st));
       }
-      for (int j = 0; j < nk; ++j) {
-        rc = finalize(last_partials, last_tiles, last_cols, C, Ls, h->resblocks[i * nk + j].n1[0], 0, reps);
+      if (nk <= 3) {
+        float* pp3[3]; const NormW* norms[3];
+        for (int j = 0; j < nk; ++j) { pp3[j] = last_partials; norms[j] = &h->resblocks[i * nk + j].n1[0]; }
+        rc = finalize_multi(pp3, nk, last_tiles, last_cols, C, Ls, norms, reps);
         if (rc) return rc;
+      } else {
+        for (int j = 0; j < nk; ++j) {
+          rc = finalize(last_partials, last_tiles, last_cols, C, Ls, h->resblocks[i * nk + j].n1[0], 0, reps);
+          if (rc) return rc;
+        }
       }
       ar.release(m);
     }
-    for (int j = 0; j < nk; ++j) {
-      int rc = resblock1(h->resblocks[i * nk + j], vw(xm), vw(runb), vw(tmp), vw(outb), 1.f / (float)nk,
-                         j > 0 ? 1 : 0, nullptr, pr);
+    if (lockstep && nk <= 3) {
+      // the nk resblocks in lock step: each needs its own run / tmp buffers (resblock 0 reuses the stage's)
+      Act<AT> runs[3], tmps[3];
+      runs[0] = vw(runb); tmps[0] = vw(tmp);
+      for (int j = 1; j < nk; ++j) { runs[j] = vw(new_act(Ls, C)); tmps[j] = vw(new_act(Ls, C)); }
+      int rc = resblocks_lockstep(&h->resblocks[i * nk], nk, vw(xm), runs, tmps, vw(outb), pr);
       if (rc) return rc;
+    } else {
+      for (int j = 0; j < nk; ++j) {
+        int rc = resblock1(h->resblocks[i * nk + j], vw(xm), vw(runb), vw(tmp), vw(outb), 1.f / (float)nk,
+                           j > 0 ? 1 : 0, nullptr, pr);
+        if (rc) return rc;
+      }
     }
     x = outb;
     if (o.tap_stage[i]) RUN(launch_act_to_ncl<AT>(x.p, x.bstride, x.ld, C, Ls, o.tap_stage[i], B, st));
@@ -1946,6 +2085,10 @@ extern "C" const char* st2_version(void) { return "st2dec 0.1 (sm_100a)"; }
 extern "C" int st2_conv_simt(const St2ConvParams* p, void* stream) {
   if (!p) return ST2_EINVAL;
   return launch_conv_simt(*p, reinterpret_cast<cudaStream_t>(stream));
+}
+extern "C" int st2_conv_umma_multi(const St2ConvParams* ps, int n, void* stream) {
+  if (!ps) return ST2_EINVAL;
+  return launch_conv_umma_multi(ps, n, reinterpret_cast<cudaStream_t>(stream));
 }
 namespace st2 { int64_t conv_simt_dense_launches(bool reset); }
 extern "C" int64_t st2_conv_simt_dense_launches(int reset) { return st2::conv_simt_dense_launches(reset != 0); }

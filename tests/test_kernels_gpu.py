@@ -328,3 +328,75 @@ def test_log_mel_kernel_vs_reference_front_end():
     assert (got - orc.log_mel(w[:, 0])).abs().max().item() < 2e-4
     with pytest.raises(ValueError):
         log_mel(torch.zeros(1, 1000).cuda())
+
+
+def _mk_job(B, L, cin, n, k, dil, seed, with_res, with_stats, acc=False, act=None):
+    """St2ConvParams of one bf16 tcgen05 conv on random data (+ the tensors it points at)"""
+    act = _cabi.ACT_SNAKE if act is None else act
+    g = torch.Generator().manual_seed(seed)
+    dev = "cuda"
+    x = torch.randn(B, L, cin, generator=g).to(torch.bfloat16).to(dev)
+    w = (torch.randn(k, cin, n, generator=g) / math.sqrt(cin * k)).contiguous()
+    packed = torch.empty(lib.st2_umma_packed_elems(k, cin, n), dtype=torch.int16)
+    check(lib.st2_umma_pack_weights(w.data_ptr(), k, cin, cin, n, packed.data_ptr()))
+    wd = packed.to(dev)
+    bias = torch.randn(n, generator=g).to(dev)
+    ss = torch.stack([1 + 0.1 * torch.randn(B, cin, generator=g), 0.1 * torch.randn(B, cin, generator=g)], -1).contiguous().to(dev)
+    alpha = (0.5 + torch.rand(cin, generator=g)).to(dev)
+    y0 = torch.randn(B, L, n, generator=g).to(torch.bfloat16).to(dev)   # y_old for accumulate, overwritten otherwise
+    res = torch.randn(B, L, n, generator=g).to(torch.bfloat16).to(dev) if with_res else None
+    tr = lib.st2_conv_tile_rows(1)
+    nt = (L + tr - 1) // tr
+    stats = torch.zeros(B, nt, n, 2, device=dev) if with_stats else None
+
+    def params(y, st):
+        p = _cabi.St2ConvParams()
+        p.B = B
+        p.x = x.data_ptr(); p.x_dtype = _cabi.DT_BF16; p.x_bstride = L * cin; p.ldx = cin; p.Lin = L; p.cin = cin
+        p.ss = ss.data_ptr(); p.ss_stride = cin; p.act = act; p.slope = 0.1; p.alpha = alpha.data_ptr()
+        p.k, p.dil, p.pad, p.stride = k, dil, dil * (k - 1) // 2, 1
+        p.w = wd.data_ptr(); p.bias = bias.data_ptr(); p.n_cols = n
+        p.y = y.data_ptr(); p.y_dtype = _cabi.DT_BF16; p.y_bstride = L * n; p.ldy = n; p.Lout = L
+        if res is not None:
+            p.res = res.data_ptr(); p.res_bstride = L * n; p.ldres = n
+        p.out_scale = 0.5 if acc else 1.0
+        p.accumulate = 1 if acc else 0
+        if st is not None:
+            p.stats = st.data_ptr(); p.n_tiles = nt
+        return p
+    return params, y0, stats, (x, wd, bias, ss, alpha, res)
+
+
+@pytest.mark.parametrize("case", [
+    # B, L, cin = n, [(k, dil, residual, stats, accumulate)]
+    (3, 1000, 128, [(3, 1, False, True, False), (11, 1, False, True, False)]),                          # the k3 + k11 pair
+    (2, 1500, 128, [(3, 1, True, True, False), (7, 3, True, True, False), (11, 5, True, False, True)]),  # 3 jobs, mixed chunks
+    (2, 700, 256, [(3, 1, False, True, False), (11, 3, True, True, False)]),                            # two N tiles
+    (1, 300, 128, [(7, 1, True, True, False), (3, 5, False, False, False), (11, 1, False, True, False)]),
+])
+def test_conv_umma_multi_equals_separate_launches(case):
+    """st2_conv_umma_multi: up to 3 same-shaped convs alternate tile by tile inside ONE persistent kernel (conv_umma.cu,
+    UmJobs).  Every output byte and every statistic must equal the separately launched convs."""
+    B, L, CH, jobs = case
+    made = [_mk_job(B, L, CH, CH, k, d, 100 + i, r, s, a) for i, (k, d, r, s, a) in enumerate(jobs)]
+    want = []
+    for params, y0, stats, keep in made:
+        y = y0.clone()
+        st = None if stats is None else stats.clone()
+        check(lib.st2_conv_umma(C.byref(params(y, st)), None))
+        torch.cuda.synchronize()
+        want.append((y, st))
+    arr = (_cabi.St2ConvParams * len(made))()
+    got = []
+    for i, (params, y0, stats, keep) in enumerate(made):
+        y = y0.clone()
+        st = None if stats is None else stats.clone()
+        arr[i] = params(y, st)
+        got.append((y, st))
+    check(lib.st2_conv_umma_multi(arr, len(made), None))
+    torch.cuda.synchronize()
+    for (yw, sw), (yg, sg) in zip(want, got):
+        assert torch.isfinite(yg.float()).all()
+        assert torch.equal(yw, yg)
+        if sw is not None:
+            assert torch.equal(sw, sg)

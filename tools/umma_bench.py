@@ -59,10 +59,45 @@ def time_it(p, iters):
     return e0.elapsed_time(e1) / iters * 1e3  # us
 
 
+def time_multi(ps, iters):
+    arr = (_cabi.St2ConvParams * len(ps))(*ps)
+    for _ in range(2):
+        check(lib.st2_conv_umma_multi(arr, len(ps), None))
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(iters):
+        check(lib.st2_conv_umma_multi(arr, len(ps), None))
+    e1.record()
+    torch.cuda.synchronize()
+    return e0.elapsed_time(e1) / iters * 1e3
+
+
+def multi_main(iters):
+    """fused (one kernel, CTAs alternate between the convs tile by tile) against separate launches"""
+    B, S = 32, _cabi.ACT_SNAKE
+    for tag, L, C in (("s2", 48001, 128), ("s1", 8000, 256)):
+        for res in (False, True):
+            made = [make(B, L, C, C, k, 1, S, res, True) for k in (3, 7, 11)]
+            ps = [m[0] for m in made]
+            sep = [time_it(p, iters) for p in ps]
+            for combo in ((0, 2), (0, 1), (1, 2), (0, 1, 2)):
+                us = time_multi([ps[i] for i in combo], iters)
+                ssum = sum(sep[i] for i in combo)
+                fl = sum(ps[i].algo_flops for i in combo)
+                ks = "+".join(f"k{(3, 7, 11)[i]}" for i in combo)
+                print(f"{tag} {'c2(res)' if res else 'c1     '} {ks:10s} fused {us:8.1f} us  separate {ssum:8.1f} us  "
+                      f"({100 * (us / ssum - 1):+5.1f} %)  {fl / us / 1e6:7.1f} TFLOP/s", flush=True)
+            del made, ps
+            torch.cuda.empty_cache()
+
+
 def main():
     iters = 5
     if "--iters" in sys.argv:
         iters = int(sys.argv[sys.argv.index("--iters") + 1])
+    if "--multi" in sys.argv:
+        return multi_main(iters)
     B = 32
     cases = []
     if "--one" in sys.argv:

@@ -37,6 +37,29 @@ if "--hifi" in sys.argv:
         ("s4 pair k2 c1", 120000, 64, 64, 2, 1, S, False, True, False),
         ("s4 pair k5 c1", 120000, 64, 64, 5, 1, S, False, True, False),
     ]
+if "--multi" in sys.argv:
+    from umma_bench import time_multi
+    for tag, L, C_ in (("s2", 48001, 128), ("s1", 8000, 256)):
+        for combo in ((3, 11), (3, 7, 11)):
+            made = [make(B, L, C_, C_, k, 1, S, False, True) for k in combo]
+            ps = [m[0] for m in made]
+            arr = (_cabi.St2ConvParams * len(ps))(*ps)
+            os.environ.pop("ST2_UMMA_DBG", None); check(lib.st2_umma_reload_env())
+            us = time_multi(ps, 5)
+            os.environ["ST2_UMMA_DBG"] = "64"; check(lib.st2_umma_reload_env())
+            out = (C.c_uint64 * 16)()
+            check(lib.st2_conv_umma_multi(arr, len(ps), None)); check(lib.st2_umma_wait_profile(out, 1))
+            us_p = time_multi(ps, 3)
+            check(lib.st2_umma_wait_profile(out, 1))
+            v = [int(x) for x in out]
+            pct = lambda i, base: 100.0 * v[i] / max(v[base], 1)
+            print(f"{tag} fused {'+'.join('k%d' % k for k in combo):10s} {us:7.1f} us ({us_p:7.1f} instr.) cyc/tile {v[0] / max(v[4], 1):7.0f} | MMA waits: t_empty {pct(1, 0):4.1f}% "
+                  f"a_full {pct(2, 0):4.1f}% w_full {pct(3, 0):4.1f}% | EPI: t_full {pct(6, 5):4.1f}% stg_free {pct(7, 5):4.1f}% stats {pct(8, 5):4.1f}% "
+                  f"| PROD: a_empty {pct(10, 9):4.1f}% raw_full {pct(11, 9):4.1f}% math {pct(12, 9):4.1f}%", flush=True)
+            os.environ.pop("ST2_UMMA_DBG", None); check(lib.st2_umma_reload_env())
+            del made, ps, arr
+            torch.cuda.empty_cache()
+    sys.exit(0)
 for name, L, cin, n, k, dil, act, r, s, acc in cases:
     p, keep = make(B, L, cin, n, k, dil, act, r, s, acc)
     os.environ.pop("ST2_UMMA_DBG", None)
