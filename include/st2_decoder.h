@@ -57,7 +57,7 @@ extern "C" {
 #define ST2_PREC_FP32 0 /* fp32 FFMA kernels, fp32 activations: the parity path        */
 #define ST2_PREC_BF16 1 /* tcgen05 bf16 x bf16 -> fp32 (TMEM), bf16 activations in HBM */
 #define ST2_PREC_FP32_TC 2 /* the parity path on the tensor cores: fp32 activations, every dense conv as three bf16
-                              products x_hi w_hi + x_lo w_hi + x_hi w_lo with fp32 accumulation in TMEM (decoders only;
+                              products x_hi w_hi + x_lo w_hi + x_hi w_lo with fp32 accumulation in TMEM (decoders and F0N;
                               needs st2_decoder_set_option(h, "fp32_tc", 1) before load: 3x the bf16 weight bytes) */
 
 #define ST2_MAX_UPS 4

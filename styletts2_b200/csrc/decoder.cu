@@ -621,7 +621,7 @@ static int do_load(St2Decoder* h, const St2Tensor* tensors, int n) {
   const St2Config& c = h->cfg;
   Loader L;
   L.style = c.style_dim;
-  L.fp32_tc = h->opt_fp32_tc && (c.kind == ST2_KIND_ISTFTNET || c.kind == ST2_KIND_HIFIGAN);
+  L.fp32_tc = h->opt_fp32_tc && (c.kind == ST2_KIND_ISTFTNET || c.kind == ST2_KIND_HIFIGAN || c.kind == ST2_KIND_F0N);
   std::vector<std::string> names(n);
   for (int i = 0; i < n; ++i) {
     ST2_REQUIRE(tensors[i].name && tensors[i].data, "tensor without name/data");
@@ -1769,9 +1769,10 @@ extern "C" int st2_decoder_forward(St2Decoder* h, const float* asr, const float*
 
 template <typename AT>
 static int f0n_t(St2Decoder* h, const float* x, const float* s, float* f0, float* n, void* ws, int64_t ws_bytes,
-                 int B, int T, cudaStream_t st, bool dry, int64_t* peak) {
+                 int B, int T, cudaStream_t st, bool dry, int64_t* peak, bool tc32 = false) {
   Fwd<AT> f;
   f.h = h; f.st = st; f.B = B; f.T = T; f.dry = dry;
+  f.tc32 = tc32;
   f.ar.base = reinterpret_cast<uint8_t*>(ws); f.ar.cap = ws_bytes; f.ar.dry = dry;
   int rc = f.run_f0n(x, s, f0, n);
   if (peak) *peak = f.ar.peak;
@@ -1781,14 +1782,16 @@ static int f0n_plan(St2Decoder* h, int B, int T, int precision, int64_t* bytes) 
   int64_t peak = 0;
   int rc = precision == ST2_PREC_BF16
                ? f0n_t<__nv_bfloat16>(h, nullptr, nullptr, nullptr, nullptr, nullptr, 0, B, T, 0, true, &peak)
-               : f0n_t<float>(h, nullptr, nullptr, nullptr, nullptr, nullptr, 0, B, T, 0, true, &peak);
+               : f0n_t<float>(h, nullptr, nullptr, nullptr, nullptr, nullptr, 0, B, T, 0, true, &peak,
+                              precision == ST2_PREC_FP32_TC);
   *bytes = round_up(peak, 256) + 256;
   return rc;
 }
 extern "C" int64_t st2_f0n_workspace_bytes(const St2Decoder* hc, int B, int T, int precision) {
   St2Decoder* h = const_cast<St2Decoder*>(hc);
   if (!h || !h->loaded || h->cfg.kind != ST2_KIND_F0N || B < 1 || T < 1 ||
-      (precision != ST2_PREC_FP32 && precision != ST2_PREC_BF16)) {
+      (precision != ST2_PREC_FP32 && precision != ST2_PREC_BF16 && precision != ST2_PREC_FP32_TC) ||
+      (precision == ST2_PREC_FP32_TC && !h->opt_fp32_tc)) {
     set_error("st2_f0n_workspace_bytes: bad argument, wrong handle kind or weights not loaded");
     return ST2_EINVAL;
   }
@@ -1809,7 +1812,9 @@ extern "C" int st2_f0n_forward(St2Decoder* h, const float* x, const float* s, fl
     return ST2_ESTATE;
   }
   ST2_REQUIRE(B >= 1 && B <= 65535 && T >= 1, "batch / length");
-  ST2_REQUIRE(precision == ST2_PREC_FP32 || precision == ST2_PREC_BF16, "precision");
+  ST2_REQUIRE(precision == ST2_PREC_FP32 || precision == ST2_PREC_BF16 || precision == ST2_PREC_FP32_TC, "precision");
+  ST2_REQUIRE(precision != ST2_PREC_FP32_TC || h->opt_fp32_tc,
+              "ST2_PREC_FP32_TC needs st2_decoder_set_option(h, \"fp32_tc\", 1) before st2_decoder_load");
   ST2_REQUIRE(((uintptr_t)workspace & 255) == 0, "workspace must be 256-byte aligned");
   int dev = -1;
   ST2_CUDA_OK(cudaGetDevice(&dev));
@@ -1825,7 +1830,8 @@ extern "C" int st2_f0n_forward(St2Decoder* h, const float* x, const float* s, fl
   cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
   rc = precision == ST2_PREC_BF16
            ? f0n_t<__nv_bfloat16>(h, x, s, f0_out, n_out, workspace, workspace_bytes, B, T, st, false, nullptr)
-           : f0n_t<float>(h, x, s, f0_out, n_out, workspace, workspace_bytes, B, T, st, false, nullptr);
+           : f0n_t<float>(h, x, s, f0_out, n_out, workspace, workspace_bytes, B, T, st, false, nullptr,
+                          precision == ST2_PREC_FP32_TC);
   h->last_launches = launch_counter() - before;
   return rc;
 }

@@ -67,7 +67,9 @@ class F0NPredictor(_DecoderBase):
             raise RuntimeError(f"input_size mismatch: x has {Cin} channels, the LSTM expects "
                                f"{self.d_hid + self.style_dim}; s has {s.shape[1]}, expected {self.style_dim}")
         prec = precision or self.precision
-        prec_id = {"fp32": _cabi.PREC_FP32, "bf16": _cabi.PREC_BF16}[prec]
+        prec_id = {"fp32": _cabi.PREC_FP32, "bf16": _cabi.PREC_BF16, "fp32tc": _cabi.PREC_FP32_TC}[prec]
+        if prec == "fp32tc" and not self.fp32_tc:
+            self.fp32_tc = True   # packs the 3 x bf16 blobs at the next weight upload
         dev = x.device
         x_ = x.to(dev, torch.float32).contiguous()
         s_ = s.to(dev, torch.float32).contiguous()

@@ -109,3 +109,21 @@ def test_f0n_error_behaviour():
             p.F0Ntrain(torch.randn(1, 640, 8, device="cuda"), torch.randn(1, 128, device="cuda"))
     finally:
         p.eval()
+
+
+@pytest.mark.parametrize("T", [20, 51])
+def test_f0n_fp32_tensor_core_path_vs_reference_golden(T):
+    """ST2_PREC_FP32_TC for F0Ntrain: the LSTM input projection and the six AdainResBlk1d convs on tcgen05 as 3 x bf16
+    products with fp32 accumulation; same golden, <= 1e-3"""
+    import styletts2_b200 as st2
+    import synthetic as synth
+    p = st2.F0NPredictor(**synth.F0N_CFG)
+    p.load_state_dict(synth.synth_f0n_state_dict(synth.F0N_CFG, seed=0), strict=True)
+    p = p.cuda().eval()
+    p.fp32_tc = True
+    g = np.load(os.path.join(GOLD, f"f0n_T{T}.npz"))
+    F0, N = p.F0Ntrain(torch.from_numpy(g["x"]).cuda(), torch.from_numpy(g["s"]).cuda(), precision="fp32tc")
+    e0 = (F0.cpu() - torch.from_numpy(g["F0"])).abs().max().item()
+    e1 = (N.cpu() - torch.from_numpy(g["N"])).abs().max().item()
+    print(f"F0Ntrain fp32tc T={T}: max-abs F0 {e0:.2e}, N {e1:.2e}")
+    assert e0 < 1e-3 and e1 < 1e-3

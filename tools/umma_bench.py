@@ -81,12 +81,12 @@ def multi_main(iters):
             made = [make(B, L, C, C, k, 1, S, res, True) for k in (3, 7, 11)]
             ps = [m[0] for m in made]
             sep = [time_it(p, iters) for p in ps]
-            for combo in ((0, 2), (0, 1), (1, 2), (0, 1, 2)):
+            for combo in ((0, 2), (0, 1), (1, 2), (0, 1, 2), (0, 2, 1)):
                 us = time_multi([ps[i] for i in combo], iters)
                 ssum = sum(sep[i] for i in combo)
                 fl = sum(ps[i].algo_flops for i in combo)
                 ks = "+".join(f"k{(3, 7, 11)[i]}" for i in combo)
-                print(f"{tag} {'c2(res)' if res else 'c1     '} {ks:10s} fused {us:8.1f} us  separate {ssum:8.1f} us  "
+                print(f"{tag} {'c2(res)' if res else 'c1     '} {ks:11s} fused {us:8.1f} us  separate {ssum:8.1f} us  "
                       f"({100 * (us / ssum - 1):+5.1f} %)  {fl / us / 1e6:7.1f} TFLOP/s", flush=True)
             del made, ps
             torch.cuda.empty_cache()
