@@ -1159,6 +1159,25 @@ struct Fwd {
     return ST2_OK;
   }
 
+  // one chain position of the lock-step schedule: ONE launch of all nk convs.  (ST2_LOCKSTEP=2, an A/B switch: large
+  // problems run the k-smallest + k-largest conv fused and the middle one alone.  The microbenchmark has that 2 % ahead
+  // of three in one -- the SIMT-bound k = 3 tiles pair best with the tensor-bound k = 11 tiles -- but whole C2 / C4
+  // steps on one box do not: 20.05 vs 20.00 ms and 41.9 vs 41.7 ms, profiles/r2_lockstep_ab.txt.)
+  int conv_position(const ConvW* const* cs, const ConvIO* ios, int nk, float** parts, int* tiles, int* cols) {
+    const int64_t tiles_per_conv = (int64_t)B * ceil_div(ios[0].Lout, 256) * ceil_div(cs[0]->n, 128);
+    if (nk != 3 || tiles_per_conv < 2 * 148 || lockstep_mode != 2) return conv_multi(cs, ios, nk, parts, tiles, cols);
+    const ConvW* c2[2] = {cs[0], cs[2]};
+    ConvIO io2[2] = {ios[0], ios[2]};
+    float* p2[2]; int t2[2], n2[2];
+    int rc = conv_multi(c2, io2, 2, p2, t2, n2);
+    if (rc) return rc;
+    parts[0] = p2[0]; tiles[0] = t2[0]; cols[0] = n2[0];
+    parts[2] = p2[1]; tiles[2] = t2[1]; cols[2] = n2[1];
+    rc = conv_multi(cs + 1, ios + 1, 1, parts + 1, tiles + 1, cols + 1);
+    return rc;
+  }
+  int lockstep_mode = 0;  // ST2_LOCKSTEP: 0 off, 1 (default) all resblocks of a position in one launch, 2 see above
+
   // The nk resblocks of a generator stage (istftnet.py:369-374: xs = sum_j resblocks[i*nk+j](x); x = xs / nk) run in
   // lock step: their convs at the same position of the chain have the same shape and no dependence on each other, so
   // each position is ONE kernel launch whose CTAs alternate between the resblocks tile by tile (conv_multi) -- the
@@ -1183,7 +1202,7 @@ struct Fwd {
         ios[j].want_stats = true;
         cs[j] = pr ? &r.c1p[it] : &r.c1[it];
       }
-      int rc = conv_multi(cs, ios, nk, parts, tiles, cols);
+      int rc = conv_position(cs, ios, nk, parts, tiles, cols);
       if (rc) return rc;
       const NormW* norms[3];
       for (int j = 0; j < nk; ++j) norms[j] = &rs[j].n2[it];
@@ -1207,7 +1226,7 @@ struct Fwd {
           if (rc) return rc;
         }
       } else {
-        rc = conv_multi(cs, ios, nk, parts, tiles, cols);
+        rc = conv_position(cs, ios, nk, parts, tiles, cols);
         if (rc) return rc;
         const NormW* norms[3];
         for (int j = 0; j < nk; ++j) norms[j] = &rs[j].n1[it + 1];
@@ -1413,8 +1432,9 @@ int Fwd<AT>::run(const float* asr, const float* f0, const float* nn, const float
   Act<AT> x = xg;
   const int nk = c.n_resblock_kernels;
   // bf16 path: the resblocks of a stage run in lock step, one fused launch per position (ST2_LOCKSTEP=0: one by one)
-  static const bool lockstep_env = [] { const char* e = getenv("ST2_LOCKSTEP"); return !(e && e[0] == '0'); }();
-  const bool lockstep = lockstep_env && DT<AT>::id == ST2_DT_BF16;
+  static const int lockstep_env = [] { const char* e = getenv("ST2_LOCKSTEP"); return e ? atoi(e) : 1; }();
+  const bool lockstep = lockstep_env != 0 && DT<AT>::id == ST2_DT_BF16;
+  lockstep_mode = lockstep_env;
   for (int i = 0; i < c.n_ups; ++i) {
     const UpW& up = h->ups[i];
     const bool lastst = i == c.n_ups - 1;
