@@ -42,6 +42,8 @@
 // Pipelines: A ring (3-4 stages: loading / transforming / feeding the MMAs), W ring, TMEM double
 // buffer (MMA <-> epilogue): the prologue of tile i+1 and the epilogue of tile i-1 overlap the
 // MMAs of tile i.  No thread of this kernel waits on a global load it has just issued.
+// One launch may run up to three same-shaped convs (UmJobs, st2_conv_umma_multi): the CTAs alternate between them tile
+// by tile and every role looks the conv's parameters up per tile; the rings and barriers run straight through.
 //
 // Reference semantics: conv_params.h (Modules/istftnet.py:66-75, 440-453, 358-374).
 #include <cuda.h>
