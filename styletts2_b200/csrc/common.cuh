@@ -6,6 +6,7 @@
 #include <stdio.h>
 
 #include <string>
+#include <vector>
 
 #include "../../include/st2_decoder.h"
 #include "conv_params.h"
@@ -146,6 +147,17 @@ __device__ __forceinline__ void box_muller(uint32_t a, uint32_t b, float& z0, fl
 int launch_conv_simt(const St2ConvParams& p, cudaStream_t st);
 int launch_conv_umma(const St2ConvParams& p, cudaStream_t st);
 int launch_conv_umma_multi(const St2ConvParams* ps, int n, cudaStream_t st);  // up to 3 same-shaped convs, one kernel
+                                                                               // (conv_umma_multi.cu)
+void umma_multi_reload_env();
+int umma_multi_wait_read(unsigned long long* h16, bool reset);
+// per-launch event timing of the tcgen05 conv launches of the calling thread (st2_prof_enable / st2_prof_read)
+struct UmProf {
+  bool on = false;
+  std::vector<cudaEvent_t> ev;  // pairs
+  size_t used = 0;
+  double flops = 0.0;
+};
+UmProf& umma_prof();
 int conv_tile_rows(bool umma);
 int umma_n_tile(int n_cols);  // GEMM columns per tcgen05 tile for a layer of n_cols (0: none)
 int umma_prepare(int acc_mult);  // conv_umma's one-time per-device setup (called by st2_decoder_load, never by forward)

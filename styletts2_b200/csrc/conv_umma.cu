@@ -42,8 +42,6 @@
 // Pipelines: A ring (3-4 stages: loading / transforming / feeding the MMAs), W ring, TMEM double
 // buffer (MMA <-> epilogue): the prologue of tile i+1 and the epilogue of tile i-1 overlap the
 // MMAs of tile i.  No thread of this kernel waits on a global load it has just issued.
-// One launch may run up to three same-shaped convs (UmJobs, st2_conv_umma_multi): the CTAs alternate between them tile
-// by tile and every role looks the conv's parameters up per tile; the rings and barriers run straight through.
 //
 // Reference semantics: conv_params.h (Modules/istftnet.py:66-75, 440-453, 358-374).
 #include <cuda.h>
@@ -136,24 +134,6 @@ struct UmMisc {
   alignas(128) uint4 bias_b[2][128];
   alignas(128) uint4 ones_a[16];   // core matrix k 0..7 = rows of (1, 1, 0, 0, 0, 0, 0, 0); k 8..15 = zeros
   alignas(16) float sred[256][2];
-};
-
-// Up to UM_MAX_JOBS convs of the same geometry (batch, length, input / output channels, tile) run as ONE persistent
-// kernel whose CTAs alternate between them tile by tile (work item wi -> job wi % n, tile slot wi / n): a conv whose
-// tiles are bound by the SIMT roles (k = 3: prologue + epilogue per element, 3 taps of MMAs) then overlaps one whose
-// tiles are bound by the tensor pipe (k = 11), through the same A / W rings and TMEM double buffer that already
-// overlap consecutive tiles of one conv.  Everything that differs between the jobs (taps, dilation, weights, AdaIN
-// parameters, residual, output, statistics) is looked up per tile; the shared-memory geometry is common.
-constexpr int UM_MAX_JOBS = 3;
-struct alignas(64) UmJob {
-  CUtensorMap ymap, rmap, xmap, xmap8;
-  St2ConvParams p;
-  UmLayout lay;
-};
-struct alignas(64) UmJobs {
-  UmJob j[UM_MAX_JOBS];
-  CUtensorMap wmap, wmap_res, wmap_acc;  // pair mode (single job only)
-  int n;
 };
 
 // ------------------------------------------------------------------ PTX wrappers
@@ -503,7 +483,7 @@ __device__ __forceinline__ UmTile um_tile_(int tile, int n_ttiles, int n_ntiles,
 // the it-th tile of this CTA (total_tiles = none left).  Pair mode: the cluster takes pair-tile q = (nt, btp) and its
 // CTA of rank r the (item, time) tile 2 btp + r, clamped to the last one (an odd count makes both CTAs compute the
 // same tile: identical bytes stored twice).
-#define um_tile_at(it, total_tiles, n_ntiles) um_tile_at_<PAIR>(um_slot_of(J.n, it), total_tiles, n_ntiles, lay)
+#define um_tile_at(it, total_tiles, n_ntiles) um_tile_at_<PAIR>(it, total_tiles, n_ntiles, lay)
 template <bool PAIR>
 __device__ __forceinline__ int um_tile_at_(int it, int total_tiles, int n_ntiles, const UmLayout& lay) {
   if (!PAIR) {
@@ -519,18 +499,13 @@ __device__ __forceinline__ int um_tile_at_(int it, int total_tiles, int n_ntiles
   return bt * n_ntiles + nt;
 }
 
-// work item wi of this CTA -> (job, tile slot): the jobs take turns
-__device__ __forceinline__ int um_slot_of(int n, int wi) { return n == 1 ? wi : (n == 2 ? wi >> 1 : wi / 3); }
-__device__ __forceinline__ int um_job_of(int n, int wi) { return wi - um_slot_of(n, wi) * n; }
-
-// one producer cursor: which (job, tile, chunk) an operation is at, the tile's coordinates, and the A
+// one producer cursor: which (tile, chunk) an operation is at, the tile's coordinates, and the A
 // stage / phase the chunk maps to
 struct UmCur {
   int tile, c, stage;
   uint32_t ph;
   int b, t0, nt;
-  int it;   // work item index
-  int job;
+  int it;
 };
 // Order of a tile's chunks in the A ring.  nh "heavy" chunks (64 input channels: k taps of MMAs, prologue arithmetic)
 // and nl "light" ones (64 residual / y_old columns: one identity tap, no arithmetic) are interleaved H L H L ...,
@@ -555,7 +530,7 @@ __device__ __forceinline__ UmSlot um_slot(int c, int nh, int nl) {
   return s;
 }
 #define um_cur_tile(q, total_tiles, n_ttiles, n_ntiles) um_cur_tile_(q, total_tiles, n_ttiles, n_ntiles, lay)
-#define um_advance(q, nchunks, na, total_tiles, n_ttiles, n_ntiles) um_advance_<PAIR>(q, nchunks, na, total_tiles, n_ttiles, n_ntiles, lay, J.n)
+#define um_advance(q, nchunks, na, total_tiles, n_ttiles, n_ntiles) um_advance_<PAIR>(q, nchunks, na, total_tiles, n_ttiles, n_ntiles, lay)
 __device__ __forceinline__ void um_cur_tile_(UmCur& q, int total_tiles, int n_ttiles, int n_ntiles, const UmLayout& lay) {
   if (q.tile < total_tiles) {
     const UmTile t = um_tile(q.tile, n_ttiles, n_ntiles);
@@ -564,12 +539,10 @@ __device__ __forceinline__ void um_cur_tile_(UmCur& q, int total_tiles, int n_tt
 }
 template <bool PAIR>
 __device__ __forceinline__ void um_advance_(UmCur& q, int nchunks, int na, int total_tiles, int n_ttiles,
-                                            int n_ntiles, const UmLayout& lay, int njobs) {
+                                            int n_ntiles, const UmLayout& lay) {
   if (++q.c == nchunks) {
     q.c = 0;
-    ++q.it;
-    q.job = um_job_of(njobs, q.it);
-    q.tile = um_tile_at_<PAIR>(um_slot_of(njobs, q.it), total_tiles, n_ntiles, lay);
+    q.tile = um_tile_at(++q.it, total_tiles, n_ntiles);
     um_cur_tile(q, total_tiles, n_ttiles, n_ntiles);
   }
   if (++q.stage == na) {
@@ -597,35 +570,27 @@ __device__ __forceinline__ float um_act(float v, float sc, float sh, float wsc, 
 }
 
 template <int ACT, bool HAS_SS, bool PAIR>
-__device__ __forceinline__ void um_produce(const UmJobs& J, uint8_t* smem,
+__device__ __forceinline__ void um_produce(const St2ConvParams& p, const UmLayout& lay, const CUtensorMap* ymap,
+                                           const CUtensorMap* rmap, const CUtensorMap* xmap,
+                                           const CUtensorMap* xmap8, uint8_t* smem,
                                            UmMisc* misc, int ptid, int total_tiles, int n_ttiles,
                                            int n_ntiles, int nchunks) {
   const int v = ptid & 7, rbase = ptid >> 3;
-  const UmLayout& lay = J.j[0].lay;  // the shared-memory geometry and the switches are common to all jobs
-  // chunks per tile of a job, incl. its residual / y_old rows
-  auto nct_of = [&](int job) { return nchunks + J.j[job].lay.n_res + J.j[job].lay.n_acc; };
+  const int r_tot = UM_TM + (p.k - 1) * p.dil;
+  const int n_light = lay.n_res + lay.n_acc;
+  const int nct = nchunks + n_light;  // chunks per tile incl. residual / y_old rows
+  const __nv_bfloat16* xg = reinterpret_cast<const __nv_bfloat16*>(p.x);
   // this thread's 16-byte slot of row rbase in stage 0; row rbase + 32 i is i * 4096 bytes further
   // (same row & 7, hence the same swizzled slot)
   const uint32_t a0 = smem_u32(smem + lay.off_a) + (uint32_t)rbase * 128u + (uint32_t)((v ^ (rbase & 7)) << 4);
+  const int64_t x_step = (int64_t)32 * p.ldx;
   constexpr bool IDENT = (ACT == ST2_ACT_NONE) && !HAS_SS;
-  // per-job view inside the lambdas below (the names shadow the common ones on purpose)
-#define UM_JOB_VIEW(q)                                                                                   \
-  const UmJob& jb = J.j[(q).job];                                                                        \
-  const St2ConvParams& p = jb.p;                                                                         \
-  const UmLayout& lay = jb.lay;                                                                          \
-  const CUtensorMap *ymap = &jb.ymap, *rmap = &jb.rmap, *xmap = &jb.xmap, *xmap8 = &jb.xmap8;            \
-  (void)ymap; (void)rmap; (void)xmap; (void)xmap8;                                                       \
-  const int r_tot = UM_TM + (p.k - 1) * p.dil, n_light = lay.n_res + lay.n_acc;                          \
-  (void)r_tot; (void)n_light
   const bool prof = (lay.dbg & 64) && ptid == 0;
   long long w_raw = 0, w_math = 0, w_empty_c = 0;
   const long long c_start = um_clk(prof);
 
   // the caller has seen a_empty[q.stage] complete for this round of the ring
   auto issue_loads = [&](const UmCur& q) {
-    UM_JOB_VIEW(q);
-    const __nv_bfloat16* xg = reinterpret_cast<const __nv_bfloat16*>(p.x);
-    const int64_t x_step = (int64_t)32 * p.ldx;
     const uint32_t dst = a0 + (uint32_t)q.stage * (uint32_t)lay.a_bytes;
     const UmSlot sl = um_slot(q.c, nchunks, n_light);
     if (sl.heavy && lay.x_tma) {
@@ -692,7 +657,6 @@ __device__ __forceinline__ void um_produce(const UmJobs& J, uint8_t* smem,
 
   // raw per-channel parameters of the chunk (scale, shift pairs and alpha), loaded one iteration early
   auto load_params = [&](const UmCur& q, float2 (&ssr)[8], float (&alr)[8]) {
-    UM_JOB_VIEW(q);
     const UmSlot sl = um_slot(q.c, nchunks, n_light);
     if (!sl.heavy || q.tile >= total_tiles) return;
     const int ch0 = sl.idx * UM_CK + v * 8;
@@ -716,7 +680,6 @@ __device__ __forceinline__ void um_produce(const UmJobs& J, uint8_t* smem,
   // `newer` = LDGSTS groups committed after chunk q's: q's group is complete once at most that many
   // are pending
   auto transform = [&](const UmCur& q, const float2 (&ssr)[8], const float (&alr)[8], int newer) {
-    UM_JOB_VIEW(q);
     const uint32_t dst = a0 + (uint32_t)q.stage * (uint32_t)lay.a_bytes;
     const UmSlot sl = um_slot(q.c, nchunks, n_light);
     if (lay.loader) {
@@ -853,7 +816,7 @@ __device__ __forceinline__ void um_produce(const UmJobs& J, uint8_t* smem,
   // a_empty barrier of the next slot and starts that chunk's loads as soon as the MMAs have released
   // it, up to na-1 chunks ahead.  (Residual / y_old chunks cost no arithmetic, so a fixed distance
   // counted in chunks would leave the following activation chunk no time to arrive.)
-  UmCur lc{um_tile_at(0, total_tiles, n_ntiles), 0, 0, 0u, 0, 0, 0, 0, 0};
+  UmCur lc{um_tile_at(0, total_tiles, n_ntiles), 0, 0, 0u, 0, 0, 0, 0};
   um_cur_tile(lc, total_tiles, n_ttiles, n_ntiles);
   UmCur tc = lc;
   int n_l = 0, n_t = 0;  // chunks whose loads are issued / that are transformed
@@ -866,7 +829,7 @@ __device__ __forceinline__ void um_produce(const UmJobs& J, uint8_t* smem,
         w_empty_c += um_clk(prof) - c0;
         issue_loads(lc);
         cp_async_commit();
-        um_advance(lc, nct_of(lc.job), lay.na, total_tiles, n_ttiles, n_ntiles);
+        um_advance(lc, nct, lay.na, total_tiles, n_ttiles, n_ntiles);
         ++n_l;
       }
       return;
@@ -876,7 +839,7 @@ __device__ __forceinline__ void um_produce(const UmJobs& J, uint8_t* smem,
       else if (!mbar_try(&misc->a_empty[lc.stage], lc.ph ^ 1u)) break;
       issue_loads(lc);
       cp_async_commit();
-      um_advance(lc, nct_of(lc.job), lay.na, total_tiles, n_ttiles, n_ntiles);
+      um_advance(lc, nct, lay.na, total_tiles, n_ttiles, n_ntiles);
       ++n_l;
       block = false;
     }
@@ -893,7 +856,7 @@ __device__ __forceinline__ void um_produce(const UmJobs& J, uint8_t* smem,
     try_issue(n_l == n_t);  // blocks only when the chunk to transform has not been requested yet
     // next chunk's parameters: their global loads are in flight during this chunk's arithmetic
     UmCur nx = tc;
-    um_advance(nx, nct_of(nx.job), lay.na, total_tiles, n_ttiles, n_ntiles);
+    um_advance(nx, nct, lay.na, total_tiles, n_ttiles, n_ntiles);
     float2 ssn[8];
     float aln[8];
 #pragma unroll
@@ -919,7 +882,6 @@ __device__ __forceinline__ void um_produce(const UmJobs& J, uint8_t* smem,
     atomicAdd(&g_um_wait[11], (unsigned long long)w_raw);
     atomicAdd(&g_um_wait[12], (unsigned long long)w_math);
   }
-#undef UM_JOB_VIEW
 }
 
 // fp32 bias -> (hi, lo, 0, ...) bf16: one 16-byte K group of the bias operand
@@ -970,9 +932,9 @@ __device__ __forceinline__ void um_stage32(const uint32_t (&chunk_addr)[8], int 
 }
 
 template <bool OUT_F32, bool PAIR>
-__device__ __forceinline__ void um_epilogue(const UmJobs& J, uint8_t* smem, UmMisc* misc, uint32_t tmem_base, int warp,
-                                            int lane, int total_tiles, int n_ttiles, int n_ntiles) {
-  const UmLayout& lay = J.j[0].lay;  // tile geometry and switches are common to all jobs
+__device__ __forceinline__ void um_epilogue(const St2ConvParams& p, const UmLayout& lay, const CUtensorMap* ymap,
+                                            uint8_t* smem, UmMisc* misc, uint32_t tmem_base, int warp, int lane,
+                                            int total_tiles, int n_ttiles, int n_ntiles) {
   const int q = warp & 3;                          // TMEM lane group this warp may access
   const int et = threadIdx.x - UM_EPI_WARP0 * 32;  // 0..127
   const int rl = q * 32 + lane;                    // row inside an accumulator = TMEM lane
@@ -983,6 +945,7 @@ __device__ __forceinline__ void um_epilogue(const UmJobs& J, uint8_t* smem, UmMi
   // statistics pass: ncp column pairs x (128 / ncp) row groups of ncp rows
   const int ncp = n_tile >> 1;
   const int cp = et % ncp, grp = et / ncp;
+  const float scale = p.out_scale;
   uint32_t chunk_addr[8];   // this row's 16-byte chunks in segment 0
   uint32_t col_addr[8];     // statistics pass: (row grp*ncp + i, column pair cp), i = 0..7
 #pragma unroll
@@ -1006,18 +969,13 @@ __device__ __forceinline__ void um_epilogue(const UmJobs& J, uint8_t* smem, UmMi
     const int tile = um_tile_at(it, total_tiles, n_ntiles);
     if (tile >= total_tiles) break;
     const UmTile tl = um_tile(tile, n_ttiles, n_ntiles);
-    const UmJob& jb = J.j[um_job_of(J.n, it)];  // this tile's conv
-    const St2ConvParams& p = jb.p;
-    const CUtensorMap* ymap = &jb.ymap;
-    const float scale = p.out_scale;
     const uint32_t tb = t_it & 1, tph = (t_it >> 1) & 1;
-    // bias of the tile that will use this TMEM buffer next (two work items ahead), loaded early
+    // bias of the tile that will use this TMEM buffer next (two tiles ahead), loaded early
     const int tile2 = um_tile_at(it + 2, total_tiles, n_ntiles);
-    const St2ConvParams& p2 = J.j[um_job_of(J.n, it + 2)].p;
     float bias2 = 0.f;
-    if (et < nb_cols && tile2 < total_tiles && p2.bias) {
+    if (et < nb_cols && tile2 < total_tiles && p.bias) {
       const UmTile t2 = um_tile(tile2, n_ttiles, n_ntiles);
-      bias2 = __ldg(p2.bias + (int64_t)t2.b * p2.bias_bstride + t2.nt * n_tile + b_col0 + et);
+      bias2 = __ldg(p.bias + (int64_t)t2.b * p.bias_bstride + t2.nt * n_tile + b_col0 + et);
     }
     // two independent accumulator sets (even / odd rows) halve the dependent FADD/FFMA chains
     // (sum, sum of squares) of this thread's two columns as packed fp32x2
@@ -1143,13 +1101,15 @@ __device__ __forceinline__ void um_epilogue(const UmJobs& J, uint8_t* smem, UmMi
 }
 
 template <bool PAIR>
-__global__ void __launch_bounds__(UM_THREADS, 1) conv_umma_kernel(const __grid_constant__ UmJobs J, int total_tiles,
-                                                                   int n_ttiles, int n_ntiles) {
-  const St2ConvParams& p = J.j[0].p;   // what all jobs share: shapes, channel counts, activation kind, dtypes
-  const UmLayout& lay = J.j[0].lay;    // shared-memory geometry, ring depths, switches
-  const CUtensorMap& wmap = J.wmap;
-  const CUtensorMap& wmap_res = J.wmap_res;
-  const CUtensorMap& wmap_acc = J.wmap_acc;
+__global__ void __launch_bounds__(UM_THREADS, 1) conv_umma_kernel(const St2ConvParams p, const UmLayout lay,
+                                                                   const __grid_constant__ CUtensorMap ymap,
+                                                                   const __grid_constant__ CUtensorMap rmap,
+                                                                   const __grid_constant__ CUtensorMap xmap,
+                                                                   const __grid_constant__ CUtensorMap xmap8,
+                                                                   const __grid_constant__ CUtensorMap wmap,
+                                                                   const __grid_constant__ CUtensorMap wmap_res,
+                                                                   const __grid_constant__ CUtensorMap wmap_acc,
+                                                                   int total_tiles, int n_ttiles, int n_ntiles) {
   extern __shared__ __align__(1024) uint8_t smem_raw[];
   // launched with the programmatic-serialization attribute (common.cuh).  Waiting after the CTA-local setup
   // (barrier init, TMEM allocation) instead of here made no measurable difference (same-box A/B, C2 step).
@@ -1159,7 +1119,7 @@ __global__ void __launch_bounds__(UM_THREADS, 1) conv_umma_kernel(const __grid_c
   const int nchunks = p.cin / UM_CK;
 
   if (threadIdx.x == 0) {
-    for (int i = 0; i < J.n; ++i) asm volatile("prefetch.tensormap [%0];" ::"l"(&J.j[i].ymap) : "memory");
+    asm volatile("prefetch.tensormap [%0];" ::"l"(&ymap) : "memory");
     for (int i = 0; i < UM_MAX_A; ++i) {
       mbar_init(&misc->a_full[i], UM_PROD_THREADS);
       mbar_init(&misc->a_empty[i], 1);
@@ -1187,11 +1147,10 @@ __global__ void __launch_bounds__(UM_THREADS, 1) conv_umma_kernel(const __grid_c
       if (et0 < nb_cols) {
         for (int i = 0; i < 2; ++i) {
           const int tile = um_tile_at(i, total_tiles, n_ntiles);
-          const St2ConvParams& pi = J.j[um_job_of(J.n, i)].p;
           float b = 0.f;
-          if (tile < total_tiles && pi.bias) {
+          if (tile < total_tiles && p.bias) {
             const UmTile t = um_tile(tile, n_ttiles, n_ntiles);
-            b = __ldg(pi.bias + (int64_t)t.b * pi.bias_bstride + t.nt * lay.n_tile + b_col0 + et0);
+            b = __ldg(p.bias + (int64_t)t.b * p.bias_bstride + t.nt * lay.n_tile + b_col0 + et0);
           }
           misc->bias_b[i][et0] = um_bias_split(b);
         }
@@ -1263,6 +1222,7 @@ __global__ void __launch_bounds__(UM_THREADS, 1) conv_umma_kernel(const __grid_c
       if (PAIR) umma2_commit_if(bar, on);
       else umma_commit_if(bar, on);
     };
+    const int nct = nchunks + lay.n_res + lay.n_acc;
     // the loop runs on ONE elected lane: the other lanes wait at the end of the kernel.  (With all lanes in the
     // loop every tcgen05.mma becomes a vote / ELECT / R2UR loop over the active lanes in the SASS.)
     const uint32_t leader = 1u;
@@ -1296,10 +1256,6 @@ __global__ void __launch_bounds__(UM_THREADS, 1) conv_umma_kernel(const __grid_c
         for (int acc = 0; acc < UM_NACC; ++acc)
           mma(d0 + (uint32_t)(acc * lay.n_tile), od, bd, idesc_main, 0u, leader);
       }
-      // this tile's conv: taps, dilation and residual / running-mean chunks
-      const St2ConvParams& pj = J.j[um_job_of(J.n, it)].p;
-      const UmLayout& lj = J.j[um_job_of(J.n, it)].lay;
-      const int nct = nchunks + lj.n_res + lj.n_acc;
       for (int c = 0; c < nct; ++c) {
         {
           const long long c0 = um_clk(prof);
@@ -1309,9 +1265,9 @@ __global__ void __launch_bounds__(UM_THREADS, 1) conv_umma_kernel(const __grid_c
         }
         const uint32_t a_u = (a_base + (uint32_t)as * (uint32_t)lay.a_bytes) >> 4;
         // residual / y_old chunks: one identity "tap" at row offset 0
-        const UmSlot sl = um_slot(c, nchunks, lj.n_res + lj.n_acc);
-        const int taps = sl.heavy ? pj.k : 1;
-        const uint32_t dil = sl.heavy ? (uint32_t)pj.dil : 0u;
+        const UmSlot sl = um_slot(c, nchunks, lay.n_res + lay.n_acc);
+        const int taps = sl.heavy ? p.k : 1;
+        const uint32_t dil = sl.heavy ? (uint32_t)p.dil : 0u;
         for (int j = 0; j < taps; ++j) {
           if (!w_ready) {
             const long long c0 = um_clk(prof);
@@ -1333,7 +1289,7 @@ __global__ void __launch_bounds__(UM_THREADS, 1) conv_umma_kernel(const __grid_c
           uint32_t idesc = idesc_main, dcol = 0;
           if (!sl.heavy && lay.n_tile == 128 && !PAIR) {
             const int e = sl.idx;
-            const uint32_t hh = (uint32_t)(e < lj.n_res ? e : e - lj.n_res);
+            const uint32_t hh = (uint32_t)(e < lay.n_res ? e : e - lay.n_res);
             idesc = lay.idesc64;
             dcol = hh * 64u;
             bd += (uint64_t)(hh * 64u);  // 64 columns x 16 bytes, in 16-byte units
@@ -1361,19 +1317,17 @@ __global__ void __launch_bounds__(UM_THREADS, 1) conv_umma_kernel(const __grid_c
   } else if (warp == UM_W_WARP) {
     // ================================================================ weight producer
     if (elect_one()) {
+      const uint8_t* wg = reinterpret_cast<const uint8_t*>(p.w);
       uint8_t* wsm = smem_raw + lay.off_w;
       const uint32_t wf0 = PAIR ? mapa_cta(smem_u32(&misc->w_full[0]), 0u) : 0u;
+      const int per_nt = nchunks * p.k;
       int ws = 0;
       uint32_t wph = 0;
       for (int it = 0;; ++it) {
         const int tile = um_tile_at(it, total_tiles, n_ntiles);
         if (tile >= total_tiles) break;
         const UmTile tl = um_tile(tile, n_ttiles, n_ntiles);
-        // this tile's conv: its blobs, tap count and identity blocks
-        const St2ConvParams& p = J.j[um_job_of(J.n, it)].p;
-        const UmLayout& lay = J.j[um_job_of(J.n, it)].lay;
-        const int per_nt = nchunks * p.k;
-        const uint8_t* src = reinterpret_cast<const uint8_t*>(p.w) + (int64_t)tl.nt * per_nt * lay.w_bytes;
+        const uint8_t* src = wg + (int64_t)tl.nt * per_nt * lay.w_bytes;
         // blobs in the order the MMA thread consumes them: chunk slots (um_slot), k taps per heavy chunk, one
         // identity blob per light chunk
         const int n_light = lay.n_res + lay.n_acc;
@@ -1421,19 +1375,15 @@ __global__ void __launch_bounds__(UM_THREADS, 1) conv_umma_kernel(const __grid_c
     //     arrivals; raw_full gets a plain arrive AFTER the expect_tx, and the producers arrive on a_full only after
     //     they have seen raw_full, so the phase cannot complete before its bytes are expected
     if (lay.loader && elect_one()) {
-      const bool ident = p.act == ST2_ACT_NONE && p.ss == nullptr;  // the same for every job (host-checked)
-      UmCur q{um_tile_at(0, total_tiles, n_ntiles), 0, 0, 0u, 0, 0, 0, 0, 0};
+      const int n_light = lay.n_res + lay.n_acc, nct = nchunks + n_light;
+      const bool ident = p.act == ST2_ACT_NONE && p.ss == nullptr;
+      const int r_tot = UM_TM + (p.k - 1) * p.dil;
+      const int nhb = (r_tot - UM_TM + 7) >> 3;
+      const uint32_t hbytes = (uint32_t)(UM_TM * 128 + nhb * 1024);
+      UmCur q{um_tile_at(0, total_tiles, n_ntiles), 0, 0, 0u, 0, 0, 0, 0};
       um_cur_tile(q, total_tiles, n_ttiles, n_ntiles);
       while (q.tile < total_tiles) {
         mbar_wait(&misc->a_empty[q.stage], q.ph ^ 1u, 0);
-        // this chunk's conv: halo, padding, tensor maps, residual / running-mean chunks
-        const UmJob& jb = J.j[q.job];
-        const St2ConvParams& p = jb.p;
-        const UmLayout& lay = jb.lay;
-        const int n_light = lay.n_res + lay.n_acc, nct = nchunks + n_light;
-        const int r_tot = UM_TM + (p.k - 1) * p.dil;
-        const int nhb = (r_tot - UM_TM + 7) >> 3;
-        const uint32_t hbytes = (uint32_t)(UM_TM * 128 + nhb * 1024);
         const UmSlot sl = um_slot(q.c, nchunks, n_light);
         const uint32_t base = smem_u32(smem_raw + lay.off_a) + (uint32_t)q.stage * (uint32_t)lay.a_bytes;
         if (sl.heavy) {
@@ -1443,9 +1393,9 @@ __global__ void __launch_bounds__(UM_THREADS, 1) conv_umma_kernel(const __grid_c
           const int row0 = q.t0 - p.pad, col = sl.idx * UM_CK;
           if (ident) mbar_expect_tx(bar, hbytes);
           else mbar_arrive_expect_tx(bar, hbytes);
-          tma_load_3d(&jb.xmap, base, col, row0, q.b, bar);
+          tma_load_3d(&xmap, base, col, row0, q.b, bar);
           for (int i = 0; i < nhb; ++i)
-            tma_load_3d(&jb.xmap8, base + (uint32_t)(UM_TM * 128 + i * 1024), col, row0 + UM_TM + 8 * i, q.b, bar);
+            tma_load_3d(&xmap8, base + (uint32_t)(UM_TM * 128 + i * 1024), col, row0 + UM_TM + 8 * i, q.b, bar);
           if (ident) mbar_arrive(&misc->raw_full[q.stage]);
         } else {
           // two 128-row boxes of residual / y_old rows in the SWIZZLE_128B pattern of the A tile, zero-filled past Lout
@@ -1455,7 +1405,7 @@ __global__ void __launch_bounds__(UM_THREADS, 1) conv_umma_kernel(const __grid_c
           const bool two = q.t0 + 128 < p.Lout;
           uint64_t* bar = &misc->a_full[q.stage];
           mbar_expect_tx(bar, two ? 32768u : 16384u);
-          const CUtensorMap* mp = is_res ? &jb.rmap : &jb.ymap;
+          const CUtensorMap* mp = is_res ? &rmap : &ymap;
           tma_load_3d(mp, base, col, q.t0, q.b, bar);
           if (two) tma_load_3d(mp, base + 16384u, col, q.t0 + 128, q.b, bar);
           mbar_arrive(&misc->raw_full[q.stage]);
@@ -1465,19 +1415,19 @@ __global__ void __launch_bounds__(UM_THREADS, 1) conv_umma_kernel(const __grid_c
     }
   } else if (warp >= UM_EPI_WARP0) {
     // ======================================================================= epilogue
-    if (p.y_dtype == ST2_DT_F32) um_epilogue<true, PAIR>(J, smem_raw, misc, tmem_base, warp, lane, total_tiles, n_ttiles, n_ntiles);
-    else um_epilogue<false, PAIR>(J, smem_raw, misc, tmem_base, warp, lane, total_tiles, n_ttiles, n_ntiles);
+    if (p.y_dtype == ST2_DT_F32) um_epilogue<true, PAIR>(p, lay, &ymap, smem_raw, misc, tmem_base, warp, lane, total_tiles, n_ttiles, n_ntiles);
+    else um_epilogue<false, PAIR>(p, lay, &ymap, smem_raw, misc, tmem_base, warp, lane, total_tiles, n_ttiles, n_ntiles);
   } else {
     // ============================================================ activation producers (warps 0-7)
     const int ptid = threadIdx.x - UM_PROD_WARP0 * 32;
     if (p.ss) {
-      if (p.act == ST2_ACT_SNAKE) um_produce<ST2_ACT_SNAKE, true, PAIR>(J, smem_raw, misc, ptid, total_tiles, n_ttiles, n_ntiles, nchunks);
-      else if (p.act == ST2_ACT_LRELU) um_produce<ST2_ACT_LRELU, true, PAIR>(J, smem_raw, misc, ptid, total_tiles, n_ttiles, n_ntiles, nchunks);
-      else um_produce<ST2_ACT_NONE, true, PAIR>(J, smem_raw, misc, ptid, total_tiles, n_ttiles, n_ntiles, nchunks);
+      if (p.act == ST2_ACT_SNAKE) um_produce<ST2_ACT_SNAKE, true, PAIR>(p, lay, &ymap, &rmap, &xmap, &xmap8, smem_raw, misc, ptid, total_tiles, n_ttiles, n_ntiles, nchunks);
+      else if (p.act == ST2_ACT_LRELU) um_produce<ST2_ACT_LRELU, true, PAIR>(p, lay, &ymap, &rmap, &xmap, &xmap8, smem_raw, misc, ptid, total_tiles, n_ttiles, n_ntiles, nchunks);
+      else um_produce<ST2_ACT_NONE, true, PAIR>(p, lay, &ymap, &rmap, &xmap, &xmap8, smem_raw, misc, ptid, total_tiles, n_ttiles, n_ntiles, nchunks);
     } else {
-      if (p.act == ST2_ACT_SNAKE) um_produce<ST2_ACT_SNAKE, false, PAIR>(J, smem_raw, misc, ptid, total_tiles, n_ttiles, n_ntiles, nchunks);
-      else if (p.act == ST2_ACT_LRELU) um_produce<ST2_ACT_LRELU, false, PAIR>(J, smem_raw, misc, ptid, total_tiles, n_ttiles, n_ntiles, nchunks);
-      else um_produce<ST2_ACT_NONE, false, PAIR>(J, smem_raw, misc, ptid, total_tiles, n_ttiles, n_ntiles, nchunks);
+      if (p.act == ST2_ACT_SNAKE) um_produce<ST2_ACT_SNAKE, false, PAIR>(p, lay, &ymap, &rmap, &xmap, &xmap8, smem_raw, misc, ptid, total_tiles, n_ttiles, n_ntiles, nchunks);
+      else if (p.act == ST2_ACT_LRELU) um_produce<ST2_ACT_LRELU, false, PAIR>(p, lay, &ymap, &rmap, &xmap, &xmap8, smem_raw, misc, ptid, total_tiles, n_ttiles, n_ntiles, nchunks);
+      else um_produce<ST2_ACT_NONE, false, PAIR>(p, lay, &ymap, &rmap, &xmap, &xmap8, smem_raw, misc, ptid, total_tiles, n_ttiles, n_ntiles, nchunks);
     }
   }
 
@@ -1557,7 +1507,6 @@ struct UmEnv {
   int wst = 0;    // 0 = default depth
   int dist = -1;  // -1 = default
   bool res_tma = true, x_tma = true, loader = true;
-  bool no_multi = false;  // ST2_UMMA_MULTI=0: launch the jobs of launch_conv_umma_multi one by one (A/B switch)
 };
 static std::mutex g_env_mu;
 static UmEnv g_env;
@@ -1572,7 +1521,6 @@ static void um_env_read_locked() {
   if (const char* v = getenv("ST2_UMMA_RES_TMA")) e.res_tma = v[0] != '0';
   if (const char* v = getenv("ST2_UMMA_X_TMA")) e.x_tma = v[0] != '0';
   if (const char* v = getenv("ST2_UMMA_LOADER")) e.loader = v[0] != '0';
-  if (const char* v = getenv("ST2_UMMA_MULTI")) e.no_multi = v[0] == '0';
   g_env = e;
   g_env_ready = true;
 }
@@ -1799,17 +1747,10 @@ int umma_prepare(int acc_mult) {
 }
 
 // optional per-launch event timing (st2_prof_enable / st2_prof_read)
-struct UmProf {
-  bool on = false;
-  std::vector<cudaEvent_t> ev;  // pairs
-  size_t used = 0;
-  double flops = 0.0;
-};
 static thread_local UmProf g_prof;
+UmProf& umma_prof() { return g_prof; }  // shared with conv_umma_multi.cu
 
-// argument checks + layout + tensor maps of one conv -> jb; n_ttiles / n_ntiles / total of its tile grid
-static int um_build_job(const St2ConvParams& p, int dev, const UmEnv& env, UmJob& jb, int* n_ttiles_o, int* n_ntiles_o,
-                        int64_t* total_o) {
+int launch_conv_umma(const St2ConvParams& p, cudaStream_t st) {
   ST2_REQUIRE(p.B > 0 && p.Lout > 0, "conv_umma: empty shape");
   ST2_REQUIRE(p.x_dtype == ST2_DT_BF16, "conv_umma: bf16 input activations only");
   ST2_REQUIRE(p.cin % UM_CK == 0 && p.cin > 0, "conv_umma: cin must be a multiple of 64");
@@ -1831,71 +1772,59 @@ static int um_build_job(const St2ConvParams& p, int dev, const UmEnv& env, UmJob
   ST2_REQUIRE(!(p.stats && p.accumulate), "conv_umma: stats with accumulate");
   ST2_REQUIRE(p.act != ST2_ACT_SNAKE || p.alpha, "conv_umma: snake needs alpha");
   ST2_REQUIRE(p.act != ST2_ACT_LRELU || (p.slope >= 0.f && p.slope <= 1.f), "conv_umma: LeakyReLU slope in [0, 1]");
-  memset(&jb, 0, sizeof(jb));
-  jb.p = p;
-  UmLayout& lay = jb.lay;
+  int dev = 0;
+  ST2_CUDA_OK(cudaGetDevice(&dev));
+  UmLayout lay;
+  memset(&lay, 0, sizeof(lay));
+  const UmEnv env = um_env();
   int rc = um_layout(p, dev, env, lay);
   if (rc) return rc;
-  rc = um_ymap(p, &jb.ymap);
+  CUtensorMap ymap;
+  rc = um_ymap(p, &ymap);
   if (rc) return rc;
   // residual / y_old rows by TMA when the source is a plain [B][Lout][>= n_cols] bf16 view (not the x2-repeated
   // shortcut of the upsampling block); ST2_UMMA_RES_TMA=0 keeps the cp.async path (A/B switch)
-  jb.rmap = jb.ymap;
+  const bool tma_ok = env.res_tma;
+  CUtensorMap rmap = ymap;
   lay.res_tma = lay.acc_tma = 0;
-  if (env.res_tma && p.y_dtype == ST2_DT_BF16) {
+  if (tma_ok && p.y_dtype == ST2_DT_BF16) {
     if (lay.n_acc) lay.acc_tma = 1;
     if (lay.n_res && p.res_shift == 0 && (((uintptr_t)p.res) & 15) == 0 && (p.ldres % 8) == 0 &&
         (p.res_bstride % 8) == 0) {
-      rc = um_rmap(p, &jb.rmap);
+      rc = um_rmap(p, &rmap);
       if (rc) return rc;
       lay.res_tma = 1;
     }
   }
-  jb.xmap = jb.ymap;
-  jb.xmap8 = jb.ymap;
+  const bool x_tma_ok = env.x_tma;
+  CUtensorMap xmap = ymap, xmap8 = ymap;
   lay.x_tma = 0;
-  if (env.x_tma && (((uintptr_t)p.x) & 15) == 0 && (p.ldx % 8) == 0 && (p.x_bstride % 8) == 0) {
-    rc = um_xmap(p, UM_TM, &jb.xmap);
+  if (x_tma_ok && (((uintptr_t)p.x) & 15) == 0 && (p.ldx % 8) == 0 && (p.x_bstride % 8) == 0) {
+    rc = um_xmap(p, UM_TM, &xmap);
     if (rc) return rc;
-    rc = um_xmap(p, 8, &jb.xmap8);
+    rc = um_xmap(p, 8, &xmap8);
     if (rc) return rc;
     lay.x_tma = 1;
   }
-  lay.loader = env.loader && lay.x_tma && (!lay.n_res || lay.res_tma) && (!lay.n_acc || lay.acc_tma);
+  const bool loader_ok = env.loader;
+  lay.loader = loader_ok && lay.x_tma && (!lay.n_res || lay.res_tma) && (!lay.n_acc || lay.acc_tma);
   const int n_ttiles = ceil_div(p.Lout, UM_TM), n_ntiles = p.n_cols / lay.n_tile;
   ST2_REQUIRE(!p.stats || p.n_tiles >= n_ttiles, "conv_umma: n_tiles");
   um_fastdiv((uint32_t)n_ntiles, lay.nt_m, lay.nt_l);
   um_fastdiv((uint32_t)n_ttiles, lay.tt_m, lay.tt_l);
   const int64_t total = (int64_t)p.B * n_ttiles * n_ntiles;
   ST2_REQUIRE(total < (1ll << 31), "conv_umma: too many tiles");
-  *n_ttiles_o = n_ttiles; *n_ntiles_o = n_ntiles; *total_o = total;
-  return ST2_OK;
-}
-
-// can jobs a and b alternate in one kernel?  Same tile grid and channel counts, same prologue kind (the producers are
-// compiled per activation), every chunk by TMA through the loader lane, no CTA-pair mode.
-static bool um_jobs_compatible(const UmJob& a, const UmJob& b) {
-  const St2ConvParams &p = a.p, &q = b.p;
-  return p.B == q.B && p.Lin == q.Lin && p.Lout == q.Lout && p.cin == q.cin && p.n_cols == q.n_cols &&
-         p.y_dtype == q.y_dtype && p.act == q.act && (p.ss != nullptr) == (q.ss != nullptr) && p.slope == q.slope &&
-         a.lay.n_tile == b.lay.n_tile && a.lay.out_row == b.lay.out_row && a.lay.loader && b.lay.loader &&
-         !a.lay.pair && !b.lay.pair && a.lay.dbg == b.lay.dbg;
-}
-
-static int um_launch_jobs(UmJobs& J, int n_ttiles, int n_ntiles, int64_t total, int dev, cudaStream_t st) {
-  UmLayout& lay = J.j[0].lay;
   int sms = 148;
-  int rc = um_device_setup(dev, &sms);
+  rc = um_device_setup(dev, &sms);
   if (rc) return rc;
   int grid = (int)(total < sms ? total : sms);
-  J.wmap = J.j[0].ymap; J.wmap_res = J.j[0].ymap; J.wmap_acc = J.j[0].ymap;
-  if (lay.pair) {  // decided in um_layout; single job only
-    const St2ConvParams& p = J.j[0].p;
-    rc = um_wmap(p.w, n_ntiles * (p.cin / UM_CK) * p.k, &J.wmap);
+  CUtensorMap wmap = ymap, wmap_res = ymap, wmap_acc = ymap;
+  if (lay.pair) {  // decided in um_layout
+    rc = um_wmap(p.w, n_ntiles * (p.cin / UM_CK) * p.k, &wmap);
     if (rc) return rc;
-    if (lay.n_res) rc = um_wmap(lay.ident_res, lay.n_res, &J.wmap_res);
+    if (lay.n_res) rc = um_wmap(lay.ident_res, lay.n_res, &wmap_res);
     if (rc) return rc;
-    if (lay.n_acc) rc = um_wmap(lay.ident_acc, lay.n_acc, &J.wmap_acc);
+    if (lay.n_acc) rc = um_wmap(lay.ident_acc, lay.n_acc, &wmap_acc);
     if (rc) return rc;
     lay.n_bt = p.B * n_ttiles;
     lay.total_ptiles = n_ntiles * ceil_div(lay.n_bt, 2);
@@ -1915,7 +1844,7 @@ static int um_launch_jobs(UmJobs& J, int n_ttiles, int n_ntiles, int64_t total, 
     e0 = g_prof.ev[g_prof.used];
     e1 = g_prof.ev[g_prof.used + 1];
     g_prof.used += 2;
-    for (int i = 0; i < J.n; ++i) g_prof.flops += J.j[i].p.algo_flops;
+    g_prof.flops += p.algo_flops;
     ST2_CUDA_OK(cudaEventRecord(e0, st));
   }
   if (lay.pair) {
@@ -1927,9 +1856,9 @@ static int um_launch_jobs(UmJobs& J, int n_ttiles, int n_ntiles, int64_t total, 
     attr[1].id = cudaLaunchAttributeClusterDimension;
     attr[1].val.clusterDim.x = 2; attr[1].val.clusterDim.y = 1; attr[1].val.clusterDim.z = 1;
     cfg.attrs = attr; cfg.numAttrs = 2;
-    ST2_CUDA_OK(cudaLaunchKernelEx(&cfg, conv_umma_kernel<true>, J, (int)total, n_ttiles, n_ntiles));
+    ST2_CUDA_OK(cudaLaunchKernelEx(&cfg, conv_umma_kernel<true>, p, lay, ymap, rmap, xmap, xmap8, wmap, wmap_res, wmap_acc, (int)total, n_ttiles, n_ntiles));
   } else {
-    ST2_CUDA_OK(launch_pdl(conv_umma_kernel<false>, dim3(grid), dim3(UM_THREADS), (size_t)lay.total, st, J, (int)total,
+    ST2_CUDA_OK(launch_pdl(conv_umma_kernel<false>, dim3(grid), dim3(UM_THREADS), (size_t)lay.total, st, p, lay, ymap, rmap, xmap, xmap8, wmap, wmap_res, wmap_acc, (int)total,
                            n_ttiles, n_ntiles));
   }
   ST2_LAUNCH_OK("conv_umma");
@@ -1937,73 +1866,24 @@ static int um_launch_jobs(UmJobs& J, int n_ttiles, int n_ntiles, int64_t total, 
   return ST2_OK;
 }
 
-int launch_conv_umma(const St2ConvParams& p, cudaStream_t st) {
-  int dev = 0;
-  ST2_CUDA_OK(cudaGetDevice(&dev));
-  const UmEnv env = um_env();
-  static thread_local UmJobs J;  // 3 KB: kept off the stack of the (deep) forward schedule
-  int n_ttiles = 0, n_ntiles = 0;
-  int64_t total = 0;
-  int rc = um_build_job(p, dev, env, J.j[0], &n_ttiles, &n_ntiles, &total);
-  if (rc) return rc;
-  J.n = 1;
-  return um_launch_jobs(J, n_ttiles, n_ntiles, total, dev, st);
-}
-
-// n (<= UM_MAX_JOBS) convs of the same geometry as ONE kernel whose CTAs alternate between them tile by tile (UmJobs).
-// Jobs that cannot share a kernel (different shapes, a fallback load path, pair mode) are launched one by one: the
-// results are the same either way, bit for bit (every tile is computed by the same code on the same operands).
-int launch_conv_umma_multi(const St2ConvParams* ps, int n, cudaStream_t st) {
-  ST2_REQUIRE(ps && n >= 1 && n <= UM_MAX_JOBS, "conv_umma_multi: 1..3 jobs");
-  if (n == 1) return launch_conv_umma(ps[0], st);
-  int dev = 0;
-  ST2_CUDA_OK(cudaGetDevice(&dev));
-  const UmEnv env = um_env();
-  static thread_local UmJobs J;
-  int n_ttiles = 0, n_ntiles = 0;
-  int64_t total = 0;
-  bool ok = !env.no_multi;
-  for (int i = 0; i < n; ++i) {
-    int tt = 0, nt = 0;
-    int64_t tot = 0;
-    int rc = um_build_job(ps[i], dev, env, J.j[i], &tt, &nt, &tot);
-    if (rc) return rc;
-    if (i == 0) { n_ttiles = tt; n_ntiles = nt; total = tot; }
-    else ok = ok && um_jobs_compatible(J.j[0], J.j[i]) && tt == n_ttiles && nt == n_ntiles;
-  }
-  if (!ok) {
-    for (int i = 0; i < n; ++i) {
-      int rc = launch_conv_umma(ps[i], st);
-      if (rc) return rc;
-    }
-    return ST2_OK;
-  }
-  // common shared-memory geometry: the job with the widest halo decides stage size and ring depths
-  int ref = 0;
-  for (int i = 1; i < n; ++i)
-    if (J.j[i].lay.a_bytes > J.j[ref].lay.a_bytes ||
-        (J.j[i].lay.a_bytes == J.j[ref].lay.a_bytes && J.j[i].p.k > J.j[ref].p.k)) ref = i;
-  const UmLayout g = J.j[ref].lay;
-  for (int i = 0; i < n; ++i) {
-    UmLayout& l = J.j[i].lay;
-    l.a_bytes = g.a_bytes; l.na = g.na; l.nw = g.nw; l.w_slot = g.w_slot; l.dist = g.dist;
-    l.off_a = g.off_a; l.off_w = g.off_w; l.off_misc = g.off_misc; l.total = g.total;
-  }
-  J.n = n;
-  return um_launch_jobs(J, n_ttiles, n_ntiles, total, dev, st);
-}
-
 }  // namespace st2
 
 extern "C" int st2_umma_reload_env(void) {
-  std::lock_guard<std::mutex> lk(st2::g_env_mu);
-  st2::um_env_read_locked();
+  {
+    std::lock_guard<std::mutex> lk(st2::g_env_mu);
+    st2::um_env_read_locked();
+  }
+  st2::umma_multi_reload_env();
   return ST2_OK;
 }
 extern "C" int st2_umma_wait_profile(uint64_t out[16], int reset) {
   unsigned long long h[16];
   ST2_CUDA_OK(cudaDeviceSynchronize());
   ST2_CUDA_OK(cudaMemcpyFromSymbol(h, st2::g_um_wait, sizeof(h)));
+  {
+    int rc = st2::umma_multi_wait_read(h, reset != 0);  // + the multi-conv kernel's counters
+    if (rc) return rc;
+  }
   if (out) for (int i = 0; i < 16; ++i) out[i] = h[i];
   if (reset) {
     memset(h, 0, sizeof(h));

@@ -1166,6 +1166,7 @@ struct Fwd {
   int conv_position(const ConvW* const* cs, const ConvIO* ios, int nk, float** parts, int* tiles, int* cols) {
     const int64_t tiles_per_conv = (int64_t)B * ceil_div(ios[0].Lout, 256) * ceil_div(cs[0]->n, 128);
     if (nk != 3 || tiles_per_conv < 2 * 148 || lockstep_mode != 2) return conv_multi(cs, ios, nk, parts, tiles, cols);
+    // (mode 2 is only reached with ST2_LOCKSTEP=2, which also forces lock step for every size)
     const ConvW* c2[2] = {cs[0], cs[2]};
     ConvIO io2[2] = {ios[0], ios[2]};
     float* p2[2]; int t2[2], n2[2];
@@ -1176,7 +1177,7 @@ struct Fwd {
     rc = conv_multi(cs + 1, ios + 1, 1, parts + 1, tiles + 1, cols + 1);
     return rc;
   }
-  int lockstep_mode = 0;  // ST2_LOCKSTEP: 0 off, 1 (default) all resblocks of a position in one launch, 2 see above
+  int lockstep_mode = 0;  // ST2_LOCKSTEP: 0 off, 1 (default) small problems only, 2 see above, 3 every size
 
   // The nk resblocks of a generator stage (istftnet.py:369-374: xs = sum_j resblocks[i*nk+j](x); x = xs / nk) run in
   // lock step: their convs at the same position of the chain have the same shape and no dependence on each other, so
@@ -1518,7 +1519,12 @@ int Fwd<AT>::run(const float* asr, const float* f0, const float* nn, const float
       }
       ar.release(m);
     }
-    if (lockstep && nk <= 3) {
+    // lock step only where it pays: a conv with fewer tiles than 2 x SMs (a single utterance) gains from one launch of
+    // three convs (3 x the SMs busy, two launches less per position: C1 1.68 -> 1.49 ms); large batches run one conv per
+    // launch on conv_umma.cu's kernel, whose MMA issue loop is 5 % faster (conv_umma_multi.cu header).  ST2_LOCKSTEP=3
+    // forces it for every size, 0 turns it off.
+    const int64_t tiles_per_conv = (int64_t)B * ceil_div(pr ? Ls / 2 : Ls, 256) * ceil_div(pr ? 2 * C : C, 128);
+    if (lockstep && nk <= 3 && (tiles_per_conv < 2 * 148 || lockstep_mode >= 2)) {
       // the nk resblocks in lock step: each needs its own run / tmp buffers (resblock 0 reuses the stage's)
       Act<AT> runs[3], tmps[3];
       runs[0] = vw(runb); tmps[0] = vw(tmp);
