@@ -36,7 +36,8 @@ __device__ __forceinline__ void pdl_wait_then_trigger() {
   asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
 }
 #endif
-bool pdl_enabled();  // decoder.cu: ST2_PDL=0 turns the attribute off (A/B switch)
+bool pdl_enabled();  // decoder.cu: ST2_PDL=0 turns the attribute off (A/B switch); consumes pdl_plain_next()
+void pdl_plain_next();
 template <typename... KArgs, typename... Args>
 static inline cudaError_t launch_pdl(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t st,
                                      Args... args) {

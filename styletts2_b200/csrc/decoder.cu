@@ -42,11 +42,19 @@ struct NvtxRange {
 static thread_local std::string g_err;
 static thread_local int64_t g_launches = 0;
 void set_error(const std::string& msg) { g_err = msg; }
+// pdl_plain_next(): the next launch of this thread goes out without the programmatic attribute (the first kernel after a
+// cross-stream event wait: its dependencies are the event's, plain ones)
+static thread_local bool g_pdl_plain_next = false;
+void pdl_plain_next() { g_pdl_plain_next = true; }
 bool pdl_enabled() {
   static const bool on = [] {
     const char* e = getenv("ST2_PDL");
     return !(e && e[0] == '0');
   }();
+  if (g_pdl_plain_next) {
+    g_pdl_plain_next = false;
+    return false;
+  }
   return on;
 }
 int64_t& launch_counter() { return g_launches; }
@@ -143,6 +151,9 @@ struct St2Decoder {
   int64_t s_four = -1, s_timeW = -1, s_timeB = -1, s_featW = -1, s_featB = -1;
   int64_t s_mapW[2] = {-1, -1}, s_mapB[2] = {-1, -1}, s_outW = -1, s_outB = -1, s_fixed = -1;
   int64_t last_launches = 0;
+  // excitation branch of a small forward (Fwd::run): second stream + fork / join events, created by st2_decoder_load
+  cudaStream_t side_st = nullptr;
+  cudaEvent_t ev_fork = nullptr, ev_join[ST2_MAX_UPS] = {};
 };
 
 namespace st2 {
@@ -852,6 +863,14 @@ struct Fwd {
   int B, T;
   bool dry;
   bool tc32 = false;            // ST2_PREC_FP32_TC: fp32 activations, dense convs as 3 x bf16 on tcgen05
+  // small forwards run the excitation branch (source -> STFT -> noise_convs -> noise_res, istftnet.py:350-356 and
+  // :366-368) on the handle's second stream, beside encode / decode; it allocates from its own arena (`side`, the
+  // first side_bytes of the workspace) so that the two branches never alias.  to_side() / to_main() swap (ar, st).
+  Arena side;
+  cudaStream_t st_side = nullptr;
+  bool on_side = false;
+  void to_side() { if (!on_side) { std::swap(ar, side); std::swap(st, st_side); on_side = true; } }
+  void to_main() { if (on_side) { std::swap(ar, side); std::swap(st, st_side); on_side = false; } }
   const float* hall = nullptr;  // [B][fc_rows]
   float* ss = nullptr;          // [B][ss_pairs][2]
 
@@ -1323,6 +1342,145 @@ int Fwd<AT>::run(const float* asr, const float* f0, const float* nn, const float
   RUN(launch_style_fc(s, W<float>(h->fcW), W<float>(h->fcB), hall_w, B, c.style_dim, h->fc_rows, st));
   RUN(cudaMemsetAsync(ss, 0, (size_t)B * h->ss_pairs * 8, st) == cudaSuccess ? ST2_OK : ST2_ECUDA);
 
+  // ---- stage geometry of the generator (istftnet.py:358-374 / hifigan.py:327-341)
+  const int nk = c.n_resblock_kernels;
+  struct StageGeo { int Lin, Ls, C, pad_rows, reps; bool pr; };
+  StageGeo geo[ST2_MAX_UPS];
+  for (int i = 0, Lin = T; i < c.n_ups; ++i) {
+    StageGeo& g = geo[i];
+    const UpW& up = h->ups[i];
+    g.Lin = Lin; g.C = up.cout;
+    g.pad_rows = (istft && i == c.n_ups - 1) ? 1 : 0;  // ReflectionPad1d((1,0)), istftnet.py:364-365
+    g.Ls = Lin * up.rate + g.pad_rows;
+    // a 32-channel stage runs on row pairs ([Ls/2][64] views of the same memory) so that its convs
+    // fit the tcgen05 kernel's 64-channel chunks (Loader::pair_conv)
+    g.pr = DT<AT>::id == ST2_DT_BF16 && g.C == 32 && g.pad_rows == 0 && g.Ls % 2 == 0 && up.rate % 2 == 0 &&
+           h->noise_res[i].paired;
+    for (int j = 0; j < nk; ++j) g.pr = g.pr && h->resblocks[i * nk + j].paired;
+    g.reps = g.pr ? 2 : 1;
+    Lin = g.Ls;
+  }
+  // fork the excitation branch when the last stage has fewer 256-row tiles than 2 x SMs (a single utterance: the step
+  // is a chain of ~100 short dependent launches, a third of them in this branch); ST2_FORK=0 never, 2 always
+  static const int fork_env = [] { const char* e = getenv("ST2_FORK"); return e ? atoi(e) : 1; }();
+  const bool forked = h->side_st && fork_env != 0 &&
+                      ((int64_t)B * ceil_div(geo[c.n_ups - 1].Ls, 256) < 2 * 148 || fork_env >= 2);
+  st_side = h->side_st;
+
+  const int n_fft = c.gen_istft_n_fft, hop = c.gen_istft_hop_size;
+  const int L2 = istft ? (int)(Lw / hop) + 1 : 0;
+  const int ldh = 32;
+  const float* hs = o.har_source;
+  bool hilo = istft && DT<AT>::id == ST2_DT_BF16;
+  int rows_pad = L2;
+  float* har = nullptr;
+  __nv_bfloat16* har16 = nullptr;
+  const bool meanfree = !istft && DT<AT>::id == ST2_DT_BF16;
+  float* hs_mean = nullptr;
+  Act<AT> xs_of[ST2_MAX_UPS];
+  float* bias_c2_of[ST2_MAX_UPS] = {};
+
+  // ---- excitation (istftnet.py:350-356 / hifigan.py:320-323)
+  auto excitation = [&]() -> int {
+  // bf16 path: `har` is kept as bf16 (hi, lo) rows and the noise convs run on the tensor cores
+  if (hilo) {
+    int len = T;
+    for (int i = 0; i < c.n_ups; ++i) {
+      len = len * c.upsample_rates[i] + (i == c.n_ups - 1 ? 1 : 0);
+      hilo = hilo && h->noise_convs16[i].w16 >= 0;
+      const int need = h->noise_group[i] > 1 ? h->noise_group[i] * (len + 1) : len;
+      if (need > rows_pad) rows_pad = need;
+    }
+  }
+  if (istft && hilo) har16 = ar.alloc<__nv_bfloat16>((int64_t)B * rows_pad * 64);
+  else if (istft) har = ar.alloc<float>((int64_t)B * L2 * ldh);
+  if (istft && o.har) {
+    if (hilo) RUN(launch_ncl_to_hilo(o.har, n_fft + 2, L2, rows_pad, har16, B, st));
+    else RUN(launch_ncl_to_cl(o.har, n_fft + 2, L2, har, ldh, B, st));
+  } else {
+    if (!hs) {
+      float* ph = ar.alloc<float>((int64_t)B * 9 * T);
+      float* hsw = ar.alloc<float>((int64_t)B * Lw);
+      RUN(launch_phase_scan(f0, B, T, spf, ph, st));
+      RUN(launch_har_source(f0, ph, o.noise, o.seed, W<float>(h->lin_w), h->lin_b, B, T, spf, hsw, st, o.item_offset, o.seed_dev));
+      hs = hsw;
+    }
+    if (istft && hilo) RUN(launch_stft_hilo(hs, B, (int)Lw, rows_pad, har16, st));
+    else if (istft) RUN(launch_stft(hs, B, (int)Lw, har, ldh, st));
+  }
+  if (o.har_source_out && hs)
+    RUN(cudaMemcpyAsync(o.har_source_out, hs, (size_t)B * Lw * 4, cudaMemcpyDeviceToDevice, st) == cudaSuccess ? ST2_OK : ST2_ECUDA);
+  if (o.har_out && istft) {
+    if (hilo) RUN(launch_hilo_to_ncl(har16, rows_pad, n_fft + 2, L2, o.har_out, B, st));
+    else RUN(launch_cl_to_ncl(har, ldh, n_fft + 2, L2, o.har_out, B, st));
+  }
+  // hifigan, bf16 path: x_source is stored without its per-(b,c) constant (elementwise.cu, noise_bias)
+  if (meanfree) {
+    hs_mean = ar.alloc<float>(B);
+    RUN(launch_row_mean(hs, Lw, hs_mean, B, st));
+  }
+  return ST2_OK;
+  };
+
+  // ---- x_source of stage i = noise_res[i](noise_convs[i](har | har_source)) into xs, tmp = scratch of the resblock
+  auto x_source = [&](int i, const Act<AT>& xs, const Act<AT>& tmp) -> int {
+    const StageGeo& g = geo[i];
+    const int C = g.C, Ls = g.Ls, reps = g.reps;
+    const bool pr = g.pr;
+    auto vw = [pr](const Act<AT>& a) {
+      Act<AT> v = a;
+      if (pr) { v.L = a.L / 2; v.ld = a.ld * 2; }
+      return v;
+    };
+    const ConvW& nc = hilo ? h->noise_convs16[i] : h->noise_convs[i];
+    ConvIO io;
+    if (hilo) {  // sf har rows = one wide row of sf * 64 channels
+      const int sf = h->noise_group[i];
+      io.x = har16; io.x_dtype = ST2_DT_BF16; io.x_bstride = (int64_t)rows_pad * 64; io.ldx = sf * 64;
+      io.Lin = sf > 1 ? Ls + 1 : L2;
+    } else if (istft) {
+      io.x = har; io.x_dtype = ST2_DT_F32; io.x_bstride = (int64_t)L2 * ldh; io.ldx = ldh; io.Lin = L2;
+    } else {
+      io.x = hs; io.x_dtype = ST2_DT_F32; io.x_bstride = Lw; io.ldx = 1; io.Lin = (int)Lw;
+    }
+    io.y = xs.p; io.y_dtype = DT<AT>::id; io.y_bstride = xs.bstride; io.ldy = xs.ld; io.Lout = Ls;
+    io.want_stats = true;
+    float* bias_c2 = nullptr;
+    if (meanfree) {
+      float* bias_nc = ar.alloc<float>((int64_t)B * C);
+      bias_c2 = ar.alloc<float>((int64_t)B * C * reps);
+      RUN(launch_noise_bias(hs_mean, W<float>(h->noise_wsum[i]), W<float>(nc.bias),
+                            W<float>(h->noise_res[i].c2[0].bias), bias_nc, bias_c2, C, B, st, reps));
+      io.bias_b = bias_nc;
+    }
+    const int64_t m = ar.mark();
+    int rc = conv(nc, io);
+    if (rc) return rc;
+    rc = finalize(last_partials, last_tiles, last_cols, C, Ls, h->noise_res[i].n1[0], 0, reps);
+    if (rc) return rc;
+    ar.release(m);
+    return resblock1(h->noise_res[i], vw(xs), vw(xs), vw(tmp), vw(xs), 1.f, 0, bias_c2, pr);
+  };
+
+  if (forked) {
+    // fork: everything below up to to_main() is issued on the second stream, from the side arena
+    RUN(cudaEventRecord(h->ev_fork, st) == cudaSuccess ? ST2_OK : ST2_ECUDA);
+    to_side();
+    RUN(cudaStreamWaitEvent(st, h->ev_fork, 0) == cudaSuccess ? ST2_OK : ST2_ECUDA);
+    if (!dry) pdl_plain_next();
+    int rc = excitation();
+    for (int i = 0; i < c.n_ups && !rc; ++i) {
+      xs_of[i] = new_act(geo[i].Ls, geo[i].C);
+      const int64_t m = ar.mark();
+      Act<AT> tmp = new_act(geo[i].Ls, geo[i].C);
+      rc = x_source(i, xs_of[i], tmp);
+      ar.release(m);
+      if (!rc) RUN(cudaEventRecord(h->ev_join[i], st) == cudaSuccess ? ST2_OK : ST2_ECUDA);
+    }
+    to_main();
+    if (rc) return rc;
+  }
+
   nvtx.next("st2.decoder.encode_decode");
   // ---- encode / decode (istftnet.py:510-524)
   const int din0 = c.dim_in + 2, ld0 = (int)round_up(din0, 64);
@@ -1377,114 +1535,36 @@ int Fwd<AT>::run(const float* asr, const float* f0, const float* nn, const float
 
   if (o.tap_decode) RUN(launch_act_to_ncl<AT>(xg.p, xg.bstride, xg.ld, 512, T, o.tap_decode, B, st));
 
-  nvtx.next("st2.generator.excitation");
-  // ---- excitation (istftnet.py:350-356 / hifigan.py:320-323)
-  const int n_fft = c.gen_istft_n_fft, hop = c.gen_istft_hop_size;
-  const int L2 = istft ? (int)(Lw / hop) + 1 : 0;
-  const int ldh = 32;
-  const float* hs = o.har_source;
-  // bf16 path: `har` is kept as bf16 (hi, lo) rows and the noise convs run on the tensor cores
-  bool hilo = istft && DT<AT>::id == ST2_DT_BF16;
-  int rows_pad = L2;
-  if (hilo) {
-    int len = T;
-    for (int i = 0; i < c.n_ups; ++i) {
-      len = len * c.upsample_rates[i] + (i == c.n_ups - 1 ? 1 : 0);
-      hilo = hilo && h->noise_convs16[i].w16 >= 0;
-      const int need = h->noise_group[i] > 1 ? h->noise_group[i] * (len + 1) : len;
-      if (need > rows_pad) rows_pad = need;
-    }
-  }
-  float* har = nullptr;
-  __nv_bfloat16* har16 = nullptr;
-  if (istft && hilo) har16 = ar.alloc<__nv_bfloat16>((int64_t)B * rows_pad * 64);
-  else if (istft) har = ar.alloc<float>((int64_t)B * L2 * ldh);
-  if (istft && o.har) {
-    if (hilo) RUN(launch_ncl_to_hilo(o.har, n_fft + 2, L2, rows_pad, har16, B, st));
-    else RUN(launch_ncl_to_cl(o.har, n_fft + 2, L2, har, ldh, B, st));
-  } else {
-    if (!hs) {
-      float* ph = ar.alloc<float>((int64_t)B * 9 * T);
-      float* hsw = ar.alloc<float>((int64_t)B * Lw);
-      RUN(launch_phase_scan(f0, B, T, spf, ph, st));
-      RUN(launch_har_source(f0, ph, o.noise, o.seed, W<float>(h->lin_w), h->lin_b, B, T, spf, hsw, st, o.item_offset, o.seed_dev));
-      hs = hsw;
-    }
-    if (istft && hilo) RUN(launch_stft_hilo(hs, B, (int)Lw, rows_pad, har16, st));
-    else if (istft) RUN(launch_stft(hs, B, (int)Lw, har, ldh, st));
-  }
-  if (o.har_source_out && hs)
-    RUN(cudaMemcpyAsync(o.har_source_out, hs, (size_t)B * Lw * 4, cudaMemcpyDeviceToDevice, st) == cudaSuccess ? ST2_OK : ST2_ECUDA);
-  if (o.har_out && istft) {
-    if (hilo) RUN(launch_hilo_to_ncl(har16, rows_pad, n_fft + 2, L2, o.har_out, B, st));
-    else RUN(launch_cl_to_ncl(har, ldh, n_fft + 2, L2, o.har_out, B, st));
-  }
-
-  // hifigan, bf16 path: x_source is stored without its per-(b,c) constant (elementwise.cu, noise_bias)
-  const bool meanfree = !istft && DT<AT>::id == ST2_DT_BF16;
-  float* hs_mean = nullptr;
-  if (meanfree) {
-    hs_mean = ar.alloc<float>(B);
-    RUN(launch_row_mean(hs, Lw, hs_mean, B, st));
+  if (!forked) {
+    nvtx.next("st2.generator.excitation");
+    int rc = excitation();
+    if (rc) return rc;
   }
 
   nvtx.next("st2.generator.stages");
   // ---- generator stages (istftnet.py:358-374 / hifigan.py:327-341)
   Act<AT> x = xg;
-  const int nk = c.n_resblock_kernels;
   // bf16 path: the resblocks of a stage run in lock step, one fused launch per position (ST2_LOCKSTEP=0: one by one)
   static const int lockstep_env = [] { const char* e = getenv("ST2_LOCKSTEP"); return e ? atoi(e) : 1; }();
   const bool lockstep = lockstep_env != 0 && DT<AT>::id == ST2_DT_BF16;
   lockstep_mode = lockstep_env;
   for (int i = 0; i < c.n_ups; ++i) {
     const UpW& up = h->ups[i];
-    const bool lastst = i == c.n_ups - 1;
-    const int Lin = x.L, C = up.cout;
-    const int pad_rows = (istft && lastst) ? 1 : 0;  // ReflectionPad1d((1,0)), istftnet.py:364-365
-    const int Ls = Lin * up.rate + pad_rows;
-    Act<AT> xs = new_act(Ls, C), xm = new_act(Ls, C), tmp = new_act(Ls, C), runb = new_act(Ls, C),
-            outb = new_act(Ls, C);
-    // a 32-channel stage runs on row pairs ([Ls/2][64] views of the same memory) so that its convs
-    // fit the tcgen05 kernel's 64-channel chunks (Loader::pair_conv)
-    bool pr = DT<AT>::id == ST2_DT_BF16 && C == 32 && pad_rows == 0 && Ls % 2 == 0 && up.rate % 2 == 0 &&
-              h->noise_res[i].paired;
-    for (int j = 0; j < nk; ++j) pr = pr && h->resblocks[i * nk + j].paired;
-    const int reps = pr ? 2 : 1;
+    const StageGeo& g = geo[i];
+    const int Lin = g.Lin, C = g.C, pad_rows = g.pad_rows, Ls = g.Ls, reps = g.reps;
+    const bool pr = g.pr;
+    Act<AT> xs = forked ? xs_of[i] : new_act(Ls, C);
+    Act<AT> xm = new_act(Ls, C), tmp = new_act(Ls, C), runb = new_act(Ls, C), outb = new_act(Ls, C);
     auto vw = [pr](const Act<AT>& a) {
       Act<AT> v = a;
       if (pr) { v.L = a.L / 2; v.ld = a.ld * 2; }
       return v;
     };
-    // x_source = noise_res[i](noise_convs[i](har | har_source))
-    {
-      const ConvW& nc = hilo ? h->noise_convs16[i] : h->noise_convs[i];
-      ConvIO io;
-      if (hilo) {  // sf har rows = one wide row of sf * 64 channels
-        const int sf = h->noise_group[i];
-        io.x = har16; io.x_dtype = ST2_DT_BF16; io.x_bstride = (int64_t)rows_pad * 64; io.ldx = sf * 64;
-        io.Lin = sf > 1 ? Ls + 1 : L2;
-      } else if (istft) {
-        io.x = har; io.x_dtype = ST2_DT_F32; io.x_bstride = (int64_t)L2 * ldh; io.ldx = ldh; io.Lin = L2;
-      } else {
-        io.x = hs; io.x_dtype = ST2_DT_F32; io.x_bstride = Lw; io.ldx = 1; io.Lin = (int)Lw;
-      }
-      io.y = xs.p; io.y_dtype = DT<AT>::id; io.y_bstride = xs.bstride; io.ldy = xs.ld; io.Lout = Ls;
-      io.want_stats = true;
-      float* bias_c2 = nullptr;
-      if (meanfree) {
-        float* bias_nc = ar.alloc<float>((int64_t)B * C);
-        bias_c2 = ar.alloc<float>((int64_t)B * C * reps);
-        RUN(launch_noise_bias(hs_mean, W<float>(h->noise_wsum[i]), W<float>(nc.bias),
-                              W<float>(h->noise_res[i].c2[0].bias), bias_nc, bias_c2, C, B, st, reps));
-        io.bias_b = bias_nc;
-      }
-      const int64_t m = ar.mark();
-      int rc = conv(nc, io);
-      if (rc) return rc;
-      rc = finalize(last_partials, last_tiles, last_cols, C, Ls, h->noise_res[i].n1[0], 0, reps);
-      if (rc) return rc;
-      ar.release(m);
-      rc = resblock1(h->noise_res[i], vw(xs), vw(xs), vw(tmp), vw(xs), 1.f, 0, bias_c2, pr);
+    if (forked) {  // join: x_source of this stage comes from the second stream
+      RUN(cudaStreamWaitEvent(st, h->ev_join[i], 0) == cudaSuccess ? ST2_OK : ST2_ECUDA);
+      if (!dry) pdl_plain_next();
+    } else {
+      int rc = x_source(i, xs, tmp);
       if (rc) return rc;
     }
     // x = ups[i](act(x)) (+ reflection pad) + x_source, with statistics for the three resblocks
@@ -1700,6 +1780,16 @@ extern "C" int st2_decoder_load(St2Decoder* h, const St2Tensor* tensors, int n) 
     const bool dec = h->cfg.kind == ST2_KIND_ISTFTNET || h->cfg.kind == ST2_KIND_HIFIGAN;
     int rc = umma_prepare(dec ? h->cfg.n_resblock_kernels : 0);
     if (!rc) rc = source_prepare();
+    if (!rc && dec && !h->side_st) {
+      bool ok = cudaStreamCreateWithFlags(&h->side_st, cudaStreamNonBlocking) == cudaSuccess &&
+                cudaEventCreateWithFlags(&h->ev_fork, cudaEventDisableTiming) == cudaSuccess;
+      for (int i = 0; i < ST2_MAX_UPS && ok; ++i)
+        ok = cudaEventCreateWithFlags(&h->ev_join[i], cudaEventDisableTiming) == cudaSuccess;
+      if (!ok) {
+        set_error(std::string("st2_decoder_load: side stream / events: ") + cudaGetErrorString(cudaGetLastError()));
+        rc = ST2_ECUDA;
+      }
+    }
     if (cur != h->device) ST2_CUDA_OK(cudaSetDevice(cur));
     if (rc) return rc;
   }
@@ -1709,24 +1799,29 @@ extern "C" int st2_decoder_load(St2Decoder* h, const St2Tensor* tensors, int n) 
 template <typename AT>
 static int forward_t(St2Decoder* h, const float* asr, const float* f0, const float* n, const float* s,
                      float* wav, void* ws, int64_t ws_bytes, int B, int T, const St2ForwardOpts& o,
-                     cudaStream_t st, bool dry, int64_t* peak) {
+                     cudaStream_t st, bool dry, int64_t* peak, int64_t* side_bytes) {
+  // workspace = [side arena (*side_bytes, from the dry run) | main arena]
   Fwd<AT> f;
   f.h = h; f.st = st; f.B = B; f.T = T; f.dry = dry;
   f.tc32 = o.precision == ST2_PREC_FP32_TC;
-  f.ar.base = reinterpret_cast<uint8_t*>(ws); f.ar.cap = ws_bytes; f.ar.dry = dry;
+  const int64_t sb = dry ? 0 : *side_bytes;
+  f.side.base = reinterpret_cast<uint8_t*>(ws); f.side.cap = sb; f.side.dry = dry;
+  f.ar.base = reinterpret_cast<uint8_t*>(ws) + sb; f.ar.cap = ws_bytes - sb; f.ar.dry = dry;
   int rc = f.run(asr, f0, n, s, wav, o);
   if (peak) *peak = f.ar.peak;
+  if (dry) *side_bytes = round_up(f.side.peak, 256);
   return rc;
 }
 
-static int plan_bytes(St2Decoder* h, int B, int T, const St2ForwardOpts& o, int64_t* bytes) {
-  int64_t peak = 0;
+static int plan_bytes(St2Decoder* h, int B, int T, const St2ForwardOpts& o, int64_t* bytes, int64_t* side_bytes = nullptr) {
+  int64_t peak = 0, side = 0;
   int rc;
   if (o.precision == ST2_PREC_BF16)
-    rc = forward_t<__nv_bfloat16>(h, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, 0, B, T, o, 0, true, &peak);
+    rc = forward_t<__nv_bfloat16>(h, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, 0, B, T, o, 0, true, &peak, &side);
   else
-    rc = forward_t<float>(h, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, 0, B, T, o, 0, true, &peak);
-  *bytes = round_up(peak, 256) + 256;
+    rc = forward_t<float>(h, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, 0, B, T, o, 0, true, &peak, &side);
+  *bytes = side + round_up(peak, 256) + 256;
+  if (side_bytes) *side_bytes = side;
   return rc;
 }
 
@@ -1775,8 +1870,8 @@ extern "C" int st2_decoder_forward(St2Decoder* h, const float* asr, const float*
   int dev = -1;
   ST2_CUDA_OK(cudaGetDevice(&dev));
   ST2_REQUIRE(dev == h->device, "handle belongs to another device");
-  int64_t need = 0;
-  int rc = plan_bytes(h, B, T, o, &need);
+  int64_t need = 0, side_bytes = 0;
+  int rc = plan_bytes(h, B, T, o, &need, &side_bytes);
   if (rc) return rc;
   if (need > workspace_bytes) {
     set_error("st2_decoder_forward: workspace too small (" + std::to_string(workspace_bytes) + " < " +
@@ -1786,9 +1881,10 @@ extern "C" int st2_decoder_forward(St2Decoder* h, const float* asr, const float*
   const int64_t before = launch_counter();
   cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
   if (o.precision == ST2_PREC_BF16)
-    rc = forward_t<__nv_bfloat16>(h, asr, f0, n, s, wav_out, workspace, workspace_bytes, B, T, o, st, false, nullptr);
+    rc = forward_t<__nv_bfloat16>(h, asr, f0, n, s, wav_out, workspace, workspace_bytes, B, T, o, st, false, nullptr,
+                                  &side_bytes);
   else
-    rc = forward_t<float>(h, asr, f0, n, s, wav_out, workspace, workspace_bytes, B, T, o, st, false, nullptr);
+    rc = forward_t<float>(h, asr, f0, n, s, wav_out, workspace, workspace_bytes, B, T, o, st, false, nullptr, &side_bytes);
   h->last_launches = launch_counter() - before;
   return rc;
 }
@@ -2107,6 +2203,10 @@ extern "C" void st2_decoder_destroy(St2Decoder* h) {
   if (h->dev) {
     cudaFree(h->dev);
   }
+  if (h->side_st) cudaStreamDestroy(h->side_st);
+  if (h->ev_fork) cudaEventDestroy(h->ev_fork);
+  for (cudaEvent_t e : h->ev_join)
+    if (e) cudaEventDestroy(e);
   delete h;
 }
 
