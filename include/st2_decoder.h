@@ -19,7 +19,9 @@
  * handles (one per device / per thread, e.g. the one-thread-per-device calling convention
  * of train_finetune.py:96-101) run concurrently.  All one-time per-device setup (identity
  * blobs, constant tables, kernel attributes) happens in st2_decoder_load: forward allocates
- * nothing and never synchronises the host, so it can be stream-captured.  sm_100a only; there is no
+ * nothing and never synchronises the host, so it can be stream-captured.  A decoder handle owns a
+ * second stream + events (made by load): a single-utterance forward forks its excitation branch
+ * onto it and joins it back, so the caller's stream still orders the whole call.  sm_100a only; there is no
  * CPU fallback: without a usable GPU every compute entry point fails with ST2_ECUDA.
  */
 #ifndef ST2_DECODER_H
