@@ -471,14 +471,24 @@ __device__ __forceinline__ UmTile um_tile_(int tile, int n_ttiles, int n_ntiles,
 // the it-th tile of this CTA (total_tiles = none left).  Pair mode: the cluster takes pair-tile q = (nt, btp) and its
 // CTA of rank r the (item, time) tile 2 btp + r, clamped to the last one (an odd count makes both CTAs compute the
 // same tile: identical bytes stored twice).
-#define um_tile_at(it, total_tiles, n_ntiles) um_tile_at_<PAIR>(um_slot_of(J.n, it), total_tiles, n_ntiles, lay)
+// Work items: the (conv, tile) pairs of a launch are numbered g = tile * n + conv and CTA b takes g = b, b + grid,
+// b + 2 grid, ... -- with a grid of min(n * tiles, SMs) a small launch (a single utterance: 32 tiles x 3 convs) spreads
+// over n times the SMs, a large one still alternates between the convs (grid % n != 0 rotates them).
+__device__ __forceinline__ int64_t um_gid(int wi) { return (int64_t)blockIdx.x + (int64_t)wi * gridDim.x; }
+__device__ __forceinline__ int64_t um_slot_of(int n, int64_t g) { return n == 1 ? g : (n == 2 ? g >> 1 : g / 3); }
+__device__ __forceinline__ int um_job_of(int n, int wi) {
+  if (n == 1) return 0;
+  const int64_t g = um_gid(wi);
+  return (int)(g - um_slot_of(n, g) * n);
+}
+#define um_tile_at(it, total_tiles, n_ntiles) um_tile_at_<PAIR>(J.n, it, total_tiles, n_ntiles, lay)
 template <bool PAIR>
-__device__ __forceinline__ int um_tile_at_(int it, int total_tiles, int n_ntiles, const UmLayout& lay) {
+__device__ __forceinline__ int um_tile_at_(int n, int it, int total_tiles, int n_ntiles, const UmLayout& lay) {
   if (!PAIR) {
-    const int64_t t = (int64_t)blockIdx.x + (int64_t)it * gridDim.x;
+    const int64_t t = um_slot_of(n, um_gid(it));
     return t < total_tiles ? (int)t : total_tiles;
   }
-  const int64_t q = (int64_t)(blockIdx.x >> 1) + (int64_t)it * (gridDim.x >> 1);
+  const int64_t q = (int64_t)(blockIdx.x >> 1) + (int64_t)it * (gridDim.x >> 1);  // single conv only
   if (q >= lay.total_ptiles) return total_tiles;
   const uint32_t btp = um_div((uint32_t)q, lay.nt_m, lay.nt_l);
   const int nt = (int)q - (int)btp * n_ntiles;
@@ -487,12 +497,6 @@ __device__ __forceinline__ int um_tile_at_(int it, int total_tiles, int n_ntiles
   return bt * n_ntiles + nt;
 }
 
-// work item wi of this CTA -> (job, tile slot): the jobs take turns
-__device__ __forceinline__ int um_slot_of(int n, int wi) { return n == 1 ? wi : (n == 2 ? wi >> 1 : wi / 3); }
-__device__ __forceinline__ int um_job_of(int n, int wi) { return wi - um_slot_of(n, wi) * n; }
-
-// one producer cursor: which (job, tile, chunk) an operation is at, the tile's coordinates, and the A
-// stage / phase the chunk maps to
 struct UmCur {
   int tile, c, stage;
   uint32_t ph;
@@ -537,7 +541,7 @@ __device__ __forceinline__ void um_advance_(UmCur& q, int nchunks, int na, int t
     q.c = 0;
     ++q.it;
     q.job = um_job_of(njobs, q.it);
-    q.tile = um_tile_at_<PAIR>(um_slot_of(njobs, q.it), total_tiles, n_ntiles, lay);
+    q.tile = um_tile_at_<PAIR>(njobs, q.it, total_tiles, n_ntiles, lay);
     um_cur_tile(q, total_tiles, n_ttiles, n_ntiles);
   }
   if (++q.stage == na) {
@@ -821,7 +825,7 @@ __device__ __forceinline__ void um_produce(const UmJobs& J, uint8_t* smem,
   // a_empty barrier of the next slot and starts that chunk's loads as soon as the MMAs have released
   // it, up to na-1 chunks ahead.  (Residual / y_old chunks cost no arithmetic, so a fixed distance
   // counted in chunks would leave the following activation chunk no time to arrive.)
-  UmCur lc{um_tile_at(0, total_tiles, n_ntiles), 0, 0, 0u, 0, 0, 0, 0, 0};
+  UmCur lc{um_tile_at(0, total_tiles, n_ntiles), 0, 0, 0u, 0, 0, 0, 0, um_job_of(J.n, 0)};
   um_cur_tile(lc, total_tiles, n_ttiles, n_ntiles);
   UmCur tc = lc;
   int n_l = 0, n_t = 0;  // chunks whose loads are issued / that are transformed
@@ -1390,7 +1394,7 @@ __global__ void __launch_bounds__(UM_THREADS, 1) conv_umma_kernel(const __grid_c
     //     they have seen raw_full, so the phase cannot complete before its bytes are expected
     if (lay.loader && elect_one()) {
       const bool ident = p.act == ST2_ACT_NONE && p.ss == nullptr;  // the same for every job (host-checked)
-      UmCur q{um_tile_at(0, total_tiles, n_ntiles), 0, 0, 0u, 0, 0, 0, 0, 0};
+      UmCur q{um_tile_at(0, total_tiles, n_ntiles), 0, 0, 0u, 0, 0, 0, 0, um_job_of(J.n, 0)};
       um_cur_tile(q, total_tiles, n_ttiles, n_ntiles);
       while (q.tile < total_tiles) {
         mbar_wait(&misc->a_empty[q.stage], q.ph ^ 1u, 0);
@@ -1824,7 +1828,9 @@ static int um_launch_jobs(UmJobs& J, int n_ttiles, int n_ntiles, int64_t total, 
   int sms = 148;
   int rc = um_device_setup(dev, &sms);
   if (rc) return rc;
-  int grid = (int)(total < sms ? total : sms);
+  const int64_t items = total * J.n;  // (conv, tile) pairs
+  ST2_REQUIRE(items < (1ll << 31), "conv_umma_multi: too many tiles");
+  int grid = (int)(items < sms ? items : sms);
   J.wmap = J.j[0].ymap; J.wmap_res = J.j[0].ymap; J.wmap_acc = J.j[0].ymap;
   if (lay.pair) {  // decided in um_layout; single job only
     const St2ConvParams& p = J.j[0].p;

@@ -895,22 +895,22 @@ struct Fwd {
     return ST2_OK;
   }
 
-  // the same for n (<= 3) norm layers with equal shapes, one launch
+  // the same for n (<= 4) norm layers with equal shapes, one launch
   int finalize_multi(float* const* partials, int n, int n_tiles, int n_cols, int C, int64_t count,
-                     const NormW* const* norms, int reps) {
-    const float* pp[3]; const float* hg[3]; float* so[3];
+                     const NormW* const* norms, int reps, int c_off = 0) {
+    const float* pp[4]; const float* hg[4]; float* so[4];
     for (int j = 0; j < n; ++j) {
       if (norms[j]->C != norms[0]->C) {  // different layers after all: one by one
         for (int q = 0; q < n; ++q) {
-          int rc = finalize(partials[q], n_tiles, n_cols, C, count, *norms[q], 0, reps);
+          int rc = finalize(partials[q], n_tiles, n_cols, C, count, *norms[q], c_off, reps);
           if (rc) return rc;
         }
         return ST2_OK;
       }
       pp[j] = partials[j]; hg[j] = hall + norms[j]->h_off; so[j] = ss + (int64_t)norms[j]->ss_off * 2;
     }
-    RUN(launch_stats_finalize_multi(pp, n, n_tiles, n_cols, C, count, hg, h->fc_rows, norms[0]->C, so, h->ss_pairs, 0, B,
-                                    st, reps));
+    RUN(launch_stats_finalize_multi(pp, n, n_tiles, n_cols, C, count, hg, h->fc_rows, norms[0]->C, so, h->ss_pairs, c_off,
+                                    B, st, reps));
     return ST2_OK;
   }
 
@@ -1060,6 +1060,22 @@ struct Fwd {
     return ST2_OK;
   }
 
+  // independent convs of the same shape (conv1 + shortcut of an AdainResBlk1d, the two asr_res copies): one multi-conv
+  // launch when all their tiles fit the SMs at once (a single utterance), one launch each otherwise.  ST2_GROUP=0: never.
+  int conv_group(const ConvW* const* cs, const ConvIO* ios, int n) {
+    static const bool group_env = [] { const char* e = getenv("ST2_GROUP"); return !(e && e[0] == '0'); }();
+    const int64_t tiles = (int64_t)B * ceil_div(ios[0].Lout, 256) * ceil_div(cs[0]->n16 > 0 ? cs[0]->n16 : cs[0]->n, 128);
+    if (group_env && DT<AT>::id == ST2_DT_BF16 && !tc32 && n <= 3 && tiles * n <= 148) {
+      float* parts[3]; int tl[3], cl[3];
+      return conv_multi(cs, ios, n, parts, tl, cl);  // last_* = the last conv that asked for statistics
+    }
+    for (int j = 0; j < n; ++j) {
+      int rc = conv(*cs[j], ios[j]);
+      if (rc) return rc;
+    }
+    return ST2_OK;
+  }
+
   ConvIO io_of(const Act<AT>& x, const Act<AT>& y) const {
     ConvIO io;
     io.x = x.p; io.x_dtype = DT<AT>::id; io.x_bstride = x.bstride; io.ldx = x.ld; io.Lin = x.L;
@@ -1091,6 +1107,8 @@ struct Fwd {
                               W<float>(r.pool_b), cin1.p, cin1.bstride, cin1.ld, B, L, r.din, r.din_pad, st));
     }
     Act<AT> hbuf = new_act(Lo, r.dout);
+    Act<AT> sc = in;  // identity shortcut when dims match (never the case in this decoder)
+    bool sc_done = false;
     // wide layers (N >= 512: every activation tile feeds >= 4 N tiles of the tcgen05 kernel): AdaIN +
     // LeakyReLU are applied once by an elementwise pass instead of once per N tile in the conv prologue
     const bool pre_act = DT<AT>::id == ST2_DT_BF16 && r.conv1.w16 >= 0 && r.dout >= 512;
@@ -1103,15 +1121,29 @@ struct Fwd {
       ConvIO io = io_of(cin1, hbuf);
       if (!r.up && !pre_act) { io.pre_norm = &r.n1; io.act = ST2_ACT_LRELU; io.slope = 0.2f; }
       io.want_stats = true;
-      const int64_t m1 = ar.mark();
-      int rc = conv(r.conv1, io);
-      if (rc) return rc;
-      rc = finalize(last_partials, last_tiles, last_cols, r.dout, Lo, r.n2, 0);
-      if (rc) return rc;
-      ar.release(m1);
+      // conv1 and the 1x1 shortcut read the same rows and are independent: one launch for both when the pair still
+      // fits the SMs (a single utterance: 2 x 8 CTAs)
+      if (r.has_sc && !r.up) {
+        sc = new_act(L, r.dout);
+        sc_done = true;
+        const int64_t m1 = ar.mark();
+        const ConvW* cs2[2] = {&r.conv1, &r.conv1x1};
+        ConvIO ios2[2] = {io, io_of(in, sc)};
+        int rc = conv_group(cs2, ios2, 2);  // statistics of conv1 = the only ones asked for
+        if (rc) return rc;
+        rc = finalize(last_partials, last_tiles, last_cols, r.dout, Lo, r.n2, 0);
+        if (rc) return rc;
+        ar.release(m1);
+      } else {
+        const int64_t m1 = ar.mark();
+        int rc = conv(r.conv1, io);
+        if (rc) return rc;
+        rc = finalize(last_partials, last_tiles, last_cols, r.dout, Lo, r.n2, 0);
+        if (rc) return rc;
+        ar.release(m1);
+      }
     }
-    Act<AT> sc = in;  // identity shortcut when dims match (never the case in this decoder)
-    if (r.has_sc) {
+    if (r.has_sc && !sc_done) {
       sc = new_act(L, r.dout);
       ConvIO io = io_of(in, sc);
       int rc = conv(r.conv1x1, io);
@@ -1492,11 +1524,12 @@ int Fwd<AT>::run(const float* asr, const float* f0, const float* nn, const float
     RUN(launch_prep_inputs<AT>(asr, f0, nn, W<float>(h->f0w), W<float>(h->nw), x0.p, ld0, ca.p, cb.p, ldc,
                                c_f0, B, c.dim_in, T2, st, o.align_idx, o.align_len));
     // asr_res = Conv1d(512 -> 64, k1)(asr) written into columns [1024, 1088) of both concat buffers
-    for (int which = 0; which < 2; ++which) {
-      Act<AT>& dstb = which == 0 ? ca : cb;
-      ConvIO io = io_of(x0, dstb);
-      io.y = dstb.p + 1024;
-      int rc = conv(h->asr_res, io);
+    {
+      const ConvW* cs2[2] = {&h->asr_res, &h->asr_res};
+      ConvIO ios2[2] = {io_of(x0, ca), io_of(x0, cb)};
+      ios2[0].y = ca.p + 1024;
+      ios2[1].y = cb.p + 1024;
+      int rc = conv_group(cs2, ios2, 2);
       if (rc) return rc;
     }
     // statistics of tensors no conv epilogue produced: x0 (encode.norm1) and the constant concat columns
@@ -1508,8 +1541,10 @@ int Fwd<AT>::run(const float* asr, const float* f0, const float* nn, const float
     RUN(launch_colstats<AT>(ca.p, ca.bstride, ca.ld, T2, 1024, n_const, p_const, B, st));
     int rc = finalize(p_x0, cs_tiles, din0, din0, T2, h->encode.n1, 0);
     if (rc) return rc;
-    for (int i = 0; i < 4; ++i) {
-      rc = finalize(p_const, cs_tiles, n_const, n_const, T2, h->decode[i].n1, 1024);
+    {
+      float* pp4[4]; const NormW* norms4[4];
+      for (int i = 0; i < 4; ++i) { pp4[i] = p_const; norms4[i] = &h->decode[i].n1; }
+      rc = finalize_multi(pp4, 4, cs_tiles, n_const, n_const, T2, norms4, 1, 1024);
       if (rc) return rc;
     }
     // encode: x0 -> ca[:, :1024]

@@ -66,11 +66,12 @@ int launch_style_fc(const float* s, const float* W, const float* bvec, float* h,
 // ... (n_cols = phases*C for a polyphase transposed conv).  Sums run in fp64 in a fixed order, so
 // the result is deterministic and independent of how the producing grid was scheduled.
 constexpr int SF_WARPS = 32;
-// up to 3 norm layers of the same shape per launch (blockIdx.z): the three resblocks of a generator stage in lock step
+// up to 4 norm layers of the same shape per launch (blockIdx.z): the three resblocks of a generator stage in lock step,
+// the four decode blocks' norm1 over the constant concat columns
 struct SfJobs {
-  const float* partials[3];
-  const float* hg[3];
-  float* ss[3];
+  const float* partials[4];
+  const float* hg[4];
+  float* ss[4];
 };
 __global__ void __launch_bounds__(SF_WARPS * 32)
 stats_finalize_kernel(const SfJobs jobs, int n_tiles, int n_cols, int C,
@@ -146,18 +147,19 @@ stats_finalize_kernel(const SfJobs jobs, int n_tiles, int n_cols, int C,
 int launch_stats_finalize(const float* partials, int n_tiles, int n_cols, int C, int64_t count,
                           const float* hg, int h_stride, int Cn, float* ss, int ss_stride,
                           int c_off, int B, cudaStream_t st, int reps) {
-  SfJobs jobs = {{partials, nullptr, nullptr}, {hg, nullptr, nullptr}, {ss, nullptr, nullptr}};
+  SfJobs jobs = {};
+  jobs.partials[0] = partials; jobs.hg[0] = hg; jobs.ss[0] = ss;
   dim3 grid(ceil_div(C, 32), B, 1);
   ST2_CUDA_OK(launch_pdl(stats_finalize_kernel, grid, dim3(SF_WARPS * 32), 0, st, jobs, n_tiles, n_cols, C,
                          1.0 / (double)count, h_stride, Cn, ss_stride, c_off, reps));
   ST2_LAUNCH_OK("stats_finalize");
   return ST2_OK;
 }
-// n (<= 3) norm layers with the same shapes (tiles, columns, channels, count) in one launch
+// n (<= 4) norm layers with the same shapes (tiles, columns, channels, count) in one launch
 int launch_stats_finalize_multi(const float* const* partials, int n, int n_tiles, int n_cols, int C, int64_t count,
                                 const float* const* hg, int h_stride, int Cn, float* const* ss, int ss_stride,
                                 int c_off, int B, cudaStream_t st, int reps) {
-  ST2_REQUIRE(n >= 1 && n <= 3, "stats_finalize_multi: 1..3 layers");
+  ST2_REQUIRE(n >= 1 && n <= 4, "stats_finalize_multi: 1..4 layers");
   SfJobs jobs = {};
   for (int j = 0; j < n; ++j) {
     jobs.partials[j] = partials[j];
