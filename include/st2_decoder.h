@@ -120,9 +120,13 @@ typedef struct St2ForwardOpts {
 /* Decoder(**kwargs): validates the config and builds the layer plan (no weights yet). */
 int st2_decoder_create(const St2Config* cfg, St2Decoder** out);
 
-/* Options that change what load builds; call between create and load.  "fp32_tc" = 1: also pack the (hi, hi, lo) bf16
- * blobs ST2_PREC_FP32_TC needs.  No counterpart in the reference (its precision is torch's dtype / autocast context,
- * train_second.py:183-186).  Unknown names -> ST2_EINVAL; after load -> ST2_ESTATE. */
+/* Options.  "fp32_tc" = 1 changes what load builds (call between create and load; after load -> ST2_ESTATE): also pack
+ * the (hi, hi, lo) bf16 blobs ST2_PREC_FP32_TC needs.  No counterpart in the reference (its precision is torch's
+ * dtype / autocast context, train_second.py:183-186).  Schedule switches, any time between forwards, results are
+ * bit-identical for every value: "fork" = 0 / 1 / 2: the excitation branch (source -> STFT -> noise_convs -> noise_res)
+ * on the handle's second stream never / for single-utterance-sized forwards (default) / always; "group" = 0 / 1:
+ * independent same-shaped convs of such a forward as one multi-conv launch (default 1).  Defaults can also come from
+ * ST2_FORK / ST2_GROUP in the environment at create time.  Unknown names -> ST2_EINVAL. */
 int st2_decoder_set_option(St2Decoder* h, const char* name, int value);
 
 /* load_state_dict: folds weight-norm (w = g*v/||v||, dim 0), repacks every conv into the

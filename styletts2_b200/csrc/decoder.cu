@@ -111,6 +111,9 @@ struct St2Decoder {
   int device = 0;
   bool loaded = false;
   bool opt_fp32_tc = false;  // st2_decoder_set_option("fp32_tc", 1) before load: pack the 3 x bf16 blobs
+  // schedule switches (st2_decoder_set_option any time; defaults from ST2_FORK / ST2_GROUP, else 1):
+  int opt_fork = 1;   // excitation branch on the second stream: 0 never, 1 small forwards, 2 every size
+  int opt_group = 1;  // independent same-shaped convs of a small forward as one multi-conv launch: 0 never
   int spf = 0;
   std::vector<std::string> key_names;
   std::vector<std::vector<int64_t>> key_shapes;
@@ -1061,9 +1064,10 @@ struct Fwd {
   }
 
   // independent convs of the same shape (conv1 + shortcut of an AdainResBlk1d, the two asr_res copies): one multi-conv
-  // launch when all their tiles fit the SMs at once (a single utterance), one launch each otherwise.  ST2_GROUP=0: never.
+  // launch when all their tiles fit the SMs at once (a single utterance), one launch each otherwise.  Option "group" /
+  // ST2_GROUP = 0: never.
   int conv_group(const ConvW* const* cs, const ConvIO* ios, int n) {
-    static const bool group_env = [] { const char* e = getenv("ST2_GROUP"); return !(e && e[0] == '0'); }();
+    const bool group_env = h->opt_group != 0;
     const int64_t tiles = (int64_t)B * ceil_div(ios[0].Lout, 256) * ceil_div(cs[0]->n16 > 0 ? cs[0]->n16 : cs[0]->n, 128);
     if (group_env && DT<AT>::id == ST2_DT_BF16 && !tc32 && n <= 3 && tiles * n <= 148) {
       float* parts[3]; int tl[3], cl[3];
@@ -1393,10 +1397,9 @@ int Fwd<AT>::run(const float* asr, const float* f0, const float* nn, const float
     Lin = g.Ls;
   }
   // fork the excitation branch when the last stage has fewer 256-row tiles than 2 x SMs (a single utterance: the step
-  // is a chain of ~100 short dependent launches, a third of them in this branch); ST2_FORK=0 never, 2 always
-  static const int fork_env = [] { const char* e = getenv("ST2_FORK"); return e ? atoi(e) : 1; }();
-  const bool forked = h->side_st && fork_env != 0 &&
-                      ((int64_t)B * ceil_div(geo[c.n_ups - 1].Ls, 256) < 2 * 148 || fork_env >= 2);
+  // is a chain of ~100 short dependent launches, a third of them in this branch); option "fork" / ST2_FORK: 0 never, 2 always
+  const bool forked = h->side_st && h->opt_fork != 0 &&
+                      ((int64_t)B * ceil_div(geo[c.n_ups - 1].Ls, 256) < 2 * 148 || h->opt_fork >= 2);
   st_side = h->side_st;
 
   const int n_fft = c.gen_istft_n_fft, hop = c.gen_istft_hop_size;
@@ -1744,6 +1747,8 @@ extern "C" int st2_decoder_create(const St2Config* cfg, St2Decoder** out) {
   if (rc) return rc;
   St2Decoder* h = new St2Decoder();
   h->cfg = *cfg;
+  if (const char* e = getenv("ST2_FORK")) h->opt_fork = std::min(2, std::max(0, atoi(e)));
+  if (const char* e = getenv("ST2_GROUP")) h->opt_group = e[0] == '0' ? 0 : 1;
   h->spf = 1;
   for (int i = 0; i < cfg->n_ups; ++i) h->spf *= cfg->upsample_rates[i];
   if (cfg->kind == ST2_KIND_ISTFTNET) h->spf *= cfg->gen_istft_hop_size;
@@ -1781,6 +1786,14 @@ extern "C" int st2_decoder_set_option(St2Decoder* h, const char* name, int value
       return ST2_ESTATE;
     }
     h->opt_fp32_tc = value != 0;
+    return ST2_OK;
+  }
+  if (strcmp(name, "fork") == 0 || strcmp(name, "group") == 0) {
+    if (value < 0 || value > 2) {
+      set_error("st2_decoder_set_option: fork / group take 0, 1 or 2");
+      return ST2_EINVAL;
+    }
+    (name[0] == 'f' ? h->opt_fork : h->opt_group) = value;
     return ST2_OK;
   }
   set_error(std::string("st2_decoder_set_option: unknown option ") + name);

@@ -307,16 +307,21 @@ int launch_stft(const float* hs, int B, int Lw, float* har_cl, int ld, cudaStrea
 constexpr int IS_NS = 1024;            // output samples per block
 constexpr int IS_MAXF = IS_NS / 5 + 8; // frames touching them
 
-// Block = IS_NS output samples of one item.  Phase 1, one thread per frame touching them: exp / sin heads
-// (istftnet.py:377-378), then the inverse 20-point DFT of the frame entirely in registers -- the twiddles are
-// compile-time indices into constant memory (FFMA constant operands, no table loads), and the symmetry
-// x[20 - n] = A_n + B_n, x[n] = A_n - B_n halves the arithmetic -- and the 20 windowed samples go to shared
-// memory (row stride 33: conflict-free; the frame's inputs were staged in the same row by coalesced loads).  Phase 2, one thread per output sample: overlap-add of the 4 frames
-// that cover it, division by the window envelope, trimmed to [10, 10 + Lw).  FAST = SFU exp / sin (bf16 path).
+// Block = IS_NS output samples of one item.  Phase 0: the block's rows ([frames][ld] fp32, 22 of them used) come in as
+// 128-bit loads, four rows per warp instruction and every load of the block in flight at once (the kernel is
+// HBM-latency-bound: one 88-byte load per warp and iteration kept too few bytes in flight, ncu: 7.3 warps per issue
+// stalled on long scoreboard).  Phase 1, one thread per frame: exp / sin heads (istftnet.py:377-378), then the inverse
+// 20-point DFT of the frame entirely in registers -- the twiddles are compile-time indices into constant memory (FFMA
+// constant operands, no table loads), and the symmetry x[20 - n] = A_n + B_n, x[n] = A_n - B_n halves the arithmetic --
+// and the 20 windowed samples go back to the frame's row.  Phase 2, one thread per output sample: overlap-add of the 4
+// frames that cover it, division by the window envelope, trimmed to [10, 10 + Lw).  Row stride IS_LD = 37 floats
+// (= 5 mod 32): conflict-free for the row-per-thread accesses of phase 1 AND for phase 2, whose 32 consecutive samples
+// read rows i / 5 at column i % 5 (+ 5 j): bank 5 (i / 5) + i % 5 = i.  FAST = SFU exp / sin (bf16 path).
+constexpr int IS_LD = 37;
 template <bool FAST>
 __global__ void __launch_bounds__(256)
-istft_kernel(const float* __restrict__ x, int ld, int frames, float* __restrict__ wav) {
-  __shared__ float fo[IS_MAXF][33];  // row fr: first the frame's 22 head inputs, then (same thread) its 20 samples
+istft_kernel(const float* __restrict__ x, int ld, int frames, float* __restrict__ wav, bool vec) {
+  __shared__ float fo[IS_MAXF][IS_LD];  // row fr: first the frame's head inputs, then (same thread) its 20 samples
   __shared__ float s_w2[20];
   const int b = blockIdx.y;
   const int Lw = 5 * (frames - 1);
@@ -327,8 +332,23 @@ istft_kernel(const float* __restrict__ x, int ld, int frames, float* __restrict_
   const int fmin = max(0, (i0 + 10) / 5 - 3);
   const int fmax = min(frames - 1, (i1 - 1 + 10) / 5);
   const int nf = fmax - fmin + 1;
-  {  // one coalesced load per row (lane = column; a thread per row would touch 32 lines per instruction)
-    const float* base = x + ((int64_t)b * frames + fmin) * ld;
+  const float* base = x + ((int64_t)b * frames + fmin) * ld;
+  if (vec) {  // ld == 32, 16-byte aligned: rows of 128 bytes: lane -> (row l / 8 of 4, columns 4 (l % 8) ..): all loads first, then the stores
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int rq = lane >> 3, c4 = (lane & 7) * 4;
+    constexpr int NIT = (IS_MAXF + 31) / 32;
+    float4 v[NIT];
+#pragma unroll
+    for (int it = 0; it < NIT; ++it) {
+      const int r = (it * 8 + warp) * 4 + rq;
+      v[it] = r < nf ? __ldg(reinterpret_cast<const float4*>(base + (int64_t)r * 32 + c4)) : make_float4(0.f, 0.f, 0.f, 0.f);
+    }
+#pragma unroll
+    for (int it = 0; it < NIT; ++it) {
+      const int r = (it * 8 + warp) * 4 + rq;
+      if (r < nf) { fo[r][c4] = v[it].x; fo[r][c4 + 1] = v[it].y; fo[r][c4 + 2] = v[it].z; fo[r][c4 + 3] = v[it].w; }
+    }
+  } else {  // any other row stride: one coalesced load per row (lane = column)
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     if (lane < 22)
       for (int r = warp; r < nf; r += 8) fo[r][lane] = __ldg(base + (int64_t)r * ld + lane);
@@ -383,8 +403,9 @@ int launch_istft(const float* x_cl, int ld, int B, int frames, float* wav, cudaS
   ST2_REQUIRE(frames >= 5 && ld >= 22, "istft: shape");
   const int Lw = 5 * (frames - 1);
   dim3 grid(ceil_div(Lw, IS_NS), B);
-  if (fast) istft_kernel<true><<<grid, 256, 0, st>>>(x_cl, ld, frames, wav);
-  else istft_kernel<false><<<grid, 256, 0, st>>>(x_cl, ld, frames, wav);
+  const bool vec = ld == 32 && (reinterpret_cast<uintptr_t>(x_cl) & 15u) == 0;
+  if (fast) istft_kernel<true><<<grid, 256, 0, st>>>(x_cl, ld, frames, wav, vec);
+  else istft_kernel<false><<<grid, 256, 0, st>>>(x_cl, ld, frames, wav, vec);
   ST2_LAUNCH_OK("istft");
   return ST2_OK;
 }

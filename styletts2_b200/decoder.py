@@ -89,6 +89,7 @@ class _DecoderBase(nn.Module):
         # blobs: set fp32_tc = True BEFORE the first forward / after changing it the weights are re-packed
         self.fp32_tc = False
         self._native_tc: Dict[int, bool] = {}
+        self._schedule: Dict[bytes, int] = {}   # set_schedule(): options re-applied to every new native handle
         self.seed = 0
         # a batch whose workspace would exceed this is decoded in micro-batches (utterances are
         # independent, SURVEY 8d: config C5 is 512 x 2400 frames); 0 = never split
@@ -171,6 +172,8 @@ class _DecoderBase(nn.Module):
                 check(lib.st2_decoder_create(C.byref(self._cfg), C.byref(h)), "st2_decoder_create")
                 if want_tc:
                     check(lib.st2_decoder_set_option(h, b"fp32_tc", 1), "st2_decoder_set_option")
+                for name, v in self._schedule.items():
+                    check(lib.st2_decoder_set_option(h, name, v), "st2_decoder_set_option")
                 self._native[idx] = h
                 self._native_tc[idx] = want_tc
             sd = {k: v.detach().to("cpu", torch.float32).contiguous() for k, v in self.state_dict().items()}
@@ -187,6 +190,20 @@ class _DecoderBase(nn.Module):
             check(lib.st2_decoder_load(h, arr, len(sd)), "st2_decoder_load")
         self._native_version[idx] = ver
         return h
+
+    def set_schedule(self, fork: Optional[int] = None, group: Optional[int] = None) -> None:
+        """Schedule switches of the native forward (``st2_decoder_set_option``; results are bit-identical for every
+        value).  ``fork``: 0 one stream, 1 (default) the excitation branch of a single-utterance-sized forward on a
+        second stream, 2 for every size.  ``group``: 0 / 1 (default) independent same-shaped convs of such a forward as
+        one launch.  Captured graphs are dropped: they hold the old schedule."""
+        with self._lock:
+            for name, v in ((b"fork", fork), (b"group", group)):
+                if v is None:
+                    continue
+                self._schedule[name] = int(v)
+                for h in self._native.values():
+                    check(lib.st2_decoder_set_option(h, name, int(v)), "st2_decoder_set_option")
+            self._graphs.clear()
 
     def __del__(self):
         try:

@@ -209,6 +209,44 @@ def test_batch_rows_are_independent_bitwise():
 
 
 @pytest.mark.parametrize("kind", ["istftnet", "hifigan"])
+def test_schedules_are_bit_identical(kind):
+    """The two-stream schedule of a small forward (excitation branch forked onto the handle's second stream, grouped
+    conv launches) must give the bytes of the plain one-stream schedule: eager, under graph replay, every precision.
+    A missing join or an aliased arena shows up here as a difference."""
+    import synthetic as synth
+    dec, sd, cfg = _get(kind)
+    inp = synth.synth_inputs(cfg, 2, 40, seed=5, with_noise=False)
+    a = {k: v.cuda() for k, v in inp.items()}
+    try:
+        for prec in ("bf16", "fp32"):
+            outs = {}
+            for fork, group in ((0, 0), (2, 1), (1, 1), (2, 0)):
+                dec.set_schedule(fork=fork, group=group)
+                dec.seed = 31
+                outs[(fork, group)] = dec(a["asr"], a["F0_curve"], a["N"], a["s"], precision=prec).clone()
+            ref = outs[(0, 0)]
+            assert torch.isfinite(ref).all()
+            for k, v in outs.items():
+                assert torch.equal(ref, v), (prec, k)
+        # graph replay of the forked schedule (both chains inside one captured graph), three replays
+        old = dec.cuda_graphs
+        try:
+            dec.set_schedule(fork=0, group=0)
+            dec.seed = 31
+            want = dec(a["asr"], a["F0_curve"], a["N"], a["s"], precision="bf16").clone()
+            dec.set_schedule(fork=2, group=1)
+            dec.cuda_graphs = True
+            for _ in range(3):
+                dec.seed = 31
+                got = dec(a["asr"], a["F0_curve"], a["N"], a["s"], precision="bf16")
+                assert torch.equal(want, got)
+        finally:
+            dec.cuda_graphs = old
+    finally:
+        dec.set_schedule(fork=1, group=1)
+
+
+@pytest.mark.parametrize("kind", ["istftnet", "hifigan"])
 def test_micro_batches_and_shards_draw_the_same_noise(kind):
     """A batch decoded in micro-batches (workspace limit, config C5) or as shards with
     ``item_offset`` equals the one-shot batch bit for bit, in-kernel Philox noise included."""
