@@ -92,12 +92,32 @@ def multi_main(iters):
             torch.cuda.empty_cache()
 
 
+def l2_main(iters):
+    """would an item-group schedule (keep a few items' activations in the 126 MB L2) speed the memory-bound
+    convs up?  The same stage-2 conv on 2 / 3 items (x + res + y = 74 / 111 MB: L2-resident when launched back to back)
+    and on 32 items (1.2 GB: streams through HBM), microseconds per 148-tile round."""
+    S = _cabi.ACT_SNAKE
+    for k, res in ((3, False), (3, True), (7, True), (11, True)):
+        for B in (2, 3, 32):
+            p, keep = make(B, 48001, 128, 128, k, 1, S, res, True)
+            p.B = B
+            us = time_it(p, iters * (8 if B < 32 else 1))
+            tiles = B * 188
+            rounds = (tiles + 147) // 148
+            print(f"s2 k{k} {'c2(res)' if res else 'c1     '} B={B:2d}: {us:8.1f} us  {tiles:5d} tiles = {rounds:2d} rounds of 148, "
+                  f"{us / rounds:6.2f} us per round, {us / B:7.2f} us per item", flush=True)
+            del p, keep
+            torch.cuda.empty_cache()
+
+
 def main():
     iters = 5
     if "--iters" in sys.argv:
         iters = int(sys.argv[sys.argv.index("--iters") + 1])
     if "--multi" in sys.argv:
         return multi_main(iters)
+    if "--l2" in sys.argv:
+        return l2_main(iters)
     B = 32
     cases = []
     if "--one" in sys.argv:
