@@ -156,109 +156,118 @@ static int launch_t(const St2ConvParams& p, cudaStream_t st) {
 
 // ---------------------------------------------------------------------------- thin conv
 // One input channel, many output channels (HiFi-GAN's strided noise convs on the raw excitation,
-// hifigan.py:301-311: Conv1d(1, C, k = 2 s, stride s)): HBM-write bound, so no GEMM tiling; a block
-// stages its 64-row input window and the [k][C] weights in shared memory, a thread owns 8 channels of a
+// hifigan.py:301-311: Conv1d(1, C, k = 2 s, stride s)): HBM-write bound (k <= 4) or FMA-bound (k = 12, 60), so no GEMM
+// tiling; a block stages its input window and the [k][C] weights in shared memory, a thread owns 8 channels of a
 // row and writes one 16-byte bf16 vector.  Same argument block, tile size (64 rows) and statistics
 // layout as conv_simt_kernel.
 constexpr int THIN_TT = SIMT_TT;
-// RT rows x 8 channels per thread: one pair of 16-byte weight loads feeds 8 RT FMAs
+// A block owns `tiles_per_block` consecutive 64-row tiles of one item: it stages their whole input window and the [k][n]
+// weights once (one __syncthreads per block, not per tile), a thread computes RT rows x 8 channels at a time (one pair
+// of 16-byte weight loads feeds 8 RT FMAs) and keeps its (sum, sumsq) in registers over all its rows; one reduction at
+// the end.  The block's statistics go to the partial slot of its FIRST tile and zeros to the slots of its other tiles
+// (the consumer sums the slots of an item in a fixed order: same result, deterministic).
 template <int RT>
 __global__ void __launch_bounds__(256)
 conv_thin_kernel(const St2ConvParams p, int tiles_per_block) {
   extern __shared__ float thin_smem[];
   const int n = p.n_cols, G = n >> 3, R = 256 / G;       // channel groups, row threads
-  const int win = (THIN_TT - 1) * p.stride + p.k;
-  float* xs = thin_smem;                                  // [win]
-  float* ws = thin_smem + ((win + 3) & ~3);               // [k][n]
+  const int win_max = (tiles_per_block * THIN_TT - 1) * p.stride + p.k;
+  float* xs = thin_smem;                                  // [win_max]
+  float* ws = thin_smem + ((win_max + 3) & ~3);           // [k][n]
   float* red = ws + p.k * n;                              // [2][8 warps][n]
   const int b = blockIdx.y, tid = threadIdx.x;
   const float* xb = reinterpret_cast<const float*>(p.x) + (int64_t)b * p.x_bstride;
   __nv_bfloat16* yb = reinterpret_cast<__nv_bfloat16*>(p.y) + (int64_t)b * p.y_bstride;
   const float* wg = reinterpret_cast<const float*>(p.w);
+  const int n_tiles_item = (p.Lout + THIN_TT - 1) / THIN_TT;
+  const int tile0 = blockIdx.x * tiles_per_block;
+  const int tile_end = min(n_tiles_item, tile0 + tiles_per_block);
+  const int t_begin = tile0 * THIN_TT, t_end = min(p.Lout, tile_end * THIN_TT);
+  const int rows = t_end - t_begin;
   for (int i = tid; i < p.k * n; i += 256) ws[i] = wg[i];
-  const int cg = tid % G, rr = tid / G;
-  float bias[8];
-#pragma unroll
-  for (int e = 0; e < 8; ++e) bias[e] = p.bias ? p.bias[(int64_t)b * p.bias_bstride + cg * 8 + e] : 0.f;
-  const int tile_end = min((p.Lout + THIN_TT - 1) / THIN_TT, (int)(blockIdx.x + 1) * tiles_per_block);
-  for (int tile = blockIdx.x * tiles_per_block; tile < tile_end; ++tile) {
-    const int t0 = tile * THIN_TT;
-    const int i0 = t0 * p.stride - p.pad;
+  {
+    const int i0 = t_begin * p.stride - p.pad;
+    const int win = (rows - 1) * p.stride + p.k;
     for (int i = tid; i < win; i += 256) {
       const int r = i0 + i;
       xs[i] = (r >= 0 && r < p.Lin) ? xb[(int64_t)r * p.ldx] : 0.f;
     }
-    __syncthreads();
-    float s1[8], s2[8];
+  }
+  const int cg = tid % G, rr = tid / G;
+  float bias[8];
 #pragma unroll
-    for (int e = 0; e < 8; ++e) s1[e] = s2[e] = 0.f;
-    for (int tl = rr * RT; tl < THIN_TT; tl += R * RT) {
-      float acc[RT][8];
+  for (int e = 0; e < 8; ++e) bias[e] = p.bias ? p.bias[(int64_t)b * p.bias_bstride + cg * 8 + e] : 0.f;
+  __syncthreads();
+  float s1[8], s2[8];
 #pragma unroll
-      for (int i = 0; i < RT; ++i)
+  for (int e = 0; e < 8; ++e) s1[e] = s2[e] = 0.f;
+  const float* wr = ws + cg * 8;
+  for (int tl = rr * RT; tl < rows; tl += R * RT) {
+    float acc[RT][8];
 #pragma unroll
-        for (int e = 0; e < 8; ++e) acc[i][e] = bias[e];
-      const float* xr = xs + tl * p.stride;
-      const float* wr = ws + cg * 8;
-      for (int j = 0; j < p.k; ++j) {
-        const float4 w0 = *reinterpret_cast<const float4*>(wr + j * n);
-        const float4 w1 = *reinterpret_cast<const float4*>(wr + j * n + 4);
+    for (int i = 0; i < RT; ++i)
 #pragma unroll
-        for (int i = 0; i < RT; ++i) {
-          const float xv = xr[i * p.stride + j];
-          acc[i][0] = fmaf(w0.x, xv, acc[i][0]); acc[i][1] = fmaf(w0.y, xv, acc[i][1]);
-          acc[i][2] = fmaf(w0.z, xv, acc[i][2]); acc[i][3] = fmaf(w0.w, xv, acc[i][3]);
-          acc[i][4] = fmaf(w1.x, xv, acc[i][4]); acc[i][5] = fmaf(w1.y, xv, acc[i][5]);
-          acc[i][6] = fmaf(w1.z, xv, acc[i][6]); acc[i][7] = fmaf(w1.w, xv, acc[i][7]);
-        }
-      }
+      for (int e = 0; e < 8; ++e) acc[i][e] = bias[e];
+    // rows past the block's last one read inside the staged window or just behind it (never stored): clamp the offset
+    int xo[RT];
+#pragma unroll
+    for (int i = 0; i < RT; ++i) xo[i] = min(tl + i, rows - 1) * p.stride;
+    for (int j = 0; j < p.k; ++j) {
+      const float4 w0 = *reinterpret_cast<const float4*>(wr + j * n);
+      const float4 w1 = *reinterpret_cast<const float4*>(wr + j * n + 4);
 #pragma unroll
       for (int i = 0; i < RT; ++i) {
-        const int t = t0 + tl + i;
-        if (t < p.Lout) {
-          uint32_t o[4];
-#pragma unroll
-          for (int e = 0; e < 4; ++e) {
-            const __nv_bfloat162 pk =
-                __floats2bfloat162_rn(acc[i][2 * e] * p.out_scale, acc[i][2 * e + 1] * p.out_scale);
-            o[e] = *reinterpret_cast<const uint32_t*>(&pk);
-            const float lo = __bfloat162float(pk.x), hi = __bfloat162float(pk.y);
-            s1[2 * e] += lo; s2[2 * e] += lo * lo;
-            s1[2 * e + 1] += hi; s2[2 * e + 1] += hi * hi;
-          }
-          *reinterpret_cast<uint4*>(yb + (int64_t)t * p.ldy + cg * 8) = make_uint4(o[0], o[1], o[2], o[3]);
-        }
+        const float xv = xs[xo[i] + j];
+        acc[i][0] = fmaf(w0.x, xv, acc[i][0]); acc[i][1] = fmaf(w0.y, xv, acc[i][1]);
+        acc[i][2] = fmaf(w0.z, xv, acc[i][2]); acc[i][3] = fmaf(w0.w, xv, acc[i][3]);
+        acc[i][4] = fmaf(w1.x, xv, acc[i][4]); acc[i][5] = fmaf(w1.y, xv, acc[i][5]);
+        acc[i][6] = fmaf(w1.z, xv, acc[i][6]); acc[i][7] = fmaf(w1.w, xv, acc[i][7]);
       }
     }
-    if (p.stats) {
-      // rows that share a warp first (lanes cg, cg + G, ...), then one partial per warp
-      for (int off = G; off < 32; off <<= 1) {
 #pragma unroll
-        for (int e = 0; e < 8; ++e) {
-          s1[e] += __shfl_xor_sync(0xffffffffu, s1[e], off);
-          s2[e] += __shfl_xor_sync(0xffffffffu, s2[e], off);
+    for (int i = 0; i < RT; ++i) {
+      if (tl + i < rows) {
+        uint32_t o[4];
+#pragma unroll
+        for (int e = 0; e < 4; ++e) {
+          const __nv_bfloat162 pk =
+              __floats2bfloat162_rn(acc[i][2 * e] * p.out_scale, acc[i][2 * e + 1] * p.out_scale);
+          o[e] = *reinterpret_cast<const uint32_t*>(&pk);
+          const float lo = __bfloat162float(pk.x), hi = __bfloat162float(pk.y);
+          s1[2 * e] += lo; s2[2 * e] = fmaf(lo, lo, s2[2 * e]);
+          s1[2 * e + 1] += hi; s2[2 * e + 1] = fmaf(hi, hi, s2[2 * e + 1]);
         }
-      }
-      if ((tid & 31) < G) {
-        float4* r1 = reinterpret_cast<float4*>(red + (0 * 8 + (tid >> 5)) * n + cg * 8);
-        float4* r2 = reinterpret_cast<float4*>(red + (1 * 8 + (tid >> 5)) * n + cg * 8);
-        r1[0] = make_float4(s1[0], s1[1], s1[2], s1[3]); r1[1] = make_float4(s1[4], s1[5], s1[6], s1[7]);
-        r2[0] = make_float4(s2[0], s2[1], s2[2], s2[3]); r2[1] = make_float4(s2[4], s2[5], s2[6], s2[7]);
+        *reinterpret_cast<uint4*>(yb + (int64_t)(t_begin + tl + i) * p.ldy + cg * 8) = make_uint4(o[0], o[1], o[2], o[3]);
       }
     }
-    __syncthreads();  // xs free for the next tile; partial sums visible
-    if (p.stats) {
-      for (int col = tid; col < n; col += 256) {
-        float a = 0.f, q2 = 0.f;
+  }
+  if (!p.stats) return;
+  // rows that share a warp first (lanes cg, cg + G, ...), then one partial per warp
+  for (int off = G; off < 32; off <<= 1) {
 #pragma unroll
-        for (int r = 0; r < 8; ++r) {  // fixed order: deterministic
-          a += red[(0 * 8 + r) * n + col];
-          q2 += red[(1 * 8 + r) * n + col];
-        }
-        *reinterpret_cast<float2*>(p.stats + (((int64_t)b * p.n_tiles + tile) * p.n_cols + col) * 2) =
-            make_float2(a, q2);
-      }
+    for (int e = 0; e < 8; ++e) {
+      s1[e] += __shfl_xor_sync(0xffffffffu, s1[e], off);
+      s2[e] += __shfl_xor_sync(0xffffffffu, s2[e], off);
     }
+  }
+  if ((tid & 31) < G) {
+    float4* r1 = reinterpret_cast<float4*>(red + (0 * 8 + (tid >> 5)) * n + cg * 8);
+    float4* r2 = reinterpret_cast<float4*>(red + (1 * 8 + (tid >> 5)) * n + cg * 8);
+    r1[0] = make_float4(s1[0], s1[1], s1[2], s1[3]); r1[1] = make_float4(s1[4], s1[5], s1[6], s1[7]);
+    r2[0] = make_float4(s2[0], s2[1], s2[2], s2[3]); r2[1] = make_float4(s2[4], s2[5], s2[6], s2[7]);
+  }
+  __syncthreads();
+  // G < 32: every warp holds all channel groups; G = 32: warp w holds rows of all 32 groups too (cg = lane)
+  for (int col = tid; col < n; col += 256) {
+    float a = 0.f, q2 = 0.f;
+#pragma unroll
+    for (int r = 0; r < 8; ++r) {  // fixed order: deterministic
+      a += red[(0 * 8 + r) * n + col];
+      q2 += red[(1 * 8 + r) * n + col];
+    }
+    float2* sp = reinterpret_cast<float2*>(p.stats + (((int64_t)b * p.n_tiles + tile0) * p.n_cols + col) * 2);
+    sp[0] = make_float2(a, q2);
+    for (int t = 1; t < tile_end - tile0; ++t) sp[(int64_t)t * p.n_cols] = make_float2(0.f, 0.f);
   }
 }
 static bool thin_ok(const St2ConvParams& p) {
@@ -270,26 +279,30 @@ static bool thin_ok(const St2ConvParams& p) {
 template <int RT>
 static int launch_thin_t(const St2ConvParams& p, cudaStream_t st) {
   const int n = p.n_cols;
-  const int win = (THIN_TT - 1) * p.stride + p.k;
+  // about 128 KB of output per block, so the [k][n] weights are read once per many tiles, but at least 16 blocks per
+  // item.  A function of the item's shape only, never of B: the grouping of rows into partial sums must not depend on
+  // the batch an item is decoded in (a shard gives bit-identical rows).
+  int tpb = max(1, (128 * 1024) / (THIN_TT * n * 2));
+  const int nt = ceil_div(p.Lout, THIN_TT);
+  while (tpb > 1 && ceil_div(nt, tpb) < 16) tpb >>= 1;
+  const int win = (tpb * THIN_TT - 1) * p.stride + p.k;
   const size_t smem = ((size_t)((win + 3) & ~3) + (size_t)p.k * n + (size_t)2 * 8 * n) * sizeof(float);
   ST2_REQUIRE(smem <= 160 * 1024, "conv_thin: tile does not fit shared memory");
   if (smem > 48 * 1024)
     ST2_CUDA_OK(cudaFuncSetAttribute(conv_thin_kernel<RT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-  // about 128 KB of output per block, so the [k][n] weights are read once per many tiles
-  int tpb = max(1, (128 * 1024) / (THIN_TT * n * 2));
-  const int nt = ceil_div(p.Lout, THIN_TT);
-  while (tpb > 1 && (int64_t)ceil_div(nt, tpb) * p.B < 2 * 148) tpb >>= 1;
   dim3 grid(ceil_div(nt, tpb), p.B);
   conv_thin_kernel<RT><<<grid, 256, smem, st>>>(p, tpb);
   ST2_LAUNCH_OK("conv_thin");
   return ST2_OK;
 }
 static int launch_thin(const St2ConvParams& p, cudaStream_t st) {
-  // row threads R = 2048 / n; RT rows each so that one pass covers at most the 64-row tile
+  // row threads R = 2048 / n, RT rows each per pass.  The long-tap layers (k = 12, 60 at n >= 128) are FMA- and
+  // shared-memory-bound: 8 rows per weight load; the short-tap ones (k <= 4 at n <= 64) are HBM-write-bound and want
+  // threads rather than registers: 2 rows (77 registers, 3 blocks per SM; measured 127 us = 3.9 TB/s at n = 32)
   switch (p.n_cols) {
-    case 32: return launch_thin_t<1>(p, st);
+    case 32: return launch_thin_t<2>(p, st);
     case 64: return launch_thin_t<2>(p, st);
-    default: return launch_thin_t<4>(p, st);
+    default: return launch_thin_t<8>(p, st);
   }
 }
 

@@ -400,3 +400,30 @@ def test_conv_umma_multi_equals_separate_launches(case):
         assert torch.equal(yw, yg)
         if sw is not None:
             assert torch.equal(sw, sg)
+
+
+@pytest.mark.parametrize("case", [
+    # B, Lin, n, k, stride: HiFi-GAN's noise_convs on the raw excitation (hifigan.py:301-311), Conv1d(1, C, 2 s, stride s)
+    (2, 12000, 256, 60, 30),
+    (2, 12000, 128, 12, 6),
+    (3, 6000, 64, 4, 2),
+    (2, 5000, 32, 1, 1),      # last stage: kernel_size 1
+    (1, 130, 64, 4, 2),       # shorter than one block's window
+])
+def test_conv_thin_one_input_channel(case):
+    """conv_simt.cu's thin kernel (cin = 1, bf16 out): a block owns several 64-row statistics tiles and writes their
+    sums into the first tile's slot; values against float64, statistics = sums of the stored bf16 values."""
+    B, Lin, n, k, stride = case
+    g = torch.Generator().manual_seed(Lin + n)
+    x = torch.randn(B, Lin, 1, generator=g)
+    w = torch.randn(k, 1, n, generator=g) / math.sqrt(k)
+    bias = torch.randn(n, generator=g) * 0.1
+    pad = (stride + 1) // 2 if stride > 1 else 0
+    Lout = (Lin + 2 * pad - (k - 1) - 1) // stride + 1
+    ref = conv_reference(x, None, _cabi.ACT_NONE, 0.0, None, w, bias, k, 1, pad, stride, Lout, None, 0, 1.0, None)
+    y, st = run_conv("simt", x.cuda(), w, bias, k=k, pad=pad, stride=stride, want_stats=True, out_dtype=torch.bfloat16)
+    yd = y.cpu().double()
+    assert torch.isfinite(yd).all()
+    assert ((yd - ref).abs() <= 2.0 ** -8 * ref.abs() + 1e-6).all()
+    s_ref = torch.stack([yd.sum(1), (yd ** 2).sum(1)], dim=-1)
+    assert torch.allclose(st.cpu().double(), s_ref, rtol=1e-4, atol=1e-2)
