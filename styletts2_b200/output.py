@@ -46,3 +46,33 @@ def log_mel(wav: torch.Tensor) -> torch.Tensor:
         check(lib.st2_log_mel(ptr(w), B, L, ptr(out), C.c_void_p(torch.cuda.current_stream(w.device).cuda_stream)),
               "st2_log_mel")
     return out
+
+
+def wav_frame(pcm16, sample_rate: int = 24000) -> bytes:
+    """RIFF / WAVE framing of one utterance (row N4: "fp32 -> int16 PCM / WAV framing"): ``pcm16`` = int16 samples, mono,
+    as a 1-D torch tensor (any device: it is downloaded here) or anything ``memoryview`` accepts -> the bytes of a
+    .wav file (44-byte PCM header + little-endian samples), what ``IPython.display.Audio`` / ``soundfile.write`` of
+    the notebooks produce from the float waveform.  24 kHz is the reference's rate (``Demo/Inference_LibriTTS.ipynb``)."""
+    import struct
+    import sys
+    if isinstance(pcm16, torch.Tensor):
+        if pcm16.dtype != torch.int16 or pcm16.dim() != 1:
+            raise ValueError("wav_frame takes one utterance of int16 samples (to_pcm16(...)[i])")
+        data = pcm16.detach().cpu().contiguous().numpy().tobytes()
+    else:
+        mv = memoryview(pcm16)
+        if mv.itemsize != 2:
+            raise ValueError("wav_frame takes 16-bit samples")
+        data = mv.tobytes()
+    if sys.byteorder != "little":  # WAVE is little-endian
+        import array
+        a = array.array("h")
+        a.frombytes(data)
+        a.byteswap()
+        data = a.tobytes()
+    if not 0 < sample_rate < 2 ** 31 or len(data) > 2 ** 32 - 45:
+        raise ValueError("wav_frame: sample rate / length out of range for a RIFF file")
+    n_ch, bits = 1, 16
+    hdr = struct.pack("<4sI4s4sIHHIIHH4sI", b"RIFF", 36 + len(data), b"WAVE", b"fmt ", 16, 1, n_ch, sample_rate,
+                      sample_rate * n_ch * bits // 8, n_ch * bits // 8, bits, b"data", len(data))
+    return hdr + data

@@ -180,3 +180,24 @@ def test_umma_blob_layout():
     expect = wp.reshape(k, cin_pad // 64, 8, 8, n // 128, 128).permute(4, 1, 0, 2, 5, 3)
     assert torch.equal(blob, expect)
     assert lib.st2_umma_pack_weights(w.data_ptr(), k, cin, 100, n, out.data_ptr()) == -1
+
+
+def test_wav_framing_reads_back_with_the_wave_module():
+    """output.wav_frame (row N4): the bytes are a valid mono 16-bit PCM .wav that the standard library reads back
+    sample for sample"""
+    import io
+    import wave
+    import numpy as np
+    import torch
+    from styletts2_b200.output import wav_frame
+    pcm = torch.from_numpy((np.sin(np.arange(2401) * 0.01) * 30000).astype(np.int16))
+    blob = wav_frame(pcm, 24000)
+    assert len(blob) == 44 + 2 * pcm.numel() and blob[:4] == b"RIFF" and blob[8:12] == b"WAVE"
+    with wave.open(io.BytesIO(blob)) as w:
+        assert (w.getnchannels(), w.getsampwidth(), w.getframerate(), w.getnframes()) == (1, 2, 24000, 2401)
+        back = np.frombuffer(w.readframes(2401), dtype="<i2")
+    assert np.array_equal(back, pcm.numpy())
+    assert wav_frame(pcm.numpy(), 16000)[24:28] == (16000).to_bytes(4, "little")
+    import pytest
+    with pytest.raises(ValueError):
+        wav_frame(pcm.float())
